@@ -1,0 +1,96 @@
+"""Freeze outputs of the REAL reference (imported from /root/reference) as small
+golden fixtures under tests/golden/.  Runs only in the build container -- the
+GPU box has no /root/reference; the tests read the committed .npz files.
+
+    python oracle/gen_golden.py            # (re)writes tests/golden/*.npz
+
+What is frozen, per case (inputs are regenerated from the seed by
+oracle.gptq_oracle.synth_linear, and stored as raw 16-bit patterns (W_bits,
+X_bits) so the fixture is self-contained):
+  * HessianHook.add_batch(use_kernel=False) -> H            (gptq_py.py:19-33)
+  * HessianHook.invert(1e-2, act_order)     -> U, perm, damped H  (:39-66)
+  * gptq_quant(gptq_use_kernel=False, quant_mse=False)      (:158-251)
+        -> quant_meta (qweight/scale/qzero/perm_inv) + 4 metrics
+  * quant.reconstruct_nn_linear(...).weight                 (quant.py:262-279)
+The reference's gptq_use_kernel=True branch needs its CUDA extension and
+cannot run here; its semantics are pinned by the C++/CUDA source restatement
+in oracle.gptq_oracle.quantize_range_ref only ("parity unpinned" for that
+compat mode beyond self-consistency).
+"""
+import os
+import sys
+import types
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+REF = '/root/reference'
+sys.path.insert(0, ROOT)
+
+CASES = [
+    # name,        R,   C,  n_seq, seqlen, bits, act_order, dtype
+    ('r64_c256_b4', 64, 256, 8, 96, 4, True, torch.float16),
+    ('r96_c384_b3', 96, 384, 6, 128, 3, True, torch.float16),
+    ('r128_c512_b4_noact', 128, 512, 4, 256, 4, False, torch.float16),
+    ('r80_c256_b4_bf16', 80, 256, 8, 64, 4, True, torch.bfloat16),
+]
+
+
+def import_reference():
+    """gptq_py.py:3 imports the CUDA extension package `gptq` unconditionally;
+    give it a two-function stub (never called on the fp32 path)."""
+    stub = types.ModuleType('gptq')
+
+    def _nope(*a, **k):
+        raise RuntimeError('reference CUDA extension is not available on CPU')
+    stub.accumulate_hessian = _nope
+    stub.gptq_quantize_range = _nope
+    sys.modules['gptq'] = stub
+    sys.path.insert(0, REF)
+    import gptq_py  # noqa
+    import quant  # noqa
+    return gptq_py, quant
+
+
+def main():
+    from oracle import gptq_oracle as O
+    gptq_py, quant = import_reference()
+    torch.set_num_threads(1)   # LAPACK/BLAS summation order fixed for the freeze
+    out_dir = os.path.join(ROOT, 'tests', 'golden')
+    os.makedirs(out_dir, exist_ok=True)
+    for name, R, C, n_seq, seqlen, bits, act, dtype in CASES:
+        W, X = O.synth_linear(R, C, n_seq, seqlen, dtype=dtype, seed=100 + R + C)
+        hook = gptq_py.HessianHook()
+        for i in range(0, n_seq, 2):
+            hook.add_batch(X[i:i + 2], use_kernel=False)
+        H_raw = hook.hessian.clone()
+        hook.invert(damp_ratio=1e-2, act_order=act)
+        G = C // 128
+        gs = torch.full([G], 128, dtype=torch.int32)
+        bw = torch.full([G], bits, dtype=torch.int32)
+        res = gptq_py.gptq_quant(weight=W, hessian_hook=hook, group_sizes=gs, group_bit_widths=bw,
+                                 scale_bit_width=None, gptq_use_kernel=False, gptq_block_sizes=gs,
+                                 quant_symmetric=False, quant_mse=False)
+        lin = quant.reconstruct_nn_linear(res['quant_meta'], dtype=dtype)
+        m = res['quant_meta']
+        to_np = lambda t: t.to(torch.float32).numpy() if t.dtype in (torch.float16, torch.bfloat16) else t.numpy()
+        np.savez_compressed(
+            os.path.join(out_dir, name + '.npz'),
+            R=R, C=C, n_seq=n_seq, seqlen=seqlen, bits=bits, act_order=int(act),
+            dtype=str(dtype).split('.')[-1],
+            W_bits=W.view(torch.int16).numpy(), X_bits=X.view(torch.int16).numpy(),
+            H_raw=H_raw.numpy(), H_damped=hook.hessian.numpy(), U=hook.hessian_inv.numpy(),
+            perm=(hook.perm.numpy() if hook.perm is not None else np.arange(C)),
+            qweight=m['qweight'].numpy(), scale=to_np(m['scale']), qzero=m['qzero'].numpy(),
+            perm_inv=m['perm_inv'].numpy(),
+            metrics=np.array([res['metrics'][k] for k in ('gptq_error', 'gptq_norm', 'l2.0_error', 'l2.0_norm')],
+                             dtype=np.float64),
+            W_hat=to_np(lin.weight.data),
+        )
+        print('wrote', name, {k: f'{v:.4e}' for k, v in res['metrics'].items()})
+
+
+if __name__ == '__main__':
+    main()

@@ -1,0 +1,31 @@
+"""Loader for tests/golden/*.npz (written by oracle/gen_golden.py from the real reference)."""
+import glob
+import os
+
+import numpy as np
+import torch
+
+GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), 'golden')
+_DT = {'float16': torch.float16, 'bfloat16': torch.bfloat16}
+
+
+def names():
+    return sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN_DIR, '*.npz')))
+
+
+def load(name):
+    z = np.load(os.path.join(GOLDEN_DIR, name + '.npz'))
+    d = {k: z[k] for k in z.files}
+    dt = _DT[str(d['dtype'])]
+    out = dict(name=name, R=int(d['R']), C=int(d['C']), n_seq=int(d['n_seq']), seqlen=int(d['seqlen']),
+               bits=int(d['bits']), act_order=bool(int(d['act_order'])), dtype=dt)
+    out['W'] = torch.from_numpy(d['W_bits'].copy()).view(dt)
+    out['X'] = torch.from_numpy(d['X_bits'].copy()).view(dt)
+    for k in ('H_raw', 'H_damped', 'U', 'scale', 'W_hat'):
+        out[k] = torch.from_numpy(d[k].copy())
+    out['perm'] = torch.from_numpy(d['perm'].copy()).to(torch.int64)
+    out['qweight'] = torch.from_numpy(d['qweight'].copy())
+    out['qzero'] = torch.from_numpy(d['qzero'].copy())
+    out['perm_inv'] = torch.from_numpy(d['perm_inv'].copy())
+    out['metrics'] = dict(zip(('gptq_error', 'gptq_norm', 'l2.0_error', 'l2.0_norm'), d['metrics'].tolist()))
+    return out
