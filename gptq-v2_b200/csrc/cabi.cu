@@ -1,0 +1,96 @@
+// extern "C" surface of libgptq_b200.so -- see include/gptq_b200.h for the contract.
+#include "../../include/gptq_b200.h"
+#include "gptq_b200_internal.h"
+
+using namespace gq;
+
+static inline cudaStream_t S(void* s) { return reinterpret_cast<cudaStream_t>(s); }
+
+extern "C" {
+
+int gq_abi_version(void) { return GQ_ABI_VERSION; }
+
+const char* gq_error_string(int code) {
+  switch (code) {
+    case GQ_OK: return "ok";
+    case GQ_ERR_CUDA: return "CUDA runtime error (launch or API call failed)";
+    case GQ_ERR_SHAPE: return "unsupported shape (see preconditions in gptq_b200.h)";
+    case GQ_ERR_DTYPE: return "unsupported dtype";
+    case GQ_ERR_ALIGN: return "pointer is not sufficiently aligned";
+    case GQ_ERR_DRIVER: return "cuTensorMapEncodeTiled driver entry point not found";
+    case GQ_ERR_TENSORMAP: return "cuTensorMapEncodeTiled rejected the tensor map";
+    case GQ_ERR_NOT_SPD: return "matrix is not positive definite";
+    case GQ_ERR_ARG: return "invalid argument";
+    default: return "unknown error";
+  }
+}
+
+int gq_accumulate_hessian_variant(void* H, const void* X, int size_hidden, int size_batch, int dtype, int mode,
+                                  int variant, void* stream) {
+  if (mode < 0 || mode > 2) return GQ_ERR_ARG;
+  return syrk_upper(static_cast<float*>(H), X, size_hidden, size_batch, dtype, mode, variant, S(stream));
+}
+int gq_accumulate_hessian(void* H, const void* X, int size_hidden, int size_batch, int dtype, int mode, void* stream) {
+  return gq_accumulate_hessian_variant(H, X, size_hidden, size_batch, dtype, mode, 2, stream);
+}
+int accumulate_hessian_fp16_fp32_cuda(void* H, const void* X, const int size_hidden, const int size_batch) {
+  return gq_accumulate_hessian(H, X, size_hidden, size_batch, GQ_DTYPE_F16, 2, nullptr);
+}
+int accumulate_hessian_bf16_fp32_cuda(void* H, const void* X, const int size_hidden, const int size_batch) {
+  return gq_accumulate_hessian(H, X, size_hidden, size_batch, GQ_DTYPE_BF16, 2, nullptr);
+}
+
+size_t gq_invert_workspace_floats(int D) {
+  const size_t d = (size_t)D;
+  return d * d + d * d / 2 + 64;
+}
+
+int gq_hessian_invert(const float* H, int D, const int64_t* perm, float scale, float damp, float* Hp, float* U,
+                      float* work, int* info_dev, void* stream) {
+  if (D <= 0) return GQ_ERR_ARG;
+  if (D % 4 != 0) return GQ_ERR_SHAPE;
+  float* A = work;
+  float* tmp = work + (size_t)D * D;
+  int rc = hessian_gather(H, D, perm, scale, damp, Hp, A, S(stream));
+  if (rc != GQ_OK) return rc;
+  return chol_inverse_upper(A, D, U, tmp, info_dev, S(stream));
+}
+
+int gq_quantize_range(float* quant, const float* scale, int16_t* out_q, const float* qzero, float maxq,
+                      const float* hessian_inv, float* weights, float* error, int C, int R, int a, int b,
+                      void* stream) {
+  return gptq_solve(weights, hessian_inv, quant, out_q, 2, error, const_cast<float*>(scale),
+                    const_cast<float*>(qzero), R, C, 128, maxq, 1, a, b, S(stream));
+}
+
+int gq_gptq_solve(float* Wt, const float* U, float* quant_t, uint8_t* codes_t, float* err_t, float* scale_gr,
+                  float* qzero_gr, int R, int C, int group, float maxq, void* stream) {
+  return gptq_solve(Wt, U, quant_t, codes_t, 1, err_t, scale_gr, qzero_gr, R, C, group, maxq, 0, 0, C, S(stream));
+}
+
+int gq_prep_weight_t(const void* W, int dtype, const int64_t* perm, float* Wt, int R, int C, void* stream) {
+  return prep_weight_t(W, dtype, perm, Wt, R, C, S(stream));
+}
+
+int gq_pack_int4(const uint8_t* codes, uint32_t* packed, int R, int C, void* stream) {
+  return pack_int4(codes, packed, R, C, S(stream));
+}
+int gq_unpack_int4(const uint32_t* packed, uint8_t* codes, int R, int C, void* stream) {
+  return unpack_int4(packed, codes, R, C, S(stream));
+}
+int gq_transpose_pack_int4(const uint8_t* codes_t, uint8_t* codes, uint32_t* packed, int R, int C, void* stream) {
+  return transpose_pack_int4(codes_t, codes, packed, R, C, S(stream));
+}
+
+int gq_w4a16_gemm(const void* x, const uint32_t* qweight, const void* scale, const uint8_t* qzero,
+                  const int32_t* perm, void* y, int M, int N, int K, int group, int dtype, void* stream) {
+  return w4a16_gemm(x, qweight, scale, qzero, perm, y, M, N, K, group, dtype, S(stream));
+}
+
+int gq_sgemm(const float* A, const float* B, float* C, int M, int N, int K, int lda, int ldb, int ldc, float alpha,
+             float beta, int flags, void* stream) {
+  GemmProblem p{A, B, C, M, N, K, lda, ldb, ldc};
+  return sgemm(p, alpha, beta, flags, S(stream));
+}
+
+}  // extern "C"

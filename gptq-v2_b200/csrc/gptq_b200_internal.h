@@ -1,0 +1,58 @@
+// Internal (C++) declarations shared by the .cu files; the public C ABI is include/gptq_b200.h
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#define GQ_OK 0
+#define GQ_ERR_CUDA 1        // a CUDA runtime call / launch failed (see cudaGetLastError)
+#define GQ_ERR_SHAPE 2       // unsupported shape (see the precondition in the header)
+#define GQ_ERR_DTYPE 3
+#define GQ_ERR_ALIGN 4       // pointer not 16-byte aligned
+#define GQ_ERR_DRIVER 5      // cuTensorMapEncodeTiled entry point not found
+#define GQ_ERR_TENSORMAP 6   // cuTensorMapEncodeTiled rejected the descriptor
+#define GQ_ERR_NOT_SPD 7     // Cholesky met a non-positive pivot (caller adds damping and retries)
+#define GQ_ERR_ARG 8
+
+namespace gq {
+
+// ---- K1
+int syrk_upper(float* H, const void* X, int D, int T, int fmt, int mode, int variant, cudaStream_t st);
+int make_tmap_2d(CUtensorMap* out, const void* base, int elem_kind, uint64_t inner, uint64_t outer,
+                 uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_outer);
+
+// ---- fp32 GEMM building block (SIMT):  C = beta*C + alpha * op(A) * B
+enum : int {
+  GEMM_TRANS_A = 1,   // A is stored (K x M) row-major  (C = A^T B); else (M x K)
+  GEMM_C_UPPER = 2,   // only tiles that touch col >= row are computed (symmetric update)
+  GEMM_A_UPPER = 4,   // A is upper triangular in its stored form -> shorter K range
+  GEMM_B_UPPER = 8,   // B (K x N) is upper triangular: B[k][n] = 0 for k > n
+};
+struct GemmProblem {
+  const float* A; const float* B; float* C;
+  int M, N, K, lda, ldb, ldc;
+};
+constexpr int GEMM_MAX_BATCH = 48;
+struct GemmBatch { GemmProblem p[GEMM_MAX_BATCH]; int count; };
+int sgemm(const GemmProblem& pr, float alpha, float beta, int flags, cudaStream_t st);
+int sgemm_batched(const GemmBatch& b, float alpha, float beta, int flags, cudaStream_t st);
+
+// ---- K2
+int hessian_gather(const float* H, int D, const int64_t* perm, float scale, float damp, float* Hp, float* Arev,
+                   cudaStream_t st);
+int chol_inverse_upper(float* A, int D, float* U, float* tmp, int* info_dev, cudaStream_t st);
+
+// ---- K3/K4
+int gptq_solve(float* Wt, const float* U, float* quant_t, void* codes_t, int codes_elem_size, float* err_t,
+               float* scale_gr, float* qzero_gr, int R, int C, int group, float maxq, int mode, int a, int b,
+               cudaStream_t st);
+
+// ---- K5/K6
+int pack_int4(const uint8_t* codes, uint32_t* packed, int R, int C, cudaStream_t st);
+int unpack_int4(const uint32_t* packed, uint8_t* codes, int R, int C, cudaStream_t st);
+int transpose_pack_int4(const uint8_t* codes_t, uint8_t* codes, uint32_t* packed, int R, int C, cudaStream_t st);
+int w4a16_gemm(const void* x, const uint32_t* qw, const void* scale, const uint8_t* qzero, const int32_t* perm,
+               void* y, int M, int N, int K, int group, int fmt, cudaStream_t st);
+int prep_weight_t(const void* W, int fmt, const int64_t* perm, float* Wt, int R, int C, cudaStream_t st);
+
+}  // namespace gq

@@ -1,0 +1,5 @@
+// one instantiation of the block solver (mode 0, 64 columns) -- see gptq_solver_kernel.cuh
+#include "gptq_solver_kernel.cuh"
+namespace gq {
+int launch_solve_block_m0_nb64(const SolveParams& p, cudaStream_t st) { return launch_block<0, 64, uint8_t>(p, st); }
+}  // namespace gq

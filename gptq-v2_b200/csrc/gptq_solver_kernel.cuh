@@ -1,0 +1,149 @@
+#pragma once
+// K3 + K4  blocked GPTQ column solver on the transposed (C, R) layout.
+//
+// Replaces, per block of <=128 columns, the reference's 2*128 per-column launches
+// (fused_quantize_adjust_kernel + vv_mul_sub_kernel, package/gptq/gptq_cpp_kernel.cu:21-158,
+// driven by quantize_range, gptq_cpp.cpp:33-84) by ONE launch, and restates the
+// fp32 PyTorch recurrence (gptq_py.py:158-193) the parity tests are judged against.
+//
+// One thread owns one weight row r: its NB columns of the block live in registers, so a
+// column step (quantise, error, rank-1 update of the remaining in-block columns) is
+// register-local; rows are independent, so there is no cross-thread communication at all.
+// The NB x NB diagonal block of U (= chol(H^-1), upper) is staged in shared memory with
+// cp.async.bulk row copies (only the upper-triangular part of each row) and read as
+// warp-wide broadcasts.  All accesses to W/quant/codes/err are coalesced because
+// consecutive threads own consecutive rows of the (C, R) layout.
+//
+// MODE 0 ("pure", gptq_py.py:169-193): scale/zero computed at the block start from the
+//   *updated* weights (quant.py:114-118), fp32 dequant, update = w - (e*u) with two
+//   roundings (torch: matmul then subtract).  Bit-exact inside a block.
+// MODE 1 ("kernel path", gptq_cpp_kernel.cu:41-73,113-137): caller-supplied static
+//   scale/zero, dequant rounded through fp16, update = fma(-e, u, w).
+//
+// The lazy-batch trailing update  W[b:, :] -= U[a:b, b:]^T E[a:b, :]  runs after each block
+// as an fp32 FMA GEMM (sgemm_f32.cu), as torch.addmm_ does in the reference with TF32 off.
+#include <cuda_fp16.h>
+#include "gptq_b200_internal.h"
+#include "ptx.cuh"
+#include "gptq_solver_params.h"
+
+namespace gq {
+
+
+// Column j of the block, j known at compile time so that every w[k] is a register:
+// template recursion instead of a 128-trip `#pragma unroll` (which ptxas demoted to
+// local memory).
+template <int MODE, int NB, typename CodeT, int J>
+struct ColumnSteps {
+  static __device__ __forceinline__ void run(float (&w)[NB], const float* Ub, const SolveParams& p, CodeT* codes,
+                                             float s, float z, __half hs, __half hz, bool active, int r) {
+    const float d = Ub[J * NB + J];
+    const float x = w[J];
+    float q = rintf(__fdiv_rn(x, s));
+    q = __fadd_rn(q, z);
+    q = fminf(fmaxf(q, 0.f), p.maxq);
+    float deq;
+    if (MODE == 0) {
+      deq = __fmul_rn(__fsub_rn(q, z), s);
+    } else {
+      const __half hq = __float2half_rn(q);
+      deq = __half2float(__hmul(__hsub(hq, hz), hs));
+    }
+    const float e = __fdiv_rn(__fsub_rn(x, deq), d);
+    if (active) {
+      const size_t o = (size_t)(p.c0 + J) * p.R + r;
+      if (MODE == 1) p.Wt[o] = x;                            // reference leaves the updated weight in place
+      if (p.quant_t) p.quant_t[o] = deq;
+      if (codes) codes[o] = static_cast<CodeT>(q);
+      p.err_t[o] = e;
+    }
+    // rank-1 update of the remaining columns of the block
+#pragma unroll
+    for (int k4 = (J + 1) / 4; k4 < NB / 4; ++k4) {
+      const float4 u = *reinterpret_cast<const float4*>(&Ub[J * NB + k4 * 4]);
+      const float uu[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+      for (int t = 0; t < 4; ++t) {
+        const int k = k4 * 4 + t;
+        if (k > J) {
+          if (MODE == 0) w[k] = __fsub_rn(w[k], __fmul_rn(e, uu[t]));
+          else w[k] = __fmaf_rn(-e, uu[t], w[k]);
+        }
+      }
+    }
+    ColumnSteps<MODE, NB, CodeT, J + 1>::run(w, Ub, p, codes, s, z, hs, hz, active, r);
+  }
+};
+template <int MODE, int NB, typename CodeT>
+struct ColumnSteps<MODE, NB, CodeT, NB> {
+  static __device__ __forceinline__ void run(float (&)[NB], const float*, const SolveParams&, CodeT*, float, float,
+                                             __half, __half, bool, int) {}
+};
+
+template <int MODE, int NB, typename CodeT>
+__global__ void __launch_bounds__(32) solve_block_kernel(const SolveParams p) {
+  extern __shared__ __align__(16) float Ub[];        // [NB][NB] + mbarrier
+  const uint32_t bar = smem_u32(Ub + NB * NB);
+  const int lane = threadIdx.x;
+  const int r = blockIdx.x * 32 + lane;
+  const bool active = r < p.R;
+  const int R = p.R;
+
+  if (lane == 0) {
+    mbar_init(bar, 1);
+    fence_mbar_init();
+    fence_proxy_async();
+    uint32_t total = 0;
+#pragma unroll 1
+    for (int j = 0; j < NB; ++j) total += (NB - (j & ~3)) * 4;
+    mbar_expect_tx(bar, total);
+#pragma unroll 1
+    for (int j = 0; j < NB; ++j) {
+      const int cs = j & ~3;                                   // 16-byte aligned start column
+      bulk_load_1d(smem_u32(Ub + j * NB + cs), p.U + (size_t)(p.c0 + j) * p.C + p.c0 + cs, (NB - cs) * 4, bar);
+    }
+  }
+  __syncwarp();
+
+  float w[NB];
+#pragma unroll
+  for (int k = 0; k < NB; ++k) w[k] = active ? p.Wt[(size_t)(p.c0 + k) * R + r] : 0.f;
+
+  float s, z;
+  if (MODE == 0) {
+    float mx = w[0], mn = w[0];
+#pragma unroll
+    for (int k = 1; k < NB; ++k) { mx = fmaxf(mx, w[k]); mn = fminf(mn, w[k]); }
+    const float xmax = fmaxf(mx, 0.f);                        // .relu()
+    const float xmin = -fmaxf(-mn, 0.f);                      // -(-min).relu()
+    s = __fadd_rn(__fdiv_rn(__fsub_rn(xmax, xmin), p.maxq), 1e-12f);
+    z = rintf(__fdiv_rn(-xmin, s));
+    if (active) { p.scale[r] = s; p.qzero[r] = z; }
+  } else {
+    s = active ? p.scale[r] : 1.f;
+    z = active ? p.qzero[r] : 0.f;
+  }
+  __half hs = __float2half_rn(0.f), hz = hs;
+  if (MODE == 1) { hs = __float2half_rn(s); hz = __float2half_rn(z); }
+
+  mbar_wait(bar, 0);
+
+  CodeT* codes = reinterpret_cast<CodeT*>(p.codes_t);
+  ColumnSteps<MODE, NB, CodeT, 0>::run(w, Ub, p, codes, s, z, hs, hz, active, r);
+}
+
+template <int MODE, int NB, typename CodeT>
+int launch_block(const SolveParams& p, cudaStream_t st) {
+  const int smem = NB * NB * 4 + 16;
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(solve_block_kernel<MODE, NB, CodeT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) !=
+        cudaSuccess)
+      return GQ_ERR_CUDA;
+    attr_set = true;
+  }
+  solve_block_kernel<MODE, NB, CodeT><<<(p.R + 31) / 32, 32, smem, st>>>(p);
+  return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
+}
+
+}  // namespace gq

@@ -1,0 +1,181 @@
+"""Drop-in for the reference's `gptq` extension package (package/gptq/__init__.py:6-28):
+
+    from gptq import accumulate_hessian, gptq_quantize_range        # gptq_py.py:3
+
+Same names, argument order, in-place semantics and dtype dispatch, backed by the
+sm_100a library libgptq_b200.so instead of `gptq_c`.  The additional ops below
+(hessian_syrk, hessian_invert, gptq_solve, pack_int4, unpack_int4, w4a16_gemm)
+are what this build's own gptq_py.HessianHook / gptq_quant call.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import _cabi
+from ._cabi import GptqB200Error, check, lib, ptr, require_contig, require_cuda, stream_of
+
+__all__ = ['accumulate_hessian', 'gptq_quantize_range', 'hessian_syrk', 'hessian_invert', 'prep_weight_t',
+           'gptq_solve', 'pack_int4', 'unpack_int4', 'transpose_pack_int4', 'w4a16_gemm', 'sgemm',
+           'GptqB200Error']
+
+
+# ----------------------------------------------------------------------------
+# reference surface
+# ----------------------------------------------------------------------------
+def accumulate_hessian(mat_hessian: torch.Tensor, mat_input: torch.Tensor) -> None:
+    """H += X^T X (fp16 or bf16 X, fp32 H), in place; both triangles are updated
+    (the CUTLASS kernel's semantics, package/gptq/accumulate_hessian_kernel.cu:47-52)."""
+    if mat_input.dtype not in (torch.float16, torch.bfloat16):
+        raise NotImplementedError                       # package/gptq/__init__.py:12-13
+    hessian_syrk(mat_hessian, mat_input, mode=2)
+
+
+def gptq_quantize_range(quant: torch.Tensor, scale: torch.Tensor, out_q: torch.Tensor, qzero: torch.Tensor,
+                        maxq: float, hessian_inv: torch.Tensor, weights: torch.Tensor, error: torch.Tensor,
+                        a: int, b: int) -> None:
+    """Columns [a, b) of the transposed (C, R) weight matrix: quantise, dequantise through
+    fp16, propagate the error inside the range and to every later column
+    (package/gptq/gptq_cpp.cpp:33-84).  All tensors are updated in place."""
+    if out_q is not None and out_q.device.type == 'meta':
+        out_q = None                                     # gptq_cpp.cpp:58
+    dev = require_cuda(quant, scale, out_q, qzero, hessian_inv, weights, error)
+    require_contig(quant=quant, scale=scale, out_q=out_q, qzero=qzero, hessian_inv=hessian_inv, weights=weights,
+                   error=error)
+    C_, R_ = weights.shape
+    if hessian_inv.size(1) != C_:
+        raise RuntimeError('H shape mismatch')           # gptq_cpp.cpp:49
+    for t in (quant, scale, qzero, hessian_inv, weights, error):
+        if t.dtype != torch.float32:
+            raise GptqB200Error('gptq_quantize_range expects float32 tensors')
+    if out_q is not None and out_q.dtype != torch.int16:
+        raise GptqB200Error('out_q must be int16')
+    with torch.cuda.device(dev):
+        check(lib.gq_quantize_range(ptr(quant), ptr(scale), ptr(out_q), ptr(qzero), float(maxq), ptr(hessian_inv),
+                                    ptr(weights), ptr(error), C_, R_, int(a), int(b), stream_of(weights)),
+              'gq_quantize_range')
+
+
+# ----------------------------------------------------------------------------
+# native ops
+# ----------------------------------------------------------------------------
+def hessian_syrk(H: torch.Tensor, X: torch.Tensor, mode: int = 1, variant: int = 2) -> None:
+    """K1.  H (D, D) fp32 += X^T X with X (T, D) fp16/bf16.
+    mode 0 upper triangle only, 1 upper + mirrored lower, 2 both triangles RMW."""
+    dev = require_cuda(H, X)
+    require_contig(H=H, X=X)
+    if X.dim() != 2 or H.dim() != 2 or H.shape[0] != H.shape[1] or H.shape[1] != X.shape[1]:
+        raise GptqB200Error(f'shape mismatch: H {tuple(H.shape)} X {tuple(X.shape)}')
+    if H.dtype != torch.float32 or X.dtype not in (torch.float16, torch.bfloat16):
+        raise NotImplementedError
+    T, D = X.shape
+    with torch.cuda.device(dev):
+        check(lib.gq_accumulate_hessian_variant(ptr(H), ptr(X), D, T, _cabi.DTYPE_CODE[X.dtype], mode, variant,
+                                                stream_of(H)), 'gq_accumulate_hessian')
+
+
+def hessian_invert(H: torch.Tensor, perm, scale: float, damp: float, want_hp: bool = True):
+    """K2.  Returns (Hp, U, info) with Hp = scale*H[perm][:, perm] + damp*I and
+    U = chol_upper(Hp^-1); info is a device int32 (1 = a pivot was not positive)."""
+    dev = require_cuda(H, perm)
+    require_contig(H=H, perm=perm)
+    D = H.shape[0]
+    if perm is not None and perm.dtype != torch.int64:
+        raise GptqB200Error('perm must be int64')
+    U = torch.empty_like(H)
+    Hp = torch.empty_like(H) if want_hp else None
+    work = torch.empty(lib.gq_invert_workspace_floats(D), dtype=torch.float32, device=dev)
+    info = torch.zeros((), dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.gq_hessian_invert(ptr(H), D, ptr(perm), float(scale), float(damp), ptr(Hp), ptr(U), ptr(work),
+                                    ptr(info), stream_of(H)), 'gq_hessian_invert')
+    return Hp, U, info
+
+
+def prep_weight_t(W: torch.Tensor, perm) -> torch.Tensor:
+    """Wt (C, R) fp32 with Wt[c, r] = W[r, perm[c]]."""
+    dev = require_cuda(W, perm)
+    require_contig(W=W, perm=perm)
+    R, C_ = W.shape
+    Wt = torch.empty(C_, R, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.gq_prep_weight_t(ptr(W), _cabi.DTYPE_CODE[W.dtype], ptr(perm), ptr(Wt), R, C_, stream_of(W)),
+              'gq_prep_weight_t')
+    return Wt
+
+
+def gptq_solve(Wt: torch.Tensor, U: torch.Tensor, group: int, maxq: float, want_quant: bool = True):
+    """K3+K4 in the fp32 semantics of gptq_quant(gptq_use_kernel=False).  Wt (C, R) is
+    consumed (updated in place).  Returns quant_t, codes_t (uint8), err_t, scale_gr, qzero_gr."""
+    dev = require_cuda(Wt, U)
+    require_contig(Wt=Wt, U=U)
+    C_, R = Wt.shape
+    quant_t = torch.empty_like(Wt) if want_quant else None
+    err_t = torch.empty_like(Wt)
+    codes_t = torch.empty(C_, R, dtype=torch.uint8, device=dev)
+    scale_gr = torch.empty(C_ // group, R, dtype=torch.float32, device=dev)
+    qzero_gr = torch.empty(C_ // group, R, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.gq_gptq_solve(ptr(Wt), ptr(U), ptr(quant_t), ptr(codes_t), ptr(err_t), ptr(scale_gr),
+                                ptr(qzero_gr), R, C_, int(group), float(maxq), stream_of(Wt)), 'gq_gptq_solve')
+    return quant_t, codes_t, err_t, scale_gr, qzero_gr
+
+
+def pack_int4(codes: torch.Tensor) -> torch.Tensor:
+    """K5.  codes (R, C) uint8 in [0, 15] -> (R, C/8) int32 words (bit pattern of uint32)."""
+    dev = require_cuda(codes)
+    require_contig(codes=codes)
+    R, C_ = codes.shape
+    out = torch.empty(R, C_ // 8, dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.gq_pack_int4(ptr(codes), ptr(out), R, C_, stream_of(codes)), 'gq_pack_int4')
+    return out
+
+
+def unpack_int4(packed: torch.Tensor) -> torch.Tensor:
+    dev = require_cuda(packed)
+    require_contig(packed=packed)
+    R, K8 = packed.shape
+    out = torch.empty(R, K8 * 8, dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.gq_unpack_int4(ptr(packed), ptr(out), R, K8 * 8, stream_of(packed)), 'gq_unpack_int4')
+    return out
+
+
+def transpose_pack_int4(codes_t: torch.Tensor, want_codes: bool = True, want_packed: bool = True):
+    """codes_t (C, R) uint8 -> codes (R, C) uint8 and/or packed (R, C/8) int32."""
+    dev = require_cuda(codes_t)
+    require_contig(codes_t=codes_t)
+    C_, R = codes_t.shape
+    codes = torch.empty(R, C_, dtype=torch.uint8, device=dev) if want_codes else None
+    packed = torch.empty(R, C_ // 8, dtype=torch.int32, device=dev) if want_packed else None
+    with torch.cuda.device(dev):
+        check(lib.gq_transpose_pack_int4(ptr(codes_t), ptr(codes), ptr(packed), R, C_, stream_of(codes_t)),
+              'gq_transpose_pack_int4')
+    return codes, packed
+
+
+def w4a16_gemm(x: torch.Tensor, qweight: torch.Tensor, scale: torch.Tensor, qzero: torch.Tensor, perm,
+               group: int = 128) -> torch.Tensor:
+    """K6.  y (M, N) = x[:, perm] @ dequant(qweight)^T;  qweight (N, K/8) int32, scale (N, G) in
+    x.dtype, qzero (N, G) uint8, perm (K) int32 or None."""
+    dev = require_cuda(x, qweight, scale, qzero, perm)
+    require_contig(x=x, qweight=qweight, scale=scale, qzero=qzero, perm=perm)
+    M, K = x.shape
+    N = qweight.shape[0]
+    if qweight.shape[1] * 8 != K or scale.dtype != x.dtype or qzero.dtype != torch.uint8:
+        raise GptqB200Error('w4a16_gemm: inconsistent operands')
+    if perm is not None and perm.dtype != torch.int32:
+        raise GptqB200Error('perm must be int32')
+    y = torch.empty(M, N, dtype=x.dtype, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.gq_w4a16_gemm(ptr(x), ptr(qweight), ptr(scale), ptr(qzero), ptr(perm), ptr(y), M, N, K, int(group),
+                                _cabi.DTYPE_CODE[x.dtype], stream_of(x)), 'gq_w4a16_gemm')
+    return y
+
+
+def sgemm(A, B, C_, M, N, K, lda, ldb, ldc, alpha, beta, flags) -> None:
+    """Test hook for the fp32 GEMM building block (operands are views into larger buffers)."""
+    dev = require_cuda(A, B, C_)
+    with torch.cuda.device(dev):
+        check(lib.gq_sgemm(ptr(A), ptr(B), ptr(C_), M, N, K, lda, ldb, ldc, float(alpha), float(beta), int(flags),
+                           stream_of(C_)), 'gq_sgemm')

@@ -1,0 +1,98 @@
+/* gptq_b200 -- C ABI of the B200-native GPTQ quantisation hot path (libgptq_b200.so).
+ *
+ * Drop-in boundary for 4PiR2/gptq-v2's native extension `gptq_c`
+ * (reference: package/gptq/pybind.cpp:31-35 and the C-linkage launchers declared in
+ * package/gptq/accumulate_hessian.cpp:4-17 and package/gptq/gptq_cpp.cpp:7-30).
+ * Plain pointers and sizes only; every pointer is a DEVICE pointer owned by the caller,
+ * borrowed for the duration of the call; results are written in place; nothing is
+ * allocated.  `stream` is a cudaStream_t passed as void* (NULL = legacy default stream,
+ * which is what the reference's <<<grid, block>>> launches use).  Kernels are launched
+ * on the CURRENT device (the reference requires torch.cuda.set_device first, gptq_py.py:127).
+ * Every function returns 0 on success or a GQ_ERR_* code; gq_error_string() names it.
+ * The library is built for sm_100a only and has no CPU path.
+ */
+#ifndef GPTQ_B200_H_
+#define GPTQ_B200_H_
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GQ_ABI_VERSION 1
+#define GQ_DTYPE_F16 0
+#define GQ_DTYPE_BF16 1
+#define GQ_DTYPE_F32 2
+
+int gq_abi_version(void);
+const char* gq_error_string(int code);
+
+/* ---- K1: Hessian accumulation  H(fp32, D x D) += X^T X,  X (T x D) row-major fp16/bf16.
+ * Replaces accumulate_hessian_{fp16,bf16}_fp32_cuda (accumulate_hessian.cpp:4-17,
+ * accumulate_hessian_kernel.cu:67-84) and the Triton launcher
+ * (gptq_triton/accumulate_hessian.py:134-149).
+ * mode 0: only the upper triangle (col >= row) of H is updated
+ * mode 1: upper triangle updated and mirrored into the lower one (Triton semantics)
+ * mode 2: both triangles read-modify-written (CUTLASS semantics; H may be asymmetric)
+ * Preconditions: D % 8 == 0, pointers 16-byte aligned. */
+int gq_accumulate_hessian(void* H, const void* X, int size_hidden, int size_batch, int dtype, int mode, void* stream);
+/* The reference's own launcher names and signatures (mode 2, default stream). */
+int accumulate_hessian_fp16_fp32_cuda(void* H, const void* X, const int size_hidden, const int size_batch);
+int accumulate_hessian_bf16_fp32_cuda(void* H, const void* X, const int size_hidden, const int size_batch);
+/* test hook: variant 1 = single-CTA tcgen05 tiles, 2 = CTA-pair (cta_group::2) tiles */
+int gq_accumulate_hessian_variant(void* H, const void* X, int size_hidden, int size_batch, int dtype, int mode,
+                                  int variant, void* stream);
+
+/* ---- K2: HessianHook.invert (gptq_py.py:39-66) after the host has chosen perm and damp.
+ * Reads the upper triangle of H; forms Hp[i][j] = scale*H[perm i][perm j] (+damp, dead
+ * diagonal -> 1) and U = chol_upper(Hp^-1).  perm may be NULL (identity).  Hp may be NULL.
+ * work: gq_invert_workspace_floats(D) floats.  *info_dev (device int, caller zeroes it) is
+ * set to 1 if a pivot is not positive (the caller adds damping and retries, as the
+ * reference's NaN loop does).  Precondition: D % 4 == 0. */
+size_t gq_invert_workspace_floats(int D);
+int gq_hessian_invert(const float* H, int D, const int64_t* perm, float scale, float damp, float* Hp, float* U,
+                      float* work, int* info_dev, void* stream);
+
+/* ---- K3+K4, compat: quantize_range (gptq_cpp.cpp:33-84) on raw pointers.
+ * Layout is the reference's transposed one: weights/quant/error/out_q are (C, R) row-major
+ * with R = number of weight rows ("columns" in the reference's naming), hessian_inv (C, C).
+ * scale/qzero (R) are static for the range; dequant is rounded through fp16.  out_q may be
+ * NULL (the reference skips it for meta tensors).  Preconditions: R % 4 == 0, a % 4 == 0,
+ * (b - a) a multiple of 128 plus an optional tail of 32 or 64. */
+int gq_quantize_range(float* quant, const float* scale, int16_t* out_q, const float* qzero, float maxq,
+                      const float* hessian_inv, float* weights, float* error, int C, int R, int a, int b,
+                      void* stream);
+
+/* ---- K3+K4, native: the whole blocked solve of one linear in the fp32 semantics of
+ * gptq_quant(gptq_use_kernel=False) (gptq_py.py:158-193): per-group scale/zero from the
+ * error-compensated weights, fp32 dequant.  Wt (C, R) in/out; outputs quant_t (C, R) (may be
+ * NULL), codes_t (C, R) uint8, err_t (C, R), scale_gr/qzero_gr (C/group, R).
+ * group in {32, 64, 128} (= the GPTQ block size, as llama.py:155 sets it). */
+int gq_gptq_solve(float* Wt, const float* U, float* quant_t, uint8_t* codes_t, float* err_t, float* scale_gr,
+                  float* qzero_gr, int R, int C, int group, float maxq, void* stream);
+/* Wt[c][r] = (float) W[r][perm[c]]; W (R, C) of dtype GQ_DTYPE_*; perm may be NULL. */
+int gq_prep_weight_t(const void* W, int dtype, const int64_t* perm, float* Wt, int R, int C, void* stream);
+
+/* ---- K5: int4 storage (new in this build; the reference stores one code per byte, gptq_py.py:217).
+ * packed (R, C/8) uint32, column 8k+i in bits [4i, 4i+4) of word k.  C % 8 == 0. */
+int gq_pack_int4(const uint8_t* codes, uint32_t* packed, int R, int C, void* stream);
+int gq_unpack_int4(const uint32_t* packed, uint8_t* codes, int R, int C, void* stream);
+/* codes_t (C, R) -> codes (R, C) (may be NULL) and packed (R, C/8) (may be NULL) */
+int gq_transpose_pack_int4(const uint8_t* codes_t, uint8_t* codes, uint32_t* packed, int R, int C, void* stream);
+
+/* ---- K6: y (M, N) = x[:, perm] (M, K) * dequant(qweight)^T, replacing reconstruct_nn_linear +
+ * nn.Linear (quant.py:262-279, llama.py:172-177).  x, y, scale share `dtype` (f16/bf16);
+ * qzero (N, K/group) uint8; perm (K) int32 or NULL.  K % group == 0, group % 32 == 0. */
+int gq_w4a16_gemm(const void* x, const uint32_t* qweight, const void* scale, const uint8_t* qzero,
+                  const int32_t* perm, void* y, int M, int N, int K, int group, int dtype, void* stream);
+
+/* ---- building block exposed for tests: C = beta*C + alpha*op(A)*B in true fp32.
+ * flags: 1 = A stored (K x M); 2 = only upper tiles of C; 4 = A upper-triangular; 8 = B upper-triangular */
+int gq_sgemm(const float* A, const float* B, float* C, int M, int N, int K, int lda, int ldb, int ldc, float alpha,
+             float beta, int flags, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GPTQ_B200_H_ */

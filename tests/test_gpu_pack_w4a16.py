@@ -1,0 +1,55 @@
+"""K5 bit-exact pack/unpack and K6 W4A16 GEMM vs the dense reconstruction (quant.py:262-279)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import gptq_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize('R,C', [(1, 8), (37, 256), (128, 4096), (1000, 11008)])
+def test_pack_unpack_bit_exact(R, C):
+    import gptq
+    rng = np.random.default_rng(R * C)
+    codes = rng.integers(0, 16, size=(R, C), dtype=np.uint8)
+    want = O.pack_int4(codes)
+    got = gptq.pack_int4(torch.from_numpy(codes).cuda())
+    assert np.array_equal(got.cpu().numpy().view(np.uint32), want)
+    back = gptq.unpack_int4(got)
+    assert np.array_equal(back.cpu().numpy(), codes)
+    c2, p2 = gptq.transpose_pack_int4(torch.from_numpy(np.ascontiguousarray(codes.T)).cuda())
+    assert np.array_equal(c2.cpu().numpy(), codes)
+    assert np.array_equal(p2.cpu().numpy().view(np.uint32), want)
+
+
+def test_pack_empty():
+    import gptq
+    out = gptq.pack_int4(torch.empty(0, 64, dtype=torch.uint8, device='cuda'))
+    assert out.shape == (0, 8)
+
+
+@pytest.mark.parametrize('dtype', [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize('M', [1, 2, 3, 4, 7, 16])
+@pytest.mark.parametrize('N,K', [(256, 512), (4096, 4096), (1024, 11008)])
+def test_w4a16_vs_dense(M, N, K, dtype):
+    """rel err <= 1e-2 vs x @ reconstruct_dense(meta)^T (the reference's evaluation path)."""
+    import gptq
+    g = torch.Generator().manual_seed(M + N + K)
+    G = K // 128
+    codes = torch.randint(0, 16, (N, K), generator=g, dtype=torch.uint8)
+    scale = (torch.rand(N, G, generator=g) * 0.01 + 1e-3).to(dtype)
+    qzero = torch.randint(0, 16, (N, G), generator=g, dtype=torch.uint8)
+    perm = torch.randperm(K, generator=g)
+    x = torch.randn(M, K, generator=g).to(dtype)
+    meta = dict(qweight=codes, scale=scale, qzero=qzero, perm_inv=perm.argsort().to(torch.int16) if K < 32768 else None,
+                group_sizes=torch.full((G,), 128, dtype=torch.int16))
+    want = O.linear_forward_dense(x, meta, dtype)
+    packed = gptq.pack_int4(codes.cuda())
+    y = gptq.w4a16_gemm(x.cuda(), packed, scale.cuda(), qzero.cuda(), perm.to(torch.int32).cuda(), 128)
+    torch.cuda.synchronize()
+    rel = ((y.float().cpu() - want).norm() / want.norm()).item()
+    assert rel <= 1e-2, rel
+    want2 = O.w4a16_reference(x, O.pack_int4(codes.numpy()), scale, qzero, perm, 128)
+    rel2 = ((y.float().cpu() - want2).norm() / want2.norm()).item()
+    assert rel2 <= 5e-3, rel2
