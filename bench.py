@@ -1,0 +1,397 @@
+#!/usr/bin/env python
+"""bench.py -- GPTQ hot-path benchmark (BASELINE.json metric: "GPTQ s/layer & Hessian TFLOP/s ...").
+
+One "step" = the whole quantisation hot path of ONE Llama-2-7B decoder layer
+(BASELINE.json configs[1], the unit the full-model run repeats 32 times):
+  4 Hessian groups   H += X^T X over 128 x 2048 synthetic calibration tokens, delivered in
+                     calls of 16 sequences (32768 rows):  D = 4096 (x3: qkv, o, gate/up) and 11008 (down)
+  4 inversions       damp + Cholesky + inverse factor (act-order)
+  7 linears          blocked GPTQ solve 4-bit g128 (q,k,v,o 4096x4096; gate,up 11008x4096; down 4096x11008)
+                     + int4 packing
+The transformer forward that produces the activations is outside the hot path.
+
+  value : s/layer with activations and weights already resident in HBM (device timed, CUDA events)
+  e2e   : the same through the reference-facing API (HessianHook.add_batch / invert / gptq_quant)
+          from pinned HOST buffers, H2D copies and the D2H of quant_meta inside the timed region
+  roofline : K1 (tcgen05 SYRK), algorithmic flops T*D*(D+1) per launch / CUDA-event time
+  cpu_baseline / --impl reference : the oracle port of gptq_py.py's fp32 path on the host cores,
+          on a bounded sample, extrapolated to one layer by the flop counts of each phase.
+
+N > 1 (torchrun): calibration sequences are sharded over ranks, partial Hessians are summed by an
+NCCL all-reduce, the factorisation is replicated, the rows of every linear are sharded over
+ranks and the codes all-gathered ("strong" scaling of one layer).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for _p in (ROOT, os.path.join(ROOT, 'gptq-v2_b200')):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import torch  # noqa: E402
+
+HIDDEN, INTER = 4096, 11008
+N_SEQ, SEQLEN, CALL_SEQ = 128, 2048, 16
+BITS, GROUP = 4, 128
+# (name, R, C, hessian group)
+LINEARS = [('v', HIDDEN, HIDDEN, 0), ('k', HIDDEN, HIDDEN, 0), ('q', HIDDEN, HIDDEN, 0), ('o', HIDDEN, HIDDEN, 1),
+           ('up', INTER, HIDDEN, 2), ('gate', INTER, HIDDEN, 2), ('down', HIDDEN, INTER, 3)]
+GROUP_D = [HIDDEN, HIDDEN, HIDDEN, INTER]
+WORKLOAD = ('llama2-7b decoder layer: 4 Hessians (D=4096 x3, 11008) over 128x2048 tokens + invert + '
+            'GPTQ 4-bit g128 act-order solve of 7 linears + int4 pack')
+
+
+def syrk_flops(T, D):
+    return float(T) * D * (D + 1)                 # upper triangle incl. diagonal, 2 flops/MAC
+
+
+def layer_phase_flops():
+    T = N_SEQ * SEQLEN
+    acc = sum(2.0 * T * D * D for D in GROUP_D)   # what the fp32 addmm of the reference computes
+    inv = sum(4.0 / 3.0 * D ** 3 for D in GROUP_D)
+    sol = sum(float(R) * C * C for _, R, C, _ in LINEARS)
+    return acc, inv, sol
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled while the timed region runs."""
+    Q = ('clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,'
+         'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,'
+         'clocks_event_reasons.sw_power_cap')
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', '-i', str(self.index), f'--query-gpu={self.Q}',
+                                          '--format=csv,noheader,nounits', '-lms', '100'],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(',')])
+
+    def stop(self):
+        if self.proc is None:
+            return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx = float(r[1])
+            except Exception:
+                continue
+            for name, v in zip(('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap'), r[3:7]):
+                if v.lower().startswith('active'):
+                    reasons.add(name)
+        busy = sorted(sm)[len(sm) // 4:] if sm else []          # drop idle samples at the edges
+        return {'sm_mhz': statistics.median(busy) if busy else None, 'sm_max_mhz': mx, 'reasons': sorted(reasons),
+                'samples': len(sm)}
+
+
+# ------------------------------------------------------------------------------------------
+# CPU arm: the oracle port of the reference's fp32 path, bounded sample
+# ------------------------------------------------------------------------------------------
+def cpu_sample(threads):
+    """One 4096x4096 linear: accumulate 16 of the 128 sequences, invert, solve (oracle port of
+    gptq_py.py's use_kernel=False path).  Returns per-phase seconds and the s/layer extrapolation."""
+    from oracle import gptq_oracle as O
+    torch.set_num_threads(threads)
+    D = HIDDEN
+    W, X = O.synth_linear(D, D, CALL_SEQ, SEQLEN, seed=0)
+    t0 = time.perf_counter()
+    H, n = O.hessian_accumulate(None, 0, X)
+    t1 = time.perf_counter()
+    inv = O.hessian_invert(H, n, 1e-2, True)
+    t2 = time.perf_counter()
+    O.gptq_solve_pure(W, inv['U'], inv['perm'], GROUP, BITS)
+    t3 = time.perf_counter()
+    acc_f, inv_f, sol_f = layer_phase_flops()
+    t_acc = (t1 - t0) * acc_f / (2.0 * CALL_SEQ * SEQLEN * D * D)
+    t_inv = (t2 - t1) * inv_f / (4.0 / 3.0 * D ** 3)
+    t_sol = (t3 - t2) * sol_f / (float(D) ** 3)
+    return {'accumulate_s': t1 - t0, 'invert_s': t2 - t1, 'solve_s': t3 - t2,
+            's_per_layer': t_acc + t_inv + t_sol,
+            'sample': (f'one {D}x{D} linear: accumulate {CALL_SEQ} of {N_SEQ} sequences, invert, solve; '
+                       'each phase scaled to the layer by its flop count (2TD^2, 4/3 D^3, RC^2)')}
+
+
+# ------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------
+class Ctx:
+    def __init__(self, n_gpus):
+        self.world = int(os.environ.get('WORLD_SIZE', '1'))
+        self.rank = int(os.environ.get('RANK', '0'))
+        self.local = int(os.environ.get('LOCAL_RANK', '0'))
+        assert self.world == n_gpus, f'--gpus {n_gpus} but WORLD_SIZE={self.world} (launch with torchrun for N>1)'
+        self.dev = torch.device('cuda', self.local)
+        torch.cuda.set_device(self.dev)
+        if self.world > 1:
+            import torch.distributed as dist
+            os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+            dist.init_process_group('nccl', device_id=self.dev)
+            self.dist = dist
+        else:
+            self.dist = None
+
+    def barrier(self):
+        if self.dist is not None:
+            self.dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(self, v):
+        if self.dist is None:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device=self.dev)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+
+def make_layer(ctx, host: bool):
+    """Synthetic layer: fp16 weights randn*0.02 (HF initializer_range), activations randn with a
+    per-column scale exp(U(-1.5, 1.5)) so that act-order is non-trivial."""
+    g = torch.Generator(device=ctx.dev).manual_seed(1234)          # same on every rank (weights, column scales)
+    W = {n: (torch.randn(R, C, device=ctx.dev, generator=g) * 0.02).half() for n, R, C, _ in LINEARS}
+    cs = {D: torch.exp(torch.rand(D, device=ctx.dev, generator=g) * 3.0 - 1.5) for D in set(GROUP_D)}
+    n_local = N_SEQ // ctx.world
+    gl = torch.Generator(device=ctx.dev).manual_seed(99 + ctx.rank)  # each rank owns different sequences
+    X = {}
+    for D in set(GROUP_D):
+        x = torch.empty(n_local, SEQLEN, D, device=ctx.dev, dtype=torch.float16)
+        for i in range(n_local):
+            x[i] = (torch.randn(SEQLEN, D, device=ctx.dev, generator=gl) * cs[D]).half()
+        X[D] = x
+    if host:
+        # pinned host staging: one call's worth per D (the same bytes are sent for every call) + the weights
+        Xh = {D: X[D][:min(CALL_SEQ, n_local)].cpu().pin_memory() for D in X}
+        Wh = {n: w.cpu().pin_memory() for n, w in W.items()}
+        return W, X, Wh, Xh
+    return W, X, None, None
+
+
+def run_step(ctx, W, X, Wh=None, Xh=None, timers=None):
+    """One layer through the reference-facing API.  Host mode (Wh/Xh given): activations and weights
+    come from pinned host memory (double-buffered H2D on a copy stream) and quant_meta goes back to
+    the host, as with the reference's save_device default."""
+    from gptq_py import HessianHook, gptq_quant
+    from gptq import pack_int4
+    host = Xh is not None
+    n_local = N_SEQ // ctx.world
+    call = min(CALL_SEQ, n_local)
+    stream = torch.cuda.current_stream()
+    copy_stream = torch.cuda.Stream() if host else None
+    h2d = d2h = 0
+    out = {}
+    for gi, D in enumerate(GROUP_D):
+        hook = HessianHook()
+        if timers is not None:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+        if host:
+            bufs = [torch.empty(call, SEQLEN, D, device=ctx.dev, dtype=torch.float16) for _ in range(2)]
+            ready = [torch.cuda.Event() for _ in range(2)]
+            freed = [torch.cuda.Event() for _ in range(2)]
+            n_calls = n_local // call
+
+            def issue(ci):
+                b = ci & 1
+                with torch.cuda.stream(copy_stream):
+                    if ci >= 2:
+                        copy_stream.wait_event(freed[b])
+                    bufs[b].copy_(Xh[D][:call], non_blocking=True)
+                    ready[b].record(copy_stream)
+            issue(0)
+            for ci in range(n_calls):
+                if ci + 1 < n_calls:
+                    issue(ci + 1)
+                stream.wait_event(ready[ci & 1])
+                hook.add_batch(bufs[ci & 1])
+                freed[ci & 1].record(stream)
+                h2d += bufs[ci & 1].numel() * 2
+            hook.n_samples = n_local
+        else:
+            for i in range(0, n_local, call):
+                hook.add_batch(X[D][i:i + call])
+        if timers is not None:
+            e1.record(stream)
+            timers['syrk'].append((e0, e1, D))
+        if ctx.dist is not None:
+            ctx.dist.all_reduce(hook.hessian)
+            hook.n_samples = N_SEQ
+        hook.invert(damp_ratio=1e-2, act_order=True)
+        for name, R, C, g in LINEARS:
+            if g != gi:
+                continue
+            rows = R // ctx.world
+            r0 = ctx.rank * rows
+            if host:
+                w = Wh[name][r0:r0 + rows].to(ctx.dev, non_blocking=True)
+                h2d += w.numel() * 2
+            else:
+                w = W[name][r0:r0 + rows]
+            gs = torch.full([C // GROUP], GROUP, dtype=torch.int32)
+            bw = torch.full([C // GROUP], BITS, dtype=torch.int32)
+            res = gptq_quant(weight=w, hessian_hook=hook, group_sizes=gs, group_bit_widths=bw, scale_bit_width=None,
+                             gptq_use_kernel=False, gptq_block_sizes=gs, quant_symmetric=False, quant_mse=False,
+                             save_device=torch.device('cpu') if host else ctx.dev)
+            m = res['quant_meta']
+            if host:
+                d2h += m['qweight'].numel() + m['scale'].numel() * 2 + m['qzero'].numel() + m['perm_inv'].numel() * 2
+                packed = None
+            else:
+                packed = pack_int4(m['qweight'])
+                if ctx.dist is not None:
+                    full = torch.empty(R, C // 8, dtype=torch.int32, device=ctx.dev)
+                    ctx.dist.all_gather_into_tensor(full, packed)
+                    sc = torch.empty(R, C // GROUP, dtype=m['scale'].dtype, device=ctx.dev)
+                    ctx.dist.all_gather_into_tensor(sc, m['scale'])
+                    packed = full
+            out[name] = (packed, res['metrics'])
+        del hook
+    return out, h2d, d2h
+
+
+def gpu_main(args):
+    import gptq
+    ctx = Ctx(args.gpus)
+    torch.backends.cuda.matmul.allow_tf32 = False
+    W, X, Wh, Xh = make_layer(ctx, host=True)
+    lib = gptq.lib
+
+    # ---------------- device-resident timing
+    for _ in range(args.warmup):
+        run_step(ctx, W, X)
+    ctx.barrier()
+    sampler = ClockSampler(ctx.local)
+    if ctx.rank == 0:
+        sampler.start()
+    timers = {'syrk': []}
+    l0 = lib.gq_launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for _ in range(args.steps):
+        out, _, _ = run_step(ctx, W, X, timers=timers)
+    ev1.record()
+    ctx.barrier()
+    launches = lib.gq_launch_count() - l0
+    clocks = sampler.stop() if ctx.rank == 0 else None
+    step_s = ctx.max_over_ranks(ev0.elapsed_time(ev1) / 1e3 / args.steps)
+
+    # K1 roofline from the CUDA events recorded around the SYRK launches of the timed steps
+    n_local = N_SEQ // ctx.world
+    syrk_s = sum(a.elapsed_time(b) for a, b, _ in timers['syrk']) / 1e3
+    syrk_f = sum(syrk_flops(n_local * SEQLEN, D) for _, _, D in timers['syrk'])
+    n_syrk = sum(n_local // min(CALL_SEQ, n_local) for _ in timers['syrk'])
+    per_d = {}
+    for a, b, D in timers['syrk']:
+        per_d.setdefault(D, []).append(a.elapsed_time(b) / 1e3)
+
+    # ---------------- end to end from host buffers
+    for _ in range(max(1, args.warmup - 1)):
+        run_step(ctx, W, X, Wh, Xh)
+    ctx.barrier()
+    t0 = time.perf_counter()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        _, h2d, d2h = run_step(ctx, W, X, Wh, Xh)
+    e1.record()
+    ctx.barrier()
+    e2e_s = ctx.max_over_ranks(max(e0.elapsed_time(e1) / 1e3, time.perf_counter() - t0) / args.steps)
+
+    if ctx.rank != 0:
+        return
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
+    except Exception:
+        pass
+    peak_tf = peaks.get('bf16_tflops_sustained', 1400.0)
+    achieved = syrk_f / syrk_s / 1e12
+    line = {
+        'metric': 'GPTQ s/layer', 'value': step_s, 'unit': 's/layer', 'n_gpus': ctx.world, 'steps': args.steps,
+        'warmup': args.warmup, 'ms_per_step': step_s * 1e3, 'higher_is_better': False, 'scaling': 'strong',
+        'vs_baseline': None, 'dtype': 'f16 x f16 -> f32 (Hessian), f32 (factorisation, solve), u4 codes',
+        'data': 'synthetic',
+        'config': {'workload': WORKLOAD, 'tokens': N_SEQ * SEQLEN, 'bits': BITS, 'group': GROUP,
+                   'l2': 'inputs larger than L2 (2.1 GB / 5.8 GB of activations per Hessian)',
+                   'parallelism': ('single GPU' if ctx.world == 1 else
+                                   f'sequences sharded x{ctx.world} + NCCL all-reduce of H; rows of each linear sharded')},
+        'clocks': clocks,
+        'e2e': {'value': e2e_s, 'unit': 's/layer', 'h2d_bytes_per_step': h2d * ctx.world,
+                'd2h_bytes_per_step': d2h * ctx.world},
+        'gpu_launches': int(launches),
+        'roofline': {'bound': 'tensor', 'kernel': 'syrk_upper_kernel<2> (K1, tcgen05 cta_group::2)',
+                     'achieved': achieved, 'peak': peak_tf, 'unit': 'TFLOP/s', 'frac': achieved / peak_tf,
+                     'peak_source': 'MEASURED_PEAKS.json bf16_tflops_sustained' if peaks else 'fallback 1.4 PF',
+                     'flops_per_launch': syrk_f / n_syrk, 'launch_s': syrk_s / n_syrk, 'traffic': None,
+                     'gemm_equivalent_tflops': 2 * achieved},
+        'detail': {'syrk_s_per_layer': syrk_s / args.steps,
+                   'syrk_s_by_D': {str(D): statistics.mean(v) for D, v in per_d.items()},
+                   'other_s_per_layer': step_s - syrk_s / args.steps,
+                   'full_model_32_layers_s': 32 * step_s},
+    }
+    if ctx.world == 1 and not args.no_cpu:
+        threads = os.cpu_count() or 1
+        cs = cpu_sample(threads)
+        line['cpu_baseline'] = {'value': cs['s_per_layer'], 'unit': 's/layer', 'cores': threads, 'kind': 'port',
+                                'sample': cs['sample'],
+                                'phases_s': {k: cs[k] for k in ('accumulate_s', 'invert_s', 'solve_s')}}
+    print(json.dumps(line))
+
+
+def reference_main(args):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    vals, last = [], None
+    for i in range(args.warmup + args.steps):
+        last = cpu_sample(threads)
+        if i >= args.warmup:
+            vals.append(last['s_per_layer'])
+    v = statistics.mean(vals)
+    line = {
+        'impl': 'reference', 'metric': 'GPTQ s/layer', 'value': v, 'unit': 's/layer', 'n_gpus': args.gpus,
+        'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': v * 1e3, 'higher_is_better': False,
+        'scaling': 'strong', 'vs_baseline': None, 'dtype': 'f32', 'data': 'synthetic',
+        'config': {'workload': WORKLOAD, 'tokens': N_SEQ * SEQLEN, 'bits': BITS, 'group': GROUP},
+        'cpu_baseline': {'value': v, 'unit': 's/layer', 'cores': threads, 'kind': 'port', 'sample': last['sample']},
+        'e2e': {'value': v, 'unit': 's/layer', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+        'gpu_launches': 0,
+    }
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=3)
+    ap.add_argument('--warmup', type=int, default=3)
+    ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
+    args = ap.parse_args()
+    if args.impl == 'reference':
+        # the reference arm's default sample is ~10 s; keep the whole run within minutes
+        args.warmup = min(args.warmup, 1)
+        args.steps = min(args.steps, 3)
+        reference_main(args)
+    else:
+        gpu_main(args)
+
+
+if __name__ == '__main__':
+    main()

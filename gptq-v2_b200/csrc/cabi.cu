@@ -6,7 +6,11 @@ using namespace gq;
 
 static inline cudaStream_t S(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 
+namespace gq { unsigned long long g_launch_count = 0; }
+
 extern "C" {
+
+unsigned long long gq_launch_count(void) { return gq::g_launch_count; }
 
 int gq_abi_version(void) { return GQ_ABI_VERSION; }
 

@@ -16,6 +16,10 @@
 
 namespace gq {
 
+// number of kernels this library has launched (bench.py reports it as gpu_launches)
+extern unsigned long long g_launch_count;
+#define GQ_LAUNCHED() (++::gq::g_launch_count)
+
 // ---- K1
 int syrk_upper(float* H, const void* X, int D, int T, int fmt, int mode, int variant, cudaStream_t st);
 int make_tmap_2d(CUtensorMap* out, const void* base, int elem_kind, uint64_t inner, uint64_t outer,

@@ -142,6 +142,7 @@ int launch_block(const SolveParams& p, cudaStream_t st) {
       return GQ_ERR_CUDA;
     attr_set = true;
   }
+  GQ_LAUNCHED();
   solve_block_kernel<MODE, NB, CodeT><<<(p.R + 31) / 32, 32, smem, st>>>(p);
   return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
 }

@@ -121,6 +121,7 @@ __global__ void antitranspose_kernel(const float* __restrict__ V, float* __restr
 int hessian_gather(const float* H, int D, const int64_t* perm, float scale, float damp, float* Hp, float* Arev,
                    cudaStream_t st) {
   dim3 block(32, 8), grid((D + 31) / 32, (D + 7) / 8);
+  GQ_LAUNCHED();
   gather_kernel<<<grid, block, 0, st>>>(H, D, perm, scale, damp, Hp, Arev);
   return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
 }
@@ -142,6 +143,7 @@ int chol_inverse_upper(float* A, int D, float* U, float* tmp, int* info_dev, cud
   for (int k = 0; k < nb; ++k) {
     const int o = k * NB;
     const int n = min(NB, D - o);
+    GQ_LAUNCHED();
     chol_diag_kernel<<<1, 256, diag_smem, st>>>(A, D, o, n, info_dev);
     if (cudaGetLastError() != cudaSuccess) return GQ_ERR_CUDA;
     const int rest = D - o - n;
@@ -183,6 +185,7 @@ int chol_inverse_upper(float* A, int D, float* U, float* tmp, int* info_dev, cud
     if (b1.count) { if ((rc = flush()) != GQ_OK) return rc; }
   }
   dim3 block(32, 8), grid((D + 31) / 32, (D + 31) / 32);
+  GQ_LAUNCHED();
   antitranspose_kernel<<<grid, block, 0, st>>>(A, U, D);
   return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
 }

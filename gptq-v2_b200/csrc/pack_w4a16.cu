@@ -219,6 +219,7 @@ int launch_w4a16(const void* x, const uint32_t* qw, const void* scale, const uin
   int m0 = 0;
   while (m0 < M) {
     const int rem = M - m0;
+    GQ_LAUNCHED();
     if (rem >= 4) { w4a16_small_m_kernel<XT, 4><<<grid, WARPS * 32, 0, st>>>(xx, qw, ss, qzero, perm, yy, M, N, K, group, m0); m0 += 4; }
     else if (rem >= 2) { w4a16_small_m_kernel<XT, 2><<<grid, WARPS * 32, 0, st>>>(xx, qw, ss, qzero, perm, yy, M, N, K, group, m0); m0 += 2; }
     else { w4a16_small_m_kernel<XT, 1><<<grid, WARPS * 32, 0, st>>>(xx, qw, ss, qzero, perm, yy, M, N, K, group, m0); m0 += 1; }
@@ -230,6 +231,7 @@ int launch_w4a16(const void* x, const uint32_t* qw, const void* scale, const uin
 
 int prep_weight_t(const void* W, int fmt, const int64_t* perm, float* Wt, int R, int C, cudaStream_t st) {
   dim3 block(32, 8), grid((R + 31) / 32, (C + 7) / 8);
+  GQ_LAUNCHED();
   if (fmt == 0) prep_weight_t_kernel<__half><<<grid, block, 0, st>>>((const __half*)W, perm, Wt, R, C);
   else if (fmt == 1) prep_weight_t_kernel<__nv_bfloat16><<<grid, block, 0, st>>>((const __nv_bfloat16*)W, perm, Wt, R, C);
   else if (fmt == 2) prep_weight_t_kernel<float><<<grid, block, 0, st>>>((const float*)W, perm, Wt, R, C);
@@ -242,6 +244,7 @@ int pack_int4(const uint8_t* codes, uint32_t* packed, int R, int C, cudaStream_t
   if (reinterpret_cast<uintptr_t>(codes) & 7) return GQ_ERR_ALIGN;
   const size_t n = (size_t)R * (C / 8);
   if (n == 0) return GQ_OK;
+  GQ_LAUNCHED();
   pack_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(codes, packed, n);
   return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
 }
@@ -251,6 +254,7 @@ int unpack_int4(const uint32_t* packed, uint8_t* codes, int R, int C, cudaStream
   if (reinterpret_cast<uintptr_t>(codes) & 7) return GQ_ERR_ALIGN;
   const size_t n = (size_t)R * (C / 8);
   if (n == 0) return GQ_OK;
+  GQ_LAUNCHED();
   unpack_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(packed, codes, n);
   return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
 }
@@ -259,6 +263,7 @@ int transpose_pack_int4(const uint8_t* codes_t, uint8_t* codes, uint32_t* packed
   if (C % 8 != 0) return GQ_ERR_SHAPE;
   if (R == 0 || C == 0) return GQ_OK;
   dim3 block(32, 8), grid((C + 31) / 32, (R + 31) / 32);
+  GQ_LAUNCHED();
   transpose_pack_kernel<<<grid, block, 0, st>>>(codes_t, codes, packed, R, C);
   return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
 }

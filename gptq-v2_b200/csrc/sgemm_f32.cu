@@ -155,6 +155,7 @@ int launch(const GemmBatch& b, float alpha, float beta, cudaStream_t st) {
   for (int i = 0; i < b.count; ++i) { maxM = max(maxM, b.p[i].M); maxN = max(maxN, b.p[i].N); }
   if (maxM <= 0 || maxN <= 0) return GQ_OK;
   dim3 grid((maxN + BN - 1) / BN, (maxM + BM - 1) / BM, b.count);
+  GQ_LAUNCHED();
   sgemm_kernel<FLAGS><<<grid, 256, 0, st>>>(b, alpha, beta);
   return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
 }

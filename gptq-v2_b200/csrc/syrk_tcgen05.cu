@@ -297,6 +297,7 @@ static int launch_syrk(const CUtensorMap& tmap, const SyrkParams& p, int n_sms, 
   at[0].val.clusterDim.z = 1;
   cfg.attrs = at;
   cfg.numAttrs = 1;
+  GQ_LAUNCHED();
   cudaError_t e = cudaLaunchKernelEx(&cfg, syrk_upper_kernel<CG>, tmap, p);
   return e == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
 }

@@ -19,6 +19,7 @@ _vp, _i, _f = C.c_void_p, C.c_int, C.c_float
 SIGNATURES = {
     'gq_abi_version': (_i, []),
     'gq_error_string': (C.c_char_p, [_i]),
+    'gq_launch_count': (C.c_ulonglong, []),
     'gq_accumulate_hessian': (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
     'gq_accumulate_hessian_variant': (_i, [_vp, _vp, _i, _i, _i, _i, _i, _vp]),
     'accumulate_hessian_fp16_fp32_cuda': (_i, [_vp, _vp, _i, _i]),

@@ -27,6 +27,8 @@ extern "C" {
 
 int gq_abi_version(void);
 const char* gq_error_string(int code);
+/* number of kernels launched by this library since it was loaded (monotonic) */
+unsigned long long gq_launch_count(void);
 
 /* ---- K1: Hessian accumulation  H(fp32, D x D) += X^T X,  X (T x D) row-major fp16/bf16.
  * Replaces accumulate_hessian_{fp16,bf16}_fp32_cuda (accumulate_hessian.cpp:4-17,

@@ -6,7 +6,7 @@ nvidia-smi --query-gpu=name,driver_version,clocks.max.sm --format=csv | tee gpur
 for f in tests/test_gpu_syrk.py tests/test_gpu_invert.py tests/test_gpu_solver.py tests/test_gpu_pack_w4a16.py tests/test_gpu_e2e.py; do
   b=$(basename $f .py)
   echo "=== $f"
-  timeout 600 python -m pytest $f -m gpu -q -x --timeout=300 "$@" > gpurun_out/$b.log 2>&1
+  timeout 600 python -m pytest $f -m gpu -q --timeout=300 "$@" > gpurun_out/$b.log 2>&1
   echo "exit $?"
   tail -25 gpurun_out/$b.log
 done
