@@ -8,9 +8,10 @@
 //        U = J (Rt^-1)^T J,   i.e.  U[i][j] = V[D-1-j][D-1-i],  V = Rt^-1.
 // Steps (all fp32, FMA, no TF32):
 //   hessian_gather      A[D-1-i][D-1-j] = scale*Hsym[perm i][perm j] (+damp on the diagonal)
-//   blocked right-looking upper Cholesky, NB=128; the 128x128 diagonal block is
-//     factored AND inverted inside one CTA (chol_diag_kernel), which turns the panel
-//     solve into a GEMM:  P = T_kk^T A[k, k+1:],  A22 -= P^T P   (both "A^T B" GEMMs)
+//   blocked right-looking upper Cholesky, NB=128: chol_diag_kernel (one CTA, the only serial
+//     piece), trsm_panel_kernel  P = R_kk^-T A[k, k+1:]  (forward substitution, 32 columns
+//     per CTA), then  A22 -= P^T P  as an "A^T B" GEMM on the upper tiles
+//   trtri_diag_kernel inverts all diagonal blocks in ONE launch (off the critical path), then
 //   blocked triangular inverse by recursive doubling (batched GEMMs per level)
 //   anti-transpose into U (zeros below the diagonal).
 #include "gptq_b200_internal.h"
@@ -41,14 +42,122 @@ __global__ void gather_kernel(const float* __restrict__ H, int D, const int64_t*
 constexpr int NB = 128;
 constexpr int PITCH = NB + 1;
 
-// Factor the n x n (n <= 128) diagonal block at offset o:  A_kk = R^T R  (upper R),
-// then overwrite it with T = R^-1 (upper).  One CTA, 256 threads.
+// Factor the n x n (n <= 128) diagonal block at offset o in place:  A_kk = R^T R  (upper R).
+// One CTA, 256 threads.  This is the only serial piece of a Cholesky step, so it does nothing else.
 __global__ void __launch_bounds__(256) chol_diag_kernel(float* __restrict__ A, int D, int o, int n,
                                                         int* __restrict__ info) {
   extern __shared__ float sm[];
+  float* S = sm;                    // [NB][PITCH]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int idx = tid; idx < n * n; idx += 256) {
+    const int r = idx / n, c = idx - r * n;
+    if (c >= r) S[r * PITCH + c] = A[(size_t)(o + r) * D + o + c];
+  }
+  __syncthreads();
+  bool bad = false;
+  float* dg = S + NB * PITCH;              // [NB] diagonal of R (S[j][j] keeps the pivot until the end)
+  for (int j = 0; j < n; ++j) {
+    const float piv = S[j * PITCH + j];     // written by the previous trailing update (barrier below)
+    if (!(piv > 0.f)) bad = true;           // also catches NaN
+    const float d = sqrtf(piv);
+    if (tid == 0) dg[j] = d;
+    for (int c = j + 1 + tid; c < n; c += 256) S[j * PITCH + c] = S[j * PITCH + c] / d;
+    __syncthreads();
+    for (int r = j + 1 + warp; r < n; r += 8) {
+      const float f = S[j * PITCH + r];
+      for (int c = r + lane; c < n; c += 32) S[r * PITCH + c] = fmaf(-f, S[j * PITCH + c], S[r * PITCH + c]);
+    }
+    __syncthreads();
+  }
+  for (int j = tid; j < n; j += 256) S[j * PITCH + j] = dg[j];
+  __syncthreads();
+  if (bad && tid == 0) atomicExch(info, 1);
+  for (int idx = tid; idx < n * n; idx += 256) {
+    const int r = idx / n, c = idx - r * n;
+    if (c >= r) A[(size_t)(o + r) * D + o + c] = S[r * PITCH + c];
+  }
+}
+
+// Panel solve  P = R_kk^-T A[k, k+1:]  in place by forward substitution, 32 panel columns per CTA
+// (lane = column, coalesced along the panel row).  Same shape as the GPTQ block solver: warp 0
+// runs the 16-row triangular recurrence on registers, all 4 warps apply the rank-16 update to
+// the remaining rows.
+constexpr int TSB = 16;
+template <int J>
+struct TrsmSteps {
+  static __device__ __forceinline__ void run(float (&w)[TSB], const float* Rrow0, float* xs, float* gout, size_t gstride,
+                                             bool active, int lane) {
+    const float* Rrow = Rrow0 + J * NB;                // row (row0 + J) of R_kk starting at column row0
+    const float x = w[J] / Rrow[J];
+    xs[J * 32 + lane] = x;
+    if (active) gout[(size_t)J * gstride] = x;
+#pragma unroll
+    for (int k = J + 1; k < TSB; ++k) w[k] = fmaf(-x, Rrow[k], w[k]);
+    TrsmSteps<J + 1>::run(w, Rrow0, xs, gout, gstride, active, lane);
+  }
+};
+template <>
+struct TrsmSteps<TSB> {
+  static __device__ __forceinline__ void run(float (&)[TSB], const float*, float*, float*, size_t, bool, int) {}
+};
+
+__global__ void __launch_bounds__(128) trsm_panel_kernel(float* __restrict__ A, int D, int o, int n, int rest) {
+  extern __shared__ __align__(16) float sm[];
+  float* Rb = sm;                   // [NB][NB] upper factor of the diagonal block
+  float* ws = Rb + NB * NB;         // [NB][32]
+  float* xs = ws + NB * 32;         // [16][32]
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int col = blockIdx.x * 32 + lane;
+  const bool active = col < rest;
+  for (int idx = tid; idx < n * (n / 4); idx += 128) {
+    const int r = idx / (n / 4), c4 = (idx - r * (n / 4)) * 4;
+    *reinterpret_cast<float4*>(Rb + r * NB + c4) =
+        *reinterpret_cast<const float4*>(A + (size_t)(o + r) * D + o + c4);
+  }
+  float* panel = A + (size_t)o * D + o + n + col;
+  for (int i = warp; i < n; i += 4) ws[i * 32 + lane] = active ? panel[(size_t)i * D] : 0.f;
+  __syncthreads();
+#pragma unroll 1
+  for (int sb = 0; sb < n / TSB; ++sb) {
+    const int row0 = sb * TSB;
+    if (warp == 0) {
+      float w[TSB];
+#pragma unroll
+      for (int j = 0; j < TSB; ++j) w[j] = ws[(row0 + j) * 32 + lane];
+      TrsmSteps<0>::run(w, Rb + row0 * NB + row0, xs, panel + (size_t)row0 * D, (size_t)D, active, lane);
+    }
+    __syncthreads();
+    if (row0 + TSB < n) {
+      float x[TSB];
+#pragma unroll
+      for (int j = 0; j < TSB; ++j) x[j] = xs[j * 32 + lane];
+#pragma unroll 1
+      for (int i = row0 + TSB + 4 * warp; i < n; i += 16) {
+        float w0 = ws[(i + 0) * 32 + lane], w1 = ws[(i + 1) * 32 + lane];
+        float w2 = ws[(i + 2) * 32 + lane], w3 = ws[(i + 3) * 32 + lane];
+#pragma unroll
+        for (int j = 0; j < TSB; ++j) {
+          const float4 u = *reinterpret_cast<const float4*>(Rb + (row0 + j) * NB + i);
+          w0 = fmaf(-x[j], u.x, w0); w1 = fmaf(-x[j], u.y, w1);
+          w2 = fmaf(-x[j], u.z, w2); w3 = fmaf(-x[j], u.w, w3);
+        }
+        ws[(i + 0) * 32 + lane] = w0; ws[(i + 1) * 32 + lane] = w1;
+        ws[(i + 2) * 32 + lane] = w2; ws[(i + 3) * 32 + lane] = w3;
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// Invert every diagonal block R_kk (upper) in place, one CTA per block, all blocks in one launch
+// (off the critical path: runs once after the factorisation).
+__global__ void __launch_bounds__(256) trtri_diag_kernel(float* __restrict__ A, int D) {
+  extern __shared__ float sm[];
   float* S = sm;                    // [NB][PITCH] upper factor
   float* Tm = sm + NB * PITCH;      // [NB][PITCH] its inverse
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int o = blockIdx.x * NB;
+  const int n = min(NB, D - o);
+  const int tid = threadIdx.x;
   for (int idx = tid; idx < NB * NB; idx += 256) {
     const int r = idx >> 7, c = idx & 127;
     float v = (r == c) ? 1.f : 0.f;
@@ -57,43 +166,30 @@ __global__ void __launch_bounds__(256) chol_diag_kernel(float* __restrict__ A, i
     Tm[r * PITCH + c] = 0.f;
   }
   __syncthreads();
-  bool bad = false;
-  for (int j = 0; j < n; ++j) {
-    const float piv = S[j * PITCH + j];
-    if (!(piv > 0.f)) bad = true;           // also catches NaN
-    const float d = sqrtf(piv);
-    __syncthreads();                        // everyone has read the pivot
-    for (int c = j + tid; c < n; c += 256) S[j * PITCH + c] = (c == j) ? d : S[j * PITCH + c] / d;
-    __syncthreads();
-    for (int r = j + 1 + warp; r < n; r += 8) {
-      const float f = S[j * PITCH + r];
-      for (int c = r + lane; c < n; c += 32) S[r * PITCH + c] = fmaf(-f, S[j * PITCH + c], S[r * PITCH + c]);
-    }
-    __syncthreads();
-  }
-  if (bad && tid == 0) atomicExch(info, 1);
-  // inverse: two adjacent lanes share column c and split the dot product by parity of k
-  {
-    const int c = tid >> 1, par = tid & 1;
-    for (int i = NB - 1; i >= 0; --i) {
-      // all threads run the same trip count (uniform shuffles); inactive ones contribute 0
-      float s = 0.f;
-      if (c < n && i < c) {
-        for (int k = i + 1 + par; k <= c; k += 2) s = fmaf(S[i * PITCH + k], Tm[k * PITCH + c], s);
+  // two adjacent lanes share column c and split the dot product by parity of k
+  const int c = tid >> 1, par = tid & 1;
+  for (int i = NB - 1; i >= 0; --i) {
+    float s0 = 0.f, s1 = 0.f;
+    if (c < n && i < c) {
+      int k = i + 1 + par;
+      for (; k + 2 <= c; k += 4) {
+        s0 = fmaf(S[i * PITCH + k], Tm[k * PITCH + c], s0);
+        s1 = fmaf(S[i * PITCH + k + 2], Tm[(k + 2) * PITCH + c], s1);
       }
-      s += __shfl_xor_sync(0xffffffffu, s, 1);
-      if (c < n && i <= c && par == 0) {
-        const float rhs = (i == c) ? 1.f : 0.f;
-        Tm[i * PITCH + c] = (rhs - s) / S[i * PITCH + i];
-      }
-      __syncwarp();
-      // column c only depends on rows of the same column -> no block-level sync needed
+      for (; k <= c; k += 2) s0 = fmaf(S[i * PITCH + k], Tm[k * PITCH + c], s0);
     }
+    float s = s0 + s1;
+    s += __shfl_xor_sync(0xffffffffu, s, 1);
+    if (c < n && i <= c && par == 0) {
+      const float rhs = (i == c) ? 1.f : 0.f;
+      Tm[i * PITCH + c] = (rhs - s) / S[i * PITCH + i];
+    }
+    __syncwarp();                   // column c only depends on earlier rows of the same column
   }
   __syncthreads();
   for (int idx = tid; idx < NB * NB; idx += 256) {
-    const int r = idx >> 7, c = idx & 127;
-    if (r < n && c < n) A[(size_t)(o + r) * D + o + c] = (c >= r) ? Tm[r * PITCH + c] : 0.f;
+    const int r = idx >> 7, cc = idx & 127;
+    if (r < n && cc < n) A[(size_t)(o + r) * D + o + cc] = (cc >= r) ? Tm[r * PITCH + cc] : 0.f;
   }
 }
 
@@ -129,17 +225,21 @@ int hessian_gather(const float* H, int D, const int64_t* perm, float scale, floa
 // A: (D x D) work buffer holding the (reversed) SPD matrix, overwritten.
 // U: (D x D) output.  tmp: >= D*D/2 floats.  info_dev: device int, set to 1 on a bad pivot.
 int chol_inverse_upper(float* A, int D, float* U, float* tmp, int* info_dev, cudaStream_t st) {
-  if (D % 4 != 0) return GQ_ERR_SHAPE;
+  if (D % 16 != 0) return GQ_ERR_SHAPE;
   static bool attr_set = false;
-  const int diag_smem = 2 * NB * PITCH * (int)sizeof(float);
+  const int diag_smem = (NB * PITCH + NB) * (int)sizeof(float);
+  const int trtri_smem = 2 * NB * PITCH * (int)sizeof(float);
+  const int trsm_smem = (NB * NB + NB * 32 + TSB * 32) * (int)sizeof(float);
   if (!attr_set) {
-    if (cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, diag_smem) != cudaSuccess)
+    if (cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, diag_smem) != cudaSuccess ||
+        cudaFuncSetAttribute(trtri_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, trtri_smem) != cudaSuccess ||
+        cudaFuncSetAttribute(trsm_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, trsm_smem) != cudaSuccess)
       return GQ_ERR_CUDA;
     attr_set = true;
   }
   const int nb = (D + NB - 1) / NB;
   int rc;
-  // ---- blocked upper Cholesky; diagonal blocks end up holding T_kk = R_kk^-1
+  // ---- blocked right-looking upper Cholesky
   for (int k = 0; k < nb; ++k) {
     const int o = k * NB;
     const int n = min(NB, D - o);
@@ -148,15 +248,20 @@ int chol_inverse_upper(float* A, int D, float* U, float* tmp, int* info_dev, cud
     if (cudaGetLastError() != cudaSuccess) return GQ_ERR_CUDA;
     const int rest = D - o - n;
     if (rest <= 0) break;
-    float* panel = A + (size_t)o * D + o + n;
-    // P = T_kk^T * A[k, k+1:]   (in place: each CTA owns whole columns, K = n fits one tile pass)
-    GemmProblem p1{A + (size_t)o * D + o, panel, panel, n, rest, n, D, D, D};
-    if ((rc = sgemm(p1, 1.f, 0.f, GEMM_TRANS_A | GEMM_A_UPPER, st)) != GQ_OK) return rc;
+    // P = R_kk^-T * A[k, k+1:]  (forward substitution, in place)
+    GQ_LAUNCHED();
+    trsm_panel_kernel<<<(rest + 31) / 32, 128, trsm_smem, st>>>(A, D, o, n, rest);
+    if (cudaGetLastError() != cudaSuccess) return GQ_ERR_CUDA;
     // A22 -= P^T P  (upper tiles only)
+    float* panel = A + (size_t)o * D + o + n;
     float* a22 = A + (size_t)(o + n) * D + o + n;
     GemmProblem p2{panel, panel, a22, rest, rest, n, D, D, D};
     if ((rc = sgemm(p2, -1.f, 1.f, GEMM_TRANS_A | GEMM_C_UPPER, st)) != GQ_OK) return rc;
   }
+  // ---- all diagonal blocks: R_kk -> R_kk^-1, one launch
+  GQ_LAUNCHED();
+  trtri_diag_kernel<<<nb, 256, trtri_smem, st>>>(A, D);
+  if (cudaGetLastError() != cudaSuccess) return GQ_ERR_CUDA;
   // ---- V = R^-1 by recursive doubling over diagonal blocks: V12 = -V11 (R12 V22)
   for (int w = 1; w < nb; w *= 2) {
     GemmBatch b1, b2;

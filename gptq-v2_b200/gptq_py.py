@@ -51,7 +51,7 @@ class HessianHook:
             inp = inp.to(dtype=torch.float32)
             torch.addmm(self.hessian, inp.t(), inp, beta=1, alpha=1, out=self.hessian)
         else:
-            _ops.hessian_syrk(self.hessian, inp.contiguous(), mode=1)
+            _ops.hessian_syrk(self.hessian, inp.contiguous(), mode=0)   # upper triangle only: invert() reads nothing else
 
     @torch.no_grad()
     def invert(self, damp_ratio: float = 1e-2, act_order: bool = True) -> torch.Tensor:

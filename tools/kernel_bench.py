@@ -1,0 +1,118 @@
+#!/usr/bin/env python
+"""Per-kernel timings with CUDA events (no profiler): K1 SYRK, K2 invert, K3+K4 solve, K5 pack, K6 W4A16.
+usage: python tools/kernel_bench.py [syrk] [invert] [solve] [w4a16] [sgemm]"""
+import json
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, 'gptq-v2_b200'))
+import torch  # noqa: E402
+import gptq  # noqa: E402
+
+dev = torch.device('cuda')
+
+
+def timeit(fn, iters=5, warm=2):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(iters):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); fn(); b.record(); torch.cuda.synchronize()
+        ts.append(a.elapsed_time(b) / 1e3)
+    ts.sort()
+    return ts[len(ts) // 2]
+
+
+def bench_syrk():
+    for D in (4096, 11008, 5120, 13824):
+        T = 32768
+        X = torch.randn(T, D, device=dev).half()
+        H = torch.zeros(D, D, device=dev)
+        for variant in (1, 2):
+            for mode in (0, 1):
+                t = timeit(lambda: gptq.hessian_syrk(H, X, mode=mode, variant=variant))
+                print(json.dumps({'k': 'syrk', 'D': D, 'T': T, 'variant': variant, 'mode': mode, 'ms': t * 1e3,
+                                  'tflops_tri': T * D * (D + 1) / t / 1e12}))
+        del X, H
+
+
+def bench_invert():
+    for D in (4096, 11008):
+        X = torch.randn(2 * D, D, device=dev) * torch.exp(torch.rand(D, device=dev) * 3 - 1.5)
+        H = (X.t() @ X)
+        perm = torch.argsort(H.diagonal(), descending=True)
+        damp = 0.01 * float(H.diagonal().mean())
+        t = timeit(lambda: gptq.hessian_invert(H, perm, 1.0, damp), iters=3, warm=1)
+        print(json.dumps({'k': 'invert', 'D': D, 'ms': t * 1e3, 'tflops_2_3_D3': 2 / 3 * D ** 3 / t / 1e12}))
+        torch.backends.cuda.matmul.allow_tf32 = False
+        Hp = H[perm][:, perm] + damp * torch.eye(D, device=dev)
+
+        def ref():
+            L = torch.linalg.cholesky_ex(Hp)[0]
+            Hi = torch.cholesky_inverse(L)
+            return torch.linalg.cholesky_ex(Hi, upper=True)[0]
+        t2 = timeit(ref, iters=3, warm=1)
+        print(json.dumps({'k': 'invert_torch_cusolver', 'D': D, 'ms': t2 * 1e3}))
+        del X, H, Hp
+
+
+def bench_solve():
+    for R, C in ((4096, 4096), (11008, 4096), (4096, 11008)):
+        X = torch.randn(2 * C, C, device=dev) * torch.exp(torch.rand(C, device=dev) * 3 - 1.5)
+        H = X.t() @ X
+        _, U, _ = gptq.hessian_invert(H, None, 1.0, 0.01 * float(H.diagonal().mean()), want_hp=False)
+        W = (torch.randn(R, C, device=dev) * 0.02).half()
+        Wt0 = gptq.prep_weight_t(W, None)
+
+        def run():
+            Wt = Wt0.clone()
+            gptq.gptq_solve(Wt, U, 128, 15.0)
+        t = timeit(run, iters=3, warm=1)
+        tc = timeit(lambda: Wt0.clone(), iters=3, warm=1)
+        print(json.dumps({'k': 'solve', 'R': R, 'C': C, 'ms': (t - tc) * 1e3, 'trailing_tflops': R * C * C / (t - tc) / 1e12,
+                          'us_per_block': (t - tc) / (C / 128) * 1e6}))
+        del X, H, U, W, Wt0
+
+
+def bench_sgemm():
+    torch.backends.cuda.matmul.allow_tf32 = False
+    for M, N, K, flags in ((3968, 4096, 128, 1), (10880, 4096, 128, 1), (4096, 4096, 128, 3), (4096, 4096, 4096, 0)):
+        A = torch.randn((K, M) if flags & 1 else (M, K), device=dev)
+        B = torch.randn(K, N, device=dev)
+        Cm = torch.zeros(M, N, device=dev)
+        t = timeit(lambda: gptq.sgemm(A, B, Cm, M, N, K, A.stride(0), B.stride(0), N, -1.0, 1.0, flags))
+        print(json.dumps({'k': 'sgemm', 'M': M, 'N': N, 'K': K, 'flags': flags, 'us': t * 1e6,
+                          'tflops': 2.0 * M * N * K / t / 1e12}))
+
+
+def bench_w4a16():
+    for N, K in ((4096, 4096), (11008, 4096), (4096, 11008), (8192, 8192), (28672, 8192), (8192, 28672)):
+        G = K // 128
+        nbuf = max(2, int(600e6 // (N * K // 2)) + 1)          # rotate through > 4x L2 of weights
+        qs = [torch.randint(-2 ** 31, 2 ** 31 - 1, (N, K // 8), device=dev, dtype=torch.int32) for _ in range(nbuf)]
+        sc = (torch.rand(N, G, device=dev) * 0.01 + 1e-3).half()
+        qz = torch.randint(0, 16, (N, G), device=dev, dtype=torch.uint8)
+        perm = torch.randperm(K, device=dev).to(torch.int32)
+        for M in (1, 2, 4, 8, 16):
+            x = torch.randn(M, K, device=dev).half()
+            i = [0]
+
+            def run():
+                i[0] = (i[0] + 1) % nbuf
+                gptq.w4a16_gemm(x, qs[i[0]], sc, qz, perm, 128)
+            t = timeit(run, iters=11, warm=3)
+            byts = N * K / 2 + N * G * 3 + 2 * M * K + 2 * M * N
+            print(json.dumps({'k': 'w4a16', 'M': M, 'N': N, 'K': K, 'us': t * 1e6, 'GBps': byts / t / 1e9,
+                              'tflops': 2.0 * M * N * K / t / 1e12}))
+        del qs
+
+
+if __name__ == '__main__':
+    which = sys.argv[1:] or ['syrk', 'invert', 'solve', 'sgemm', 'w4a16']
+    for w in which:
+        globals()['bench_' + w]()
