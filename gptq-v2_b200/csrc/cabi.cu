@@ -6,7 +6,7 @@ using namespace gq;
 
 static inline cudaStream_t S(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 
-namespace gq { unsigned long long g_launch_count = 0; }
+namespace gq { unsigned long long g_launch_count = 0; int g_use_tf32x3 = 1; }
 
 extern "C" {
 
@@ -86,15 +86,27 @@ int gq_transpose_pack_int4(const uint8_t* codes_t, uint8_t* codes, uint32_t* pac
   return transpose_pack_int4(codes_t, codes, packed, R, C, S(stream));
 }
 
+size_t gq_w4a16_workspace_bytes(int M, int K) { return w4a16_workspace_bytes(M, K); }
 int gq_w4a16_gemm(const void* x, const uint32_t* qweight, const void* scale, const uint8_t* qzero,
-                  const int32_t* perm, void* y, int M, int N, int K, int group, int dtype, void* stream) {
-  return w4a16_gemm(x, qweight, scale, qzero, perm, y, M, N, K, group, dtype, S(stream));
+                  const int32_t* perm, void* y, void* workspace, int M, int N, int K, int group, int dtype,
+                  void* stream) {
+  return w4a16_gemm(x, qweight, scale, qzero, perm, y, workspace, M, N, K, group, dtype, S(stream));
 }
 
 int gq_sgemm(const float* A, const float* B, float* C, int M, int N, int K, int lda, int ldb, int ldc, float alpha,
              float beta, int flags, void* stream) {
   GemmProblem p{A, B, C, M, N, K, lda, ldb, ldc};
   return sgemm(p, alpha, beta, flags, S(stream));
+}
+
+int gq_set_tf32x3(int enable) { int old = gq::g_use_tf32x3; gq::g_use_tf32x3 = enable ? 1 : 0; return old; }
+
+int gq_gemm_tf32x3(const float* A, const float* B, float* C, int M, int N, int K, int lda, int ldb, int ldc, float alpha,
+                   int upper_only, void* stream) {
+  Tf32Maps maps;
+  int rc = gemm_tf32x3_maps(&maps, A, K, M, lda, B, K, N, ldb, C, M, N, ldc);
+  if (rc != GQ_OK) return rc;
+  return gemm_tf32x3(maps, M, N, K, 0, 0, 0, 0, 0, 0, alpha, upper_only, S(stream));
 }
 
 }  // extern "C"

@@ -1,0 +1,285 @@
+// fp32-faithful "A^T B" GEMM on the 5th-gen tensor cores:   C += alpha * A^T B
+//   A stored (K x M) row-major, B stored (K x N) row-major, C (M x N) row-major, all fp32.
+//
+// Used for the two K=128-deep updates that dominate everything after the Hessian:
+//   K4  lazy-batch trailing update  W[b:, :] -= Hinv[a:b, b:]^T err[a:b, :]   (gptq_py.py:193,
+//       gptq_cpp.cpp:81-83 -- an fp32 addmm_ in the reference, TF32 disabled by main.py:12-13)
+//   K2  Cholesky trailing update    A22 -= P^T P  (upper tiles only)
+// tcgen05 has no fp32 x fp32 kind, and a single TF32 pass (10-bit mantissa) flips quantisation
+// codes, so each operand is split on the fly  x = hi + lo,  hi = rna_tf32(x), lo = x - hi,  and
+//   A^T B ~= hi^T hi + hi^T lo + lo^T hi        (3 x kind::tf32, fp32 accumulation in TMEM)
+// whose relative error (~2^-21) is below what reordering an fp32 sum already causes.
+//
+// Pipeline per CTA (persistent over 128 x 256 output tiles, 384 threads):
+//   warp 0      TMA producer: [16 k][32 cols] fp32 boxes, SWIZZLE_128B_ATOM_32B (both operands MN-major)
+//   warps 8-11  split: read the landed tile, write hi back in place and lo next to it
+//               (element-wise on identical swizzled addresses, so no layout knowledge needed)
+//   warp 1      one thread issues 3 x tcgen05.mma.kind::tf32 per 8-deep k-slice
+//   warps 4-7   epilogue: tcgen05.ld -> * alpha -> swizzled smem -> TMA reduce-add
+//               (cp.reduce.async.bulk.tensor ... add.f32): C is never read by the SM, the
+//               read-modify-write happens in L2, edges are clipped by the tensor map.
+#include "gptq_b200_internal.h"
+#include "ptx.cuh"
+
+namespace gq {
+namespace {
+
+constexpr int TM = 128, TN = 256, BK = 16;
+constexpr int SUB = BK * 128;                       // one [16 k][32 fp32] box = 2 KB
+constexpr int A_SUBS = TM / 32, B_SUBS = TN / 32;   // 4, 8
+constexpr int HI_BYTES = (A_SUBS + B_SUBS) * SUB;   // 24 KB
+constexpr int STAGE_BYTES = 2 * HI_BYTES;           // hi + lo
+constexpr int STAGES = 4;
+constexpr int EPI_BUF = 32 * 128;                   // one 32 x 32 fp32 staging tile
+constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 4 * 2 * EPI_BUF + 1024 + 256;
+
+struct GemmTf32Params {
+  int M, N, K;
+  int a_col0, a_row0;      // A^T operand: element (k, m) is at tensor-map coordinate (a_col0 + m, a_row0 + k)
+  int b_col0, b_row0;
+  int c_col0, c_row0;      // C element (m, n) at (c_col0 + n, c_row0 + m)
+  float alpha;
+  int upper_only;          // skip tiles entirely below the diagonal (M == N)
+};
+
+__device__ __forceinline__ void tma_reduce_add_2d(const void* tmap, uint32_t src, int c0, int c1) {
+  asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];"
+               :: "l"(reinterpret_cast<uint64_t>(tmap)), "r"(src), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ float rna_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+
+__global__ void __launch_bounds__(384, 1)
+gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
+                   const __grid_constant__ CUtensorMap map_c, const GemmTf32Params p) {
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
+  const uint32_t epi_base = smem_base + STAGES * STAGE_BYTES;
+  const uint32_t bar_base = epi_base + 4 * 2 * EPI_BUF;
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto ready_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (2 * STAGES + s); };
+  auto tfull_bar = [&](int s) { return bar_base + 8u * (3 * STAGES + s); };
+  auto tempty_bar = [&](int s) { return bar_base + 8u * (3 * STAGES + 2 + s); };
+  const uint32_t tmem_slot = bar_base + 8u * (3 * STAGES + 4);
+  volatile uint32_t* tmem_slot_ptr =
+      reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int tiles_m = (p.M + TM - 1) / TM, tiles_n = (p.N + TN - 1) / TN;
+  const int n_tiles = tiles_m * tiles_n;
+  const int num_kb = p.K / BK;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&map_a); tma_prefetch_desc(&map_b); tma_prefetch_desc(&map_c);
+    for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(ready_bar(s), 128); mbar_init(empty_bar(s), 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 4); }
+    fence_mbar_init();
+  }
+  if (warp == 2) { tmem_alloc<1>(tmem_slot, 512); tmem_relinquish<1>(); }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  auto tile_skipped = [&](int t) {
+    if (!p.upper_only) return false;
+    const int m0 = (t / tiles_n) * TM, n0 = (t % tiles_n) * TN;
+    return m0 >= n0 + TN;
+  };
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        if (tile_skipped(t)) continue;
+        const int m0 = (t / tiles_n) * TM, n0 = (t % tiles_n) * TN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1u);
+          const uint32_t sa = smem_base + stage * STAGE_BYTES;
+          mbar_expect_tx(full_bar(stage), HI_BYTES);
+#pragma unroll
+          for (int i = 0; i < A_SUBS; ++i)
+            tma_load_2d(sa + i * SUB, &map_a, full_bar(stage), p.a_col0 + m0 + 32 * i, p.a_row0 + kb * BK);
+#pragma unroll
+          for (int j = 0; j < B_SUBS; ++j)
+            tma_load_2d(sa + (A_SUBS + j) * SUB, &map_b, full_bar(stage), p.b_col0 + n0 + 32 * j, p.b_row0 + kb * BK);
+          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      const uint32_t idesc = umma_idesc(2u /*tf32*/, 1u, 1u, TM, TN);
+      int stage = 0; uint32_t phase = 0;
+      int it = 0;
+      for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        if (tile_skipped(t)) continue;
+        const int acc = it & 1;
+        const uint32_t acc_phase = (it >> 1) & 1u;
+        ++it;
+        mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * TN;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(ready_bar(stage), phase);
+          tc_fence_after();
+          const uint32_t a_hi = smem_base + stage * STAGE_BYTES;
+          const uint32_t b_hi = a_hi + A_SUBS * SUB;
+          const uint32_t a_lo = a_hi + HI_BYTES;
+          const uint32_t b_lo = b_hi + HI_BYTES;
+#pragma unroll
+          for (int k8 = 0; k8 < BK / 8; ++k8) {
+            // MN-major tf32: SWIZZLE_128B_BASE32B, atoms of [4 k][32 fp32]; an MMA (K = 8) spans two
+            // atoms (SBO = 512 B) and 32-column groups sit LBO = one sub-block apart; +1024 B per MMA
+            const uint64_t ah = umma_smem_desc(a_hi + k8 * 1024, SUB, 512, 1u);
+            const uint64_t bh = umma_smem_desc(b_hi + k8 * 1024, SUB, 512, 1u);
+            const uint64_t al = umma_smem_desc(a_lo + k8 * 1024, SUB, 512, 1u);
+            const uint64_t bl = umma_smem_desc(b_lo + k8 * 1024, SUB, 512, 1u);
+            mma_tf32<1>(d_tmem, al, bh, idesc, (kb | k8) ? 1u : 0u);     // small terms first
+            mma_tf32<1>(d_tmem, ah, bl, idesc, 1u);
+            mma_tf32<1>(d_tmem, ah, bh, idesc, 1u);
+          }
+          tc_commit_cg1(empty_bar(stage));
+          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+        }
+        tc_commit_cg1(tfull_bar(acc));
+      }
+    }
+  } else if (warp >= 8) {
+    // ---- split hi / lo, element-wise over the 24 KB that just landed
+    const int tid = threadIdx.x - 256;                 // 0..127
+    int stage = 0; uint32_t phase = 0;
+    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+      if (tile_skipped(t)) continue;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(full_bar(stage), phase);
+        float4* hi = reinterpret_cast<float4*>(smem_gen + stage * STAGE_BYTES);
+        float4* lo = reinterpret_cast<float4*>(smem_gen + stage * STAGE_BYTES + HI_BYTES);
+#pragma unroll
+        for (int i = 0; i < HI_BYTES / 16 / 128; ++i) {
+          const int idx = i * 128 + tid;
+          const float4 v = hi[idx];
+          float4 h, l;
+          h.x = rna_tf32(v.x); h.y = rna_tf32(v.y); h.z = rna_tf32(v.z); h.w = rna_tf32(v.w);
+          l.x = v.x - h.x; l.y = v.y - h.y; l.z = v.z - h.z; l.w = v.w - h.w;
+          hi[idx] = h;
+          lo[idx] = l;
+        }
+        fence_proxy_async();                            // generic-proxy writes -> visible to the tensor core
+        mbar_arrive(ready_bar(stage));
+        if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+      }
+    }
+  } else if (warp >= 4) {
+    // ---- epilogue
+    const int we = warp - 4;
+    const uint32_t stg0 = epi_base + we * 2 * EPI_BUF;
+    int it = 0;
+    int buf = 0;
+    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+      if (tile_skipped(t)) continue;
+      const int m0 = (t / tiles_n) * TM, n0 = (t % tiles_n) * TN;
+      const int acc = it & 1;
+      const uint32_t acc_phase = (it >> 1) & 1u;
+      ++it;
+      mbar_wait(tfull_bar(acc), acc_phase);
+      tc_fence_after();
+      const uint32_t t_row = tmem_base + (uint32_t(32 * we) << 16) + acc * TN;
+      const bool rows_live = (m0 + 32 * we) < p.M;
+#pragma unroll 1
+      for (int c = 0; c < TN / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32(t_row + c * 32, v);
+        tmem_ld_wait();
+        if (c == TN / 32 - 1) {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(tempty_bar(acc));
+        }
+        if (rows_live && n0 + c * 32 < p.N) {
+          const uint32_t stg = stg0 + buf * EPI_BUF;
+          // the previous reduce from this buffer must have finished reading it
+          if (lane == 0) bulk_wait_read0();
+          __syncwarp();
+#pragma unroll
+          for (int q = 0; q < 8; ++q) {
+            float4 o;
+            o.x = p.alpha * __uint_as_float(v[4 * q + 0]); o.y = p.alpha * __uint_as_float(v[4 * q + 1]);
+            o.z = p.alpha * __uint_as_float(v[4 * q + 2]); o.w = p.alpha * __uint_as_float(v[4 * q + 3]);
+            // SWIZZLE_128B staging: row = lane, 16-byte chunk q lands at q ^ (row & 7)
+            const uint32_t addr = stg + lane * 128 + ((q ^ (lane & 7)) << 4);
+            asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};"
+                         :: "r"(addr), "f"(o.x), "f"(o.y), "f"(o.z), "f"(o.w) : "memory");
+          }
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) {
+            tma_reduce_add_2d(&map_c, stg, p.c_col0 + n0 + c * 32, p.c_row0 + m0 + 32 * we);
+            bulk_commit();
+          }
+          buf ^= 1;
+        }
+      }
+    }
+    if (lane == 0) bulk_wait_all();
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc<1>(tmem_base, 512);
+}
+
+int make_map_f32(CUtensorMap* out, const float* base, int rows, int cols, int ld, int box_cols, int box_rows,
+                 int atom32) {
+  return make_tmap_2d(out, base, 2, (uint64_t)cols, (uint64_t)rows, (uint64_t)ld * 4, box_cols, box_rows, atom32);
+}
+
+}  // namespace
+
+// Tensor maps are over whole matrices; the operands are windows given by coordinates.
+int gemm_tf32x3_maps(Tf32Maps* maps, const float* A, int a_rows, int a_cols, int lda, const float* B, int b_rows,
+                     int b_cols, int ldb, float* C, int c_rows, int c_cols, int ldc) {
+  int rc;
+  if ((lda | ldb | ldc) & 3) return GQ_ERR_SHAPE;
+  if ((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B) | reinterpret_cast<uintptr_t>(C)) & 15)
+    return GQ_ERR_ALIGN;
+  if ((rc = make_map_f32(&maps->a, A, a_rows, a_cols, lda, 32, BK, 1)) != GQ_OK) return rc;
+  if ((rc = make_map_f32(&maps->b, B, b_rows, b_cols, ldb, 32, BK, 1)) != GQ_OK) return rc;
+  if ((rc = make_map_f32(&maps->c, C, c_rows, c_cols, ldc, 32, 32, 0)) != GQ_OK) return rc;
+  return GQ_OK;
+}
+
+int gemm_tf32x3(const Tf32Maps& maps, int M, int N, int K, int a_row0, int a_col0, int b_row0, int b_col0, int c_row0,
+                int c_col0, float alpha, int upper_only, cudaStream_t st) {
+  if (M <= 0 || N <= 0 || K <= 0) return GQ_OK;
+  if (K % BK != 0) return GQ_ERR_SHAPE;
+  static bool attr_set = false;
+  static int n_sms = 0;
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(gemm_tf32x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES) != cudaSuccess)
+      return GQ_ERR_CUDA;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev);
+    attr_set = true;
+  }
+  GemmTf32Params p;
+  p.M = M; p.N = N; p.K = K;
+  p.a_col0 = a_col0; p.a_row0 = a_row0; p.b_col0 = b_col0; p.b_row0 = b_row0; p.c_col0 = c_col0; p.c_row0 = c_row0;
+  p.alpha = alpha; p.upper_only = upper_only;
+  const int tiles = ((M + TM - 1) / TM) * ((N + TN - 1) / TN);
+  const int grid = tiles < n_sms ? tiles : n_sms;
+  GQ_LAUNCHED();
+  gemm_tf32x3_kernel<<<grid, 384, SMEM_BYTES, st>>>(maps.a, maps.b, maps.c, p);
+  return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
+}
+
+}  // namespace gq

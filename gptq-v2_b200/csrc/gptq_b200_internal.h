@@ -23,7 +23,7 @@ extern unsigned long long g_launch_count;
 // ---- K1
 int syrk_upper(float* H, const void* X, int D, int T, int fmt, int mode, int variant, cudaStream_t st);
 int make_tmap_2d(CUtensorMap* out, const void* base, int elem_kind, uint64_t inner, uint64_t outer,
-                 uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_outer);
+                 uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_outer, int swizzle_atom32 = 0);
 
 // ---- fp32 GEMM building block (SIMT):  C = beta*C + alpha * op(A) * B
 enum : int {
@@ -41,6 +41,14 @@ struct GemmBatch { GemmProblem p[GEMM_MAX_BATCH]; int count; };
 int sgemm(const GemmProblem& pr, float alpha, float beta, int flags, cudaStream_t st);
 int sgemm_batched(const GemmBatch& b, float alpha, float beta, int flags, cudaStream_t st);
 
+// ---- fp32-faithful tensor-core GEMM  C += alpha * A^T B  (3 x TF32 split, tcgen05)
+extern int g_use_tf32x3;   // 1 (default): K4 / Cholesky updates on tcgen05 3xTF32; 0: fp32 SIMT GEMM (A/B parity hook)
+struct Tf32Maps { CUtensorMap a, b, c; };
+int gemm_tf32x3_maps(Tf32Maps* maps, const float* A, int a_rows, int a_cols, int lda, const float* B, int b_rows,
+                     int b_cols, int ldb, float* C, int c_rows, int c_cols, int ldc);
+int gemm_tf32x3(const Tf32Maps& maps, int M, int N, int K, int a_row0, int a_col0, int b_row0, int b_col0, int c_row0,
+                int c_col0, float alpha, int upper_only, cudaStream_t st);
+
 // ---- K2
 int hessian_gather(const float* H, int D, const int64_t* perm, float scale, float damp, float* Hp, float* Arev,
                    cudaStream_t st);
@@ -55,8 +63,9 @@ int gptq_solve(float* Wt, const float* U, float* quant_t, void* codes_t, int cod
 int pack_int4(const uint8_t* codes, uint32_t* packed, int R, int C, cudaStream_t st);
 int unpack_int4(const uint32_t* packed, uint8_t* codes, int R, int C, cudaStream_t st);
 int transpose_pack_int4(const uint8_t* codes_t, uint8_t* codes, uint32_t* packed, int R, int C, cudaStream_t st);
+size_t w4a16_workspace_bytes(int M, int K);
 int w4a16_gemm(const void* x, const uint32_t* qw, const void* scale, const uint8_t* qzero, const int32_t* perm,
-               void* y, int M, int N, int K, int group, int fmt, cudaStream_t st);
+               void* y, void* workspace, int M, int N, int K, int group, int fmt, cudaStream_t st);
 int prep_weight_t(const void* W, int fmt, const int64_t* perm, float* Wt, int R, int C, cudaStream_t st);
 
 }  // namespace gq

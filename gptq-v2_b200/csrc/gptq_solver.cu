@@ -45,6 +45,12 @@ int gptq_solve(float* Wt, const float* U, float* quant_t, void* codes_t, int cod
   if (mode == 0 && (group != 32 && group != 64 && group != 128)) return GQ_ERR_SHAPE;
   if (mode == 0 && ((a % group) || (b % group))) return GQ_ERR_SHAPE;
   if ((a % 4) != 0) return GQ_ERR_SHAPE;                        // 16-byte aligned U row starts
+  Tf32Maps maps;
+  const bool tc = g_use_tf32x3 != 0;
+  if (tc) {
+    int rcm = gemm_tf32x3_maps(&maps, U, C, C, C, err_t, C, R, R, Wt, C, R, R);
+    if (rcm != GQ_OK) return rcm;
+  }
   int c = a;
   while (c < b) {
     int nb = (mode == 0) ? group : ((b - c >= 128) ? 128 : (b - c));
@@ -62,8 +68,12 @@ int gptq_solve(float* Wt, const float* U, float* quant_t, void* codes_t, int cod
     const int e = c + nb;
     if (e < C) {
       // W[e:, :] -= U[c:e, e:]^T * E[c:e, :]
-      GemmProblem g{U + (size_t)c * C + e, err_t + (size_t)c * R, Wt + (size_t)e * R, C - e, R, nb, C, R, R};
-      if ((rc = sgemm(g, -1.f, 1.f, GEMM_TRANS_A, st)) != GQ_OK) return rc;
+      if (tc && nb % 16 == 0) {
+        if ((rc = gemm_tf32x3(maps, C - e, R, nb, c, e, c, 0, e, 0, -1.f, 0, st)) != GQ_OK) return rc;
+      } else {
+        GemmProblem g{U + (size_t)c * C + e, err_t + (size_t)c * R, Wt + (size_t)e * R, C - e, R, nb, C, R, R};
+        if ((rc = sgemm(g, -1.f, 1.f, GEMM_TRANS_A, st)) != GQ_OK) return rc;
+      }
     }
     c = e;
   }

@@ -6,13 +6,15 @@
 // driven by quantize_range, gptq_cpp.cpp:33-84) by ONE launch, and restates the
 // fp32 PyTorch recurrence (gptq_py.py:158-193) the parity tests are judged against.
 //
-// One thread owns one weight row r: its NB columns of the block live in registers, so a
-// column step (quantise, error, rank-1 update of the remaining in-block columns) is
-// register-local; rows are independent, so there is no cross-thread communication at all.
-// The NB x NB diagonal block of U (= chol(H^-1), upper) is staged in shared memory with
-// cp.async.bulk row copies (only the upper-triangular part of each row) and read as
-// warp-wide broadcasts.  All accesses to W/quant/codes/err are coalesced because
-// consecutive threads own consecutive rows of the (C, R) layout.
+// A CTA of 4 warps owns 32 weight rows (lane = row; rows are independent, so there is no
+// cross-row communication).  The block's weights sit in shared memory as ws[column][lane]
+// (conflict-free), the NB x NB diagonal block of U (= chol(H^-1), upper) is staged with
+// cp.async.bulk row copies (upper-triangular part only) and read as warp-wide broadcasts.
+// Per 16-column sub-block warp 0 runs the serial column recurrence on registers (compile-time
+// indices, ~1 K instructions re-used by the rolled sub-block loop, so it stays in the
+// instruction cache), then all 4 warps apply the rank-16 update to the remaining columns.
+// All accesses to W/quant/codes/err are coalesced because consecutive lanes own consecutive
+// rows of the (C, R) layout.
 //
 // MODE 0 ("pure", gptq_py.py:169-193): scale/zero computed at the block start from the
 //   *updated* weights (quant.py:114-118), fp32 dequant, update = w - (e*u) with two
@@ -34,16 +36,28 @@ constexpr int SB = 16;          // columns per register sub-block
 constexpr int ROWS = 32;        // weight rows per CTA (one per lane)
 constexpr int SOLVE_WARPS = 4;
 
+// Correctly rounded a / b from rb = RN(1/b) in three dependent operations (Markstein): q = a*rb,
+// r = fma(-q, b, a) (exact), q' = fma(r, rb, q).  Same result as __fdiv_rn for normal operands
+// (checked against IEEE division on 16 M pairs incl. near-tie and all-ones-significand cases,
+// CPU test suite), but the reciprocal is loop-invariant, so the serial per-column
+// chain is ~12 cycles per division instead of ~40.
+__device__ __forceinline__ float div_by(float a, float b, float rb) {
+  const float q = __fmul_rn(a, rb);
+  const float r = __fmaf_rn(-q, b, a);
+  return __fmaf_rn(r, rb, q);
+}
+
 // One column step inside a 16-column sub-block; J is a compile-time index so w[] stays in registers.
 template <int MODE, int NB, typename CodeT, int J>
 struct SubSteps {
   static __device__ __forceinline__ void run(float (&w)[SB], const float* Urow0, float* es, const SolveParams& p,
-                                             CodeT* codes, int col0, float s, float z, __half hs, __half hz,
+                                             CodeT* codes, int col0, float s, float rs, float z, __half hs, __half hz,
                                              bool active, int r, int lane) {
     const float* Urow = Urow0 + J * NB;               // row (col0 + J) of the diagonal block, starting at column col0
     const float d = Urow[J];
+    const float rd = __frcp_rn(d);                    // independent of w: off the serial chain
     const float x = w[J];
-    float q = rintf(__fdiv_rn(x, s));
+    float q = rintf(div_by(x, s, rs));
     q = __fadd_rn(q, z);
     q = fminf(fmaxf(q, 0.f), p.maxq);
     float deq;
@@ -53,7 +67,7 @@ struct SubSteps {
       const __half hq = __float2half_rn(q);
       deq = __half2float(__hmul(__hsub(hq, hz), hs));
     }
-    const float e = __fdiv_rn(__fsub_rn(x, deq), d);
+    const float e = div_by(__fsub_rn(x, deq), d, rd);
     es[J * ROWS + lane] = e;
     if (active) {
       const size_t o = (size_t)(p.c0 + col0 + J) * p.R + r;
@@ -75,13 +89,13 @@ struct SubSteps {
         }
       }
     }
-    SubSteps<MODE, NB, CodeT, J + 1>::run(w, Urow0, es, p, codes, col0, s, z, hs, hz, active, r, lane);
+    SubSteps<MODE, NB, CodeT, J + 1>::run(w, Urow0, es, p, codes, col0, s, rs, z, hs, hz, active, r, lane);
   }
 };
 template <int MODE, int NB, typename CodeT>
 struct SubSteps<MODE, NB, CodeT, SB> {
   static __device__ __forceinline__ void run(float (&)[SB], const float*, float*, const SolveParams&, CodeT*, int,
-                                             float, float, __half, __half, bool, int, int) {}
+                                             float, float, float, __half, __half, bool, int, int) {}
 };
 
 // CTA = 4 warps x 32 rows.  Shared memory: Ub[NB][NB] (diagonal block of U), ws[NB][32] (the
@@ -147,6 +161,7 @@ __global__ void __launch_bounds__(SOLVE_WARPS * 32) solve_block_kernel(const Sol
       s = p.scale[r]; z = p.qzero[r];
     }
   }
+  const float rs = __frcp_rn(s);
   __half hs = __float2half_rn(0.f), hz = hs;
   if (MODE == 1) { hs = __float2half_rn(s); hz = __float2half_rn(z); }
   CodeT* codes = reinterpret_cast<CodeT*>(p.codes_t);
@@ -160,7 +175,7 @@ __global__ void __launch_bounds__(SOLVE_WARPS * 32) solve_block_kernel(const Sol
       float w[SB];
 #pragma unroll
       for (int j = 0; j < SB; ++j) w[j] = ws[(col0 + j) * ROWS + lane];
-      SubSteps<MODE, NB, CodeT, 0>::run(w, Ub + col0 * NB + col0, es, p, codes, col0, s, z, hs, hz, active, r, lane);
+      SubSteps<MODE, NB, CodeT, 0>::run(w, Ub + col0 * NB + col0, es, p, codes, col0, s, rs, z, hs, hz, active, r, lane);
     }
     __syncthreads();
     if (col0 + SB < NB) {

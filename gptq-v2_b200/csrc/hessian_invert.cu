@@ -43,39 +43,75 @@ constexpr int NB = 128;
 constexpr int PITCH = NB + 1;
 
 // Factor the n x n (n <= 128) diagonal block at offset o in place:  A_kk = R^T R  (upper R).
-// One CTA, 256 threads.  This is the only serial piece of a Cholesky step, so it does nothing else.
+// One CTA, 256 threads = 16 x 16, register tiled: thread (ty, tx) owns the 8 x 8 elements
+// (ty + 16 i, tx + 16 k) of the block (2-D cyclic, so the shrinking trailing matrix stays
+// balanced).  Column step j: the owners of row j publish it to shared memory (double buffered),
+// ONE barrier, then every thread scales with 1/sqrt(pivot) and applies the rank-1 update to its
+// 64 registers.  This is the only serial piece of a Cholesky step, so it does nothing else.
 __global__ void __launch_bounds__(256) chol_diag_kernel(float* __restrict__ A, int D, int o, int n,
                                                         int* __restrict__ info) {
-  extern __shared__ float sm[];
-  float* S = sm;                    // [NB][PITCH]
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  for (int idx = tid; idx < n * n; idx += 256) {
-    const int r = idx / n, c = idx - r * n;
-    if (c >= r) S[r * PITCH + c] = A[(size_t)(o + r) * D + o + c];
+  __shared__ float rowbuf[2][NB];
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  float a[8][8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int r = ty + 16 * i, c = tx + 16 * k;
+      // only the upper triangle is meaningful; pad a partial block with the identity
+      a[i][k] = (r < n && c < n) ? ((c >= r) ? A[(size_t)(o + r) * D + o + c] : 0.f) : (r == c ? 1.f : 0.f);
+    }
+  // publish row 0
+  if (ty == 0) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) rowbuf[0][tx + 16 * k] = a[0][k];
   }
   __syncthreads();
   bool bad = false;
-  float* dg = S + NB * PITCH;              // [NB] diagonal of R (S[j][j] keeps the pivot until the end)
-  for (int j = 0; j < n; ++j) {
-    const float piv = S[j * PITCH + j];     // written by the previous trailing update (barrier below)
-    if (!(piv > 0.f)) bad = true;           // also catches NaN
+#pragma unroll 1
+  for (int j = 0; j < NB; ++j) {
+    const float* rb = rowbuf[j & 1];
+    const float piv = rb[j];
+    if (j < n && !(piv > 0.f)) bad = true;          // also catches NaN
     const float d = sqrtf(piv);
-    if (tid == 0) dg[j] = d;
-    for (int c = j + 1 + tid; c < n; c += 256) S[j * PITCH + c] = S[j * PITCH + c] / d;
-    __syncthreads();
-    for (int r = j + 1 + warp; r < n; r += 8) {
-      const float f = S[j * PITCH + r];
-      for (int c = r + lane; c < n; c += 32) S[r * PITCH + c] = fmaf(-f, S[j * PITCH + c], S[r * PITCH + c]);
+    const float rinv = 1.0f / d;
+    float sc[8], sr[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int c = tx + 16 * k;
+      sc[k] = (c > j) ? rb[c] * rinv : 0.f;
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int r = ty + 16 * i;
+      sr[i] = (r > j) ? rb[r] * rinv : 0.f;
+    }
+    // final values of row j of R go straight to global memory
+    if (ty == (j & 15) && j < n) {
+      float* out = A + (size_t)(o + j) * D + o;
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const int c = tx + 16 * k;
+        if (c < n) { if (c > j) out[c] = sc[k]; else if (c == j) out[c] = d; }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+      for (int k = 0; k < 8; ++k) a[i][k] = fmaf(-sr[i], sc[k], a[i][k]);
+    // row j+1 is final now: publish it into the other buffer
+    if (j + 1 < NB && ty == ((j + 1) & 15)) {
+      const int i1 = (j + 1) >> 4;
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        if (i == i1) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) rowbuf[(j + 1) & 1][tx + 16 * k] = a[i][k];
+        }
     }
     __syncthreads();
   }
-  for (int j = tid; j < n; j += 256) S[j * PITCH + j] = dg[j];
-  __syncthreads();
   if (bad && tid == 0) atomicExch(info, 1);
-  for (int idx = tid; idx < n * n; idx += 256) {
-    const int r = idx / n, c = idx - r * n;
-    if (c >= r) A[(size_t)(o + r) * D + o + c] = S[r * PITCH + c];
-  }
 }
 
 // Panel solve  P = R_kk^-T A[k, k+1:]  in place by forward substitution, 32 panel columns per CTA
@@ -227,18 +263,20 @@ int hessian_gather(const float* H, int D, const int64_t* perm, float scale, floa
 int chol_inverse_upper(float* A, int D, float* U, float* tmp, int* info_dev, cudaStream_t st) {
   if (D % 16 != 0) return GQ_ERR_SHAPE;
   static bool attr_set = false;
-  const int diag_smem = (NB * PITCH + NB) * (int)sizeof(float);
+  const int diag_smem = 0;
   const int trtri_smem = 2 * NB * PITCH * (int)sizeof(float);
   const int trsm_smem = (NB * NB + NB * 32 + TSB * 32) * (int)sizeof(float);
   if (!attr_set) {
-    if (cudaFuncSetAttribute(chol_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, diag_smem) != cudaSuccess ||
-        cudaFuncSetAttribute(trtri_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, trtri_smem) != cudaSuccess ||
+    if (cudaFuncSetAttribute(trtri_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, trtri_smem) != cudaSuccess ||
         cudaFuncSetAttribute(trsm_panel_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, trsm_smem) != cudaSuccess)
       return GQ_ERR_CUDA;
     attr_set = true;
   }
   const int nb = (D + NB - 1) / NB;
   int rc;
+  Tf32Maps maps;
+  const bool tc = g_use_tf32x3 != 0;
+  if (tc && (rc = gemm_tf32x3_maps(&maps, A, D, D, D, A, D, D, D, A, D, D, D)) != GQ_OK) return rc;
   // ---- blocked right-looking upper Cholesky
   for (int k = 0; k < nb; ++k) {
     const int o = k * NB;
@@ -255,8 +293,12 @@ int chol_inverse_upper(float* A, int D, float* U, float* tmp, int* info_dev, cud
     // A22 -= P^T P  (upper tiles only)
     float* panel = A + (size_t)o * D + o + n;
     float* a22 = A + (size_t)(o + n) * D + o + n;
-    GemmProblem p2{panel, panel, a22, rest, rest, n, D, D, D};
-    if ((rc = sgemm(p2, -1.f, 1.f, GEMM_TRANS_A | GEMM_C_UPPER, st)) != GQ_OK) return rc;
+    if (tc) {
+      if ((rc = gemm_tf32x3(maps, rest, rest, n, o, o + n, o, o + n, o + n, o + n, -1.f, 1, st)) != GQ_OK) return rc;
+    } else {
+      GemmProblem p2{panel, panel, a22, rest, rest, n, D, D, D};
+      if ((rc = sgemm(p2, -1.f, 1.f, GEMM_TRANS_A | GEMM_C_UPPER, st)) != GQ_OK) return rc;
+    }
   }
   // ---- all diagonal blocks: R_kk -> R_kk^-1, one launch
   GQ_LAUNCHED();

@@ -258,7 +258,7 @@ static PFN_encodeTiled get_encode_fn() {
 }
 
 int make_tmap_2d(CUtensorMap* out, const void* base, int elem_kind, uint64_t inner, uint64_t outer,
-                 uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_outer) {
+                 uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_outer, int swizzle_atom32) {
   PFN_encodeTiled enc = get_encode_fn();
   if (!enc) return GQ_ERR_DRIVER;
   CUtensorMapDataType dt = elem_kind == 0 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16
@@ -269,7 +269,7 @@ int make_tmap_2d(CUtensorMap* out, const void* base, int elem_kind, uint64_t inn
   cuuint32_t box[2] = {box_inner, box_outer};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = enc(out, dt, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                   swizzle_atom32 ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   return r == CUDA_SUCCESS ? GQ_OK : GQ_ERR_TENSORMAP;
 }
 
@@ -308,7 +308,7 @@ int syrk_upper(float* H, const void* X, int D, int T, int fmt, int mode, int var
   if (fmt != 0 && fmt != 1) return GQ_ERR_DTYPE;
   if ((reinterpret_cast<uintptr_t>(X) & 15) || (reinterpret_cast<uintptr_t>(H) & 15)) return GQ_ERR_ALIGN;
   CUtensorMap tmap;
-  int rc = make_tmap_2d(&tmap, X, fmt, (uint64_t)D, (uint64_t)T, (uint64_t)D * 2, 64, 64);
+  int rc = make_tmap_2d(&tmap, X, fmt, (uint64_t)D, (uint64_t)T, (uint64_t)D * 2, 64, 64, 0);
   if (rc != GQ_OK) return rc;
   SyrkParams p;
   p.H = H; p.D = D; p.T = T; p.mode = mode; p.fmt = fmt;

@@ -15,7 +15,7 @@ from . import _cabi
 from ._cabi import GptqB200Error, check, lib, ptr, require_contig, require_cuda, stream_of
 
 __all__ = ['accumulate_hessian', 'gptq_quantize_range', 'hessian_syrk', 'hessian_invert', 'prep_weight_t',
-           'gptq_solve', 'pack_int4', 'unpack_int4', 'transpose_pack_int4', 'w4a16_gemm', 'sgemm',
+           'gptq_solve', 'pack_int4', 'unpack_int4', 'transpose_pack_int4', 'w4a16_gemm', 'sgemm', 'gemm_tf32x3', 'set_tf32x3',
            'GptqB200Error']
 
 
@@ -167,8 +167,10 @@ def w4a16_gemm(x: torch.Tensor, qweight: torch.Tensor, scale: torch.Tensor, qzer
     if perm is not None and perm.dtype != torch.int32:
         raise GptqB200Error('perm must be int32')
     y = torch.empty(M, N, dtype=x.dtype, device=dev)
+    work = torch.empty(lib.gq_w4a16_workspace_bytes(M, K), dtype=torch.uint8, device=dev)
     with torch.cuda.device(dev):
-        check(lib.gq_w4a16_gemm(ptr(x), ptr(qweight), ptr(scale), ptr(qzero), ptr(perm), ptr(y), M, N, K, int(group),
+        check(lib.gq_w4a16_gemm(ptr(x), ptr(qweight), ptr(scale), ptr(qzero), ptr(perm), ptr(y), ptr(work), M, N, K,
+                                int(group),
                                 _cabi.DTYPE_CODE[x.dtype], stream_of(x)), 'gq_w4a16_gemm')
     return y
 
@@ -179,3 +181,16 @@ def sgemm(A, B, C_, M, N, K, lda, ldb, ldc, alpha, beta, flags) -> None:
     with torch.cuda.device(dev):
         check(lib.gq_sgemm(ptr(A), ptr(B), ptr(C_), M, N, K, lda, ldb, ldc, float(alpha), float(beta), int(flags),
                            stream_of(C_)), 'gq_sgemm')
+
+
+def gemm_tf32x3(A, B, C_, M, N, K, lda, ldb, ldc, alpha, upper_only=False) -> None:
+    """C (M, N) += alpha * A^T B on the tensor cores with a 3 x TF32 split (A stored (K, M), B (K, N))."""
+    dev = require_cuda(A, B, C_)
+    with torch.cuda.device(dev):
+        check(lib.gq_gemm_tf32x3(ptr(A), ptr(B), ptr(C_), M, N, K, lda, ldb, ldc, float(alpha), int(upper_only),
+                                 stream_of(C_)), 'gq_gemm_tf32x3')
+
+
+def set_tf32x3(enable: bool) -> bool:
+    """A/B parity hook; returns the previous setting."""
+    return bool(lib.gq_set_tf32x3(int(enable)))

@@ -86,13 +86,25 @@ int gq_transpose_pack_int4(const uint8_t* codes_t, uint8_t* codes, uint32_t* pac
 /* ---- K6: y (M, N) = x[:, perm] (M, K) * dequant(qweight)^T, replacing reconstruct_nn_linear +
  * nn.Linear (quant.py:262-279, llama.py:172-177).  x, y, scale share `dtype` (f16/bf16);
  * qzero (N, K/group) uint8; perm (K) int32 or NULL.  K % group == 0, group % 32 == 0. */
+/* workspace: gq_w4a16_workspace_bytes(M, K) bytes of device scratch (the permuted activations). */
+size_t gq_w4a16_workspace_bytes(int M, int K);
 int gq_w4a16_gemm(const void* x, const uint32_t* qweight, const void* scale, const uint8_t* qzero,
-                  const int32_t* perm, void* y, int M, int N, int K, int group, int dtype, void* stream);
+                  const int32_t* perm, void* y, void* workspace, int M, int N, int K, int group, int dtype,
+                  void* stream);
 
 /* ---- building block exposed for tests: C = beta*C + alpha*op(A)*B in true fp32.
  * flags: 1 = A stored (K x M); 2 = only upper tiles of C; 4 = A upper-triangular; 8 = B upper-triangular */
 int gq_sgemm(const float* A, const float* B, float* C, int M, int N, int K, int lda, int ldb, int ldc, float alpha,
              float beta, int flags, void* stream);
+
+/* ---- fp32-faithful tensor-core GEMM used by K4 and the Cholesky update:  C += alpha * A^T B  with A stored
+ * (K x M), B (K x N), C (M x N), fp32, computed as 3 x tcgen05 kind::tf32 on hi/lo splits.  K % 16 == 0,
+ * lda/ldb/ldc % 4 == 0.  upper_only: skip tiles entirely below the diagonal. */
+int gq_gemm_tf32x3(const float* A, const float* B, float* C, int M, int N, int K, int lda, int ldb, int ldc, float alpha,
+                   int upper_only, void* stream);
+/* A/B parity hook: 0 routes K4 and the Cholesky trailing update through the fp32 SIMT GEMM instead of the
+ * 3xTF32 tensor-core GEMM.  Returns the previous setting. */
+int gq_set_tf32x3(int enable);
 
 #ifdef __cplusplus
 }

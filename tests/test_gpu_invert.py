@@ -92,3 +92,55 @@ def test_invert_golden(name):
     rel = O.rel_fro(U.cpu(), g['U'])
     assert rel < 1e-4, rel
     assert hook.invert_tries == 1
+
+
+@pytest.mark.parametrize('M,N,K,upper', [(128, 256, 16, False), (128, 256, 128, False), (256, 512, 128, False),
+                                         (3968, 4096, 128, False), (200, 300, 64, False), (1024, 1024, 128, True),
+                                         (640, 640, 64, True)])
+def test_gemm_tf32x3_is_fp32_faithful(M, N, K, upper):
+    """C += alpha A^T B on tcgen05 with the 3xTF32 split: error must be at fp32-reordering level,
+    far below a single TF32 pass (~5e-4)."""
+    import gptq
+    g = torch.Generator(device='cuda').manual_seed(M + N + K)
+    lda, ldb, ldc = M + 64, N + 32, N + 16                     # operands are windows of larger matrices
+    A = torch.randn(K, lda, device='cuda', generator=g)
+    B = torch.randn(K, ldb, device='cuda', generator=g)
+    C0 = torch.randn(M, ldc, device='cuda', generator=g)
+    C = C0.clone()
+    gptq.gemm_tf32x3(A, B, C, M, N, K, lda, ldb, ldc, -1.0, upper)
+    torch.cuda.synchronize()
+    want = C0[:, :N].double() - A[:, :M].double().t() @ B[:, :N].double()
+    got = C[:, :N].double()
+    assert torch.equal(C[:, N:], C0[:, N:])                  # nothing outside the window is touched
+    if upper:
+        tm, tn = 128, 256
+        mask = torch.zeros(M, N, dtype=torch.bool, device='cuda')
+        for m0 in range(0, M, tm):
+            for n0 in range(0, N, tn):
+                if not (m0 >= n0 + tn):
+                    mask[m0:m0 + tm, n0:n0 + tn] = True
+        assert torch.equal(C[:, :N][~mask], C0[:, :N][~mask])
+        err = ((got - want)[mask]).abs().max().item()
+    else:
+        err = (got - want).abs().max().item()
+    scale = (A[:, :M].abs().double().t() @ B[:, :N].abs().double()).max().item()
+    assert err <= 4e-6 * scale, (err, scale)
+
+
+def test_tf32x3_switch_gives_same_codes():
+    """K4 on tensor cores (3xTF32) vs fp32 SIMT: the quantisation codes must agree to >= 99.9%."""
+    import gptq
+    W, X = O.synth_linear(512, 1024, 8, 512, seed=77)
+    H, n = O.hessian_accumulate(None, 0, X)
+    inv = O.hessian_invert(H, n, 1e-2, True)
+    U = inv['U'].cuda().contiguous()
+    outs = []
+    for enable in (True, False):
+        prev = gptq.set_tf32x3(enable)
+        try:
+            Wt = gptq.prep_weight_t(W.cuda().contiguous(), inv['perm'].cuda())
+            _, codes_t, _, _, _ = gptq.gptq_solve(Wt, U, 128, 15.0)
+            outs.append(codes_t.cpu())
+        finally:
+            gptq.set_tf32x3(prev)
+    assert (outs[0] == outs[1]).float().mean().item() >= 0.999

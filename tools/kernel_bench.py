@@ -90,29 +90,45 @@ def bench_sgemm():
                           'tflops': 2.0 * M * N * K / t / 1e12}))
 
 
+def bench_tf32():
+    for M, N, K, up in ((3968, 4096, 128, 0), (10880, 4096, 128, 0), (3968, 11008, 128, 0), (10880, 10880, 128, 1),
+                        (128, 4096, 128, 0)):
+        A = torch.randn(K, M, device=dev)
+        B = torch.randn(K, N, device=dev)
+        Cm = torch.zeros(M, N, device=dev)
+        t = timeit(lambda: gptq.gemm_tf32x3(A, B, Cm, M, N, K, M, N, N, -1.0, bool(up)))
+        frac = 0.5 if up else 1.0
+        print(json.dumps({'k': 'gemm_tf32x3', 'M': M, 'N': N, 'K': K, 'upper': up, 'us': t * 1e6,
+                          'tflops': frac * 2.0 * M * N * K / t / 1e12, 'C_GBps_rw': frac * M * N * 8 / t / 1e9}))
+
+
 def bench_w4a16():
+    """Weights rotate through > 4x L2 of distinct buffers; the launches of one rotation are captured in
+    a CUDA graph so that the host (ctypes + allocator) is out of the timed region."""
     for N, K in ((4096, 4096), (11008, 4096), (4096, 11008), (8192, 8192), (28672, 8192), (8192, 28672)):
         G = K // 128
-        nbuf = max(2, int(600e6 // (N * K // 2)) + 1)          # rotate through > 4x L2 of weights
+        nbuf = max(4, int(600e6 // (N * K // 2)) + 1)
         qs = [torch.randint(-2 ** 31, 2 ** 31 - 1, (N, K // 8), device=dev, dtype=torch.int32) for _ in range(nbuf)]
         sc = (torch.rand(N, G, device=dev) * 0.01 + 1e-3).half()
         qz = torch.randint(0, 16, (N, G), device=dev, dtype=torch.uint8)
         perm = torch.randperm(K, device=dev).to(torch.int32)
         for M in (1, 2, 4, 8, 16):
             x = torch.randn(M, K, device=dev).half()
-            i = [0]
-
-            def run():
-                i[0] = (i[0] + 1) % nbuf
-                gptq.w4a16_gemm(x, qs[i[0]], sc, qz, perm, 128)
-            t = timeit(run, iters=11, warm=3)
+            gptq.w4a16_gemm(x, qs[0], sc, qz, perm, 128)
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                for q in qs:
+                    gptq.w4a16_gemm(x, q, sc, qz, perm, 128)
+            t = timeit(graph.replay, iters=7, warm=2) / nbuf
             byts = N * K / 2 + N * G * 3 + 2 * M * K + 2 * M * N
             print(json.dumps({'k': 'w4a16', 'M': M, 'N': N, 'K': K, 'us': t * 1e6, 'GBps': byts / t / 1e9,
-                              'tflops': 2.0 * M * N * K / t / 1e12}))
+                              'tflops': 2.0 * M * N * K / t / 1e12, 'frac_hbm_6455': byts / t / 6455.6e9}))
+            del graph
         del qs
 
 
 if __name__ == '__main__':
-    which = sys.argv[1:] or ['syrk', 'invert', 'solve', 'sgemm', 'w4a16']
+    which = sys.argv[1:] or ['syrk', 'invert', 'solve', 'sgemm', 'tf32', 'w4a16']
     for w in which:
         globals()['bench_' + w]()
