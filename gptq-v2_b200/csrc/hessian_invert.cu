@@ -45,9 +45,41 @@ constexpr int PITCH = NB + 1;
 // Factor the n x n (n <= 128) diagonal block at offset o in place:  A_kk = R^T R  (upper R).
 // One CTA, 256 threads = 16 x 16, register tiled: thread (ty, tx) owns the 8 x 8 elements
 // (ty + 16 i, tx + 16 k) of the block (2-D cyclic, so the shrinking trailing matrix stays
-// balanced).  Column step j: the owners of row j publish it to shared memory (double buffered),
-// ONE barrier, then every thread scales with 1/sqrt(pivot) and applies the rank-1 update to its
-// 64 registers.  This is the only serial piece of a Cholesky step, so it does nothing else.
+// balanced).  Column step j: every thread applies the rank-1 update of the (already scaled) row j
+// to its registers; the half-warp that owns row j+1 updates that row FIRST, takes the pivot with
+// one shuffle, and publishes the scaled row j+1 (double-buffered shared memory, one barrier per
+// step) while the other warps are still busy with their FMAs.  Row blocks that are finished are
+// skipped.  This is the only serial piece of a Cholesky step, so it does nothing else.
+__device__ __forceinline__ void chol_publish_row(float (&a)[8][8], int jn, int n, int tx, float* rb, float* gout,
+                                                 bool& bad) {
+  // caller guarantees: this thread's ty == (jn & 15); the 16 such threads form one half-warp
+  const int i1 = jn >> 4;
+  float v[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+    if (i == i1) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) v[k] = a[i][k];
+    }
+  float pv = 0.f;
+#pragma unroll
+  for (int k = 0; k < 8; ++k)
+    if (k == i1) pv = v[k];                                  // the diagonal element lives where tx == (jn & 15)
+  const unsigned half_mask = (jn & 1) ? 0xFFFF0000u : 0x0000FFFFu;    // lane = (ty & 1) * 16 + tx, ty = jn & 15
+  const int src_lane = ((jn & 15) & 1) * 16 + (jn & 15);
+  const float piv = __shfl_sync(half_mask, pv, src_lane);
+  if (jn < n && !(piv > 0.f)) bad = true;                    // also catches NaN
+  const float d = sqrtf(piv);
+  const float rinv = 1.0f / d;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int c = tx + 16 * k;
+    const float val = (c > jn) ? v[k] * rinv : (c == jn ? d : 0.f);
+    rb[c] = val;
+    if (jn < n && c >= jn && c < n) gout[c] = val;
+  }
+}
+
 __global__ void __launch_bounds__(256) chol_diag_kernel(float* __restrict__ A, int D, int o, int n,
                                                         int* __restrict__ info) {
   __shared__ float rowbuf[2][NB];
@@ -61,57 +93,49 @@ __global__ void __launch_bounds__(256) chol_diag_kernel(float* __restrict__ A, i
       // only the upper triangle is meaningful; pad a partial block with the identity
       a[i][k] = (r < n && c < n) ? ((c >= r) ? A[(size_t)(o + r) * D + o + c] : 0.f) : (r == c ? 1.f : 0.f);
     }
-  // publish row 0
-  if (ty == 0) {
-#pragma unroll
-    for (int k = 0; k < 8; ++k) rowbuf[0][tx + 16 * k] = a[0][k];
-  }
-  __syncthreads();
   bool bad = false;
+  // NB: the half-warp test below must use the same lane formula as chol_publish_row
+  if (ty == 0) chol_publish_row(a, 0, n, tx, rowbuf[0], A + (size_t)o * D + o, bad);
+  __syncthreads();
 #pragma unroll 1
-  for (int j = 0; j < NB; ++j) {
+  for (int j = 0; j < NB - 1; ++j) {
     const float* rb = rowbuf[j & 1];
-    const float piv = rb[j];
-    if (j < n && !(piv > 0.f)) bad = true;          // also catches NaN
-    const float d = sqrtf(piv);
-    const float rinv = 1.0f / d;
     float sc[8], sr[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
       const int c = tx + 16 * k;
-      sc[k] = (c > j) ? rb[c] * rinv : 0.f;
+      sc[k] = (c > j) ? rb[c] : 0.f;
     }
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       const int r = ty + 16 * i;
-      sr[i] = (r > j) ? rb[r] * rinv : 0.f;
+      sr[i] = (r > j) ? rb[r] : 0.f;
     }
-    // final values of row j of R go straight to global memory
-    if (ty == (j & 15) && j < n) {
-      float* out = A + (size_t)(o + j) * D + o;
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        const int c = tx + 16 * k;
-        if (c < n) { if (c > j) out[c] = sc[k]; else if (c == j) out[c] = d; }
-      }
-    }
-#pragma unroll
-    for (int i = 0; i < 8; ++i)
-#pragma unroll
-      for (int k = 0; k < 8; ++k) a[i][k] = fmaf(-sr[i], sc[k], a[i][k]);
-    // row j+1 is final now: publish it into the other buffer
-    if (j + 1 < NB && ty == ((j + 1) & 15)) {
-      const int i1 = (j + 1) >> 4;
+    const int jn = j + 1;
+    const int i1 = jn >> 4;
+    const bool pub = (ty == (jn & 15));
+    if (pub) {
+      // row j+1 first, so that its pivot chain overlaps the other warps' FMAs
 #pragma unroll
       for (int i = 0; i < 8; ++i)
         if (i == i1) {
 #pragma unroll
-          for (int k = 0; k < 8; ++k) rowbuf[(j + 1) & 1][tx + 16 * k] = a[i][k];
+          for (int k = 0; k < 8; ++k) a[i][k] = fmaf(-sr[i], sc[k], a[i][k]);
         }
+      chol_publish_row(a, jn, n, tx, rowbuf[jn & 1], A + (size_t)(o + jn) * D + o, bad);
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      if (16 * i + 15 > j) {                                   // uniform: block of rows not finished yet
+        if (!(pub && i == i1)) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) a[i][k] = fmaf(-sr[i], sc[k], a[i][k]);
+        }
+      }
     }
     __syncthreads();
   }
-  if (bad && tid == 0) atomicExch(info, 1);
+  if (bad) atomicExch(info, 1);
 }
 
 // Panel solve  P = R_kk^-T A[k, k+1:]  in place by forward substitution, 32 panel columns per CTA
