@@ -188,6 +188,7 @@ def run_step(ctx, W, X, Wh=None, Xh=None, timers=None):
     the host, as with the reference's save_device default."""
     from gptq_py import HessianHook, gptq_quant
     from gptq import pack_int4
+    import sharded
     host = Xh is not None
     n_local = N_SEQ // ctx.world
     call = min(CALL_SEQ, n_local)
@@ -229,14 +230,13 @@ def run_step(ctx, W, X, Wh=None, Xh=None, timers=None):
             e1.record(stream)
             timers['syrk'].append((e0, e1, D))
         if ctx.dist is not None:
-            ctx.dist.all_reduce(hook.hessian)
-            hook.n_samples = N_SEQ
+            sharded.allreduce_hessian(hook, N_SEQ)             # NCCL all-reduce of the partial Hessians
         hook.invert(damp_ratio=1e-2, act_order=True)
         for name, R, C, g in LINEARS:
             if g != gi:
                 continue
-            rows = R // ctx.world
-            r0 = ctx.rank * rows
+            r0, r1 = sharded.shard_range(R, ctx.world, ctx.rank, 4)
+            rows = r1 - r0
             if host:
                 w = Wh[name][r0:r0 + rows].to(ctx.dev, non_blocking=True)
                 h2d += w.numel() * 2

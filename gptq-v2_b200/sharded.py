@@ -1,0 +1,148 @@
+"""Multi-GPU sharding of the GPTQ hot path on one NVSwitch box (absent in the reference,
+which is single-process single-GPU: main.py:25, parse_args.py:53-55).
+
+One process per GPU (`torch.distributed`, backend nccl on the box, gloo in the CPU tests).  The path shards in the
+two ways the algebra allows:
+
+  1. H = sum over calibration sequences of X^T X  ->  rank p accumulates sequences [p*n/P, (p+1)*n/P) with K1,
+     then ONE all_reduce(sum, fp32) of H per Hessian group.  `n_samples` becomes the global sequence count, so the
+     2/n scale of invert() (gptq_py.py:41) is unchanged.
+  2. Given U = chol(H^-1), the rows of W are independent (gptq_py.py:187-193, quant.py:114-118 are per row) ->
+     rank p solves rows [p*R/P, (p+1)*R/P) of every linear of the group; codes / scales / zeros are all-gathered.
+     Alternatively the linears of one Hessian group go to different ranks ("modules" mode, the north_star wording).
+
+The factorisation (K2) is replicated on every rank: no broadcast of U (67-765 MB), lowest wall time.
+The compute objects (`HessianHook`, `gptq_quant`) are parameters so that the CPU tests can drive the same host
+logic with the oracle as the compute backend; the defaults are this build's CUDA implementations.
+"""
+from __future__ import annotations
+
+from typing import Callable, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+
+def world_info(group=None) -> tuple[int, int]:
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(group), dist.get_world_size(group)
+    return 0, 1
+
+
+def shard_range(n: int, world: int, rank: int, multiple: int = 1) -> tuple[int, int]:
+    """Contiguous shard [lo, hi) of n items for `rank`; shard boundaries are multiples of `multiple`
+    (the solver needs row counts that are multiples of 4, gptq_cpp_kernel.cu:130-131).  Ragged n is allowed:
+    the first ranks get one more unit, trailing ranks may be empty."""
+    if n % multiple != 0:
+        raise ValueError(f'{n} is not a multiple of {multiple}')
+    units = n // multiple
+    base, extra = divmod(units, world)
+    lo = rank * base + min(rank, extra)
+    hi = lo + base + (1 if rank < extra else 0)
+    return lo * multiple, hi * multiple
+
+
+def allreduce_hessian(hook, n_samples_global: Optional[int] = None, group=None) -> None:
+    """Sum the partial Hessians of all ranks in place and make n_samples global.
+    When n_samples_global is None it is all-reduced too (ragged shards)."""
+    rank, world = world_info(group)
+    if world == 1:
+        if n_samples_global is not None:
+            hook.n_samples = n_samples_global
+        return
+    dist.all_reduce(hook.hessian, op=dist.ReduceOp.SUM, group=group)
+    if n_samples_global is None:
+        t = torch.tensor([hook.n_samples], dtype=torch.int64, device=hook.hessian.device)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+        n_samples_global = int(t.item())
+    hook.n_samples = n_samples_global
+
+
+def _all_gather_rows(local: torch.Tensor, rows_total: int, world: int, multiple: int, group=None) -> torch.Tensor:
+    """Concatenate row shards produced with shard_range(rows_total, world, r, multiple)."""
+    sizes = [shard_range(rows_total, world, r, multiple) for r in range(world)]
+    if all(hi - lo == sizes[0][1] - sizes[0][0] for lo, hi in sizes):
+        out = torch.empty((rows_total,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+        dist.all_gather_into_tensor(out, local.contiguous(), group=group)
+        return out
+    # ragged: pad every shard to the largest one (uneven all_gather is not portable across backends)
+    mx = max(hi - lo for lo, hi in sizes)
+    padded = torch.zeros((mx,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+    padded[:local.shape[0]] = local
+    out = torch.empty((world * mx,) + tuple(local.shape[1:]), dtype=local.dtype, device=local.device)
+    dist.all_gather_into_tensor(out, padded, group=group)
+    return torch.cat([out[r * mx:r * mx + (hi - lo)] for r, (lo, hi) in enumerate(sizes)], dim=0)
+
+
+def gptq_quant_row_sharded(weight: torch.Tensor, hessian_hook, quant_fn: Optional[Callable] = None, group=None,
+                           gather: bool = True, **quant_kwargs) -> dict:
+    """gptq_quant of one linear with its rows sharded over the ranks.
+
+    weight: the FULL (R, C) weight on every rank (weights are replicated; only the work is sharded).
+    Returns the same {'quant_meta', 'metrics'} dict as gptq_quant; with gather=True quant_meta holds all R rows on
+    every rank, metrics are the global means.  `quant_fn` defaults to this build's CUDA gptq_quant."""
+    if quant_fn is None:
+        from gptq_py import gptq_quant as quant_fn
+    rank, world = world_info(group)
+    R = weight.shape[0]
+    if world == 1:
+        return quant_fn(weight=weight, hessian_hook=hessian_hook, **quant_kwargs)
+    lo, hi = shard_range(R, world, rank, 4)
+    dev = weight.device
+    kw = dict(quant_kwargs)
+    kw['save_device'] = dev                                   # gather on the compute device, move afterwards
+    save_device = quant_kwargs.get('save_device', torch.device('cpu'))
+    if hi > lo:
+        res = quant_fn(weight=weight[lo:hi], hessian_hook=hessian_hook, **kw)
+        meta, met = res['quant_meta'], res['metrics']
+    else:
+        meta, met = None, None
+    # metrics are means over the shard's elements (gptq_py.py:196-199, 232-237): combine weighted by row count
+    keys = ('gptq_error', 'gptq_norm', 'l2.0_error', 'l2.0_norm')
+    m = torch.tensor([(met[k] if met is not None else 0.0) * (hi - lo) for k in keys], dtype=torch.float64, device=dev)
+    dist.all_reduce(m, group=group)
+    metrics = {k: float(v) / R for k, v in zip(keys, m.tolist())}
+    if not gather:
+        return {'quant_meta': meta, 'metrics': metrics, 'rows': (lo, hi)}
+    C = weight.shape[1]
+    # every rank derives the same G / dtypes even when its own shard is empty
+    gs = quant_kwargs['group_sizes']
+    G = len(gs)
+    if meta is None:
+        meta = {'qweight': torch.empty(0, C, dtype=torch.uint8, device=dev),
+                'scale': torch.empty(0, G, dtype=weight.dtype, device=dev),
+                'qzero': torch.empty(0, G, dtype=torch.uint8, device=dev)}
+    full = {}
+    for k in ('qweight', 'scale', 'qzero'):
+        full[k] = _all_gather_rows(meta[k].to(dev), R, world, 4, group).to(save_device)
+    perm = getattr(hessian_hook, 'perm', None)
+    if perm is not None:
+        perm_inv = perm.to(torch.int16).argsort().to(torch.int16)
+    else:
+        perm_inv = torch.arange(C, dtype=torch.int16, device=dev)
+    full.update({'qscale': None, 'sscale': None, 'perm_inv': perm_inv.to(save_device),
+                 'group_sizes': gs.to(dtype=torch.int16, device=save_device),
+                 'group_bit_widths': quant_kwargs['group_bit_widths'].to(dtype=torch.uint8, device=save_device),
+                 'scale_bit_width': None})
+    return {'quant_meta': full, 'metrics': metrics}
+
+
+def assign_modules(names: Sequence[str], world: int) -> dict[str, int]:
+    """"modules" mode: the linears of one Hessian group go round-robin to ranks (q,k,v -> 3 ranks; up,gate -> 2)."""
+    return {n: i % world for i, n in enumerate(names)}
+
+
+def broadcast_quant_meta(meta: Optional[dict], src: int, R: int, C: int, G: int, scale_dtype: torch.dtype,
+                         device: torch.device, group=None) -> dict:
+    """"modules" mode: the owner of a linear broadcasts its quant_meta tensors to every rank."""
+    out = {}
+    rank, world = world_info(group)
+    spec = (('qweight', (R, C), torch.uint8), ('scale', (R, G), scale_dtype), ('qzero', (R, G), torch.uint8),
+            ('perm_inv', (C,), torch.int16), ('group_sizes', (G,), torch.int16), ('group_bit_widths', (G,), torch.uint8))
+    for k, shape, dt in spec:
+        t = meta[k].to(device).contiguous() if rank == src else torch.empty(shape, dtype=dt, device=device)
+        if world > 1:
+            dist.broadcast(t, src=src, group=group)
+        out[k] = t
+    out.update({'qscale': None, 'sscale': None, 'scale_bit_width': None})
+    return out

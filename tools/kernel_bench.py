@@ -128,7 +128,51 @@ def bench_w4a16():
         del qs
 
 
+def bench_refext():
+    """The reference's own CUDA extension (oracle/_ref/gptq_c.so, built from /root/reference/package/gptq) on this
+    B200, beside ours: a2 CUTLASS Hessian GEMM and a6 gptq_quantize_range over a whole 4096x4096 linear."""
+    sys.path.insert(0, os.path.join(ROOT, 'tests'))
+    import ref_ext
+    ref = ref_ext.load()
+    if ref is None:
+        print(json.dumps({'k': 'refext', 'unavailable': 'oracle/_ref/gptq_c.so not built'}))
+        return
+    torch.backends.cuda.matmul.allow_tf32 = False
+    for D in (4096, 11008):
+        T = 32768
+        X = torch.randn(T, D, device=dev).half()
+        H = torch.zeros(D, D, device=dev)
+        t_ref = timeit(lambda: ref.accumulate_hessian_fp16_fp32(H, X))
+        t_our2 = timeit(lambda: gptq.accumulate_hessian(H, X))
+        t_our0 = timeit(lambda: gptq.hessian_syrk(H, X, mode=0))
+        print(json.dumps({'k': 'refext_hessian', 'D': D, 'T': T, 'ref_cutlass_ms': t_ref * 1e3,
+                          'ref_gemm_tflops': 2.0 * T * D * D / t_ref / 1e12, 'ours_mode2_ms': t_our2 * 1e3,
+                          'ours_mode0_ms': t_our0 * 1e3, 'speedup_mode0': t_ref / t_our0}))
+        del X, H
+    R = C = 4096
+    Xc = torch.randn(2 * C, C, device=dev) * torch.exp(torch.rand(C, device=dev) * 3 - 1.5)
+    Hc = Xc.t() @ Xc
+    _, U, _ = gptq.hessian_invert(Hc, None, 1.0, 0.01 * float(Hc.diagonal().mean()), want_hp=False)
+    W = (torch.randn(R, C, device=dev) * 0.02)
+    Wt0 = W.t().contiguous()
+    w3 = Wt0.view(C // 128, 128, R)
+    xmax, xmin = w3.amax(dim=1).relu(), -(-w3.amin(dim=1)).relu()
+    scale = (xmax - xmin) / 15.0 + 1e-12
+    qzero = (-xmin / scale).round()
+    quant_t, err_t = torch.empty_like(Wt0), torch.empty_like(Wt0)
+    q_t = torch.empty_like(Wt0, dtype=torch.int16)
+
+    def run(fn):
+        wt = Wt0.clone()
+        for g in range(C // 128):
+            fn(quant_t, scale[g], q_t, qzero[g], 15.0, U, wt, err_t, g * 128, (g + 1) * 128)
+    t_ref = timeit(lambda: run(ref.gptq_quantize_range), iters=3, warm=1)
+    t_our = timeit(lambda: run(gptq.gptq_quantize_range), iters=3, warm=1)
+    print(json.dumps({'k': 'refext_quantize_range', 'R': R, 'C': C, 'ref_ms': t_ref * 1e3, 'ours_ms': t_our * 1e3,
+                      'speedup': t_ref / t_our}))
+
+
 if __name__ == '__main__':
-    which = sys.argv[1:] or ['syrk', 'invert', 'solve', 'sgemm', 'tf32', 'w4a16']
+    which = sys.argv[1:] or ['syrk', 'invert', 'solve', 'sgemm', 'tf32', 'w4a16', 'refext']
     for w in which:
         globals()['bench_' + w]()
