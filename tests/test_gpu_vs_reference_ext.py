@@ -80,7 +80,8 @@ def test_quantize_range_vs_reference_kernels(ref, R, C, bits):
     match = (q_o == q_r).float().mean().item()
     assert match >= 0.999, match
     same = (q_o == q_r)
-    assert torch.allclose(err_o[same], err_r[same], rtol=2e-3, atol=1e-6)
+    # err = (w - q_hat) / U[c, c] can sit near zero, so the bound is relative to the error scale of the matrix
+    assert (err_o[same] - err_r[same]).abs().max() <= 1e-3 * err_r.abs().max()
     # the weights left behind (updated in place) agree to fp32 reordering noise where no code flipped upstream
     rows_ok = same.all(dim=0)
-    assert torch.allclose(w_o[:, rows_ok], w_r[:, rows_ok], rtol=1e-3, atol=1e-6)
+    assert (w_o[:, rows_ok] - w_r[:, rows_ok]).abs().max() <= 1e-4 * w_r.abs().max()
