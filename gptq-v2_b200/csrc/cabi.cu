@@ -46,7 +46,7 @@ int accumulate_hessian_bf16_fp32_cuda(void* H, const void* X, const int size_hid
 
 size_t gq_invert_workspace_floats(int D) {
   const size_t d = (size_t)D;
-  return d * d + d * d / 2 + 64;
+  return 2 * d * d + d * d / 2 + 32 * d + 64;     // A (reversed matrix / factor / V), W = V^T, T^T blocks
 }
 
 int gq_hessian_invert(const float* H, int D, const int64_t* perm, float scale, float damp, float* Hp, float* U,
@@ -54,10 +54,11 @@ int gq_hessian_invert(const float* H, int D, const int64_t* perm, float scale, f
   if (D <= 0) return GQ_ERR_ARG;
   if (D % 4 != 0) return GQ_ERR_SHAPE;
   float* A = work;
-  float* tmp = work + (size_t)D * D;
+  float* Wb = work + (size_t)D * D;
+  float* tmp = work + 2 * (size_t)D * D;
   int rc = hessian_gather(H, D, perm, scale, damp, Hp, A, S(stream));
   if (rc != GQ_OK) return rc;
-  return chol_inverse_upper(A, D, U, tmp, info_dev, S(stream));
+  return chol_inverse_upper(A, D, U, Wb, tmp, info_dev, S(stream));
 }
 
 int gq_quantize_range(float* quant, const float* scale, int16_t* out_q, const float* qzero, float maxq,

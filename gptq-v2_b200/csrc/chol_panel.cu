@@ -1,0 +1,198 @@
+// K2, critical path of one blocked-Cholesky step:  factor the 128 x 128 diagonal block AND solve the
+// panel to its right in ONE launch.
+//
+//   A_kk = R_kk^T R_kk (upper R_kk),   P = R_kk^-T A[k, k+1:]
+//
+// Every CTA redundantly factors the (identical) diagonal block in shared memory and extends the
+// same elimination to its own PC panel columns, i.e. it eliminates the 128 x (128 + PC) block row
+// [A_kk | A_k,cols].  The diagonal factorisation is a latency-bound dependent chain that occupies
+// one SM for ~8 us whether or not the other SMs repeat it, so repeating it removes a launch, a
+// grid-wide dependency and the global round trip of R_kk from every step of the factorisation
+// (previously: chol_diag_kernel 74 us + trsm_panel_kernel 25 us per step).
+//
+// In-CTA algorithm, 16-column sub-blocks (8 per block), 256 threads:
+//   A  warp 0 factors the 16 x 16 diagonal sub-block on registers: lane k owns column k, every lane
+//      tracks a private copy of the diagonal, so a step costs one shuffle + rsqrt (Newton-refined):
+//      ~70 cycles per column instead of a block-wide barrier per column.
+//   B  one thread per remaining column: 16-row forward substitution on registers.
+//   C  all warps: rank-16 update of the remaining rows (4-row groups per warp, lanes along columns).
+// fp32 FMA throughout (the reference runs LAPACK potrf in fp32; TF32 is off, main.py:12-13).
+#include "gptq_b200_internal.h"
+
+namespace gq {
+namespace {
+
+constexpr int NB = 128;
+constexpr int SBK = 16;
+
+// 1/sqrt(p) to ~1 ulp: MUFU.RSQ + one Newton step (off the IEEE sqrt/div subroutines: this sits on
+// the serial chain of the factorisation).
+__device__ __forceinline__ float rsqrt_nr(float p) {
+  const float y0 = rsqrtf(p);
+  const float e = fmaf(-p * y0, y0, 1.0f);
+  return fmaf(0.5f * y0, e, y0);
+}
+
+template <int PC>
+__global__ void __launch_bounds__(256, (PC <= 64) ? 2 : 1)
+chol_panel_kernel(float* __restrict__ A, int D, int o, int n, int rest, int* __restrict__ info) {
+  constexpr int W = NB + PC;                 // row pitch of the shared block row
+  extern __shared__ __align__(16) float sm[];
+  float* S = sm;                             // [NB][W]
+  float* rinv = sm + NB * W;                 // [NB] reciprocals of the diagonal of R_kk
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int pc0 = blockIdx.x * PC;           // first panel column of this CTA (relative to o + n)
+  const int pcn = max(0, min(PC, rest - pc0));
+
+  // ---- stage [A_kk (upper) | panel columns]; a partial block is padded with the identity
+  for (int idx = tid; idx < NB * (NB / 4); idx += 256) {
+    const int r = idx / (NB / 4), c4 = (idx - r * (NB / 4)) * 4;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (r < n && c4 < n) v = *reinterpret_cast<const float4*>(A + (size_t)(o + r) * D + o + c4);   // n % 4 == 0
+    if (r >= n) { v.x = (c4 == r) ? 1.f : 0.f; v.y = (c4 + 1 == r) ? 1.f : 0.f; v.z = (c4 + 2 == r) ? 1.f : 0.f; v.w = (c4 + 3 == r) ? 1.f : 0.f; }
+    *reinterpret_cast<float4*>(S + r * W + c4) = v;
+  }
+  if constexpr (PC > 0) {
+    for (int idx = tid; idx < NB * (PC / 4); idx += 256) {
+      const int r = idx / (PC / 4), c4 = (idx - r * (PC / 4)) * 4;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (r < n && c4 < pcn) v = *reinterpret_cast<const float4*>(A + (size_t)(o + r) * D + o + n + pc0 + c4);   // rest % 4 == 0
+      *reinterpret_cast<float4*>(S + r * W + NB + c4) = v;
+    }
+  }
+  __syncthreads();
+
+  bool bad = false;
+#pragma unroll 1
+  for (int s = 0; s < NB / SBK; ++s) {
+    const int so = s * SBK;
+    // ---- A: 16 x 16 diagonal sub-block on warp 0
+    if (warp == 0) {
+      const int k = lane & 15;
+      float a[SBK], dg[SBK];
+#pragma unroll
+      for (int i = 0; i < SBK; ++i) {
+        a[i] = S[(so + i) * W + so + k];
+        dg[i] = S[(so + i) * W + so + i];
+      }
+#pragma unroll
+      for (int j = 0; j < SBK; ++j) {
+        const float p = dg[j];
+        if (!(p > 0.f)) bad = true;                          // also catches NaN
+        const float ri = rsqrt_nr(p);
+        float d = p * ri;
+        d = fmaf(fmaf(-d, d, p), 0.5f * ri, d);              // sqrt(p) refined
+        const float r = (k > j) ? a[j] * ri : (k == j ? d : 0.f);
+        if (lane < 16) {
+          S[(so + j) * W + so + k] = r;
+          if (k == j) rinv[so + j] = ri;
+        }
+#pragma unroll
+        for (int i = j + 1; i < SBK; ++i) {
+          const float rji = __shfl_sync(0xffffffffu, r, i);  // R[j][i]
+          a[i] = fmaf(-rji, r, a[i]);
+          dg[i] = fmaf(-rji, rji, dg[i]);
+        }
+      }
+    }
+    __syncthreads();
+    // ---- B: rows so..so+15 of every later column: forward substitution, one thread per column
+    {
+      const int c = so + SBK + tid;
+      if (c < W) {
+        float x[SBK];
+#pragma unroll
+        for (int j = 0; j < SBK; ++j) x[j] = S[(so + j) * W + c];
+#pragma unroll
+        for (int j = 0; j < SBK; ++j) {
+          x[j] *= rinv[so + j];
+#pragma unroll
+          for (int i = j + 1; i < SBK; ++i) x[i] = fmaf(-S[(so + j) * W + so + i], x[j], x[i]);
+        }
+#pragma unroll
+        for (int j = 0; j < SBK; ++j) S[(so + j) * W + c] = x[j];
+      }
+    }
+    __syncthreads();
+    // ---- C: rank-16 update of rows so+16.. : S[i][c] -= sum_j X[j][i] X[j][c]   (c >= i needed)
+    {
+      const int r0 = so + SBK;
+      const int groups = (NB - r0) / 4;
+#pragma unroll 1
+      for (int g = warp; g < groups; g += 8) {
+        const int i0 = r0 + 4 * g;
+        float4 xi[SBK];
+#pragma unroll
+        for (int j = 0; j < SBK; ++j) xi[j] = *reinterpret_cast<const float4*>(S + (so + j) * W + i0);
+#pragma unroll 1
+        for (int c = (i0 & ~31) + lane; c < W; c += 32) {
+          float a0 = S[(i0 + 0) * W + c], a1 = S[(i0 + 1) * W + c];
+          float a2 = S[(i0 + 2) * W + c], a3 = S[(i0 + 3) * W + c];
+#pragma unroll
+          for (int j = 0; j < SBK; ++j) {
+            const float xc = S[(so + j) * W + c];
+            a0 = fmaf(-xi[j].x, xc, a0); a1 = fmaf(-xi[j].y, xc, a1);
+            a2 = fmaf(-xi[j].z, xc, a2); a3 = fmaf(-xi[j].w, xc, a3);
+          }
+          S[(i0 + 0) * W + c] = a0; S[(i0 + 1) * W + c] = a1;
+          S[(i0 + 2) * W + c] = a2; S[(i0 + 3) * W + c] = a3;
+        }
+      }
+    }
+    __syncthreads();
+  }
+
+  // ---- write back: the factor (CTA 0 only) and this CTA's panel columns
+  if (blockIdx.x == 0) {
+    for (int idx = tid; idx < n * (n / 4); idx += 256) {
+      const int r = idx / (n / 4), c4 = (idx - r * (n / 4)) * 4;
+      if (c4 + 3 >= r) {                       // only groups that touch the upper triangle; entries below it untouched
+        float4 v = *reinterpret_cast<const float4*>(S + r * W + c4);
+        float* dst = A + (size_t)(o + r) * D + o + c4;
+        if (c4 >= r) *reinterpret_cast<float4*>(dst) = v;
+        else {
+          if (c4 + 0 >= r) dst[0] = v.x;
+          if (c4 + 1 >= r) dst[1] = v.y;
+          if (c4 + 2 >= r) dst[2] = v.z;
+          if (c4 + 3 >= r) dst[3] = v.w;
+        }
+      }
+    }
+    if (bad) atomicExch(info, 1);
+  }
+  if constexpr (PC > 0) {
+    for (int idx = tid; idx < n * (PC / 4); idx += 256) {
+      const int r = idx / (PC / 4), c4 = (idx - r * (PC / 4)) * 4;
+      if (c4 < pcn)
+        *reinterpret_cast<float4*>(A + (size_t)(o + r) * D + o + n + pc0 + c4) =
+            *reinterpret_cast<const float4*>(S + r * W + NB + c4);
+    }
+  }
+}
+
+template <int PC>
+int launch_cp(float* A, int D, int o, int n, int rest, int* info, cudaStream_t st) {
+  const int smem = (NB * (NB + PC) + NB) * (int)sizeof(float);
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(chol_panel_kernel<PC>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess)
+      return GQ_ERR_CUDA;
+    attr_set = true;
+  }
+  const int grid = PC > 0 ? (rest + PC - 1) / PC : 1;
+  GQ_LAUNCHED();
+  chol_panel_kernel<PC><<<grid, 256, smem, st>>>(A, D, o, n, rest, info);
+  return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
+}
+
+}  // namespace
+
+// One step of the blocked upper Cholesky of A (D x D, upper triangle meaningful): factor the n x n block at
+// (o, o) in place and overwrite A[o:o+n, o+n:] with the solved panel.  rest = D - o - n.
+int chol_factor_panel(float* A, int D, int o, int n, int rest, int* info_dev, cudaStream_t st) {
+  if ((n & 3) || (rest & 3) || (D & 3)) return GQ_ERR_SHAPE;
+  if (rest <= 0) return launch_cp<0>(A, D, o, n, 0, info_dev, st);
+  return launch_cp<64>(A, D, o, n, rest, info_dev, st);
+}
+
+}  // namespace gq

@@ -34,16 +34,37 @@ constexpr int EPI_BUF = 32 * 128;                   // one 32 x 32 fp32 staging 
 constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 4 * 2 * EPI_BUF + 1024 + 256;
 
 struct GemmTf32Params {
-  int M, N, K;
-  int a_col0, a_row0;      // A^T operand: element (k, m) is at tensor-map coordinate (a_col0 + m, a_row0 + k)
-  int b_col0, b_row0;
-  int c_col0, c_row0;      // C element (m, n) at (c_col0 + n, c_row0 + m)
+  int count;               // problems in this launch (identical tile grid, individually clipped)
+  int tiles_m, tiles_n;    // tile grid of the largest problem
   float alpha;
-  int upper_only;          // skip tiles entirely below the diagonal (M == N)
+  int flags;               // TF32_* (gptq_b200_internal.h)
+  Tf32Problem p[TF32_MAX_BATCH];
 };
+
+struct TileInfo { int m0, n0, kb0, kb1, prob; bool skip; };
+
+__device__ __forceinline__ TileInfo decode_tile(const GemmTf32Params& P, int t) {
+  TileInfo ti;
+  const int per = P.tiles_m * P.tiles_n;
+  ti.prob = t / per;
+  const int r = t - ti.prob * per;
+  ti.m0 = (r / P.tiles_n) * TM;
+  ti.n0 = (r % P.tiles_n) * TN;
+  const Tf32Problem& q = P.p[ti.prob];
+  ti.skip = ti.m0 >= q.M || ti.n0 >= q.N || ((P.flags & TF32_UPPER_ONLY) && ti.m0 >= ti.n0 + TN);
+  // triangular operands shorten the k range (16-deep blocks; the rest of the triangle inside a block is stored as zeros)
+  ti.kb0 = (P.flags & TF32_B_LOWER) ? ti.n0 / BK : 0;                                  // B[k][n] = 0 for k < n
+  const int kend = (P.flags & TF32_A_UPPER) ? min(q.K, ti.m0 + TM) : q.K;              // A[k][m] = 0 for k > m
+  ti.kb1 = kend / BK;
+  return ti;
+}
 
 __device__ __forceinline__ void tma_reduce_add_2d(const void* tmap, uint32_t src, int c0, int c1) {
   asm volatile("cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];"
+               :: "l"(reinterpret_cast<uint64_t>(tmap)), "r"(src), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_store_2d(const void* tmap, uint32_t src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.tile.bulk_group [%0, {%2, %3}], [%1];"
                :: "l"(reinterpret_cast<uint64_t>(tmap)), "r"(src), "r"(c0), "r"(c1) : "memory");
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
@@ -73,9 +94,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
       reinterpret_cast<volatile uint32_t*>(smem_gen + (tmem_slot - smem_base));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int tiles_m = (p.M + TM - 1) / TM, tiles_n = (p.N + TN - 1) / TN;
-  const int n_tiles = tiles_m * tiles_n;
-  const int num_kb = p.K / BK;
+  const int n_tiles = p.count * p.tiles_m * p.tiles_n;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&map_a); tma_prefetch_desc(&map_b); tma_prefetch_desc(&map_c);
@@ -89,28 +108,24 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
 
-  auto tile_skipped = [&](int t) {
-    if (!p.upper_only) return false;
-    const int m0 = (t / tiles_n) * TM, n0 = (t % tiles_n) * TN;
-    return m0 >= n0 + TN;
-  };
-
   if (warp == 0) {
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
       for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-        if (tile_skipped(t)) continue;
-        const int m0 = (t / tiles_n) * TM, n0 = (t % tiles_n) * TN;
-        for (int kb = 0; kb < num_kb; ++kb) {
+        const TileInfo ti = decode_tile(p, t);
+        if (ti.skip) continue;
+        const Tf32Problem& q = p.p[ti.prob];
+        const int m0 = ti.m0, n0 = ti.n0;
+        for (int kb = ti.kb0; kb < ti.kb1; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t sa = smem_base + stage * STAGE_BYTES;
           mbar_expect_tx(full_bar(stage), HI_BYTES);
 #pragma unroll
           for (int i = 0; i < A_SUBS; ++i)
-            tma_load_2d(sa + i * SUB, &map_a, full_bar(stage), p.a_col0 + m0 + 32 * i, p.a_row0 + kb * BK);
+            tma_load_2d(sa + i * SUB, &map_a, full_bar(stage), q.a_col0 + m0 + 32 * i, q.a_row0 + kb * BK);
 #pragma unroll
           for (int j = 0; j < B_SUBS; ++j)
-            tma_load_2d(sa + (A_SUBS + j) * SUB, &map_b, full_bar(stage), p.b_col0 + n0 + 32 * j, p.b_row0 + kb * BK);
+            tma_load_2d(sa + (A_SUBS + j) * SUB, &map_b, full_bar(stage), q.b_col0 + n0 + 32 * j, q.b_row0 + kb * BK);
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
       }
@@ -121,14 +136,15 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
       int stage = 0; uint32_t phase = 0;
       int it = 0;
       for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-        if (tile_skipped(t)) continue;
+        const TileInfo ti = decode_tile(p, t);
+        if (ti.skip) continue;
         const int acc = it & 1;
         const uint32_t acc_phase = (it >> 1) & 1u;
         ++it;
         mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * TN;
-        for (int kb = 0; kb < num_kb; ++kb) {
+        for (int kb = ti.kb0; kb < ti.kb1; ++kb) {
           mbar_wait(ready_bar(stage), phase);
           tc_fence_after();
           const uint32_t a_hi = smem_base + stage * STAGE_BYTES;
@@ -143,7 +159,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
             const uint64_t bh = umma_smem_desc(b_hi + k8 * 1024, SUB, 512, 1u);
             const uint64_t al = umma_smem_desc(a_lo + k8 * 1024, SUB, 512, 1u);
             const uint64_t bl = umma_smem_desc(b_lo + k8 * 1024, SUB, 512, 1u);
-            mma_tf32<1>(d_tmem, al, bh, idesc, (kb | k8) ? 1u : 0u);     // small terms first
+            mma_tf32<1>(d_tmem, al, bh, idesc, ((kb - ti.kb0) | k8) ? 1u : 0u);     // small terms first
             mma_tf32<1>(d_tmem, ah, bl, idesc, 1u);
             mma_tf32<1>(d_tmem, ah, bh, idesc, 1u);
           }
@@ -158,8 +174,9 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
     const int tid = threadIdx.x - 256;                 // 0..127
     int stage = 0; uint32_t phase = 0;
     for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-      if (tile_skipped(t)) continue;
-      for (int kb = 0; kb < num_kb; ++kb) {
+      const TileInfo ti = decode_tile(p, t);
+      if (ti.skip) continue;
+      for (int kb = ti.kb0; kb < ti.kb1; ++kb) {
         mbar_wait(full_bar(stage), phase);
         float4* hi = reinterpret_cast<float4*>(smem_gen + stage * STAGE_BYTES);
         float4* lo = reinterpret_cast<float4*>(smem_gen + stage * STAGE_BYTES + HI_BYTES);
@@ -185,15 +202,17 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
     int it = 0;
     int buf = 0;
     for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-      if (tile_skipped(t)) continue;
-      const int m0 = (t / tiles_n) * TM, n0 = (t % tiles_n) * TN;
+      const TileInfo ti = decode_tile(p, t);
+      if (ti.skip) continue;
+      const Tf32Problem& pq = p.p[ti.prob];
+      const int m0 = ti.m0, n0 = ti.n0;
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1u;
       ++it;
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
       const uint32_t t_row = tmem_base + (uint32_t(32 * we) << 16) + acc * TN;
-      const bool rows_live = (m0 + 32 * we) < p.M;
+      const bool rows_live = (m0 + 32 * we) < pq.M;
 #pragma unroll 1
       for (int c = 0; c < TN / 32; ++c) {
         uint32_t v[32];
@@ -204,7 +223,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
           __syncwarp();
           if (lane == 0) mbar_arrive(tempty_bar(acc));
         }
-        if (rows_live && n0 + c * 32 < p.N) {
+        if (rows_live && n0 + c * 32 < pq.N) {
           const uint32_t stg = stg0 + buf * EPI_BUF;
           // the previous reduce from this buffer must have finished reading it
           if (lane == 0) bulk_wait_read0();
@@ -222,7 +241,8 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
           fence_proxy_async();
           __syncwarp();
           if (lane == 0) {
-            tma_reduce_add_2d(&map_c, stg, p.c_col0 + n0 + c * 32, p.c_row0 + m0 + 32 * we);
+            if (p.flags & TF32_STORE) tma_store_2d(&map_c, stg, pq.c_col0 + n0 + c * 32, pq.c_row0 + m0 + 32 * we);
+            else tma_reduce_add_2d(&map_c, stg, pq.c_col0 + n0 + c * 32, pq.c_row0 + m0 + 32 * we);
             bulk_commit();
           }
           buf ^= 1;
@@ -257,10 +277,9 @@ int gemm_tf32x3_maps(Tf32Maps* maps, const float* A, int a_rows, int a_cols, int
   return GQ_OK;
 }
 
-int gemm_tf32x3(const Tf32Maps& maps, int M, int N, int K, int a_row0, int a_col0, int b_row0, int b_col0, int c_row0,
-                int c_col0, float alpha, int upper_only, cudaStream_t st) {
-  if (M <= 0 || N <= 0 || K <= 0) return GQ_OK;
-  if (K % BK != 0) return GQ_ERR_SHAPE;
+int gemm_tf32x3_batch(const Tf32Maps& maps, const Tf32Problem* probs, int count, float alpha, int flags, cudaStream_t st) {
+  if (count <= 0) return GQ_OK;
+  if (count > TF32_MAX_BATCH) return GQ_ERR_ARG;
   static bool attr_set = false;
   static int n_sms = 0;
   if (!attr_set) {
@@ -272,14 +291,29 @@ int gemm_tf32x3(const Tf32Maps& maps, int M, int N, int K, int a_row0, int a_col
     attr_set = true;
   }
   GemmTf32Params p;
-  p.M = M; p.N = N; p.K = K;
-  p.a_col0 = a_col0; p.a_row0 = a_row0; p.b_col0 = b_col0; p.b_row0 = b_row0; p.c_col0 = c_col0; p.c_row0 = c_row0;
-  p.alpha = alpha; p.upper_only = upper_only;
-  const int tiles = ((M + TM - 1) / TM) * ((N + TN - 1) / TN);
+  p.count = 0; p.tiles_m = 0; p.tiles_n = 0; p.alpha = alpha; p.flags = flags;
+  for (int i = 0; i < count; ++i) {
+    const Tf32Problem& q = probs[i];
+    if (q.M <= 0 || q.N <= 0 || q.K <= 0) continue;
+    if (q.K % BK != 0) return GQ_ERR_SHAPE;
+    // the tensor maps clip at the edge of the WHOLE matrix, not of the window: a store-mode window must be tile-exact
+    // in N (32-column boxes) and M (32-row boxes) unless it ends at the matrix edge -- callers guarantee % 32 == 0
+    p.p[p.count++] = q;
+    p.tiles_m = max(p.tiles_m, (q.M + TM - 1) / TM);
+    p.tiles_n = max(p.tiles_n, (q.N + TN - 1) / TN);
+  }
+  if (p.count == 0) return GQ_OK;
+  const int tiles = p.count * p.tiles_m * p.tiles_n;
   const int grid = tiles < n_sms ? tiles : n_sms;
   GQ_LAUNCHED();
   gemm_tf32x3_kernel<<<grid, 384, SMEM_BYTES, st>>>(maps.a, maps.b, maps.c, p);
   return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
+}
+
+int gemm_tf32x3(const Tf32Maps& maps, int M, int N, int K, int a_row0, int a_col0, int b_row0, int b_col0, int c_row0,
+                int c_col0, float alpha, int upper_only, cudaStream_t st) {
+  Tf32Problem q{M, N, K, a_col0, a_row0, b_col0, b_row0, c_col0, c_row0};
+  return gemm_tf32x3_batch(maps, &q, 1, alpha, upper_only ? TF32_UPPER_ONLY : 0, st);
 }
 
 }  // namespace gq

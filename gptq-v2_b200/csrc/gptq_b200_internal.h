@@ -44,6 +44,21 @@ int sgemm_batched(const GemmBatch& b, float alpha, float beta, int flags, cudaSt
 // ---- fp32-faithful tensor-core GEMM  C += alpha * A^T B  (3 x TF32 split, tcgen05)
 extern int g_use_tf32x3;   // 1 (default): K4 / Cholesky updates on tcgen05 3xTF32; 0: fp32 SIMT GEMM (A/B parity hook)
 struct Tf32Maps { CUtensorMap a, b, c; };
+// one GEMM of a batched launch: windows into the matrices the three tensor maps describe
+struct Tf32Problem {
+  int M, N, K;
+  int a_col0, a_row0;      // A^T operand: element (k, m) at tensor-map coordinate (a_col0 + m, a_row0 + k)
+  int b_col0, b_row0;
+  int c_col0, c_row0;      // C element (m, n) at (c_col0 + n, c_row0 + m)
+};
+constexpr int TF32_MAX_BATCH = 56;
+enum : int {
+  TF32_UPPER_ONLY = 1,     // M == N: skip tiles entirely below the diagonal
+  TF32_STORE = 2,          // C = alpha * A^T B (plain TMA store) instead of C += (TMA reduce-add)
+  TF32_A_UPPER = 4,        // A (K x M) is upper triangular: k range of a tile ends at m0 + 128
+  TF32_B_LOWER = 8,        // B (K x N) is lower triangular: k range of a tile starts at n0
+};
+int gemm_tf32x3_batch(const Tf32Maps& maps, const Tf32Problem* probs, int count, float alpha, int flags, cudaStream_t st);
 int gemm_tf32x3_maps(Tf32Maps* maps, const float* A, int a_rows, int a_cols, int lda, const float* B, int b_rows,
                      int b_cols, int ldb, float* C, int c_rows, int c_cols, int ldc);
 int gemm_tf32x3(const Tf32Maps& maps, int M, int N, int K, int a_row0, int a_col0, int b_row0, int b_col0, int c_row0,
@@ -52,7 +67,8 @@ int gemm_tf32x3(const Tf32Maps& maps, int M, int N, int K, int a_row0, int a_col
 // ---- K2
 int hessian_gather(const float* H, int D, const int64_t* perm, float scale, float damp, float* Hp, float* Arev,
                    cudaStream_t st);
-int chol_inverse_upper(float* A, int D, float* U, float* tmp, int* info_dev, cudaStream_t st);
+int chol_inverse_upper(float* A, int D, float* U, float* Wb, float* tmp, int* info_dev, cudaStream_t st);
+int chol_factor_panel(float* A, int D, int o, int n, int rest, int* info_dev, cudaStream_t st);
 
 // ---- K3/K4
 int gptq_solve(float* Wt, const float* U, float* quant_t, void* codes_t, int codes_elem_size, float* err_t,
