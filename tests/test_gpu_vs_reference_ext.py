@@ -79,9 +79,9 @@ def test_quantize_range_vs_reference_kernels(ref, R, C, bits):
     assert torch.equal(err_o[:128], err_r[:128])
     match = (q_o == q_r).float().mean().item()
     assert match >= 0.999, match
-    same = (q_o == q_r)
-    # err = (w - q_hat) / U[c, c] can sit near zero, so the bound is relative to the error scale of the matrix
-    assert (err_o[same] - err_r[same]).abs().max() <= 1e-3 * err_r.abs().max()
-    # the weights left behind (updated in place) agree to fp32 reordering noise where no code flipped upstream
-    rows_ok = same.all(dim=0)
+    # a flipped code (allowed: < 0.1%) changes the compensation of the rest of its row, so errors and weights are
+    # compared on the rows without any flip; there they agree to fp32 reordering noise of the trailing GEMM
+    rows_ok = (q_o == q_r).all(dim=0)
+    assert rows_ok.float().mean().item() >= 0.5
+    assert (err_o[:, rows_ok] - err_r[:, rows_ok]).abs().max() <= 1e-3 * err_r.abs().max()
     assert (w_o[:, rows_ok] - w_r[:, rows_ok]).abs().max() <= 1e-4 * w_r.abs().max()
