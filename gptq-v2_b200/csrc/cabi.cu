@@ -107,7 +107,8 @@ int gq_gemm_tf32x3(const float* A, const float* B, float* C, int M, int N, int K
   Tf32Maps maps;
   int rc = gemm_tf32x3_maps(&maps, A, K, M, lda, B, K, N, ldb, C, M, N, ldc);
   if (rc != GQ_OK) return rc;
-  return gemm_tf32x3(maps, M, N, K, 0, 0, 0, 0, 0, 0, alpha, upper_only, S(stream));
+  Tf32Problem q{M, N, K, 0, 0, 0, 0, 0, 0};
+  return gemm_tf32x3_batch(maps, &q, 1, alpha, upper_only & (TF32_UPPER_ONLY | TF32_STORE), S(stream));
 }
 
 }  // extern "C"

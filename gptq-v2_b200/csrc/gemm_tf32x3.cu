@@ -30,6 +30,7 @@ constexpr int A_SUBS = TM / 32, B_SUBS = TN / 32;   // 4, 8
 constexpr int HI_BYTES = (A_SUBS + B_SUBS) * SUB;   // 24 KB
 constexpr int STAGE_BYTES = 2 * HI_BYTES;           // hi + lo
 constexpr int STAGES = 4;
+constexpr int SPLIT_THREADS = 128;                  // warps 8..11 split the landed tile into hi / lo
 constexpr int EPI_BUF = 32 * 128;                   // one 32 x 32 fp32 staging tile
 constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 4 * 2 * EPI_BUF + 1024 + 256;
 
@@ -76,7 +77,7 @@ __device__ __forceinline__ float rna_tf32(float x) {
   return __uint_as_float(r);
 }
 
-__global__ void __launch_bounds__(384, 1)
+__global__ void __launch_bounds__(256 + SPLIT_THREADS, 1)
 gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                    const __grid_constant__ CUtensorMap map_c, const GemmTf32Params p) {
   extern __shared__ uint8_t smem_raw[];
@@ -98,7 +99,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&map_a); tma_prefetch_desc(&map_b); tma_prefetch_desc(&map_c);
-    for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(ready_bar(s), 128); mbar_init(empty_bar(s), 1); }
+    for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(ready_bar(s), SPLIT_THREADS); mbar_init(empty_bar(s), 1); }
     for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 4); }
     fence_mbar_init();
   }
@@ -171,7 +172,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
     }
   } else if (warp >= 8) {
     // ---- split hi / lo, element-wise over the 24 KB that just landed
-    const int tid = threadIdx.x - 256;                 // 0..127
+    const int tid = threadIdx.x - 256;                 // 0..SPLIT_THREADS-1
     int stage = 0; uint32_t phase = 0;
     for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
       const TileInfo ti = decode_tile(p, t);
@@ -181,8 +182,8 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
         float4* hi = reinterpret_cast<float4*>(smem_gen + stage * STAGE_BYTES);
         float4* lo = reinterpret_cast<float4*>(smem_gen + stage * STAGE_BYTES + HI_BYTES);
 #pragma unroll
-        for (int i = 0; i < HI_BYTES / 16 / 128; ++i) {
-          const int idx = i * 128 + tid;
+        for (int i = 0; i < HI_BYTES / 16 / SPLIT_THREADS; ++i) {
+          const int idx = i * SPLIT_THREADS + tid;
           const float4 v = hi[idx];
           float4 h, l;
           h.x = rna_tf32(v.x); h.y = rna_tf32(v.y); h.z = rna_tf32(v.z); h.w = rna_tf32(v.w);
@@ -306,7 +307,7 @@ int gemm_tf32x3_batch(const Tf32Maps& maps, const Tf32Problem* probs, int count,
   const int tiles = p.count * p.tiles_m * p.tiles_n;
   const int grid = tiles < n_sms ? tiles : n_sms;
   GQ_LAUNCHED();
-  gemm_tf32x3_kernel<<<grid, 384, SMEM_BYTES, st>>>(maps.a, maps.b, maps.c, p);
+  gemm_tf32x3_kernel<<<grid, 256 + SPLIT_THREADS, SMEM_BYTES, st>>>(maps.a, maps.b, maps.c, p);
   return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
 }
 

@@ -183,7 +183,7 @@ def sgemm(A, B, C_, M, N, K, lda, ldb, ldc, alpha, beta, flags) -> None:
                            stream_of(C_)), 'gq_sgemm')
 
 
-def gemm_tf32x3(A, B, C_, M, N, K, lda, ldb, ldc, alpha, upper_only=False) -> None:
+def gemm_tf32x3(A, B, C_, M, N, K, lda, ldb, ldc, alpha, upper_only=0) -> None:
     """C (M, N) += alpha * A^T B on the tensor cores with a 3 x TF32 split (A stored (K, M), B (K, N))."""
     dev = require_cuda(A, B, C_)
     with torch.cuda.device(dev):

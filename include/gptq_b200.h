@@ -99,7 +99,8 @@ int gq_sgemm(const float* A, const float* B, float* C, int M, int N, int K, int 
 
 /* ---- fp32-faithful tensor-core GEMM used by K4 and the Cholesky update:  C += alpha * A^T B  with A stored
  * (K x M), B (K x N), C (M x N), fp32, computed as 3 x tcgen05 kind::tf32 on hi/lo splits.  K % 16 == 0,
- * lda/ldb/ldc % 4 == 0.  upper_only: skip tiles entirely below the diagonal. */
+ * lda/ldb/ldc % 4 == 0.  upper_only: bit 0 = skip tiles entirely below the diagonal; bit 1 = C = alpha * A^T B
+ * (plain store instead of accumulate; M % 32 == 0 then). */
 int gq_gemm_tf32x3(const float* A, const float* B, float* C, int M, int N, int K, int lda, int ldb, int ldc, float alpha,
                    int upper_only, void* stream);
 /* A/B parity hook: 0 routes K4 and the Cholesky trailing update through the fp32 SIMT GEMM instead of the

@@ -91,13 +91,13 @@ def bench_sgemm():
 
 
 def bench_tf32():
-    for M, N, K, up in ((3968, 4096, 128, 0), (10880, 4096, 128, 0), (3968, 11008, 128, 0), (10880, 10880, 128, 1),
-                        (128, 4096, 128, 0)):
+    for M, N, K, up in ((3968, 4096, 128, 0), (3968, 4096, 128, 2), (10880, 4096, 128, 0), (10880, 4096, 128, 2),
+                        (3968, 11008, 128, 0), (10880, 10880, 128, 1), (128, 4096, 128, 0), (4096, 4096, 4096, 0)):
         A = torch.randn(K, M, device=dev)
         B = torch.randn(K, N, device=dev)
         Cm = torch.zeros(M, N, device=dev)
-        t = timeit(lambda: gptq.gemm_tf32x3(A, B, Cm, M, N, K, M, N, N, -1.0, bool(up)))
-        frac = 0.5 if up else 1.0
+        t = timeit(lambda: gptq.gemm_tf32x3(A, B, Cm, M, N, K, M, N, N, -1.0, up))
+        frac = 0.5 if up == 1 else 1.0
         print(json.dumps({'k': 'gemm_tf32x3', 'M': M, 'N': N, 'K': K, 'upper': up, 'us': t * 1e6,
                           'tflops': frac * 2.0 * M * N * K / t / 1e12, 'C_GBps_rw': frac * M * N * 8 / t / 1e9}))
 
