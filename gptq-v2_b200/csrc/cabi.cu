@@ -87,11 +87,11 @@ int gq_transpose_pack_int4(const uint8_t* codes_t, uint8_t* codes, uint32_t* pac
   return transpose_pack_int4(codes_t, codes, packed, R, C, S(stream));
 }
 
-size_t gq_w4a16_workspace_bytes(int M, int K) { return w4a16_workspace_bytes(M, K); }
-int gq_w4a16_gemm(const void* x, const uint32_t* qweight, const void* scale, const uint8_t* qzero,
+size_t gq_w4a16_workspace_bytes(int M, int N, int K) { return w4a16_workspace_bytes(M, N, K); }
+int gq_w4a16_gemm(const void* x, const uint32_t* qweight, const void* scale_t, const uint8_t* qzero_t,
                   const int32_t* perm, void* y, void* workspace, int M, int N, int K, int group, int dtype,
                   void* stream) {
-  return w4a16_gemm(x, qweight, scale, qzero, perm, y, workspace, M, N, K, group, dtype, S(stream));
+  return w4a16_gemm(x, qweight, scale_t, qzero_t, perm, y, workspace, M, N, K, group, dtype, S(stream));
 }
 
 int gq_sgemm(const float* A, const float* B, float* C, int M, int N, int K, int lda, int ldb, int ldc, float alpha,

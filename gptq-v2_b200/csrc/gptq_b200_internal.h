@@ -25,6 +25,10 @@ int syrk_upper(float* H, const void* X, int D, int T, int fmt, int mode, int var
 int make_tmap_2d(CUtensorMap* out, const void* base, int elem_kind, uint64_t inner, uint64_t outer,
                  uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_outer, int swizzle_atom32 = 0);
 
+// general form: cu_dtype is a CUtensorMapDataType, cu_swizzle a CUtensorMapSwizzle
+int make_tmap_2d_raw(CUtensorMap* out, const void* base, int cu_dtype, uint64_t inner, uint64_t outer,
+                     uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_outer, int cu_swizzle);
+
 // ---- fp32 GEMM building block (SIMT):  C = beta*C + alpha * op(A) * B
 enum : int {
   GEMM_TRANS_A = 1,   // A is stored (K x M) row-major  (C = A^T B); else (M x K)
@@ -79,8 +83,8 @@ int gptq_solve(float* Wt, const float* U, float* quant_t, void* codes_t, int cod
 int pack_int4(const uint8_t* codes, uint32_t* packed, int R, int C, cudaStream_t st);
 int unpack_int4(const uint32_t* packed, uint8_t* codes, int R, int C, cudaStream_t st);
 int transpose_pack_int4(const uint8_t* codes_t, uint8_t* codes, uint32_t* packed, int R, int C, cudaStream_t st);
-size_t w4a16_workspace_bytes(int M, int K);
-int w4a16_gemm(const void* x, const uint32_t* qw, const void* scale, const uint8_t* qzero, const int32_t* perm,
+size_t w4a16_workspace_bytes(int M, int N, int K);
+int w4a16_gemm(const void* x, const uint32_t* qw, const void* scale_t, const uint8_t* qzero_t, const int32_t* perm,
                void* y, void* workspace, int M, int N, int K, int group, int fmt, cudaStream_t st);
 int prep_weight_t(const void* W, int fmt, const int64_t* perm, float* Wt, int R, int C, cudaStream_t st);
 

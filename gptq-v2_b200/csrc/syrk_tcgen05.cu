@@ -273,6 +273,20 @@ int make_tmap_2d(CUtensorMap* out, const void* base, int elem_kind, uint64_t inn
   return r == CUDA_SUCCESS ? GQ_OK : GQ_ERR_TENSORMAP;
 }
 
+int make_tmap_2d_raw(CUtensorMap* out, const void* base, int cu_dtype, uint64_t inner, uint64_t outer,
+                     uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_outer, int cu_swizzle) {
+  PFN_encodeTiled enc = get_encode_fn();
+  if (!enc) return GQ_ERR_DRIVER;
+  cuuint64_t dims[2] = {inner, outer};
+  cuuint64_t strides[1] = {row_stride_bytes};
+  cuuint32_t box[2] = {box_inner, box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, static_cast<CUtensorMapDataType>(cu_dtype), 2, const_cast<void*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, static_cast<CUtensorMapSwizzle>(cu_swizzle),
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? GQ_OK : GQ_ERR_TENSORMAP;
+}
+
 template <int CG>
 static int launch_syrk(const CUtensorMap& tmap, const SyrkParams& p, int n_sms, cudaStream_t st) {
   using C = SyrkCfg<CG>;

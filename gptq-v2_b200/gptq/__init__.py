@@ -154,24 +154,25 @@ def transpose_pack_int4(codes_t: torch.Tensor, want_codes: bool = True, want_pac
     return codes, packed
 
 
-def w4a16_gemm(x: torch.Tensor, qweight: torch.Tensor, scale: torch.Tensor, qzero: torch.Tensor, perm,
+def w4a16_gemm(x: torch.Tensor, qweight: torch.Tensor, scale_t: torch.Tensor, qzero_t: torch.Tensor, perm,
                group: int = 128) -> torch.Tensor:
-    """K6.  y (M, N) = x[:, perm] @ dequant(qweight)^T;  qweight (N, K/8) int32, scale (N, G) in
-    x.dtype, qzero (N, G) uint8, perm (K) int32 or None."""
-    dev = require_cuda(x, qweight, scale, qzero, perm)
-    require_contig(x=x, qweight=qweight, scale=scale, qzero=qzero, perm=perm)
+    """K6.  y (M, N) = x[:, perm] @ dequant(qweight)^T;  qweight (N, K/8) int32; scale_t (G, N) in x.dtype and
+    qzero_t (G, N) uint8 are group-major (transposes of quant_meta's scale / qzero); perm (K) int32 or None."""
+    dev = require_cuda(x, qweight, scale_t, qzero_t, perm)
+    require_contig(x=x, qweight=qweight, scale_t=scale_t, qzero_t=qzero_t, perm=perm)
     M, K = x.shape
     N = qweight.shape[0]
-    if qweight.shape[1] * 8 != K or scale.dtype != x.dtype or qzero.dtype != torch.uint8:
-        raise GptqB200Error('w4a16_gemm: inconsistent operands')
+    G = K // int(group)
+    if (qweight.shape[1] * 8 != K or scale_t.dtype != x.dtype or qzero_t.dtype != torch.uint8
+            or tuple(scale_t.shape) != (G, N) or tuple(qzero_t.shape) != (G, N)):
+        raise GptqB200Error('w4a16_gemm: inconsistent operands (scale_t / qzero_t must be (K/group, N))')
     if perm is not None and perm.dtype != torch.int32:
         raise GptqB200Error('perm must be int32')
     y = torch.empty(M, N, dtype=x.dtype, device=dev)
-    work = torch.empty(lib.gq_w4a16_workspace_bytes(M, K), dtype=torch.uint8, device=dev)
+    work = torch.empty(lib.gq_w4a16_workspace_bytes(M, N, K), dtype=torch.uint8, device=dev)
     with torch.cuda.device(dev):
-        check(lib.gq_w4a16_gemm(ptr(x), ptr(qweight), ptr(scale), ptr(qzero), ptr(perm), ptr(y), ptr(work), M, N, K,
-                                int(group),
-                                _cabi.DTYPE_CODE[x.dtype], stream_of(x)), 'gq_w4a16_gemm')
+        check(lib.gq_w4a16_gemm(ptr(x), ptr(qweight), ptr(scale_t), ptr(qzero_t), ptr(perm), ptr(y), ptr(work), M, N, K,
+                                int(group), _cabi.DTYPE_CODE[x.dtype], stream_of(x)), 'gq_w4a16_gemm')
     return y
 
 

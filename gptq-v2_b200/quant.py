@@ -95,7 +95,7 @@ def reconstruct_nn_linear(quant_meta: dict, dtype: torch.dtype, device: torch.de
 
 def pack_quant_meta(quant_meta: dict, device: torch.device) -> dict:
     """quant_meta (one uint8 per code) -> packed storage for K6:
-    qweight_packed (R, C/8) int32, scale (R, G), qzero (R, G) uint8, perm (C) int32."""
+    qweight_packed (R, C/8) int32, scale_t (G, R) and qzero_t (G, R) uint8 (group-major), perm (C) int32."""
     gs = _uniform_group(quant_meta['group_sizes'])
     codes = quant_meta['qweight'].to(device=device).contiguous()
     perm = None
@@ -103,8 +103,8 @@ def pack_quant_meta(quant_meta: dict, device: torch.device) -> dict:
         perm = quant_meta['perm_inv'].to(device=device, dtype=torch.int64).argsort().to(torch.int32).contiguous()
     return {
         'qweight_packed': _ops.pack_int4(codes),
-        'scale': quant_meta['scale'].to(device=device).contiguous(),
-        'qzero': quant_meta['qzero'].to(device=device).contiguous(),
+        'scale_t': quant_meta['scale'].to(device=device).t().contiguous(),
+        'qzero_t': quant_meta['qzero'].to(device=device).t().contiguous(),
         'perm': perm,
         'group_size': gs,
     }
@@ -116,8 +116,8 @@ class W4A16Linear(nn.Module):
     def __init__(self, packed: dict):
         super().__init__()
         self.register_buffer('qweight_packed', packed['qweight_packed'])
-        self.register_buffer('scale', packed['scale'])
-        self.register_buffer('qzero', packed['qzero'])
+        self.register_buffer('scale_t', packed['scale_t'])
+        self.register_buffer('qzero_t', packed['qzero_t'])
         self.register_buffer('perm', packed['perm'])
         self.group_size = packed['group_size']
         self.out_features, self.in_features = self.qweight_packed.shape[0], self.qweight_packed.shape[1] * 8
@@ -130,6 +130,6 @@ class W4A16Linear(nn.Module):
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         lead = x.shape[:-1]
         x2 = x.reshape(-1, self.in_features).contiguous()
-        scale = self.scale if self.scale.dtype == x2.dtype else self.scale.to(x2.dtype)
-        y = _ops.w4a16_gemm(x2, self.qweight_packed, scale, self.qzero, self.perm, self.group_size)
+        scale_t = self.scale_t if self.scale_t.dtype == x2.dtype else self.scale_t.to(x2.dtype)
+        y = _ops.w4a16_gemm(x2, self.qweight_packed, scale_t, self.qzero_t, self.perm, self.group_size)
         return y.view(*lead, self.out_features)

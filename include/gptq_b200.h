@@ -84,11 +84,13 @@ int gq_unpack_int4(const uint32_t* packed, uint8_t* codes, int R, int C, void* s
 int gq_transpose_pack_int4(const uint8_t* codes_t, uint8_t* codes, uint32_t* packed, int R, int C, void* stream);
 
 /* ---- K6: y (M, N) = x[:, perm] (M, K) * dequant(qweight)^T, replacing reconstruct_nn_linear +
- * nn.Linear (quant.py:262-279, llama.py:172-177).  x, y, scale share `dtype` (f16/bf16);
- * qzero (N, K/group) uint8; perm (K) int32 or NULL.  K % group == 0, group % 32 == 0. */
-/* workspace: gq_w4a16_workspace_bytes(M, K) bytes of device scratch (the permuted activations). */
-size_t gq_w4a16_workspace_bytes(int M, int K);
-int gq_w4a16_gemm(const void* x, const uint32_t* qweight, const void* scale, const uint8_t* qzero,
+ * nn.Linear (quant.py:262-279, llama.py:172-177).  x, y, scale_t share `dtype` (f16/bf16).  scale_t and
+ * qzero_t are GROUP-MAJOR: (K/group, N) 16-bit and (K/group, N) uint8 (the transposes of quant_meta's scale /
+ * qzero).  perm (K) int32 or NULL.  K % group == 0, group a power of two >= 32.
+ * workspace: gq_w4a16_workspace_bytes(M, N, K) bytes of device scratch, 256-byte aligned (the permuted activations
+ * and, for k-split work units, an fp32 accumulator). */
+size_t gq_w4a16_workspace_bytes(int M, int N, int K);
+int gq_w4a16_gemm(const void* x, const uint32_t* qweight, const void* scale_t, const uint8_t* qzero_t,
                   const int32_t* perm, void* y, void* workspace, int M, int N, int K, int group, int dtype,
                   void* stream);
 

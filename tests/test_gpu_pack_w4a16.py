@@ -46,10 +46,33 @@ def test_w4a16_vs_dense(M, N, K, dtype):
                 group_sizes=torch.full((G,), 128, dtype=torch.int16))
     want = O.linear_forward_dense(x, meta, dtype)
     packed = gptq.pack_int4(codes.cuda())
-    y = gptq.w4a16_gemm(x.cuda(), packed, scale.cuda(), qzero.cuda(), perm.to(torch.int32).cuda(), 128)
+    y = gptq.w4a16_gemm(x.cuda(), packed, scale.t().contiguous().cuda(), qzero.t().contiguous().cuda(),
+                        perm.to(torch.int32).cuda(), 128)
     torch.cuda.synchronize()
     rel = ((y.float().cpu() - want).norm() / want.norm()).item()
     assert rel <= 1e-2, rel
     want2 = O.w4a16_reference(x, O.pack_int4(codes.numpy()), scale, qzero, perm, 128)
     rel2 = ((y.float().cpu() - want2).norm() / want2.norm()).item()
     assert rel2 <= 5e-3, rel2
+
+
+@pytest.mark.parametrize('dtype', [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize('M,N,K,group', [(17, 200, 384, 128), (33, 1000, 1024, 64), (64, 640, 2048, 32), (65, 512, 768, 128),
+                                         (130, 384, 4096, 128), (300, 136, 288, 32)])
+def test_w4a16_tcgen05_ragged_shapes(M, N, K, group, dtype):
+    """batch tiles of 64 with padding, weight rows not a multiple of 128, K not a multiple
+    of 256, groups of 32/64/128, no permutation."""
+    import gptq
+    g = torch.Generator().manual_seed(M * 7 + N + K)
+    G = K // group
+    codes = torch.randint(0, 16, (N, K), generator=g, dtype=torch.uint8)
+    scale = (torch.rand(N, G, generator=g) * 0.01 + 1e-3).to(dtype)
+    qzero = torch.randint(0, 16, (N, G), generator=g, dtype=torch.uint8)
+    x = torch.randn(M, K, generator=g).to(dtype)
+    meta = dict(qweight=codes, scale=scale, qzero=qzero, perm_inv=None, group_sizes=torch.full((G,), group, dtype=torch.int16))
+    want = O.linear_forward_dense(x, meta, dtype)
+    y = gptq.w4a16_gemm(x.cuda(), gptq.pack_int4(codes.cuda()), scale.t().contiguous().cuda(),
+                        qzero.t().contiguous().cuda(), None, group)
+    torch.cuda.synchronize()
+    rel = ((y.float().cpu() - want).norm() / want.norm()).item()
+    assert rel <= 1e-2, rel

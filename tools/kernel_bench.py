@@ -109,22 +109,26 @@ def bench_w4a16():
         G = K // 128
         nbuf = max(4, int(600e6 // (N * K // 2)) + 1)
         qs = [torch.randint(-2 ** 31, 2 ** 31 - 1, (N, K // 8), device=dev, dtype=torch.int32) for _ in range(nbuf)]
-        sc = (torch.rand(N, G, device=dev) * 0.01 + 1e-3).half()
-        qz = torch.randint(0, 16, (N, G), device=dev, dtype=torch.uint8)
+        sc = (torch.rand(G, N, device=dev) * 0.01 + 1e-3).half()
+        qz = torch.randint(0, 16, (G, N), device=dev, dtype=torch.uint8)
         perm = torch.randperm(K, device=dev).to(torch.int32)
-        for M in (1, 2, 4, 8, 16):
-            x = torch.randn(M, K, device=dev).half()
-            gptq.w4a16_gemm(x, qs[0], sc, qz, perm, 128)
-            torch.cuda.synchronize()
-            graph = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(graph):
-                for q in qs:
-                    gptq.w4a16_gemm(x, q, sc, qz, perm, 128)
-            t = timeit(graph.replay, iters=7, warm=2) / nbuf
-            byts = N * K / 2 + N * G * 3 + 2 * M * K + 2 * M * N
-            print(json.dumps({'k': 'w4a16', 'M': M, 'N': N, 'K': K, 'us': t * 1e6, 'GBps': byts / t / 1e9,
-                              'tflops': 2.0 * M * N * K / t / 1e12, 'frac_hbm_6455': byts / t / 6455.6e9}))
-            del graph
+        for variant, Ms in ((2, (1, 2, 4, 8, 16, 64, 256, 1024)),):
+            for M in Ms:
+                if M > 16 and nbuf > 8:
+                    continue                              # large M only on the big (HBM-resident) shapes
+                x = torch.randn(M, K, device=dev).half()
+                gptq.w4a16_gemm(x, qs[0], sc, qz, perm, 128)
+                torch.cuda.synchronize()
+                graph = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph):
+                    for q in qs:
+                        gptq.w4a16_gemm(x, q, sc, qz, perm, 128)
+                t = timeit(graph.replay, iters=7, warm=2) / nbuf
+                byts = N * K / 2 + N * G * 3 + 2 * M * K + 2 * M * N
+                print(json.dumps({'k': 'w4a16', 'variant': variant, 'M': M, 'N': N, 'K': K, 'us': t * 1e6,
+                                  'GBps': byts / t / 1e9, 'tflops': 2.0 * M * N * K / t / 1e12,
+                                  'frac_hbm': byts / t / 6560.6e9, 'frac_bf16_peak': 2.0 * M * N * K / t / 1626.9e12}))
+                del graph
         del qs
 
 

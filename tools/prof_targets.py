@@ -33,7 +33,7 @@ elif which == 'solve':
 elif which == 'w4a16':
     N, K = 28672, 8192
     q = torch.randint(-2 ** 31, 2 ** 31 - 1, (N, K // 8), device=dev, dtype=torch.int32)
-    sc = (torch.rand(N, K // 128, device=dev) * 0.01).half(); qz = torch.randint(0, 16, (N, K // 128), device=dev, dtype=torch.uint8)
+    sc = (torch.rand(K // 128, N, device=dev) * 0.01).half(); qz = torch.randint(0, 16, (K // 128, N), device=dev, dtype=torch.uint8)
     x = torch.randn(1, K, device=dev).half()
     for _ in range(3):
         gptq.w4a16_gemm(x, q, sc, qz, None, 128)
