@@ -84,6 +84,11 @@ int pack_int4(const uint8_t* codes, uint32_t* packed, int R, int C, cudaStream_t
 int unpack_int4(const uint32_t* packed, uint8_t* codes, int R, int C, cudaStream_t st);
 int transpose_pack_int4(const uint8_t* codes_t, uint8_t* codes, uint32_t* packed, int R, int C, cudaStream_t st);
 size_t w4a16_workspace_bytes(int M, int N, int K);
+size_t w4a16_gemv_workspace_bytes(int M, int K);
+int w4a16_gemv(const void* x, const uint32_t* qw, const void* scale_t, const uint8_t* qzero_t, const int32_t* perm,
+               void* y, void* workspace, int M, int N, int K, int group, int fmt, cudaStream_t st);
+int w4a16_mma(const void* x, const uint32_t* qw, const void* scale_t, const uint8_t* qzero_t, const int32_t* perm,
+              void* y, void* workspace, int M, int N, int K, int group, int fmt, cudaStream_t st);
 int w4a16_gemm(const void* x, const uint32_t* qw, const void* scale_t, const uint8_t* qzero_t, const int32_t* perm,
                void* y, void* workspace, int M, int N, int K, int group, int fmt, cudaStream_t st);
 int prep_weight_t(const void* W, int fmt, const int64_t* perm, float* Wt, int R, int C, cudaStream_t st);

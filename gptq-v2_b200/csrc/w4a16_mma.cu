@@ -433,7 +433,7 @@ size_t w4a16_workspace_bytes(int M, int N, int K) {
   return ((((size_t)M * K * 2) + 255) & ~(size_t)255) + (size_t)M * N * sizeof(float);
 }
 
-int w4a16_gemm(const void* x, const uint32_t* qw, const void* scale, const uint8_t* qzero, const int32_t* perm, void* y,
+int w4a16_mma(const void* x, const uint32_t* qw, const void* scale, const uint8_t* qzero, const int32_t* perm, void* y,
                void* workspace, int M, int N, int K, int group, int fmt, cudaStream_t st) {
   if (M <= 0 || N <= 0) return GQ_OK;
   if (group < 32 || (group & (group - 1)) != 0 || K % group != 0) return GQ_ERR_SHAPE;   // group: power of two >= 32
@@ -442,6 +442,16 @@ int w4a16_gemm(const void* x, const uint32_t* qw, const void* scale, const uint8
   if (fmt == 0) return run_w4a16_mma<__half>(x, qw, scale, qzero, perm, y, workspace, M, N, K, group, fmt, st);
   if (fmt == 1) return run_w4a16_mma<__nv_bfloat16>(x, qw, scale, qzero, perm, y, workspace, M, N, K, group, fmt, st);
   return GQ_ERR_DTYPE;
+}
+
+// Batch 1-2 goes to the CUDA-core GEMV (w4a16_gemv.cu), everything else to the tcgen05 kernel: measured on B200, a
+// tcgen05.mma with M = 128, K = 16 occupies the tensor core for 171.6 cycles for EVERY N from 16 to 256
+// (tools/micro/umma_small_n.cu), so with the weights on the M side the tensor path streams at most
+// 128*16/2 B / 171.6 clk * 148 SMs * 1.85 GHz = 1.6 TB/s of packed int4 however small the batch is.
+int w4a16_gemm(const void* x, const uint32_t* qw, const void* scale_t, const uint8_t* qzero_t, const int32_t* perm, void* y,
+               void* workspace, int M, int N, int K, int group, int fmt, cudaStream_t st) {
+  if (M <= 2 && K <= 16384) return w4a16_gemv(x, qw, scale_t, qzero_t, perm, y, workspace, M, N, K, group, fmt, st);
+  return w4a16_mma(x, qw, scale_t, qzero_t, perm, y, workspace, M, N, K, group, fmt, st);
 }
 
 }  // namespace gq
