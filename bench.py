@@ -321,6 +321,13 @@ def gpu_main(args):
         pass
     peak_tf = peaks.get('bf16_tflops_sustained', 1400.0)
     achieved = syrk_f / syrk_s / 1e12
+    # dram__bytes_read.sum + dram__bytes_write.sum per SYRK launch from the committed `ncu --set full` capture
+    # (profiles/r01_v3_ncu_full_summary.txt), weighted over the launches of one layer; tensor-bound kernel, so the
+    # re-reads of X column panels (L2 misses at D = 11008) cost bandwidth headroom, not time.
+    ncu_dram = {4096: 509.3e6, 11008: 12.853e9}
+    traffic = None
+    if ctx.world == 1 and all(D in ncu_dram for _, _, D in timers['syrk']):
+        traffic = sum(ncu_dram[D] for _, _, D in timers['syrk']) / len(timers['syrk'])
     line = {
         'metric': 'GPTQ s/layer', 'value': step_s, 'unit': 's/layer', 'n_gpus': ctx.world, 'steps': args.steps,
         'warmup': args.warmup, 'ms_per_step': step_s * 1e3, 'higher_is_better': False, 'scaling': 'strong',
@@ -337,7 +344,8 @@ def gpu_main(args):
         'roofline': {'bound': 'tensor', 'kernel': 'syrk_upper_kernel<2> (K1, tcgen05 cta_group::2)',
                      'achieved': achieved, 'peak': peak_tf, 'unit': 'TFLOP/s', 'frac': achieved / peak_tf,
                      'peak_source': 'MEASURED_PEAKS.json bf16_tflops_sustained' if peaks else 'fallback 1.4 PF',
-                     'flops_per_launch': syrk_f / n_syrk, 'launch_s': syrk_s / n_syrk, 'traffic': None,
+                     'flops_per_launch': syrk_f / n_syrk, 'launch_s': syrk_s / n_syrk, 'traffic': traffic,
+                     'traffic_source': 'ncu --set full, profiles/r01_v3_ncu_full_summary.txt (weighted per launch)',
                      'gemm_equivalent_tflops': 2 * achieved},
         'detail': {'syrk_s_per_layer': syrk_s / args.steps,
                    'syrk_s_by_D': {str(D): statistics.mean(v) for D, v in per_d.items()},
@@ -390,7 +398,12 @@ def main():
         args.steps = min(args.steps, 3)
         reference_main(args)
     else:
-        gpu_main(args)
+        try:
+            gpu_main(args)
+        finally:
+            import torch.distributed as dist
+            if dist.is_available() and dist.is_initialized():
+                dist.destroy_process_group()
 
 
 if __name__ == '__main__':

@@ -1,0 +1,353 @@
+"""Layer-by-layer GPTQ of a Llama model on the B200 hot path  (BASELINE configs 2-4).
+
+Follows the flow of the reference's quantize_llama (/root/reference/llama.py:65-204): for every decoder block, the
+four Hessian groups are processed in dependency order
+
+    [v, k, q] <- input_layernorm(x)     [o] <- attention output     [up, gate] <- post_attention_layernorm(h)
+    [down] <- silu(gate) * up
+
+each group accumulates its Hessian over all calibration batches (HessianHook.add_batch, llama.py:121-125 /
+model_utils.py:101-103), inverts it (llama.py:138), quantises its linears (llama.py:148-163), rebuilds them
+(reconstruct_nn_linear, llama.py:172) and replays the calibration batches through the QUANTISED weights so that later
+groups see error-compensated activations (llama.py:176-177).  What is different from the reference:
+
+  * the block structure of Llama is written down explicitly instead of being rediscovered per block by tracing the
+    autograd graph under FakeTensorMode (model_utils.py:146-248, H9 in SURVEY.md: identical for all blocks);
+  * activations stay on the GPU (the reference's save_gpu_mem=False setting) as whole tensors, not Python lists;
+  * with torch.distributed initialised, calibration sequences are sharded over ranks, Hessians are all-reduced and the
+    rows of every linear are sharded (sharded.py); every rank keeps its own sequences through all layers.
+
+The transformer forward itself (RMSNorm, RoPE, SDPA, SwiGLU, dense replay GEMMs) is plain PyTorch: it is outside the
+hot path ("caller of the hot path").
+"""
+from __future__ import annotations
+
+import time
+from dataclasses import dataclass
+from typing import Callable, Optional
+
+import torch
+import torch.nn.functional as F
+
+import sharded
+from gptq_py import HessianHook, gptq_quant
+from quant import reconstruct_nn_linear
+
+
+@dataclass
+class LlamaShape:
+    hidden: int = 4096
+    inter: int = 11008
+    layers: int = 32
+    heads: int = 32
+    vocab: int = 32000
+    rms_eps: float = 1e-5
+    rope_theta: float = 10000.0
+
+    @staticmethod
+    def llama2_7b() -> 'LlamaShape':
+        return LlamaShape()
+
+    @staticmethod
+    def llama2_13b() -> 'LlamaShape':
+        return LlamaShape(hidden=5120, inter=13824, layers=40, heads=40)
+
+
+LINEAR_NAMES = ('self_attn.v_proj', 'self_attn.k_proj', 'self_attn.q_proj', 'self_attn.o_proj', 'mlp.up_proj',
+                'mlp.gate_proj', 'mlp.down_proj')
+
+
+def random_block_weights(shape: LlamaShape, layer: int, device: torch.device, dtype=torch.float16, seed: int = 0) -> dict:
+    """Random-init weights of one decoder block (normal, std 0.02 = HF initializer_range; norms = 1), generated on the
+    device from (seed, layer) so that every rank builds the same model without holding all 32 blocks."""
+    g = torch.Generator(device=device).manual_seed(seed * 1000 + layer)
+    h, i = shape.hidden, shape.inter
+
+    def w(r, c):
+        return (torch.randn(r, c, device=device, generator=g) * 0.02).to(dtype)
+    return {'self_attn.q_proj': w(h, h), 'self_attn.k_proj': w(h, h), 'self_attn.v_proj': w(h, h),
+            'self_attn.o_proj': w(h, h), 'mlp.gate_proj': w(i, h), 'mlp.up_proj': w(i, h), 'mlp.down_proj': w(h, i),
+            'input_layernorm': torch.ones(h, device=device, dtype=dtype),
+            'post_attention_layernorm': torch.ones(h, device=device, dtype=dtype)}
+
+
+def hf_block_weights(block, device: torch.device) -> dict:
+    """Weights of a transformers LlamaDecoderLayer in the dict form used here."""
+    out = {n: block.get_submodule(n).weight.detach().to(device) for n in LINEAR_NAMES}
+    out['input_layernorm'] = block.input_layernorm.weight.detach().to(device)
+    out['post_attention_layernorm'] = block.post_attention_layernorm.weight.detach().to(device)
+    return out
+
+
+def rms_norm(x: torch.Tensor, weight: torch.Tensor, eps: float) -> torch.Tensor:
+    xf = x.float()
+    return (weight * (xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + eps)).to(x.dtype))
+
+
+def rope_tables(seqlen: int, head_dim: int, theta: float, device, dtype):
+    inv = 1.0 / (theta ** (torch.arange(0, head_dim, 2, device=device, dtype=torch.float32) / head_dim))
+    ang = torch.outer(torch.arange(seqlen, device=device, dtype=torch.float32), inv)
+    emb = torch.cat([ang, ang], dim=-1)
+    return emb.cos().to(dtype), emb.sin().to(dtype)
+
+
+def apply_rope(x: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor) -> torch.Tensor:
+    """x (B, H, N, hd); HF Llama convention (rotate_half)."""
+    hd = x.shape[-1]
+    rot = torch.cat([-x[..., hd // 2:], x[..., :hd // 2]], dim=-1)
+    return x * cos + rot * sin
+
+
+def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int, cos, sin) -> torch.Tensor:
+    B, N, Hd = q.shape
+    hd = Hd // heads
+    q, k, v = (t.view(B, N, heads, hd).transpose(1, 2) for t in (q, k, v))
+    o = F.scaled_dot_product_attention(apply_rope(q, cos, sin), apply_rope(k, cos, sin), v, is_causal=True)
+    return o.transpose(1, 2).reshape(B, N, Hd)
+
+
+@torch.no_grad()
+def block_forward(shape: LlamaShape, weights: dict, x: torch.Tensor) -> torch.Tensor:
+    """Dense forward of one decoder block with the given (original or reconstructed) weights; x (B, N, hidden)."""
+    cos, sin = rope_tables(x.shape[1], shape.hidden // shape.heads, shape.rope_theta, x.device, x.dtype)
+    h = rms_norm(x, weights['input_layernorm'], shape.rms_eps)
+    a = attention(h @ weights['self_attn.q_proj'].t(), h @ weights['self_attn.k_proj'].t(),
+                  h @ weights['self_attn.v_proj'].t(), shape.heads, cos, sin)
+    x = x + a @ weights['self_attn.o_proj'].t()
+    h = rms_norm(x, weights['post_attention_layernorm'], shape.rms_eps)
+    m = F.silu(h @ weights['mlp.gate_proj'].t()) * (h @ weights['mlp.up_proj'].t())
+    return x + m @ weights['mlp.down_proj'].t()
+
+
+class PhaseTimer:
+    """CUDA-event phase timing without host syncs inside the loop; summary() resolves the events."""
+
+    def __init__(self, enabled: bool = True):
+        self.enabled = enabled and torch.cuda.is_available()
+        self._spans: list[tuple[str, torch.cuda.Event, torch.cuda.Event]] = []
+
+    class _Span:
+        def __init__(self, owner, name):
+            self.owner, self.name = owner, name
+
+        def __enter__(self):
+            if self.owner.enabled:
+                self.t0 = torch.cuda.Event(enable_timing=True)
+                self.t0.record()
+            return self
+
+        def __exit__(self, *exc):
+            if self.owner.enabled:
+                t1 = torch.cuda.Event(enable_timing=True)
+                t1.record()
+                self.owner._spans.append((self.name, self.t0, t1))
+            return False
+
+    def __call__(self, name: str) -> 'PhaseTimer._Span':
+        return PhaseTimer._Span(self, name)
+
+    def summary(self) -> dict[str, float]:
+        out: dict[str, float] = {}
+        if not self.enabled:
+            return out
+        torch.cuda.synchronize()
+        for name, t0, t1 in self._spans:
+            out[name] = out.get(name, 0.0) + t0.elapsed_time(t1) * 1e-3
+        return out
+
+
+def _batches(n: int, bs: int):
+    for b in range(0, n, bs):
+        yield slice(b, min(n, b + bs))
+
+
+class _GroupQuantizer:
+    """One Hessian group: accumulate -> (all-reduce) -> invert -> quantise each linear -> dense replay weights."""
+
+    def __init__(self, n_global: int, timer: PhaseTimer, pgroup, damp: float, act_order: bool, bits: int, gsize: int,
+                 use_kernel_semantics: bool, save_device: torch.device):
+        self.hook = HessianHook()
+        self.n_global, self.timer, self.pgroup = n_global, timer, pgroup
+        self.damp, self.act_order, self.bits, self.gsize = damp, act_order, bits, gsize
+        self.use_kernel_semantics, self.save_device = use_kernel_semantics, save_device
+
+    def add(self, x: torch.Tensor) -> None:
+        with self.timer('hessian'):
+            self.hook.add_batch(x)                                       # llama.py:121-125 -> model_utils.py:101-103
+
+    def finish(self) -> None:
+        with self.timer('allreduce'):
+            sharded.allreduce_hessian(self.hook, self.n_global, self.pgroup)
+        with self.timer('invert'):
+            self.hook.invert(self.damp, self.act_order)                  # llama.py:138
+
+    def quantize(self, weight: torch.Tensor) -> tuple[dict, dict, torch.Tensor]:
+        """-> (quant_meta on save_device, metrics, dense reconstructed weight on the GPU)."""
+        dev = weight.device
+        G = weight.shape[1] // self.gsize
+        gs = torch.full([G], self.gsize, dtype=torch.int32, device=dev)          # llama.py:146-147
+        gb = torch.full([G], self.bits, dtype=torch.int32, device=dev)
+        with self.timer('solve'):
+            res = sharded.gptq_quant_row_sharded(
+                weight, self.hook, group=self.pgroup, group_sizes=gs, group_bit_widths=gb, scale_bit_width=None,
+                gptq_use_kernel=self.use_kernel_semantics, gptq_block_sizes=gs, quant_symmetric=False, quant_mse=False,
+                save_device=dev)                                                  # llama.py:148-163
+        with self.timer('reconstruct'):
+            what = reconstruct_nn_linear(res['quant_meta'], dtype=weight.dtype, device=dev).weight.data   # llama.py:172
+        with self.timer('offload'):
+            meta = {k: (v.to(self.save_device) if torch.is_tensor(v) else v) for k, v in res['quant_meta'].items()}
+        return meta, res['metrics'], what
+
+
+@torch.no_grad()
+def quantize_block(shape: LlamaShape, weights: dict, inps: torch.Tensor, n_global: int, batch_size: int = 16,
+                   timer: Optional[PhaseTimer] = None, pgroup=None, damp: float = 1e-2, act_order: bool = True,
+                   bits: int = 4, gsize: int = 128, use_kernel_semantics: bool = True,
+                   save_device: torch.device = torch.device('cpu')) -> tuple[torch.Tensor, dict, dict]:
+    """GPTQ of one decoder block.  inps (n_local, N, hidden) on the GPU -> (next inps, {name: quant_meta},
+    {name: metrics}).  Group order and the order inside a group are the reference's (v, k, q / o / up, gate / down:
+    the hoisted dependency list of model_utils.py:146-248 on a Llama block)."""
+    timer = timer or PhaseTimer(False)
+    n, N, _ = inps.shape
+    dev, dt = inps.device, inps.dtype
+    data: dict = {}
+    metrics: dict = {}
+    cos, sin = rope_tables(N, shape.hidden // shape.heads, shape.rope_theta, dev, dt)
+
+    def make_group():
+        return _GroupQuantizer(n_global, timer, pgroup, damp, act_order, bits, gsize, use_kernel_semantics, save_device)
+
+    def quantize_into(grp: _GroupQuantizer, name: str) -> torch.Tensor:
+        meta, met, what = grp.quantize(weights[name])
+        data[name], metrics[name] = meta, met
+        return what
+
+    # ---- group 1: v, k, q on input_layernorm(x)
+    grp = make_group()
+    h1 = torch.empty_like(inps)
+    with timer('forward'):
+        for b in _batches(n, batch_size):
+            h1[b] = rms_norm(inps[b], weights['input_layernorm'], shape.rms_eps)
+    for b in _batches(n, batch_size):
+        grp.add(h1[b])
+    grp.finish()
+    wv = quantize_into(grp, 'self_attn.v_proj')
+    wk = quantize_into(grp, 'self_attn.k_proj')
+    wq = quantize_into(grp, 'self_attn.q_proj')
+    del grp
+    # ---- group 2: o on the attention output (computed from the QUANTISED q/k/v, llama.py:176-177)
+    grp = make_group()
+    att = torch.empty_like(inps)
+    with timer('forward'):
+        for b in _batches(n, batch_size):
+            x = h1[b]
+            att[b] = attention(x @ wq.t(), x @ wk.t(), x @ wv.t(), shape.heads, cos, sin)
+    del h1, wq, wk, wv
+    for b in _batches(n, batch_size):
+        grp.add(att[b])
+    grp.finish()
+    wo = quantize_into(grp, 'self_attn.o_proj')
+    del grp
+    # ---- group 3: up, gate on post_attention_layernorm(x + o)
+    grp = make_group()
+    h2 = torch.empty_like(inps)
+    h3 = torch.empty_like(inps)
+    with timer('forward'):
+        for b in _batches(n, batch_size):
+            h2[b] = inps[b] + att[b] @ wo.t()
+            h3[b] = rms_norm(h2[b], weights['post_attention_layernorm'], shape.rms_eps)
+    del att, wo
+    for b in _batches(n, batch_size):
+        grp.add(h3[b])
+    grp.finish()
+    wu = quantize_into(grp, 'mlp.up_proj')
+    wg = quantize_into(grp, 'mlp.gate_proj')
+    del grp
+    # ---- group 4: down on silu(gate) * up
+    grp = make_group()
+    act = torch.empty(n, N, shape.inter, dtype=dt, device=dev)
+    with timer('forward'):
+        for b in _batches(n, batch_size):
+            x = h3[b]
+            act[b] = F.silu(x @ wg.t()) * (x @ wu.t())
+    del h3, wu, wg
+    for b in _batches(n, batch_size):
+        grp.add(act[b])
+    grp.finish()
+    wd = quantize_into(grp, 'mlp.down_proj')
+    del grp
+    # ---- inputs of the next block (llama.py:181-189)
+    with timer('forward'):
+        for b in _batches(n, batch_size):
+            h2[b] += act[b] @ wd.t()
+    return h2, data, metrics
+
+
+@torch.no_grad()
+def quantize_llama(shape: LlamaShape, block_weights: Callable[[int], dict], inps: torch.Tensor,
+                   n_global: Optional[int] = None, batch_size: int = 16, n_blocks: Optional[int] = None, pgroup=None,
+                   timing: bool = True, log: Optional[Callable[[str], None]] = None, **block_kw) -> dict:
+    """The reference's quantize_llama (llama.py:65-204) on this build's hot path.
+
+    block_weights(i) -> the weights of decoder block i on the GPU (random_block_weights / hf_block_weights);
+    inps: this rank's embedded calibration sequences (n_local, N, hidden), fp16/bf16 on the GPU;
+    n_global: total number of calibration sequences over all ranks (default: n_local x world).
+    Returns {'data': {canonical name: quant_meta}, 'metrics': {canonical name: metrics}, 'timing': {phase: s},
+    'seconds': wall seconds, 'block_seconds': [...]} -- 'data' / 'metrics' as the reference's results dict."""
+    rank, world = sharded.world_info(pgroup)
+    if n_global is None:
+        n_global = inps.shape[0] * world
+    timer = PhaseTimer(timing)
+    results: dict = {'data': {}, 'metrics': {}, 'block_seconds': []}
+    n_blocks = shape.layers if n_blocks is None else n_blocks
+    torch.cuda.synchronize(inps.device)
+    t_all = time.perf_counter()
+    for i in range(n_blocks):
+        t0 = time.perf_counter()
+        with timer('weights'):
+            w = block_weights(i)
+        inps, data, metrics = quantize_block(shape, w, inps, n_global, batch_size, timer, pgroup, **block_kw)
+        for name in LINEAR_NAMES:
+            results['data'][f'model.layers.{i}.{name}'] = data[name]
+            results['metrics'][f'model.layers.{i}.{name}'] = metrics[name]
+        del w
+        torch.cuda.synchronize(inps.device)
+        results['block_seconds'].append(time.perf_counter() - t0)
+        if log is not None and rank == 0:
+            log(f'finished block {i} in {results["block_seconds"][-1]:.2f} s')
+    results['seconds'] = time.perf_counter() - t_all
+    results['timing'] = timer.summary()
+    results['final_hidden'] = inps
+    return results
+
+
+def synthetic_inputs(shape: LlamaShape, n_seq: int, seqlen: int, device: torch.device, dtype=torch.float16,
+                     seed: int = 1234) -> torch.Tensor:
+    """Embedded synthetic calibration batch: random token ids through a random-init embedding table (std 0.02).
+    There is no network for wikitext2/c4 (data_utils.py) or checkpoints, so calibration data is synthetic."""
+    g = torch.Generator(device=device).manual_seed(seed)
+    emb = (torch.randn(shape.vocab, shape.hidden, device=device, generator=g) * 0.02).to(dtype)
+    tok = torch.randint(0, shape.vocab, (n_seq, seqlen), device=device, generator=g)
+    return emb[tok]
+
+
+def _rope_theta(cfg) -> float:
+    theta = getattr(cfg, 'rope_theta', None)
+    if theta is None:                                   # transformers >= 5 keeps it under rope_parameters
+        theta = (getattr(cfg, 'rope_parameters', None) or {}).get('rope_theta', 10000.0)
+    return float(theta)
+
+
+def quantize_hf_llama(model, encodings: torch.Tensor, device: torch.device, batch_size: int = 16, **kw) -> dict:
+    """Same entry point shape as the reference's quantize_llama(model, encodings, device, batch_size): a transformers
+    LlamaForCausalLM and token ids (n_seq, N)."""
+    cfg = model.config
+    shape = LlamaShape(hidden=cfg.hidden_size, inter=cfg.intermediate_size, layers=cfg.num_hidden_layers,
+                       heads=cfg.num_attention_heads, vocab=cfg.vocab_size, rms_eps=cfg.rms_norm_eps,
+                       rope_theta=_rope_theta(cfg))
+    if getattr(cfg, 'num_key_value_heads', shape.heads) != shape.heads:
+        raise NotImplementedError('grouped-query attention is not handled by this driver')
+    emb = model.model.embed_tokens.weight.detach().to(device)
+    inps = emb[encodings.to(device)]
+    layers = model.model.layers
+    return quantize_llama(shape, lambda i: hf_block_weights(layers[i], device), inps, batch_size=batch_size, **kw)

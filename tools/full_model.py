@@ -1,0 +1,77 @@
+"""Full-model GPTQ wall time (BASELINE config 2 / north_star: Llama-2-7B, 4-bit g128, 128 x 2048 calibration tokens).
+
+  python tools/full_model.py [--blocks 32] [--n-seq 128] [--seqlen 2048] [--model 7b|13b]
+  python -m torch.distributed.run --nproc-per-node N --master-addr 127.0.0.1 tools/full_model.py ...
+
+Random-init weights and synthetic token ids (no network for checkpoints / wikitext2).  Prints one JSON line on rank 0:
+wall seconds for the whole model, seconds per block, and the CUDA-event phase breakdown of rank 0.
+"""
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+for _p in (ROOT, os.path.join(ROOT, 'gptq-v2_b200')):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+import llama_driver as L  # noqa: E402
+import sharded  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--blocks', type=int, default=None)
+    ap.add_argument('--n-seq', type=int, default=128)
+    ap.add_argument('--seqlen', type=int, default=2048)
+    ap.add_argument('--batch', type=int, default=16)
+    ap.add_argument('--model', default='7b')
+    ap.add_argument('--pure', action='store_true', help='fp32 PyTorch-path semantics (gptq_use_kernel=False)')
+    ap.add_argument('--keep', default='cpu', help='where quant_meta ends up: cpu (as the reference) or cuda')
+    args = ap.parse_args()
+
+    world = int(os.environ.get('WORLD_SIZE', '1'))
+    rank = int(os.environ.get('RANK', '0'))
+    local = int(os.environ.get('LOCAL_RANK', '0'))
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    shape = L.LlamaShape.llama2_13b() if args.model == '13b' else L.LlamaShape.llama2_7b()
+    lo, hi = sharded.shard_range(args.n_seq, world, rank)
+    # every rank draws the same global batch and keeps its own sequences
+    inps = L.synthetic_inputs(shape, args.n_seq, args.seqlen, dev)[lo:hi].contiguous()
+    # warm-up: one block at a tiny size loads the library, builds tensor maps, primes cuBLAS / SDPA
+    warm = L.LlamaShape(hidden=256, inter=512, layers=1, heads=4, vocab=64)
+    L.quantize_llama(warm, lambda i: L.random_block_weights(warm, i, dev), L.synthetic_inputs(warm, 2 * world, 128, dev)[:2],
+                     n_global=2 * world, batch_size=2, timing=False)
+    if world > 1:
+        dist.barrier()
+    res = L.quantize_llama(shape, lambda i: L.random_block_weights(shape, i, dev), inps, n_global=args.n_seq,
+                           batch_size=args.batch, n_blocks=args.blocks, use_kernel_semantics=not args.pure,
+                           save_device=torch.device(args.keep if args.keep == 'cpu' else dev),
+                           log=(lambda s: print(s, file=sys.stderr, flush=True)))
+    secs = torch.tensor([res['seconds']], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(secs, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        nb = len(res['block_seconds'])
+        errs = [m['l2.0_error'] / max(m['l2.0_norm'], 1e-30) for m in res['metrics'].values()]
+        print(json.dumps({
+            'what': 'full-model GPTQ', 'model': f'llama-2-{args.model} (random init)', 'blocks': nb, 'n_gpus': world,
+            'n_seq': args.n_seq, 'seqlen': args.seqlen, 'seconds': round(float(secs.item()), 3),
+            'seconds_per_block': round(float(secs.item()) / nb, 4),
+            'extrapolated_full_model_s': round(float(secs.item()) / nb * shape.layers, 2),
+            'phases_rank0_s': {k: round(v, 3) for k, v in sorted(res['timing'].items())},
+            'mean_rel_l2_error': sum(errs) / len(errs),
+            'semantics': 'fp32-pure' if args.pure else 'kernel-compat', 'quant_meta_on': args.keep}), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == '__main__':
+    main()
