@@ -89,6 +89,9 @@ int w4a16_gemv(const void* x, const uint32_t* qw, const void* scale_t, const uin
                void* y, void* workspace, int M, int N, int K, int group, int fmt, cudaStream_t st);
 int w4a16_mma(const void* x, const uint32_t* qw, const void* scale_t, const uint8_t* qzero_t, const int32_t* perm,
               void* y, void* workspace, int M, int N, int K, int group, int fmt, cudaStream_t st);
+bool w4a16_smallm_supports(int M, int N, int K, int group);
+int w4a16_smallm(const void* x, const uint32_t* qw, const void* scale_t, const uint8_t* qzero_t, const int32_t* perm,
+                 void* y, void* workspace, int M, int N, int K, int group, int fmt, cudaStream_t st);
 int w4a16_gemm(const void* x, const uint32_t* qw, const void* scale_t, const uint8_t* qzero_t, const int32_t* perm,
                void* y, void* workspace, int M, int N, int K, int group, int fmt, cudaStream_t st);
 int prep_weight_t(const void* W, int fmt, const int64_t* perm, float* Wt, int R, int C, cudaStream_t st);

@@ -430,7 +430,9 @@ int run_w4a16_mma(const void* x, const uint32_t* qw, const void* scale, const ui
 }  // namespace
 
 size_t w4a16_workspace_bytes(int M, int N, int K) {
-  return ((((size_t)M * K * 2) + 255) & ~(size_t)255) + (size_t)M * N * sizeof(float);
+  // xs (M, K) 16-bit | max(yacc (M, N) fp32 of the tcgen05 split-K path, chunk sums (M, K/128) fp32 of the small-batch path)
+  const size_t tail = (size_t)M * sizeof(float) * (size_t)(N > K / 128 + 8 ? N : K / 128 + 8);
+  return ((((size_t)M * K * 2) + 255) & ~(size_t)255) + tail;
 }
 
 int w4a16_mma(const void* x, const uint32_t* qw, const void* scale, const uint8_t* qzero, const int32_t* perm, void* y,
@@ -450,6 +452,7 @@ int w4a16_mma(const void* x, const uint32_t* qw, const void* scale, const uint8_
 // 128*16/2 B / 171.6 clk * 148 SMs * 1.85 GHz = 1.6 TB/s of packed int4 however small the batch is.
 int w4a16_gemm(const void* x, const uint32_t* qw, const void* scale_t, const uint8_t* qzero_t, const int32_t* perm, void* y,
                void* workspace, int M, int N, int K, int group, int fmt, cudaStream_t st) {
+  if (w4a16_smallm_supports(M, N, K, group)) return w4a16_smallm(x, qw, scale_t, qzero_t, perm, y, workspace, M, N, K, group, fmt, st);
   if (M <= 2 && K <= 16384) return w4a16_gemv(x, qw, scale_t, qzero_t, perm, y, workspace, M, N, K, group, fmt, st);
   return w4a16_mma(x, qw, scale_t, qzero_t, perm, y, workspace, M, N, K, group, fmt, st);
 }

@@ -1,0 +1,433 @@
+// K6, batch 1..8:  y (M, N) = x (M, K) . W_hat^T   with W_hat = (q - z) s  from packed int4, one pass over the weights.
+//
+// The op is a byte stream: 0.5 B per weight from HBM and, at batch <= 8, at most 16 MACs per weight.  What limits a
+// CUDA-core GEMV here is instruction issue (unpack + convert + FMA per weight), what limits the tcgen05 path is the
+// 128-row MMA floor (w4a16_mma.cu).  This kernel keeps the stream on plain coalesced 16-byte loads and spends
+// ~1 issue slot per weight:
+//
+//   * a packed word becomes four half2 / bf162 registers with one shift + one LOP3 each: the nibble is OR-ed into the
+//     mantissa of a constant whose ulp lines up with it (fp16: 64 + q, bf16: 16 + q, both exact);
+//   * those registers ARE the A fragment of a warp-level mma.m16n8k16 (16 weight rows x 16 k); the B fragment is the
+//     activation, so up to 8 batch columns ride along for free and the products accumulate in fp32;
+//   * the constant offset and the zero point come out per 128-column chunk through the chunk's activation sum S:
+//         sum_k (q - z) x  =  sum_k (off + q) x  -  (off + z) S,     then  y += s * (...)     (fp32)
+//     off is small (64 / 16) so that the cancellation costs < 1e-4 of the chunk's own magnitude.
+//
+// Work split: units of (16 rows x 128 k).  A CTA (one per SM) owns whole 16-row tiles; its units are dealt to its 16
+// warps as equal CONTIGUOUS ranges (stream-K inside the CTA), so a warp carries its fp32 row sums in registers and
+// adds them into the tile's shared-memory sums only when its range leaves a tile; the warp that completes a tile
+// converts and stores it: no global atomics, no zero-fill, no second pass.  The k order inside a chunk is free (it
+// only has to agree between A and B), so lane (r, t) simply takes the 16 contiguous bytes t of rows r and r + 8.
+//
+// Needs group % 128 == 0, K % 128 == 0, N % 16 == 0, M <= 8; the dispatcher sends everything else elsewhere.
+// Reference semantics: reconstruct_nn_linear (quant.py:262-279) followed by nn.Linear on the same input.
+#include "gptq_b200_internal.h"
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+
+namespace gq {
+namespace {
+
+constexpr int SM_WARPS = 16;                 // one CTA of 512 threads per SM
+constexpr int SM_THREADS = SM_WARPS * 32;
+constexpr int SM_CHUNK = 128;                // k per unit
+constexpr int SM_MAXM = 8;
+constexpr int SM_PF = 6;                     // units in flight per warp (register ring)
+
+template <typename T> struct Fmt;
+template <> struct Fmt<__half> {
+  static constexpr uint32_t MASK = 0x00f000f0u, MAGIC = 0x54005400u;   // 64 + q, ulp 1/16
+  static constexpr float OFF = 64.f;
+  // shifts that bring nibbles (0,4) (1,5) (2,6) (3,7) onto mantissa bits 4..7
+  __device__ static __forceinline__ uint32_t p0(uint32_t w) { return w << 4; }
+  __device__ static __forceinline__ uint32_t p1(uint32_t w) { return w; }
+  __device__ static __forceinline__ uint32_t p2(uint32_t w) { return w >> 4; }
+  __device__ static __forceinline__ uint32_t p3(uint32_t w) { return w >> 8; }
+  __device__ static __forceinline__ float to_f(__half v) { return __half2float(v); }
+  __device__ static __forceinline__ __half from_f(float v) { return __float2half_rn(v); }
+  __device__ static __forceinline__ void mma(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+  }
+};
+template <> struct Fmt<__nv_bfloat16> {
+  static constexpr uint32_t MASK = 0x00780078u, MAGIC = 0x41804180u;   // 16 + q, ulp 1/8
+  static constexpr float OFF = 16.f;
+  __device__ static __forceinline__ uint32_t p0(uint32_t w) { return w << 3; }
+  __device__ static __forceinline__ uint32_t p1(uint32_t w) { return w >> 1; }
+  __device__ static __forceinline__ uint32_t p2(uint32_t w) { return w >> 5; }
+  __device__ static __forceinline__ uint32_t p3(uint32_t w) { return w >> 9; }
+  __device__ static __forceinline__ float to_f(__nv_bfloat16 v) { return __bfloat162float(v); }
+  __device__ static __forceinline__ __nv_bfloat16 from_f(float v) { return __float2bfloat16_rn(v); }
+  __device__ static __forceinline__ void mma(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+  }
+};
+
+template <uint32_t MASK, uint32_t MAGIC>
+__device__ __forceinline__ uint32_t and_or(uint32_t a) {
+  uint32_t r;
+  asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(r) : "r"(a), "n"(MASK), "n"(MAGIC));
+  return r;
+}
+
+__device__ __forceinline__ uint4 ldg_stream(const uint32_t* p) {
+  uint4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.L2::128B.v4.u32 {%0,%1,%2,%3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+}
+
+struct SmallMParams {
+  const void* x;            // (M, K)
+  const uint32_t* qw;       // (N, K/8)
+  const void* scale_t;      // (G, N)
+  const uint8_t* qzero_t;   // (G, N)
+  const int32_t* perm;      // (K) or null
+  const void* xs_pre;       // PRE: (M, K) activation already in fragment order (w4a16_smallm_xprep_kernel)
+  const float* s_pre;       // PRE: (M, K/128) chunk sums
+  void* y;                  // (M, N) 16-bit
+  int M, N, K, group;
+  int tiles_per_cta;        // row tiles (16 rows) owned by one CTA
+};
+
+// One 8-element slot of the fragment order: gathers x[n][perm[...]] for source word `sl` (16 slots per 128-k chunk),
+// returns the 16 bytes to store and the slot's sum.
+//   slot (c, i, t) of column n holds  x[n][perm[c*128 + t*32 + i*8 + j + 4*e]]  at  2*j + e      (j = 0..3, e = 0..1)
+// i.e. lane t's i-th 16 bytes are the B registers of the two MMAs fed by component i of its 16-byte weight load.
+template <typename T>
+__device__ __forceinline__ void gather_slot(const T* __restrict__ xrow, const int32_t* __restrict__ perm, int k0, uint4& out,
+                                            float& sum) {
+  int pk[8];
+  if (perm) {
+    const int4 a = *reinterpret_cast<const int4*>(perm + k0), b = *reinterpret_cast<const int4*>(perm + k0 + 4);
+    pk[0] = a.x; pk[1] = a.y; pk[2] = a.z; pk[3] = a.w; pk[4] = b.x; pk[5] = b.y; pk[6] = b.z; pk[7] = b.w;
+  } else {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) pk[j] = k0 + j;
+  }
+  T v[8];
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    v[2 * j] = xrow[pk[j]];
+    v[2 * j + 1] = xrow[pk[j + 4]];
+  }
+  sum = 0.f;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) sum += Fmt<T>::to_f(v[j]);
+  out = *reinterpret_cast<const uint4*>(v);
+}
+
+// Large M*K: the gather is done once here instead of once per CTA.  xs_pre[n][c*128 + i*32 + t*8 ..], s_pre[n][c].
+template <typename T>
+__global__ void w4a16_smallm_xprep_kernel(const T* __restrict__ x, const int32_t* __restrict__ perm, T* __restrict__ xs_pre,
+                                          float* __restrict__ s_pre, int K) {
+  const int n = blockIdx.y;
+  const int sl = blockIdx.x * blockDim.x + threadIdx.x;          // blockDim.x % 32 == 0, K/8 % 16 == 0
+  const bool valid = sl < K / 8;
+  const int cc = sl >> 4, tt = (sl >> 2) & 3, ii = sl & 3;
+  uint4 out = make_uint4(0, 0, 0, 0);
+  float sum = 0.f;
+  if (valid) {
+    gather_slot<T>(x + (size_t)n * K, perm, cc * SM_CHUNK + tt * 32 + ii * 8, out, sum);
+    *reinterpret_cast<uint4*>(xs_pre + (size_t)n * K + cc * SM_CHUNK + ii * 32 + tt * 8) = out;
+  }
+  sum += __shfl_xor_sync(0xffffffffu, sum, 8);
+  sum += __shfl_xor_sync(0xffffffffu, sum, 4);
+  sum += __shfl_xor_sync(0xffffffffu, sum, 2);
+  sum += __shfl_xor_sync(0xffffffffu, sum, 1);
+  if (valid && (sl & 15) == 0) s_pre[(size_t)n * (K / SM_CHUNK) + cc] = sum;
+}
+
+// shared memory: xs[MP][K + 32] 16-bit (row pitch + 64 B keeps the two batch columns of a quarter-warp phase on
+// different banks) | S[K/128][8] fp32 chunk sums | acc[tiles_per_cta][16][MP] fp32 row sums | done[tiles_per_cta] int
+template <typename T, int MP, bool PRE>
+__global__ void __launch_bounds__(SM_THREADS, 1) w4a16_smallm_kernel(const SmallMParams p) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  const int K = p.K, N = p.N;
+  const int chunks = K / SM_CHUNK;
+  const int pitch = K + 32;                                  // elements
+  T* xs = reinterpret_cast<T*>(smem_raw);
+  float* S = reinterpret_cast<float*>(smem_raw + (size_t)MP * pitch * sizeof(T));
+  float* acc = S + chunks * 8;
+  int* done = reinterpret_cast<int*>(acc + p.tiles_per_cta * 16 * MP);
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int r = lane >> 2, t = lane & 3;
+
+  // ---- this CTA owns whole row tiles; its (tile, chunk) units are dealt to the warps as equal contiguous ranges
+  const int n_tiles = N / 16;
+  const int tile0 = min(n_tiles, (int)blockIdx.x * p.tiles_per_cta);
+  const int my_tiles = min(n_tiles, tile0 + p.tiles_per_cta) - tile0;
+  const int units = my_tiles * chunks;
+  const int u0 = (int)((long long)units * warp / SM_WARPS);
+  int left = (int)((long long)units * (warp + 1) / SM_WARPS) - u0;   // units still to compute
+  int tile = tile0 + u0 / chunks, c = u0 % chunks;
+  const int kw = K / 8;                                      // words per row
+
+  // ---- register ring of SM_PF units (weights of rows r / r+8 and one metadata word per lane: lanes t = 0, 1 carry
+  // the scales of rows r, r+8, lanes t = 2, 3 their zero points); the first loads go out before the prologue.
+  // Load cursor: running pointers, advanced by one chunk per issue.
+  const int gshift = 31 - __clz(p.group / SM_CHUNK);          // chunk -> group
+  const int G = K / p.group;
+  uint4 qa[SM_PF], qb[SM_PF];
+  uint32_t qm[SM_PF];
+  int lleft = left, lc = c;
+  const uint32_t* wp = p.qw + ((size_t)tile * 16 + r) * kw + c * 16 + t * 4;
+  const size_t row8 = (size_t)8 * kw;
+  const size_t wrap_w = (size_t)15 * kw + 16;                 // last chunk of a row tile -> first chunk of the next
+  const bool is_scale = t < 2;
+  // byte cursor into scale_t (2 B) or qzero_t (1 B)
+  const unsigned char* mp = is_scale
+      ? reinterpret_cast<const unsigned char*>(p.scale_t) + 2 * ((size_t)(c >> gshift) * N + tile * 16 + r + 8 * (t & 1))
+      : p.qzero_t + ((size_t)(c >> gshift) * N + tile * 16 + r + 8 * (t & 1));
+  const long long mstep = is_scale ? 2ll * N : (long long)N;                      // next group
+  const long long mwrap = (is_scale ? 2ll : 1ll) * (16 - (long long)(G - 1) * N);  // last group -> next row tile
+  const int gmask = (1 << gshift) - 1;
+  auto issue = [&](uint4& a, uint4& b, uint32_t& m) {
+    if (lleft > 0) {
+      a = ldg_stream(wp);
+      b = ldg_stream(wp + row8);
+      if (is_scale) m = *reinterpret_cast<const unsigned short*>(mp);
+      else m = *mp;
+      --lleft;
+      if (++lc == chunks) { lc = 0; wp += wrap_w; mp += mwrap; }
+      else { wp += 16; if ((lc & gmask) == 0) mp += mstep; }
+    }
+  };
+#pragma unroll
+  for (int s = 0; s < SM_PF; ++s) { qa[s] = make_uint4(0, 0, 0, 0); qb[s] = qa[s]; qm[s] = 0; issue(qa[s], qb[s], qm[s]); }
+
+  // ---- prologue: the activation in fragment order + chunk sums into shared memory; clear the row sums
+  for (int idx = tid; idx < p.tiles_per_cta * (16 * MP + 1); idx += SM_THREADS) acc[idx] = 0.f;   // acc and done (0 bits)
+  if (PRE) {
+    const int vec = K / 8;                                   // uint4 per column
+    for (int idx = tid; idx < MP * vec; idx += SM_THREADS) {
+      const int n = idx / vec, v = idx - n * vec;
+      uint4 val = make_uint4(0, 0, 0, 0);
+      if (n < p.M) val = reinterpret_cast<const uint4*>(p.xs_pre)[(size_t)n * vec + v];
+      *reinterpret_cast<uint4*>(xs + (size_t)n * pitch + v * 8) = val;
+    }
+    for (int idx = tid; idx < chunks * 8; idx += SM_THREADS) {
+      const int cc = idx >> 3, n = idx & 7;
+      S[idx] = n < p.M ? p.s_pre[(size_t)n * chunks + cc] : 0.f;
+    }
+  } else {
+    const T* x = reinterpret_cast<const T*>(p.x);
+    const int slots = K / 8;                                 // 8 elements per slot, 16 slots per chunk
+    const int total = MP * slots;                            // multiple of 16
+    for (int base = 0; base < total; base += 2 * SM_THREADS) {   // warp-uniform trip count (shuffles below), 2 slots in flight
+      uint4 out[2];
+      float sum[2];
+      int nn[2], sl[2];
+      bool valid[2];
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int idx = base + h * SM_THREADS + tid;
+        valid[h] = idx < total;
+        nn[h] = valid[h] ? idx / slots : 0;
+        sl[h] = valid[h] ? idx - nn[h] * slots : 0;
+        out[h] = make_uint4(0, 0, 0, 0);
+        sum[h] = 0.f;
+        if (valid[h] && nn[h] < p.M)
+          gather_slot<T>(x + (size_t)nn[h] * K, p.perm, (sl[h] >> 4) * SM_CHUNK + ((sl[h] >> 2) & 3) * 32 + (sl[h] & 3) * 8, out[h], sum[h]);
+      }
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int cc = sl[h] >> 4, tt = (sl[h] >> 2) & 3, ii = sl[h] & 3;
+        if (valid[h]) *reinterpret_cast<uint4*>(xs + (size_t)nn[h] * pitch + cc * SM_CHUNK + ii * 32 + tt * 8) = out[h];
+        float sm = sum[h];                                   // 16 consecutive idx = one chunk of one column
+        sm += __shfl_xor_sync(0xffffffffu, sm, 8);
+        sm += __shfl_xor_sync(0xffffffffu, sm, 4);
+        sm += __shfl_xor_sync(0xffffffffu, sm, 2);
+        sm += __shfl_xor_sync(0xffffffffu, sm, 1);
+        if (valid[h] && (sl[h] & 15) == 0) S[cc * 8 + nn[h]] = sm;
+      }
+    }
+    if (MP < 8)
+      for (int idx = tid; idx < chunks * 8; idx += SM_THREADS)
+        if ((idx & 7) >= MP) S[idx] = 0.f;
+  }
+  __syncthreads();
+  if (left <= 0) return;
+
+  const bool has_x = r < MP;                                  // lane (n = r, t) carries batch column r in B
+  const T* xrow = xs + (size_t)(has_x ? r : 0) * pitch + t * 8;
+  float ya[2] = {0.f, 0.f}, yb[2] = {0.f, 0.f};               // rows r / r+8, batch columns 2t, 2t+1
+  const int lane4 = lane & ~3;
+  int run = 0;                                                // chunks accumulated since the last flush
+
+  for (;;) {
+#pragma unroll
+    for (int s = 0; s < SM_PF; ++s) {
+      // ---- 8 MMAs over this chunk, two independent accumulator chains
+      float d0[4] = {0.f, 0.f, 0.f, 0.f}, d1[4] = {0.f, 0.f, 0.f, 0.f};
+      const uint32_t wra[4] = {qa[s].x, qa[s].y, qa[s].z, qa[s].w}, wrb[4] = {qb[s].x, qb[s].y, qb[s].z, qb[s].w};
+      const uint32_t m_sa = __shfl_sync(0xffffffffu, qm[s], lane4), m_sb = __shfl_sync(0xffffffffu, qm[s], lane4 + 1);
+      const uint32_t z_a = __shfl_sync(0xffffffffu, qm[s], lane4 + 2), z_b = __shfl_sync(0xffffffffu, qm[s], lane4 + 3);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        uint4 xb = make_uint4(0, 0, 0, 0);
+        if (MP == 8 || has_x) xb = *reinterpret_cast<const uint4*>(xrow + c * SM_CHUNK + i * 32);
+        uint32_t a[4];
+        a[0] = and_or<Fmt<T>::MASK, Fmt<T>::MAGIC>(Fmt<T>::p0(wra[i]));
+        a[1] = and_or<Fmt<T>::MASK, Fmt<T>::MAGIC>(Fmt<T>::p0(wrb[i]));
+        a[2] = and_or<Fmt<T>::MASK, Fmt<T>::MAGIC>(Fmt<T>::p1(wra[i]));
+        a[3] = and_or<Fmt<T>::MASK, Fmt<T>::MAGIC>(Fmt<T>::p1(wrb[i]));
+        Fmt<T>::mma(d0, a, xb.x, xb.y);
+        a[0] = and_or<Fmt<T>::MASK, Fmt<T>::MAGIC>(Fmt<T>::p2(wra[i]));
+        a[1] = and_or<Fmt<T>::MASK, Fmt<T>::MAGIC>(Fmt<T>::p2(wrb[i]));
+        a[2] = and_or<Fmt<T>::MASK, Fmt<T>::MAGIC>(Fmt<T>::p3(wra[i]));
+        a[3] = and_or<Fmt<T>::MASK, Fmt<T>::MAGIC>(Fmt<T>::p3(wrb[i]));
+        Fmt<T>::mma(d1, a, xb.z, xb.w);
+      }
+      issue(qa[s], qb[s], qm[s]);                             // refill this stage: unit u + SM_PF
+      // ---- chunk epilogue: remove offset and zero point, scale
+      {
+        const float2 Sc = *reinterpret_cast<const float2*>(S + c * 8 + 2 * t);
+        const unsigned short ha = (unsigned short)m_sa, hb = (unsigned short)m_sb;
+        const float fa = Fmt<T>::to_f(*reinterpret_cast<const T*>(&ha)), fb = Fmt<T>::to_f(*reinterpret_cast<const T*>(&hb));
+        const float oa = Fmt<T>::OFF + (float)z_a, ob = Fmt<T>::OFF + (float)z_b;
+        ya[0] = fmaf(fa, fmaf(-oa, Sc.x, d0[0] + d1[0]), ya[0]);
+        ya[1] = fmaf(fa, fmaf(-oa, Sc.y, d0[1] + d1[1]), ya[1]);
+        yb[0] = fmaf(fb, fmaf(-ob, Sc.x, d0[2] + d1[2]), yb[0]);
+        yb[1] = fmaf(fb, fmaf(-ob, Sc.y, d0[3] + d1[3]), yb[1]);
+      }
+      ++run;
+      // ---- leave the row tile (or the range): add the row sums into the CTA's tile; the warp that completes a
+      // tile converts and stores it
+      const bool last = --left == 0;
+      const bool wrap = c + 1 == chunks;
+      if (last || wrap) {
+        const int tl = tile - tile0;
+        float* at = acc + (size_t)tl * 16 * MP;
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const int n = 2 * t + e;
+          if (n < MP) {
+            atomicAdd(at + r * MP + n, ya[e]);
+            atomicAdd(at + (r + 8) * MP + n, yb[e]);
+          }
+        }
+        ya[0] = ya[1] = yb[0] = yb[1] = 0.f;
+        __syncwarp();
+        int fin = 0;
+        if (lane == 0) {
+          __threadfence_block();
+          fin = atomicAdd(done + tl, run) + run == chunks;
+        }
+        run = 0;
+        fin = __shfl_sync(0xffffffffu, fin, 0);
+        if (fin) {
+          __threadfence_block();
+          T* y = reinterpret_cast<T*>(p.y);
+          for (int idx = lane; idx < 16 * p.M; idx += 32) {
+            const int row = idx & 15, n = idx >> 4;
+            y[(size_t)n * N + tile * 16 + row] = Fmt<T>::from_f(*reinterpret_cast<volatile float*>(at + row * MP + n));
+          }
+        }
+        if (last) return;
+      }
+      if (wrap) { c = 0; ++tile; } else ++c;
+    }
+  }
+}
+
+template <typename T, int MP, bool PRE>
+int launch_smallm(const SmallMParams& p, size_t smem, int grid, cudaStream_t st) {
+  static size_t smem_set = 0;
+  if (smem > smem_set) {
+    if (cudaFuncSetAttribute(w4a16_smallm_kernel<T, MP, PRE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
+      return GQ_ERR_CUDA;
+    smem_set = smem;
+  }
+  GQ_LAUNCHED();
+  w4a16_smallm_kernel<T, MP, PRE><<<grid, SM_THREADS, smem, st>>>(p);
+  return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
+}
+
+inline int pad_m(int M) { return M <= 1 ? 1 : M <= 2 ? 2 : M <= 4 ? 4 : 8; }
+
+int sm_count() {
+  static int n_sms = 0;
+  if (n_sms == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n_sms <= 0) n_sms = 148;
+  }
+  return n_sms;
+}
+
+// grid and row tiles per CTA: whole tiles per CTA, at most one CTA per SM
+void split_tiles(int N, int& grid, int& tiles_per_cta) {
+  const int n_tiles = N / 16;
+  tiles_per_cta = (n_tiles + sm_count() - 1) / sm_count();
+  grid = (n_tiles + tiles_per_cta - 1) / tiles_per_cta;
+}
+
+size_t smallm_smem(int M, int N, int K) {
+  int grid, tpc;
+  split_tiles(N, grid, tpc);
+  const int mp = pad_m(M);
+  return (size_t)mp * (K + 32) * 2 + (size_t)(K / SM_CHUNK) * 32 + (size_t)tpc * (16 * mp + 1) * 4;
+}
+
+constexpr int SM_PRE_ELEMS = 32768;          // M_pad * K above which the gather is hoisted into its own launch
+
+template <typename T>
+int run_smallm(SmallMParams p, void* workspace, cudaStream_t st) {
+  const int mp = pad_m(p.M);
+  int grid;
+  split_tiles(p.N, grid, p.tiles_per_cta);
+  const size_t smem = smallm_smem(p.M, p.N, p.K);
+  const bool pre = (long long)mp * p.K > SM_PRE_ELEMS;
+  if (pre) {
+    T* xs_pre = reinterpret_cast<T*>(workspace);
+    float* s_pre = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(workspace) + ((((size_t)p.M * p.K * 2) + 255) & ~(size_t)255));
+    p.xs_pre = xs_pre;
+    p.s_pre = s_pre;
+    dim3 pg((p.K / 8 + 255) / 256, p.M);
+    GQ_LAUNCHED();
+    w4a16_smallm_xprep_kernel<T><<<pg, 256, 0, st>>>(reinterpret_cast<const T*>(p.x), p.perm, xs_pre, s_pre, p.K);
+  }
+#define GQ_SMALLM_CASE(MPV)                                                               \
+  case MPV: return pre ? launch_smallm<T, MPV, true>(p, smem, grid, st) : launch_smallm<T, MPV, false>(p, smem, grid, st);
+  switch (mp) {
+    GQ_SMALLM_CASE(1)
+    GQ_SMALLM_CASE(2)
+    GQ_SMALLM_CASE(4)
+    default: return pre ? launch_smallm<T, 8, true>(p, smem, grid, st) : launch_smallm<T, 8, false>(p, smem, grid, st);
+  }
+#undef GQ_SMALLM_CASE
+}
+
+}  // namespace
+
+// Does the batch-1..8 kernel take this shape?  (shared memory: the whole activation, M_pad x (K + 32) x 2 B)
+bool w4a16_smallm_supports(int M, int N, int K, int group) {
+  if (M < 1 || M > SM_MAXM || N < 16 || (N & 15) || K < SM_CHUNK || (K % SM_CHUNK) || group < SM_CHUNK ||
+      (group & (group - 1)) || (K % group))
+    return false;
+  return smallm_smem(M, N, K) <= 200 * 1024;
+}
+
+// workspace (only used when M_pad * K > 32768): M*K*2 B rounded to 256 + M*(K/128)*4 B
+int w4a16_smallm(const void* x, const uint32_t* qw, const void* scale_t, const uint8_t* qzero_t, const int32_t* perm, void* y,
+                 void* workspace, int M, int N, int K, int group, int fmt, cudaStream_t st) {
+  if (!w4a16_smallm_supports(M, N, K, group)) return GQ_ERR_SHAPE;
+  if (!workspace) return GQ_ERR_ARG;
+  if ((reinterpret_cast<uintptr_t>(qw) & 15) || (reinterpret_cast<uintptr_t>(workspace) & 255) ||
+      (perm && (reinterpret_cast<uintptr_t>(perm) & 15)))
+    return GQ_ERR_ALIGN;
+  SmallMParams p;
+  p.x = x; p.qw = qw; p.scale_t = scale_t; p.qzero_t = qzero_t; p.perm = perm;
+  p.xs_pre = nullptr; p.s_pre = nullptr; p.y = y;
+  p.M = M; p.N = N; p.K = K; p.group = group; p.tiles_per_cta = 0;
+  if (fmt == 0) return run_smallm<__half>(p, workspace, st);
+  if (fmt == 1) return run_smallm<__nv_bfloat16>(p, workspace, st);
+  return GQ_ERR_DTYPE;
+}
+
+}  // namespace gq

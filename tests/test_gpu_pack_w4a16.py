@@ -76,3 +76,33 @@ def test_w4a16_tcgen05_ragged_shapes(M, N, K, group, dtype):
     torch.cuda.synchronize()
     rel = ((y.float().cpu() - want).norm() / want.norm()).item()
     assert rel <= 1e-2, rel
+
+
+@pytest.mark.parametrize('dtype', [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize('M,N,K,group,use_perm', [(1, 592, 384, 128, True), (2, 4096, 4096, 128, True), (3, 16, 128, 128, False),
+                                                  (5, 1024, 11008, 128, True), (8, 2048, 2048, 256, False),
+                                                  (1, 28672, 8192, 128, True), (8, 320, 1024, 512, True)])
+def test_w4a16_small_batch_kernel(M, N, K, group, use_perm, dtype):
+    """Batch 1..8 path (w4a16_smallm.cu): offset-carrying mma fragments + per-chunk correction through the activation
+    sums.  Activations with a large mean make that cancellation visible; the bound is the 16-bit rounding of y."""
+    import gptq
+    g = torch.Generator().manual_seed(M * 131 + N + K + group)
+    G = K // group
+    codes = torch.randint(0, 16, (N, K), generator=g, dtype=torch.uint8)
+    scale = (torch.rand(N, G, generator=g) * 0.01 + 1e-3).to(dtype)
+    qzero = torch.randint(0, 16, (N, G), generator=g, dtype=torch.uint8)
+    perm = torch.randperm(K, generator=g) if use_perm else None
+    x = (torch.randn(M, K, generator=g) + 1.5).to(dtype)
+    # float64 ground truth on the same 16-bit inputs: y = sum_k (q - z) s x[perm[k]]
+    w = (codes.double() - qzero.double().repeat_interleave(group, dim=1)) * scale.double().repeat_interleave(group, dim=1)
+    xp = x.double()[:, perm] if use_perm else x.double()
+    want = xp @ w.t()
+    y = gptq.w4a16_gemm(x.cuda(), gptq.pack_int4(codes.cuda()), scale.t().contiguous().cuda(), qzero.t().contiguous().cuda(),
+                        perm.to(torch.int32).cuda() if use_perm else None, group)
+    torch.cuda.synchronize()
+    rel = ((y.double().cpu() - want).norm() / want.norm()).item()
+    assert rel <= (6e-4 if dtype == torch.float16 else 4e-3), rel
+    # the fp32 sums themselves (before the 16-bit store) must be far tighter: re-round the truth and compare elementwise
+    # elementwise: one 16-bit ulp of the result plus 2e-6 of the absolute sum (fp32 accumulation incl. the offset term)
+    bound = want.abs() * (2.0 ** -10 if dtype == torch.float16 else 2.0 ** -7) + 2e-6 * (xp.abs() @ w.abs().t())
+    assert ((y.double().cpu() - want).abs() <= bound).all()

@@ -105,14 +105,20 @@ def bench_tf32():
 def bench_w4a16():
     """Weights rotate through > 4x L2 of distinct buffers; the launches of one rotation are captured in
     a CUDA graph so that the host (ctypes + allocator) is out of the timed region."""
-    for N, K in ((4096, 4096), (11008, 4096), (4096, 11008), (8192, 8192), (28672, 8192), (8192, 28672)):
+    shapes = ((4096, 4096), (11008, 4096), (4096, 11008), (8192, 8192), (28672, 8192), (8192, 28672))
+    if os.environ.get('W4_SHAPES'):                       # e.g. W4_SHAPES=28672x8192 W4_MS=1,8 (profiling runs)
+        shapes = tuple(tuple(int(v) for v in sh.split('x')) for sh in os.environ['W4_SHAPES'].split(','))
+    m_list = (1, 2, 4, 8, 16, 64, 256, 1024)
+    if os.environ.get('W4_MS'):
+        m_list = tuple(int(v) for v in os.environ['W4_MS'].split(','))
+    for N, K in shapes:
         G = K // 128
         nbuf = max(4, int(600e6 // (N * K // 2)) + 1)
         qs = [torch.randint(-2 ** 31, 2 ** 31 - 1, (N, K // 8), device=dev, dtype=torch.int32) for _ in range(nbuf)]
         sc = (torch.rand(G, N, device=dev) * 0.01 + 1e-3).half()
         qz = torch.randint(0, 16, (G, N), device=dev, dtype=torch.uint8)
         perm = torch.randperm(K, device=dev).to(torch.int32)
-        for variant, Ms in ((2, (1, 2, 4, 8, 16, 64, 256, 1024)),):
+        for variant, Ms in ((2, m_list),):
             for M in Ms:
                 if M > 16 and nbuf > 8:
                     continue                              # large M only on the big (HBM-resident) shapes
