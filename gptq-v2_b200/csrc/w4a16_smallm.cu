@@ -6,12 +6,12 @@
 // ~1 issue slot per weight:
 //
 //   * a packed word becomes four half2 / bf162 registers with one shift + one LOP3 each: the nibble is OR-ed into the
-//     mantissa of a constant whose ulp lines up with it (fp16: 64 + q, bf16: 16 + q, both exact);
+//     mantissa of a constant whose ulp lines up with it (fp16: 64 + q, bf16: 128 + q, both exact);
 //   * those registers ARE the A fragment of a warp-level mma.m16n8k16 (16 weight rows x 16 k); the B fragment is the
 //     activation, so up to 8 batch columns ride along for free and the products accumulate in fp32;
 //   * the constant offset and the zero point come out per 128-column chunk through the chunk's activation sum S:
 //         sum_k (q - z) x  =  sum_k (off + q) x  -  (off + z) S,     then  y += s * (...)     (fp32)
-//     off is small (64 / 16) so that the cancellation costs < 1e-4 of the chunk's own magnitude.
+//     off is small (64 / 128) so that the cancellation costs < 1e-4 of the chunk's own magnitude.
 //
 // Work split: units of (16 rows x 128 k).  A CTA (one per SM) owns whole 16-row tiles; its units are dealt to its 16
 // warps as equal CONTIGUOUS ranges (stream-K inside the CTA), so a warp carries its fp32 row sums in registers and
@@ -34,45 +34,56 @@ constexpr int SM_CHUNK = 128;                // k per unit
 constexpr int SM_MAXM = 8;
 constexpr int SM_PF = 6;                     // units in flight per warp (register ring)
 
-template <typename T> struct Fmt;
-template <> struct Fmt<__half> {
-  static constexpr uint32_t MASK = 0x00f000f0u, MAGIC = 0x54005400u;   // 64 + q, ulp 1/16
-  static constexpr float OFF = 64.f;
-  // shifts that bring nibbles (0,4) (1,5) (2,6) (3,7) onto mantissa bits 4..7
-  __device__ static __forceinline__ uint32_t p0(uint32_t w) { return w << 4; }
-  __device__ static __forceinline__ uint32_t p1(uint32_t w) { return w; }
-  __device__ static __forceinline__ uint32_t p2(uint32_t w) { return w >> 4; }
-  __device__ static __forceinline__ uint32_t p3(uint32_t w) { return w >> 8; }
-  __device__ static __forceinline__ float to_f(__half v) { return __half2float(v); }
-  __device__ static __forceinline__ __half from_f(float v) { return __float2half_rn(v); }
-  __device__ static __forceinline__ void mma(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
-    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
-                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
-  }
-};
-template <> struct Fmt<__nv_bfloat16> {
-  static constexpr uint32_t MASK = 0x00780078u, MAGIC = 0x41804180u;   // 16 + q, ulp 1/8
-  static constexpr float OFF = 16.f;
-  __device__ static __forceinline__ uint32_t p0(uint32_t w) { return w << 3; }
-  __device__ static __forceinline__ uint32_t p1(uint32_t w) { return w >> 1; }
-  __device__ static __forceinline__ uint32_t p2(uint32_t w) { return w >> 5; }
-  __device__ static __forceinline__ uint32_t p3(uint32_t w) { return w >> 9; }
-  __device__ static __forceinline__ float to_f(__nv_bfloat16 v) { return __bfloat162float(v); }
-  __device__ static __forceinline__ __nv_bfloat16 from_f(float v) { return __float2bfloat16_rn(v); }
-  __device__ static __forceinline__ void mma(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
-    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
-                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
-  }
-};
-
 template <uint32_t MASK, uint32_t MAGIC>
 __device__ __forceinline__ uint32_t and_or(uint32_t a) {
   uint32_t r;
   asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(r) : "r"(a), "n"(MASK), "n"(MAGIC));
   return r;
 }
+
+template <typename T> struct Fmt;
+// unpack(w, o): one packed word -> four 2 x 16-bit registers  o0 = (n0, n4), o1 = (n1, n5), o2 = (n2, n6), o3 = (n3, n7),
+// each nibble OR-ed into the mantissa of a constant whose ulp lines up with it.  The ALU pipe (LOP3, PRMT, right
+// shifts: one warp instruction per 2 clk per scheduler) is what this kernel runs out of first, so the byte permute
+// v = (byte 1, 0, byte 3, 0) serves two registers and left shifts are left to the FMA pipe (IMAD.SHL).
+template <> struct Fmt<__half> {
+  static constexpr uint32_t MASK = 0x00f000f0u, MAGIC = 0x54005400u;   // 64 + q, ulp 1/16: nibble on mantissa bits 4..7
+  static constexpr float OFF = 64.f;
+  __device__ static __forceinline__ void unpack(uint32_t w, uint32_t (&o)[4]) {
+    const uint32_t v = __byte_perm(w, 0u, 0x4341u);
+    o[0] = and_or<MASK, MAGIC>(w << 4);
+    o[1] = and_or<MASK, MAGIC>(w);
+    o[2] = and_or<MASK, MAGIC>(v << 4);
+    o[3] = and_or<MASK, MAGIC>(v);
+  }
+  __device__ static __forceinline__ float to_f(__half v) { return __half2float(v); }
+  __device__ static __forceinline__ __half from_f(float v) { return __float2half_rn(v); }
+  __device__ static __forceinline__ void mma(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+  }
+};
+template <> struct Fmt<__nv_bfloat16> {
+  static constexpr uint32_t MASK = 0x000f000fu, MAGIC = 0x43004300u;   // 128 + q, ulp 1: nibble on mantissa bits 0..3
+  static constexpr float OFF = 128.f;
+  __device__ static __forceinline__ void unpack(uint32_t w, uint32_t (&o)[4]) {
+    const uint32_t v = __byte_perm(w, 0u, 0x4341u);
+    o[0] = and_or<MASK, MAGIC>(w);
+    o[1] = and_or<MASK, MAGIC>(w >> 4);
+    o[2] = and_or<MASK, MAGIC>(v);
+    o[3] = and_or<MASK, MAGIC>(v >> 4);
+  }
+  __device__ static __forceinline__ float to_f(__nv_bfloat16 v) { return __bfloat162float(v); }
+  __device__ static __forceinline__ __nv_bfloat16 from_f(float v) { return __float2bfloat16_rn(v); }
+  __device__ static __forceinline__ void mma(float (&d)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+  }
+};
+
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 __device__ __forceinline__ uint4 ldg_stream(const uint32_t* p) {
   uint4 v;
@@ -143,7 +154,8 @@ __global__ void w4a16_smallm_xprep_kernel(const T* __restrict__ x, const int32_t
 }
 
 // shared memory: xs[MP][K + 32] 16-bit (row pitch + 64 B keeps the two batch columns of a quarter-warp phase on
-// different banks) | S[K/128][8] fp32 chunk sums | acc[tiles_per_cta][16][MP] fp32 row sums | done[tiles_per_cta] int
+// different banks) | S[K/128][8] fp32 chunk sums | acc[tiles_per_cta][16][MP] fp32 row sums | done[tiles_per_cta] int |
+// 256 B of zeros (16 B aligned): the B fragment of the lanes whose batch column does not exist
 template <typename T, int MP, bool PRE>
 __global__ void __launch_bounds__(SM_THREADS, 1) w4a16_smallm_kernel(const SmallMParams p) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -154,8 +166,10 @@ __global__ void __launch_bounds__(SM_THREADS, 1) w4a16_smallm_kernel(const Small
   float* S = reinterpret_cast<float*>(smem_raw + (size_t)MP * pitch * sizeof(T));
   float* acc = S + chunks * 8;
   int* done = reinterpret_cast<int*>(acc + p.tiles_per_cta * 16 * MP);
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tid = threadIdx.x, lane = tid & 31;
+  const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);     // broadcast: the compiler keeps what derives from it uniform
   const int r = lane >> 2, t = lane & 3;
+  const uint32_t zero_blk = (smem_addr(done + p.tiles_per_cta) + 15u) & ~15u;
 
   // ---- this CTA owns whole row tiles; its (tile, chunk) units are dealt to the warps as equal contiguous ranges
   const int n_tiles = N / 16;
@@ -201,7 +215,7 @@ __global__ void __launch_bounds__(SM_THREADS, 1) w4a16_smallm_kernel(const Small
   for (int s = 0; s < SM_PF; ++s) { qa[s] = make_uint4(0, 0, 0, 0); qb[s] = qa[s]; qm[s] = 0; issue(qa[s], qb[s], qm[s]); }
 
   // ---- prologue: the activation in fragment order + chunk sums into shared memory; clear the row sums
-  for (int idx = tid; idx < p.tiles_per_cta * (16 * MP + 1); idx += SM_THREADS) acc[idx] = 0.f;   // acc and done (0 bits)
+  for (int idx = tid; idx < p.tiles_per_cta * (16 * MP + 1) + 68; idx += SM_THREADS) acc[idx] = 0.f;   // acc, done (0 bits), zero block
   if (PRE) {
     const int vec = K / 8;                                   // uint4 per column
     for (int idx = tid; idx < MP * vec; idx += SM_THREADS) {
@@ -253,8 +267,13 @@ __global__ void __launch_bounds__(SM_THREADS, 1) w4a16_smallm_kernel(const Small
   __syncthreads();
   if (left <= 0) return;
 
-  const bool has_x = r < MP;                                  // lane (n = r, t) carries batch column r in B
-  const T* xrow = xs + (size_t)(has_x ? r : 0) * pitch + t * 8;
+  // B fragment source: lane (n = r, t) carries batch column r; lanes without a column read the zero block (stride 0)
+  const bool has_x = r < MP;
+  const uint32_t x_base = has_x ? smem_addr(xs + (size_t)r * pitch + t * 8) : zero_blk;
+  const uint32_t x_step = has_x ? SM_CHUNK * (uint32_t)sizeof(T) : 0u;
+  uint32_t x_addr = x_base + (uint32_t)c * x_step;
+  const uint32_t s_base = smem_addr(S + 2 * t);
+  uint32_t s_addr = s_base + (uint32_t)c * 32u;
   float ya[2] = {0.f, 0.f}, yb[2] = {0.f, 0.f};               // rows r / r+8, batch columns 2t, 2t+1
   const int lane4 = lane & ~3;
   int run = 0;                                                // chunks accumulated since the last flush
@@ -262,34 +281,34 @@ __global__ void __launch_bounds__(SM_THREADS, 1) w4a16_smallm_kernel(const Small
   for (;;) {
 #pragma unroll
     for (int s = 0; s < SM_PF; ++s) {
+      // metadata: the loading lane converts (scale -> fp32, zero point -> OFF + z), then the quad shares it
+      float mv;
+      {
+        const unsigned short hs = (unsigned short)qm[s];
+        const float as_scale = Fmt<T>::to_f(*reinterpret_cast<const T*>(&hs));
+        const float as_zero = Fmt<T>::OFF + (float)qm[s];
+        mv = is_scale ? as_scale : as_zero;
+      }
+      const float fa = __shfl_sync(0xffffffffu, mv, lane4), fb = __shfl_sync(0xffffffffu, mv, lane4 + 1);
+      const float oa = __shfl_sync(0xffffffffu, mv, lane4 + 2), ob = __shfl_sync(0xffffffffu, mv, lane4 + 3);
       // ---- 8 MMAs over this chunk, two independent accumulator chains
       float d0[4] = {0.f, 0.f, 0.f, 0.f}, d1[4] = {0.f, 0.f, 0.f, 0.f};
       const uint32_t wra[4] = {qa[s].x, qa[s].y, qa[s].z, qa[s].w}, wrb[4] = {qb[s].x, qb[s].y, qb[s].z, qb[s].w};
-      const uint32_t m_sa = __shfl_sync(0xffffffffu, qm[s], lane4), m_sb = __shfl_sync(0xffffffffu, qm[s], lane4 + 1);
-      const uint32_t z_a = __shfl_sync(0xffffffffu, qm[s], lane4 + 2), z_b = __shfl_sync(0xffffffffu, qm[s], lane4 + 3);
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
-        uint4 xb = make_uint4(0, 0, 0, 0);
-        if (MP == 8 || has_x) xb = *reinterpret_cast<const uint4*>(xrow + c * SM_CHUNK + i * 32);
-        uint32_t a[4];
-        a[0] = and_or<Fmt<T>::MASK, Fmt<T>::MAGIC>(Fmt<T>::p0(wra[i]));
-        a[1] = and_or<Fmt<T>::MASK, Fmt<T>::MAGIC>(Fmt<T>::p0(wrb[i]));
-        a[2] = and_or<Fmt<T>::MASK, Fmt<T>::MAGIC>(Fmt<T>::p1(wra[i]));
-        a[3] = and_or<Fmt<T>::MASK, Fmt<T>::MAGIC>(Fmt<T>::p1(wrb[i]));
-        Fmt<T>::mma(d0, a, xb.x, xb.y);
-        a[0] = and_or<Fmt<T>::MASK, Fmt<T>::MAGIC>(Fmt<T>::p2(wra[i]));
-        a[1] = and_or<Fmt<T>::MASK, Fmt<T>::MAGIC>(Fmt<T>::p2(wrb[i]));
-        a[2] = and_or<Fmt<T>::MASK, Fmt<T>::MAGIC>(Fmt<T>::p3(wra[i]));
-        a[3] = and_or<Fmt<T>::MASK, Fmt<T>::MAGIC>(Fmt<T>::p3(wrb[i]));
-        Fmt<T>::mma(d1, a, xb.z, xb.w);
+        uint4 xb;
+        asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(xb.x), "=r"(xb.y), "=r"(xb.z), "=r"(xb.w) : "r"(x_addr + i * 64));
+        uint32_t ua[4], ub[4];
+        Fmt<T>::unpack(wra[i], ua);
+        Fmt<T>::unpack(wrb[i], ub);
+        Fmt<T>::mma(d0, ua[0], ub[0], ua[1], ub[1], xb.x, xb.y);
+        Fmt<T>::mma(d1, ua[2], ub[2], ua[3], ub[3], xb.z, xb.w);
       }
       issue(qa[s], qb[s], qm[s]);                             // refill this stage: unit u + SM_PF
       // ---- chunk epilogue: remove offset and zero point, scale
       {
-        const float2 Sc = *reinterpret_cast<const float2*>(S + c * 8 + 2 * t);
-        const unsigned short ha = (unsigned short)m_sa, hb = (unsigned short)m_sb;
-        const float fa = Fmt<T>::to_f(*reinterpret_cast<const T*>(&ha)), fb = Fmt<T>::to_f(*reinterpret_cast<const T*>(&hb));
-        const float oa = Fmt<T>::OFF + (float)z_a, ob = Fmt<T>::OFF + (float)z_b;
+        float2 Sc;
+        asm volatile("ld.shared.v2.f32 {%0,%1}, [%2];" : "=f"(Sc.x), "=f"(Sc.y) : "r"(s_addr));
         ya[0] = fmaf(fa, fmaf(-oa, Sc.x, d0[0] + d1[0]), ya[0]);
         ya[1] = fmaf(fa, fmaf(-oa, Sc.y, d0[1] + d1[1]), ya[1]);
         yb[0] = fmaf(fb, fmaf(-ob, Sc.x, d0[2] + d1[2]), yb[0]);
@@ -330,7 +349,7 @@ __global__ void __launch_bounds__(SM_THREADS, 1) w4a16_smallm_kernel(const Small
         }
         if (last) return;
       }
-      if (wrap) { c = 0; ++tile; } else ++c;
+      if (wrap) { c = 0; ++tile; x_addr = x_base; s_addr = s_base; } else { ++c; x_addr += x_step; s_addr += 32u; }
     }
   }
 }
@@ -371,7 +390,7 @@ size_t smallm_smem(int M, int N, int K) {
   int grid, tpc;
   split_tiles(N, grid, tpc);
   const int mp = pad_m(M);
-  return (size_t)mp * (K + 32) * 2 + (size_t)(K / SM_CHUNK) * 32 + (size_t)tpc * (16 * mp + 1) * 4;
+  return (size_t)mp * (K + 32) * 2 + (size_t)(K / SM_CHUNK) * 32 + (size_t)tpc * (16 * mp + 1) * 4 + 272;
 }
 
 constexpr int SM_PRE_ELEMS = 32768;          // M_pad * K above which the gather is hoisted into its own launch
