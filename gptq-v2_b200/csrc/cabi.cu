@@ -6,7 +6,7 @@ using namespace gq;
 
 static inline cudaStream_t S(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 
-namespace gq { unsigned long long g_launch_count = 0; int g_use_tf32x3 = 1; }
+namespace gq { unsigned long long g_launch_count = 0; int g_use_tf32x3 = 1; int g_solve_super = 8; }
 
 extern "C" {
 
@@ -73,6 +73,12 @@ int gq_gptq_solve(float* Wt, const float* U, float* quant_t, uint8_t* codes_t, f
   return gptq_solve(Wt, U, quant_t, codes_t, 1, err_t, scale_gr, qzero_gr, R, C, group, maxq, 0, 0, C, S(stream));
 }
 
+int gq_gptq_solve_static(float* Wt, const float* U, float* quant_t, int16_t* codes_t, float* err_t, const float* scale_gr,
+                         const float* qzero_gr, int R, int C, int group, float maxq, void* stream) {
+  return gptq_solve(Wt, U, quant_t, codes_t, 2, err_t, const_cast<float*>(scale_gr), const_cast<float*>(qzero_gr), R, C,
+                    group, maxq, 3, 0, C, S(stream));
+}
+
 int gq_prep_weight_t(const void* W, int dtype, const int64_t* perm, float* Wt, int R, int C, void* stream) {
   return prep_weight_t(W, dtype, perm, Wt, R, C, S(stream));
 }
@@ -100,6 +106,11 @@ int gq_sgemm(const float* A, const float* B, float* C, int M, int N, int K, int 
   return sgemm(p, alpha, beta, flags, S(stream));
 }
 
+int gq_set_solve_super(int blocks) {
+  int old = gq::g_solve_super;
+  if (blocks >= 1 && blocks <= 16) gq::g_solve_super = blocks;
+  return old;
+}
 int gq_set_tf32x3(int enable) { int old = gq::g_use_tf32x3; gq::g_use_tf32x3 = enable ? 1 : 0; return old; }
 
 int gq_gemm_tf32x3(const float* A, const float* B, float* C, int M, int N, int K, int lda, int ldb, int ldc, float alpha,

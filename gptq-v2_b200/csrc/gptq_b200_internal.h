@@ -46,6 +46,7 @@ int sgemm(const GemmProblem& pr, float alpha, float beta, int flags, cudaStream_
 int sgemm_batched(const GemmBatch& b, float alpha, float beta, int flags, cudaStream_t st);
 
 // ---- fp32-faithful tensor-core GEMM  C += alpha * A^T B  (3 x TF32 split, tcgen05)
+extern int g_solve_super;  // K4: blocks per super-block of the two-level lazy-batch update (1 = update everything after every block)
 extern int g_use_tf32x3;   // 1 (default): K4 / Cholesky updates on tcgen05 3xTF32; 0: fp32 SIMT GEMM (A/B parity hook)
 struct Tf32Maps { CUtensorMap a, b, c; };
 // one GEMM of a batched launch: windows into the matrices the three tensor maps describe

@@ -35,15 +35,20 @@ static int launch_block_nb(int mode, const SolveParams& p, int nb, cudaStream_t 
 // every later column.  mode 0: `group`-sized blocks, scale_gr/qzero_gr are (C/group, R)
 // outputs.  mode 1: scale_gr/qzero_gr are (R) inputs valid for the whole range (the
 // reference's gptq_quantize_range contract); the range is processed in chunks of <=128.
+// mode 3: mode 1's arithmetic (static parameters, 16-bit-rounded dequant) with the per-group
+// (C/group, R) parameter layout of mode 0: all groups of a linear in ONE call (one tensor-map
+// build, no host round trip per group).
 int gptq_solve(float* Wt, const float* U, float* quant_t, void* codes_t, int codes_elem_size, float* err_t,
                float* scale_gr, float* qzero_gr, int R, int C, int group, float maxq, int mode, int a, int b,
                cudaStream_t st) {
   if (R % 4 != 0 || C % 4 != 0) return GQ_ERR_SHAPE;           // float4 path, as the reference (gptq_cpp_kernel.cu:130)
   if (a < 0 || b > C || a >= b) return GQ_ERR_ARG;
+  const bool per_group = mode == 0 || mode == 3;
+  if (mode == 3) mode = 1;
   // codes are uint8 in mode 0 (this build's storage type) and int16 in mode 1 (the reference's out_q)
   if (codes_t && codes_elem_size != (mode == 0 ? 1 : 2)) return GQ_ERR_ARG;
-  if (mode == 0 && (group != 32 && group != 64 && group != 128)) return GQ_ERR_SHAPE;
-  if (mode == 0 && ((a % group) || (b % group))) return GQ_ERR_SHAPE;
+  if (per_group && (group != 32 && group != 64 && group != 128)) return GQ_ERR_SHAPE;
+  if (per_group && ((a % group) || (b % group))) return GQ_ERR_SHAPE;
   if ((a % 4) != 0) return GQ_ERR_SHAPE;                        // 16-byte aligned U row starts
   Tf32Maps maps;
   const bool tc = g_use_tf32x3 != 0;
@@ -51,13 +56,18 @@ int gptq_solve(float* Wt, const float* U, float* quant_t, void* codes_t, int cod
     int rcm = gemm_tf32x3_maps(&maps, U, C, C, C, err_t, C, R, R, Wt, C, R, R);
     if (rcm != GQ_OK) return rcm;
   }
+  // Two-level lazy batching: inside a super-block of `super` blocks the update only runs over the super-block's own
+  // later columns (they are needed next); the columns behind it get ONE rank-(super x nb) update when the
+  // super-block is finished: a quarter of the read-modify-write passes over W and a deeper, more efficient GEMM.
+  const int super = tc ? g_solve_super : 1;
   int c = a;
+  int sb_start = a, sb_blocks = 0;
   while (c < b) {
-    int nb = (mode == 0) ? group : ((b - c >= 128) ? 128 : (b - c));
+    int nb = per_group ? group : ((b - c >= 128) ? 128 : (b - c));
     SolveParams p;
     p.Wt = Wt; p.U = U; p.quant_t = quant_t; p.codes_t = codes_t; p.err_t = err_t;
     p.R = R; p.C = C; p.c0 = c; p.maxq = maxq;
-    if (mode == 0) {
+    if (per_group) {
       p.scale = scale_gr + (size_t)(c / group) * R;
       p.qzero = qzero_gr + (size_t)(c / group) * R;
     } else {
@@ -66,15 +76,31 @@ int gptq_solve(float* Wt, const float* U, float* quant_t, void* codes_t, int cod
     int rc = launch_block_nb(mode, p, nb, st);
     if (rc != GQ_OK) return rc;
     const int e = c + nb;
+    ++sb_blocks;
+    const bool two_level = tc && nb % 16 == 0 && super > 1;
+    const bool close_super = !two_level || sb_blocks == super || e >= b;
     if (e < C) {
-      // W[e:, :] -= U[c:e, e:]^T * E[c:e, :]
-      if (tc && nb % 16 == 0) {
+      if (two_level) {
+        if (close_super) {
+          // near part of the last block, then everything behind the super-block at once
+          // (rows [e, C) all take U[sb_start:e, .]^T E[sb_start:e, :]; the blocks before this one already reached
+          //  rows [., e) through their near updates, so only this block's near range is empty)
+          const int k = e - sb_start;
+          if ((rc = gemm_tf32x3(maps, C - e, R, k, sb_start, e, sb_start, 0, e, 0, -1.f, 0, st)) != GQ_OK) return rc;
+        } else {
+          // W[e:se, :] -= U[c:e, e:se]^T E[c:e, :]   with se = end of the super-block
+          const int se = std::min(std::min(sb_start + super * nb, b), C);
+          if (se > e && (rc = gemm_tf32x3(maps, se - e, R, nb, c, e, c, 0, e, 0, -1.f, 0, st)) != GQ_OK) return rc;
+        }
+      } else if (tc && nb % 16 == 0) {
+        // W[e:, :] -= U[c:e, e:]^T * E[c:e, :]
         if ((rc = gemm_tf32x3(maps, C - e, R, nb, c, e, c, 0, e, 0, -1.f, 0, st)) != GQ_OK) return rc;
       } else {
         GemmProblem g{U + (size_t)c * C + e, err_t + (size_t)c * R, Wt + (size_t)e * R, C - e, R, nb, C, R, R};
         if ((rc = sgemm(g, -1.f, 1.f, GEMM_TRANS_A, st)) != GQ_OK) return rc;
       }
     }
+    if (close_super) { sb_start = e; sb_blocks = 0; }
     c = e;
   }
   return GQ_OK;

@@ -146,7 +146,11 @@ int chol_inverse_upper(float* A, int D, float* U, float* Wb, float* tmp, int* in
   int rc;
   Tf32Maps maps;
   if ((rc = gemm_tf32x3_maps(&maps, A, D, D, D, A, D, D, D, A, D, D, D)) != GQ_OK) return rc;
-  // ---- blocked right-looking upper Cholesky
+  // ---- blocked right-looking upper Cholesky, trailing update in two levels: inside a super-block of `super` steps
+  // only the super-block's own later row blocks are brought up to date after every step (the next panels need
+  // them); everything behind the super-block gets ONE rank-(super x 128) update when it closes
+  const int super = g_use_tf32x3 ? g_solve_super : 1;
+  int sb_o = 0, sb_cnt = 0;
   for (int k = 0; k < nb; ++k) {
     const int o = k * NB;
     const int n = min(NB, D - o);
@@ -154,9 +158,18 @@ int chol_inverse_upper(float* A, int D, float* U, float* Wb, float* tmp, int* in
     // diagonal block factor + panel solve P = R_kk^-T * A[k, k+1:], one launch (chol_panel.cu)
     if ((rc = chol_factor_panel(A, D, o, n, rest, info_dev, st)) != GQ_OK) return rc;
     if (rest <= 0) break;
-    // A22 -= P^T P  (upper tiles only)
+    const int e = o + n;
+    ++sb_cnt;
     if (g_use_tf32x3) {
-      if ((rc = gemm_tf32x3(maps, rest, rest, n, o, o + n, o, o + n, o + n, o + n, -1.f, 1, st)) != GQ_OK) return rc;
+      if (sb_cnt == super) {
+        // A[e:, e:] -= P^T P with P = A[sb_o:e, e:]  (upper tiles only)
+        if ((rc = gemm_tf32x3(maps, rest, rest, e - sb_o, sb_o, e, sb_o, e, e, e, -1.f, 1, st)) != GQ_OK) return rc;
+        sb_o = e; sb_cnt = 0;
+      } else {
+        // rows [e, se) of the trailing matrix only:  A[e:se, e:] -= A[o:e, e:se]^T A[o:e, e:]
+        const int se = min(sb_o + super * NB, D);
+        if ((rc = gemm_tf32x3(maps, se - e, rest, n, o, e, o, e, e, e, -1.f, 1, st)) != GQ_OK) return rc;
+      }
     } else {
       float* panel = A + (size_t)o * D + o + n;
       GemmProblem p2{panel, panel, A + (size_t)(o + n) * D + o + n, rest, rest, n, D, D, D};

@@ -15,7 +15,7 @@ from . import _cabi
 from ._cabi import GptqB200Error, check, lib, ptr, require_contig, require_cuda, stream_of
 
 __all__ = ['accumulate_hessian', 'gptq_quantize_range', 'hessian_syrk', 'hessian_invert', 'prep_weight_t',
-           'gptq_solve', 'pack_int4', 'unpack_int4', 'transpose_pack_int4', 'w4a16_gemm', 'sgemm', 'gemm_tf32x3', 'set_tf32x3',
+           'gptq_solve', 'gptq_solve_static', 'pack_int4', 'unpack_int4', 'transpose_pack_int4', 'w4a16_gemm', 'sgemm', 'gemm_tf32x3', 'set_tf32x3', 'set_solve_super',
            'GptqB200Error']
 
 
@@ -120,6 +120,24 @@ def gptq_solve(Wt: torch.Tensor, U: torch.Tensor, group: int, maxq: float, want_
     return quant_t, codes_t, err_t, scale_gr, qzero_gr
 
 
+def gptq_solve_static(Wt: torch.Tensor, U: torch.Tensor, scale_gr: torch.Tensor, qzero_gr: torch.Tensor, group: int, maxq: float):
+    """K3+K4 in the kernel-path semantics of gptq_quant(gptq_use_kernel=True): static per-group scale_gr / qzero_gr
+    (C/group, R) fp32, fp16-rounded dequant -- the reference's per-group gptq_quantize_range loop in one call.
+    Wt (C, R) is consumed.  Returns quant_t, codes_t (int16), err_t."""
+    dev = require_cuda(Wt, U, scale_gr, qzero_gr)
+    require_contig(Wt=Wt, U=U, scale_gr=scale_gr, qzero_gr=qzero_gr)
+    C_, R = Wt.shape
+    assert scale_gr.shape == (C_ // group, R) and qzero_gr.shape == (C_ // group, R)
+    assert scale_gr.dtype == torch.float32 and qzero_gr.dtype == torch.float32
+    quant_t = torch.empty_like(Wt)
+    err_t = torch.empty_like(Wt)
+    codes_t = torch.empty(C_, R, dtype=torch.int16, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.gq_gptq_solve_static(ptr(Wt), ptr(U), ptr(quant_t), ptr(codes_t), ptr(err_t), ptr(scale_gr),
+                                       ptr(qzero_gr), R, C_, int(group), float(maxq), stream_of(Wt)), 'gq_gptq_solve_static')
+    return quant_t, codes_t, err_t
+
+
 def pack_int4(codes: torch.Tensor) -> torch.Tensor:
     """K5.  codes (R, C) uint8 in [0, 15] -> (R, C/8) int32 words (bit pattern of uint32)."""
     dev = require_cuda(codes)
@@ -190,6 +208,11 @@ def gemm_tf32x3(A, B, C_, M, N, K, lda, ldb, ldc, alpha, upper_only=0) -> None:
     with torch.cuda.device(dev):
         check(lib.gq_gemm_tf32x3(ptr(A), ptr(B), ptr(C_), M, N, K, lda, ldb, ldc, float(alpha), int(upper_only),
                                  stream_of(C_)), 'gq_gemm_tf32x3')
+
+
+def set_solve_super(blocks: int) -> int:
+    """Blocks per super-block of K4's two-level update (1 = one full trailing update per block); returns the old value."""
+    return int(lib.gq_set_solve_super(int(blocks)))
 
 
 def set_tf32x3(enable: bool) -> bool:

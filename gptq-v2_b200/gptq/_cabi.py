@@ -28,6 +28,7 @@ SIGNATURES = {
     'gq_hessian_invert': (_i, [_vp, _i, _vp, _f, _f, _vp, _vp, _vp, _vp, _vp]),
     'gq_quantize_range': (_i, [_vp, _vp, _vp, _vp, _f, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     'gq_gptq_solve': (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _f, _vp]),
+    'gq_gptq_solve_static': (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _f, _vp]),
     'gq_prep_weight_t': (_i, [_vp, _i, _vp, _vp, _i, _i, _vp]),
     'gq_pack_int4': (_i, [_vp, _vp, _i, _i, _vp]),
     'gq_unpack_int4': (_i, [_vp, _vp, _i, _i, _vp]),
@@ -36,6 +37,7 @@ SIGNATURES = {
     'gq_w4a16_gemm': (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     'gq_gemm_tf32x3': (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _f, _i, _vp]),
     'gq_set_tf32x3': (_i, [_i]),
+    'gq_set_solve_super': (_i, [_i]),
     'gq_sgemm': (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _f, _f, _i, _vp]),
 }
 

@@ -138,12 +138,16 @@ def gptq_quant(
         xmin = -(-w3.amin(dim=1)).relu()
         scale_gr = (xmax - xmin) / maxq + 1e-12                               # (G, R)
         qzero_gr = (-xmin / scale_gr).round()
-        quant_t = torch.empty_like(Wt)
-        err_t = torch.empty_like(Wt)
-        q_t = torch.empty_like(Wt, dtype=torch.int16)
-        for g in range(n_groups):
-            gptq_quantize_range(quant_t, scale_gr[g].contiguous(), q_t, qzero_gr[g].contiguous(), maxq, U, Wt, err_t,
-                                g * gs, (g + 1) * gs)
+        if gs in (32, 64, 128):
+            # the reference's per-group gptq_quantize_range loop (ref :135-139), host loop inside the library
+            quant_t, q_t, err_t = _ops.gptq_solve_static(Wt, U, scale_gr.contiguous(), qzero_gr.contiguous(), gs, maxq)
+        else:
+            quant_t = torch.empty_like(Wt)
+            err_t = torch.empty_like(Wt)
+            q_t = torch.empty_like(Wt, dtype=torch.int16)
+            for g in range(n_groups):
+                gptq_quantize_range(quant_t, scale_gr[g].contiguous(), q_t, qzero_gr[g].contiguous(), maxq, U, Wt, err_t,
+                                    g * gs, (g + 1) * gs)
         codes_t = q_t.to(torch.uint8)
     else:
         quant_t, codes_t, err_t, scale_gr, qzero_gr = _ops.gptq_solve(Wt, U, gs, maxq)

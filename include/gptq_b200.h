@@ -73,6 +73,12 @@ int gq_quantize_range(float* quant, const float* scale, int16_t* out_q, const fl
  * group in {32, 64, 128} (= the GPTQ block size, as llama.py:155 sets it). */
 int gq_gptq_solve(float* Wt, const float* U, float* quant_t, uint8_t* codes_t, float* err_t, float* scale_gr,
                   float* qzero_gr, int R, int C, int group, float maxq, void* stream);
+/* The kernel-path semantics of gptq_quant(gptq_use_kernel=True) (gptq_py.py:125-157) for ALL groups of one linear:
+ * equivalent to the reference's loop `for g: gptq_quantize_range(..., scale[g], ..., qzero[g], ..., g*group, (g+1)*group)`
+ * (static per-group scale_gr/qzero_gr (C/group, R) INPUTS, fp16-rounded dequant, out_q int16), without a host round
+ * trip per group.  group in {32, 64, 128}. */
+int gq_gptq_solve_static(float* Wt, const float* U, float* quant_t, int16_t* codes_t, float* err_t, const float* scale_gr,
+                         const float* qzero_gr, int R, int C, int group, float maxq, void* stream);
 /* Wt[c][r] = (float) W[r][perm[c]]; W (R, C) of dtype GQ_DTYPE_*; perm may be NULL. */
 int gq_prep_weight_t(const void* W, int dtype, const int64_t* perm, float* Wt, int R, int C, void* stream);
 
@@ -108,6 +114,9 @@ int gq_gemm_tf32x3(const float* A, const float* B, float* C, int M, int N, int K
 /* A/B parity hook: 0 routes K4 and the Cholesky trailing update through the fp32 SIMT GEMM instead of the
  * 3xTF32 tensor-core GEMM.  Returns the previous setting. */
 int gq_set_tf32x3(int enable);
+/* Tuning hook: blocks per super-block of K4's two-level lazy-batch update (default 8; 1 = the reference's schedule, one
+ * full trailing update per block, gptq_py.py:139).  Returns the previous setting. */
+int gq_set_solve_super(int blocks);
 
 #ifdef __cplusplus
 }

@@ -76,3 +76,35 @@ def test_quantize_range_compat_vs_oracle(R, C, bits):
     with pytest.raises(RuntimeError):
         gptq.gptq_quantize_range(quant_t, scale[:, 0].contiguous().to(dev), q_t, qzero[:, 0].contiguous().to(dev),
                                  maxq, U[:, :-4].contiguous(), wt2, err_t, 0, 128)
+
+
+@pytest.mark.parametrize('R,C,group', [(64, 256, 128), (128, 512, 64), (256, 1024, 128), (32, 128, 32)])
+def test_solve_static_equals_per_group_range_calls(R, C, group):
+    """gq_gptq_solve_static = the reference's `for g: gptq_quantize_range(...)` loop (gptq_py.py:135-139), bit for bit."""
+    import gptq
+    W, inv = _setup(R, C, seed=3 * R + C)
+    scale, qzero, maxq = O.static_group_params(W, inv['perm'], group, 4)
+    dev = 'cuda'
+    U = inv['U'].to(dev).contiguous()
+    wt = W.float()[:, inv['perm']].t().contiguous().to(dev)
+    quant_t = torch.empty_like(wt)
+    err_t = torch.empty_like(wt)
+    q_t = torch.empty_like(wt, dtype=torch.int16)
+    for g, i1 in enumerate(range(0, C, group)):
+        gptq.gptq_quantize_range(quant_t, scale[:, g].contiguous().to(dev), q_t, qzero[:, g].contiguous().to(dev),
+                                 maxq, U, wt, err_t, i1, i1 + group)
+    # one full trailing update per block (the reference's schedule): bit for bit
+    old = gptq.set_solve_super(1)
+    try:
+        wt2 = W.float()[:, inv['perm']].t().contiguous().to(dev)
+        quant2, q2, err2 = gptq.gptq_solve_static(wt2, U, scale.t().contiguous().to(dev), qzero.t().contiguous().to(dev), group, maxq)
+        torch.cuda.synchronize()
+    finally:
+        gptq.set_solve_super(old)
+    assert torch.equal(q_t, q2) and torch.equal(quant_t, quant2) and torch.equal(err_t, err2) and torch.equal(wt, wt2)
+    # default two-level schedule: same arithmetic, the far updates summed in a different order
+    wt3 = W.float()[:, inv['perm']].t().contiguous().to(dev)
+    quant3, q3, err3 = gptq.gptq_solve_static(wt3, U, scale.t().contiguous().to(dev), qzero.t().contiguous().to(dev), group, maxq)
+    torch.cuda.synchronize()
+    assert torch.equal(q_t[:group], q3[:group])
+    assert (q_t == q3).float().mean().item() >= 0.999

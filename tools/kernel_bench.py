@@ -41,14 +41,21 @@ def bench_syrk():
         del X, H
 
 
+def _supers():
+    return tuple(int(v) for v in os.environ.get('GQ_SUPERS', '4').split(','))
+
+
 def bench_invert():
     for D in (4096, 11008):
         X = torch.randn(2 * D, D, device=dev) * torch.exp(torch.rand(D, device=dev) * 3 - 1.5)
         H = (X.t() @ X)
         perm = torch.argsort(H.diagonal(), descending=True)
         damp = 0.01 * float(H.diagonal().mean())
-        t = timeit(lambda: gptq.hessian_invert(H, perm, 1.0, damp), iters=3, warm=1)
-        print(json.dumps({'k': 'invert', 'D': D, 'ms': t * 1e3, 'tflops_2_3_D3': 2 / 3 * D ** 3 / t / 1e12}))
+        for sup in _supers():
+            old = gptq.set_solve_super(sup)
+            t = timeit(lambda: gptq.hessian_invert(H, perm, 1.0, damp), iters=3, warm=1)
+            gptq.set_solve_super(old)
+            print(json.dumps({'k': 'invert', 'D': D, 'super': sup, 'ms': t * 1e3, 'tflops_2_3_D3': 2 / 3 * D ** 3 / t / 1e12}))
         torch.backends.cuda.matmul.allow_tf32 = False
         Hp = H[perm][:, perm] + damp * torch.eye(D, device=dev)
 
@@ -72,10 +79,13 @@ def bench_solve():
         def run():
             Wt = Wt0.clone()
             gptq.gptq_solve(Wt, U, 128, 15.0)
-        t = timeit(run, iters=3, warm=1)
         tc = timeit(lambda: Wt0.clone(), iters=3, warm=1)
-        print(json.dumps({'k': 'solve', 'R': R, 'C': C, 'ms': (t - tc) * 1e3, 'trailing_tflops': R * C * C / (t - tc) / 1e12,
-                          'us_per_block': (t - tc) / (C / 128) * 1e6}))
+        for sup in _supers():
+            old = gptq.set_solve_super(sup)
+            t = timeit(run, iters=3, warm=1)
+            gptq.set_solve_super(old)
+            print(json.dumps({'k': 'solve', 'R': R, 'C': C, 'super': sup, 'ms': (t - tc) * 1e3,
+                              'trailing_tflops': R * C * C / (t - tc) / 1e12, 'us_per_block': (t - tc) / (C / 128) * 1e6}))
         del X, H, U, W, Wt0
 
 
