@@ -23,6 +23,7 @@ hot path ("caller of the hot path").
 from __future__ import annotations
 
 import time
+from concurrent.futures import Future, ThreadPoolExecutor
 from dataclasses import dataclass
 from typing import Callable, Optional
 
@@ -156,6 +157,70 @@ class PhaseTimer:
         return out
 
 
+class MetaOffloader:
+    """Moves finished quant_meta dicts to the host in the background (the reference does it inline, llama.py:173).
+
+    The device->host copy goes through two recycled pinned staging buffers on a side stream; a worker thread copies
+    staging -> pageable result tensors.  The main stream never waits for it; results() joins at the end."""
+
+    def __init__(self, device: torch.device, staging_bytes: int = 64 << 20):
+        self.device = device
+        self.pool = ThreadPoolExecutor(max_workers=1)
+        self.stream = torch.cuda.Stream(device=device)
+        self.staging_bytes = staging_bytes
+        self._staging: list[torch.Tensor] = []
+        self._futures: dict[str, Future] = {}
+
+    def _stage(self, nbytes: int, which: int) -> torch.Tensor:
+        while len(self._staging) < 2:
+            self._staging.append(torch.empty(self.staging_bytes, dtype=torch.uint8, pin_memory=True))
+        if nbytes > self._staging[which].numel():
+            self._staging[which] = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+        return self._staging[which][:nbytes]
+
+    def _work(self, meta: dict, ready: torch.cuda.Event) -> dict:
+        out = {}
+        with torch.cuda.device(self.device), torch.cuda.stream(self.stream):
+            self.stream.wait_event(ready)
+            which = 0
+            pending = []                                            # (key, staging view, dtype, shape, event)
+            for k, v in meta.items():
+                if not torch.is_tensor(v) or v.device.type != 'cuda':
+                    out[k] = v
+                    continue
+                src = v.contiguous()
+                if len(pending) == 2:                               # both staging buffers busy: drain the older one
+                    self._drain(pending.pop(0), out)
+                st = self._stage(src.numel() * src.element_size(), which)
+                st.copy_(src.view(-1).view(torch.uint8), non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(self.stream)
+                pending.append((k, st, src.dtype, tuple(src.shape), ev, src))
+                which ^= 1
+            for item in pending:
+                self._drain(item, out)
+        return {k: out[k] for k in meta}                            # original key order
+
+    @staticmethod
+    def _drain(item, out: dict) -> None:
+        k, st, dtype, shape, ev, _keep = item
+        ev.synchronize()
+        out[k] = st.clone().view(dtype).view(shape)                 # pageable copy made by this thread
+
+    def submit(self, name: str, meta: dict) -> None:
+        ready = torch.cuda.Event()
+        ready.record(torch.cuda.current_stream(self.device))
+        self._futures[name] = self.pool.submit(self._work, meta, ready)
+
+    def results(self) -> dict:
+        out = {name: f.result() for name, f in self._futures.items()}
+        self._futures.clear()
+        return out
+
+    def close(self) -> None:
+        self.pool.shutdown(wait=True)
+
+
 def _batches(n: int, bs: int):
     for b in range(0, n, bs):
         yield slice(b, min(n, b + bs))
@@ -194,8 +259,10 @@ class _GroupQuantizer:
                 save_device=dev)                                                  # llama.py:148-163
         with self.timer('reconstruct'):
             what = reconstruct_nn_linear(res['quant_meta'], dtype=weight.dtype, device=dev).weight.data   # llama.py:172
-        with self.timer('offload'):
-            meta = {k: (v.to(self.save_device) if torch.is_tensor(v) else v) for k, v in res['quant_meta'].items()}
+        meta = res['quant_meta']
+        if self.save_device != dev:
+            with self.timer('offload'):
+                meta = {k: (v.to(self.save_device) if torch.is_tensor(v) else v) for k, v in meta.items()}
         return meta, res['metrics'], what
 
 
@@ -300,21 +367,32 @@ def quantize_llama(shape: LlamaShape, block_weights: Callable[[int], dict], inps
     timer = PhaseTimer(timing)
     results: dict = {'data': {}, 'metrics': {}, 'block_seconds': []}
     n_blocks = shape.layers if n_blocks is None else n_blocks
-    torch.cuda.synchronize(inps.device)
+    dev = inps.device
+    save_device = block_kw.pop('save_device', torch.device('cpu'))
+    offloader = MetaOffloader(dev) if torch.device(save_device).type == 'cpu' else None
+    torch.cuda.synchronize(dev)
     t_all = time.perf_counter()
     for i in range(n_blocks):
         t0 = time.perf_counter()
         with timer('weights'):
             w = block_weights(i)
-        inps, data, metrics = quantize_block(shape, w, inps, n_global, batch_size, timer, pgroup, **block_kw)
+        inps, data, metrics = quantize_block(shape, w, inps, n_global, batch_size, timer, pgroup, save_device=dev, **block_kw)
         for name in LINEAR_NAMES:
-            results['data'][f'model.layers.{i}.{name}'] = data[name]
-            results['metrics'][f'model.layers.{i}.{name}'] = metrics[name]
-        del w
-        torch.cuda.synchronize(inps.device)
+            full = f'model.layers.{i}.{name}'
+            results['data'][full] = data[name]
+            results['metrics'][full] = metrics[name]
+            if offloader is not None:
+                offloader.submit(full, data[name])            # host copy in the background (llama.py:173 does it inline)
+        del w, data
+        torch.cuda.synchronize(dev)
         results['block_seconds'].append(time.perf_counter() - t0)
         if log is not None and rank == 0:
             log(f'finished block {i} in {results["block_seconds"][-1]:.2f} s')
+    if offloader is not None:
+        t0 = time.perf_counter()
+        results['data'].update(offloader.results())
+        offloader.close()
+        results['offload_join_seconds'] = time.perf_counter() - t0
     results['seconds'] = time.perf_counter() - t_all
     results['timing'] = timer.summary()
     results['final_hidden'] = inps
