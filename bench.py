@@ -183,45 +183,56 @@ def make_layer(ctx, host: bool):
 
 
 def run_step(ctx, W, X, Wh=None, Xh=None, timers=None):
-    """One layer through the reference-facing API.  Host mode (Wh/Xh given): activations and weights
-    come from pinned host memory (double-buffered H2D on a copy stream) and quant_meta goes back to
-    the host, as with the reference's save_device default."""
+    """One layer through the reference-facing API.  Host mode (Wh/Xh given): activations and weights come from pinned
+    host memory and quant_meta goes back to (pinned) host memory, all inside the step.  The host->device copies of the
+    whole layer are queued on a copy stream in consumption order when the step starts, so that PCIe keeps streaming
+    the next group's activations while the current group is inverted and solved; results leave on a second stream."""
     from gptq_py import HessianHook, gptq_quant
     from gptq import pack_int4
     import sharded
     host = Xh is not None
     n_local = N_SEQ // ctx.world
     call = min(CALL_SEQ, n_local)
+    n_calls = n_local // call
     stream = torch.cuda.current_stream()
-    copy_stream = torch.cuda.Stream() if host else None
     h2d = d2h = 0
     out = {}
+    if host:
+        if not hasattr(ctx, 'h2d_stream'):
+            ctx.h2d_stream, ctx.d2h_stream = torch.cuda.Stream(), torch.cuda.Stream()
+            ctx.pinned_out = {}
+        xdev, xready, wdev, wready = {}, {}, {}, {}
+        with torch.cuda.stream(ctx.h2d_stream):
+            for gi, D in enumerate(GROUP_D):
+                for ci in range(n_calls):
+                    buf = torch.empty(call, SEQLEN, D, device=ctx.dev, dtype=torch.float16)
+                    buf.copy_(Xh[D][:call], non_blocking=True)
+                    ev = torch.cuda.Event()
+                    ev.record(ctx.h2d_stream)
+                    xdev[gi, ci], xready[gi, ci] = buf, ev
+                    h2d += buf.numel() * 2
+                for name, R, C, g in LINEARS:
+                    if g != gi:
+                        continue
+                    r0, r1 = sharded.shard_range(R, ctx.world, ctx.rank, 4)
+                    w = torch.empty(r1 - r0, C, device=ctx.dev, dtype=torch.float16)
+                    w.copy_(Wh[name][r0:r1], non_blocking=True)
+                    ev = torch.cuda.Event()
+                    ev.record(ctx.h2d_stream)
+                    wdev[name], wready[name] = w, ev
+                    h2d += w.numel() * 2
     for gi, D in enumerate(GROUP_D):
         hook = HessianHook()
         if timers is not None:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record(stream)
         if host:
-            bufs = [torch.empty(call, SEQLEN, D, device=ctx.dev, dtype=torch.float16) for _ in range(2)]
-            ready = [torch.cuda.Event() for _ in range(2)]
-            freed = [torch.cuda.Event() for _ in range(2)]
-            n_calls = n_local // call
-
-            def issue(ci):
-                b = ci & 1
-                with torch.cuda.stream(copy_stream):
-                    if ci >= 2:
-                        copy_stream.wait_event(freed[b])
-                    bufs[b].copy_(Xh[D][:call], non_blocking=True)
-                    ready[b].record(copy_stream)
-            issue(0)
             for ci in range(n_calls):
-                if ci + 1 < n_calls:
-                    issue(ci + 1)
-                stream.wait_event(ready[ci & 1])
-                hook.add_batch(bufs[ci & 1])
-                freed[ci & 1].record(stream)
-                h2d += bufs[ci & 1].numel() * 2
+                stream.wait_event(xready[gi, ci])
+                xb = xdev.pop((gi, ci))
+                xb.record_stream(stream)                       # allocated on the copy stream, consumed here
+                hook.add_batch(xb)
+                del xb
             hook.n_samples = n_local
         else:
             for i in range(0, n_local, call):
@@ -236,20 +247,32 @@ def run_step(ctx, W, X, Wh=None, Xh=None, timers=None):
             if g != gi:
                 continue
             r0, r1 = sharded.shard_range(R, ctx.world, ctx.rank, 4)
-            rows = r1 - r0
             if host:
-                w = Wh[name][r0:r0 + rows].to(ctx.dev, non_blocking=True)
-                h2d += w.numel() * 2
+                stream.wait_event(wready[name])
+                w = wdev.pop(name)
+                w.record_stream(stream)
             else:
-                w = W[name][r0:r0 + rows]
+                w = W[name][r0:r1]
             gs = torch.full([C // GROUP], GROUP, dtype=torch.int32)
             bw = torch.full([C // GROUP], BITS, dtype=torch.int32)
             res = gptq_quant(weight=w, hessian_hook=hook, group_sizes=gs, group_bit_widths=bw, scale_bit_width=None,
                              gptq_use_kernel=False, gptq_block_sizes=gs, quant_symmetric=False, quant_mse=False,
-                             save_device=torch.device('cpu') if host else ctx.dev)
+                             save_device=ctx.dev)
             m = res['quant_meta']
             if host:
-                d2h += m['qweight'].numel() + m['scale'].numel() * 2 + m['qzero'].numel() + m['perm_inv'].numel() * 2
+                # quant_meta -> pinned host buffers on the result stream (joined at the end of the step)
+                done = torch.cuda.Event()
+                done.record(stream)
+                with torch.cuda.stream(ctx.d2h_stream):
+                    ctx.d2h_stream.wait_event(done)
+                    for key in ('qweight', 'scale', 'qzero', 'perm_inv'):
+                        t = m[key]
+                        hb = ctx.pinned_out.get((name, key))
+                        if hb is None or hb.shape != t.shape:
+                            hb = ctx.pinned_out[name, key] = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+                        hb.copy_(t, non_blocking=True)
+                        t.record_stream(ctx.d2h_stream)
+                        d2h += t.numel() * t.element_size()
                 packed = None
             else:
                 packed = pack_int4(m['qweight'])
@@ -261,6 +284,8 @@ def run_step(ctx, W, X, Wh=None, Xh=None, timers=None):
                     packed = full
             out[name] = (packed, res['metrics'])
         del hook
+    if host:
+        ctx.d2h_stream.synchronize()                           # the step's results are on the host
     return out, h2d, d2h
 
 
