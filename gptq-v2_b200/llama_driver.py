@@ -160,30 +160,35 @@ class PhaseTimer:
 class MetaOffloader:
     """Moves finished quant_meta dicts to the host in the background (the reference does it inline, llama.py:173).
 
-    The device->host copy goes through two recycled pinned staging buffers on a side stream; a worker thread copies
-    staging -> pageable result tensors.  The main stream never waits for it; results() joins at the end."""
+    A few lanes work side by side; in each, the device->host copy goes through two recycled pinned staging buffers on
+    the lane's stream and the lane's thread copies staging -> pageable result tensors.  The main stream never waits for it; results() joins at the end."""
 
-    def __init__(self, device: torch.device, staging_bytes: int = 64 << 20):
+    def __init__(self, device: torch.device, staging_bytes: int = 64 << 20, workers: int = 3):
         self.device = device
-        self.pool = ThreadPoolExecutor(max_workers=1)
-        self.stream = torch.cuda.Stream(device=device)
+        self.workers = workers
+        # one single-thread executor per lane: a lane owns its stream and staging buffers, lanes run side by side
+        self.lanes = [ThreadPoolExecutor(max_workers=1) for _ in range(workers)]
+        self.streams = [torch.cuda.Stream(device=device) for _ in range(workers)]
         self.staging_bytes = staging_bytes
-        self._staging: list[torch.Tensor] = []
+        self._staging: list[list[torch.Tensor]] = [[] for _ in range(workers)]
         self._futures: dict[str, Future] = {}
+        self._next = 0
 
-    def _stage(self, nbytes: int, which: int) -> torch.Tensor:
-        while len(self._staging) < 2:
-            self._staging.append(torch.empty(self.staging_bytes, dtype=torch.uint8, pin_memory=True))
-        if nbytes > self._staging[which].numel():
-            self._staging[which] = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
-        return self._staging[which][:nbytes]
+    def _stage(self, lane: int, nbytes: int, which: int) -> torch.Tensor:
+        st = self._staging[lane]
+        while len(st) < 2:
+            st.append(torch.empty(self.staging_bytes, dtype=torch.uint8, pin_memory=True))
+        if nbytes > st[which].numel():
+            st[which] = torch.empty(nbytes, dtype=torch.uint8, pin_memory=True)
+        return st[which][:nbytes]
 
-    def _work(self, meta: dict, ready: torch.cuda.Event) -> dict:
+    def _work(self, lane: int, meta: dict, ready: torch.cuda.Event) -> dict:
         out = {}
-        with torch.cuda.device(self.device), torch.cuda.stream(self.stream):
-            self.stream.wait_event(ready)
+        stream = self.streams[lane]
+        with torch.cuda.device(self.device), torch.cuda.stream(stream):
+            stream.wait_event(ready)
             which = 0
-            pending = []                                            # (key, staging view, dtype, shape, event)
+            pending = []                                            # (key, staging view, dtype, shape, event, source)
             for k, v in meta.items():
                 if not torch.is_tensor(v) or v.device.type != 'cuda':
                     out[k] = v
@@ -191,10 +196,10 @@ class MetaOffloader:
                 src = v.contiguous()
                 if len(pending) == 2:                               # both staging buffers busy: drain the older one
                     self._drain(pending.pop(0), out)
-                st = self._stage(src.numel() * src.element_size(), which)
+                st = self._stage(lane, src.numel() * src.element_size(), which)
                 st.copy_(src.view(-1).view(torch.uint8), non_blocking=True)
                 ev = torch.cuda.Event()
-                ev.record(self.stream)
+                ev.record(stream)
                 pending.append((k, st, src.dtype, tuple(src.shape), ev, src))
                 which ^= 1
             for item in pending:
@@ -210,7 +215,9 @@ class MetaOffloader:
     def submit(self, name: str, meta: dict) -> None:
         ready = torch.cuda.Event()
         ready.record(torch.cuda.current_stream(self.device))
-        self._futures[name] = self.pool.submit(self._work, meta, ready)
+        lane = self._next
+        self._next = (self._next + 1) % self.workers
+        self._futures[name] = self.lanes[lane].submit(self._work, lane, meta, ready)
 
     def results(self) -> dict:
         out = {name: f.result() for name, f in self._futures.items()}
@@ -218,7 +225,8 @@ class MetaOffloader:
         return out
 
     def close(self) -> None:
-        self.pool.shutdown(wait=True)
+        for lane in self.lanes:
+            lane.shutdown(wait=True)
 
 
 def _batches(n: int, bs: int):
@@ -369,7 +377,9 @@ def quantize_llama(shape: LlamaShape, block_weights: Callable[[int], dict], inps
     n_blocks = shape.layers if n_blocks is None else n_blocks
     dev = inps.device
     save_device = block_kw.pop('save_device', torch.device('cpu'))
-    offloader = MetaOffloader(dev) if torch.device(save_device).type == 'cpu' else None
+    to_host = torch.device(save_device).type == 'cpu'
+    # the gathered quant_meta is identical on every rank: rank 0 keeps the host copy, the others drop it
+    offloader = MetaOffloader(dev) if to_host and rank == 0 else None
     torch.cuda.synchronize(dev)
     t_all = time.perf_counter()
     for i in range(n_blocks):
@@ -379,7 +389,7 @@ def quantize_llama(shape: LlamaShape, block_weights: Callable[[int], dict], inps
         inps, data, metrics = quantize_block(shape, w, inps, n_global, batch_size, timer, pgroup, save_device=dev, **block_kw)
         for name in LINEAR_NAMES:
             full = f'model.layers.{i}.{name}'
-            results['data'][full] = data[name]
+            results['data'][full] = data[name] if (rank == 0 or not to_host) else None
             results['metrics'][full] = metrics[name]
             if offloader is not None:
                 offloader.submit(full, data[name])            # host copy in the background (llama.py:173 does it inline)
