@@ -42,7 +42,7 @@ def bench_syrk():
 
 
 def _supers():
-    return tuple(int(v) for v in os.environ.get('GQ_SUPERS', '4').split(','))
+    return tuple(int(v) for v in os.environ.get('GQ_SUPERS', '8').split(','))
 
 
 def bench_invert():
