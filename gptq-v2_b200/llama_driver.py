@@ -439,3 +439,69 @@ def quantize_hf_llama(model, encodings: torch.Tensor, device: torch.device, batc
     inps = emb[encodings.to(device)]
     layers = model.model.layers
     return quantize_llama(shape, lambda i: hf_block_weights(layers[i], device), inps, batch_size=batch_size, **kw)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# Evaluation on the quantised model  (the reference's evaluate_llama, llama.py:207-247)
+
+def _linear(x: torch.Tensor, w) -> torch.Tensor:
+    """w: dense (R, C) weight or a module (W4A16Linear / nn.Linear)."""
+    return x @ w.t() if torch.is_tensor(w) else w(x)
+
+
+@torch.no_grad()
+def block_forward_any(shape: LlamaShape, weights: dict, x: torch.Tensor) -> torch.Tensor:
+    """block_forward with each linear either a dense weight or a module (e.g. quant.W4A16Linear on packed codes)."""
+    cos, sin = rope_tables(x.shape[1], shape.hidden // shape.heads, shape.rope_theta, x.device, x.dtype)
+    h = rms_norm(x, weights['input_layernorm'], shape.rms_eps)
+    a = attention(_linear(h, weights['self_attn.q_proj']), _linear(h, weights['self_attn.k_proj']),
+                  _linear(h, weights['self_attn.v_proj']), shape.heads, cos, sin)
+    x = x + _linear(a, weights['self_attn.o_proj'])
+    h = rms_norm(x, weights['post_attention_layernorm'], shape.rms_eps)
+    m = F.silu(_linear(h, weights['mlp.gate_proj'])) * _linear(h, weights['mlp.up_proj'])
+    return x + _linear(m, weights['mlp.down_proj'])
+
+
+@torch.no_grad()
+def evaluate_llama(shape: LlamaShape, block_weights: Callable[[int], dict], embed: torch.Tensor, final_norm: torch.Tensor,
+                   lm_head: torch.Tensor, encodings: torch.Tensor, batch_size: int = 1,
+                   n_blocks: Optional[int] = None) -> torch.Tensor:
+    """Layer-streamed perplexity as the reference computes it (llama.py:207-247): all sequences go through block i
+    before block i+1 is touched, then final norm, lm_head, and the mean over sequences of the per-batch mean token NLL,
+    exponentiated.  block_weights(i) may mix dense weights and W4A16Linear modules (checkpoint.quantized_linears), so
+    the quantised model is evaluated straight from its packed codes through K6."""
+    dev = embed.device
+    inps = embed[encodings.to(dev)]
+    n_blocks = shape.layers if n_blocks is None else n_blocks
+    for i in range(n_blocks):
+        w = block_weights(i)
+        for b in _batches(len(inps), batch_size):
+            inps[b] = block_forward_any(shape, w, inps[b])
+        del w
+    nlls = []
+    for b in _batches(len(inps), batch_size):
+        h = rms_norm(inps[b], final_norm, shape.rms_eps)
+        logits = h @ lm_head.t()
+        shift_logits = logits[:, :-1, :]
+        shift_labels = encodings[b, 1:].to(dev)
+        nll = F.cross_entropy(shift_logits.flatten(end_dim=-2).float(), shift_labels.flatten())
+        nlls.extend([nll] * logits.shape[0])
+    return torch.stack(nlls).to(torch.float32).mean().exp()
+
+
+def packed_block_weights(packed: dict, norms: Callable[[int], dict], device: torch.device, dtype: torch.dtype) -> Callable[[int], dict]:
+    """block_weights(i) for evaluate_llama from a packed model (checkpoint.pack_results / load_packed): the seven
+    linears of block i as W4A16Linear modules, the two norm weights from norms(i)."""
+    from quant import W4A16Linear
+
+    def get(i: int) -> dict:
+        out = dict(norms(i))
+        for name in LINEAR_NAMES:
+            layer = packed['layers'][f'model.layers.{i}.{name}']
+            out[name] = W4A16Linear({
+                'qweight_packed': layer['qweight_packed'].to(device),
+                'scale_t': layer['scale_t'].to(device=device, dtype=dtype), 'qzero_t': layer['qzero_t'].to(device),
+                'perm': layer['perm'].to(device) if layer.get('perm') is not None else None,
+                'group_size': int(layer['group_size'])})
+        return out
+    return get

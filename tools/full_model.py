@@ -31,6 +31,7 @@ def main():
     ap.add_argument('--batch', type=int, default=16)
     ap.add_argument('--model', default='7b')
     ap.add_argument('--pure', action='store_true', help='fp32 PyTorch-path semantics (gptq_use_kernel=False)')
+    ap.add_argument('--eval-seqs', type=int, default=0, help='after quantising: pack the result (checkpoint.py) and run the layer-streamed perplexity of N sequences through K6 and through dense reconstructed weights (rank 0, N=1 only)')
     ap.add_argument('--keep', default='cpu', help='where quant_meta ends up: cpu (as the reference) or cuda')
     args = ap.parse_args()
 
@@ -69,6 +70,41 @@ def main():
             'phases_rank0_s': {k: round(v, 3) for k, v in sorted(res['timing'].items())},
             'mean_rel_l2_error': sum(errs) / len(errs),
             'semantics': 'fp32-pure' if args.pure else 'kernel-compat', 'quant_meta_on': args.keep}), flush=True)
+    if args.eval_seqs > 0 and world == 1:
+        import time
+        import checkpoint
+        from quant import reconstruct_nn_linear
+        nb = len(res['block_seconds'])
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        packed = checkpoint.pack_results(res, dev)
+        torch.cuda.synchronize()
+        t_pack = time.perf_counter() - t0
+        g = torch.Generator(device=dev).manual_seed(77)
+        emb = (torch.randn(shape.vocab, shape.hidden, device=dev, generator=g) * 0.02).half()
+        head = (torch.randn(shape.vocab, shape.hidden, device=dev, generator=g) * 0.02).half()
+        fnorm = torch.ones(shape.hidden, device=dev, dtype=torch.float16)
+        tok = torch.randint(0, shape.vocab, (args.eval_seqs, args.seqlen), device=dev, generator=g).cpu()
+        ones = {'input_layernorm': fnorm, 'post_attention_layernorm': fnorm}
+
+        def dense_block(i):
+            out = dict(ones)
+            for n in L.LINEAR_NAMES:
+                out[n] = reconstruct_nn_linear(res['data'][f'model.layers.{i}.{n}'], torch.float16, dev).weight.data
+            return out
+        out = {}
+        for label, bw in (('packed_k6', L.packed_block_weights(packed, lambda i: ones, dev, torch.float16)), ('dense', dense_block)):
+            L.evaluate_llama(shape, bw, emb, fnorm, head, tok[:1], batch_size=1, n_blocks=1)      # warm-up
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            ppl = float(L.evaluate_llama(shape, bw, emb, fnorm, head, tok, batch_size=1, n_blocks=nb))
+            torch.cuda.synchronize()
+            dt = time.perf_counter() - t0
+            out[label] = {'ppl': ppl, 'seconds': round(dt, 3), 'tokens_per_s': round(args.eval_seqs * args.seqlen / dt, 1)}
+        raw = sum(v.numel() * v.element_size() for m in res['data'].values() for v in m.values() if torch.is_tensor(v))
+        print(json.dumps({'what': 'packed checkpoint + layer-streamed eval', 'blocks': nb, 'eval_seqs': args.eval_seqs,
+                          'pack_seconds': round(t_pack, 3), 'packed_bytes': checkpoint.packed_bytes(packed),
+                          'reference_format_bytes': raw, 'eval': out}), flush=True)
     if world > 1:
         dist.destroy_process_group()
 
