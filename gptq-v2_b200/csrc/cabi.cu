@@ -80,7 +80,15 @@ int gq_gptq_solve_static(float* Wt, const float* U, float* quant_t, int16_t* cod
 }
 
 int gq_prep_weight_t(const void* W, int dtype, const int64_t* perm, float* Wt, int R, int C, void* stream) {
-  return prep_weight_t(W, dtype, perm, Wt, R, C, S(stream));
+  return prep_weight_t(W, dtype, perm, Wt, nullptr, nullptr, R, C, S(stream));
+}
+int gq_prep_weight_t2(const void* W, int dtype, const int64_t* perm, float* Wt, void* orig_t, float* colsq, int R, int C,
+                      void* stream) {
+  return prep_weight_t(W, dtype, perm, Wt, orig_t, colsq, R, C, S(stream));
+}
+int gq_solve_metrics(const float* err_t, const float* quant_t, const void* orig_t, int dtype, size_t n, double* out2,
+                     void* stream) {
+  return solve_metrics(err_t, quant_t, orig_t, dtype, n, out2, S(stream));
 }
 
 int gq_pack_int4(const uint8_t* codes, uint32_t* packed, int R, int C, void* stream) {

@@ -95,6 +95,8 @@ int w4a16_smallm(const void* x, const uint32_t* qw, const void* scale_t, const u
                  void* y, void* workspace, int M, int N, int K, int group, int fmt, cudaStream_t st);
 int w4a16_gemm(const void* x, const uint32_t* qw, const void* scale_t, const uint8_t* qzero_t, const int32_t* perm,
                void* y, void* workspace, int M, int N, int K, int group, int fmt, cudaStream_t st);
-int prep_weight_t(const void* W, int fmt, const int64_t* perm, float* Wt, int R, int C, cudaStream_t st);
+int prep_weight_t(const void* W, int fmt, const int64_t* perm, float* Wt, void* orig_t, float* colsq, int R, int C,
+                  cudaStream_t st);
+int solve_metrics(const float* err_t, const float* quant_t, const void* orig_t, int fmt, size_t n, double* out2, cudaStream_t st);
 
 }  // namespace gq

@@ -22,14 +22,57 @@ template <> __device__ __forceinline__ float to_f32<__half>(__half v) { return _
 template <> __device__ __forceinline__ float to_f32<__nv_bfloat16>(__nv_bfloat16 v) { return __bfloat162float(v); }
 template <> __device__ __forceinline__ float to_f32<float>(float v) { return v; }
 
+// Wt[c][r] = (float) W[r][perm[c]];  optionally also the same element in W's own type (orig_t, kept for the error
+// metrics after the solver has consumed Wt) and colsq[c] += sum_r W[r][perm[c]]^2 (colsq zeroed by the caller).
 template <typename T>
 __global__ void prep_weight_t_kernel(const T* __restrict__ W, const int64_t* __restrict__ perm, float* __restrict__ Wt,
-                                     int R, int C) {
+                                     T* __restrict__ orig_t, float* __restrict__ colsq, int R, int C) {
   const int r = blockIdx.x * 32 + threadIdx.x;
   const int c = blockIdx.y * 8 + threadIdx.y;
-  if (r >= R || c >= C) return;
-  const int pc = perm ? (int)perm[c] : c;
-  Wt[(size_t)c * R + r] = to_f32<T>(W[(size_t)r * C + pc]);
+  float v = 0.f;
+  if (r < R && c < C) {
+    const int pc = perm ? (int)perm[c] : c;
+    const T w = W[(size_t)r * C + pc];
+    v = to_f32<T>(w);
+    Wt[(size_t)c * R + r] = v;
+    if (orig_t) orig_t[(size_t)c * R + r] = w;
+  }
+  if (colsq) {                                           // a warp = 32 rows of one column
+    float sq = v * v;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+    if (threadIdx.x == 0 && c < C) atomicAdd(colsq + c, sq);
+  }
+}
+
+// out[0] += sum err^2,  out[1] += sum (quant - orig)^2   over n elements of the (C, R) solver outputs
+template <typename T>
+__global__ void solve_metrics_kernel(const float* __restrict__ err_t, const float* __restrict__ quant_t,
+                                     const T* __restrict__ orig_t, size_t n, double* __restrict__ out) {
+  float e2 = 0.f, d2 = 0.f;
+  const size_t stride = (size_t)gridDim.x * blockDim.x * 4;
+  for (size_t i = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i < n; i += stride) {   // n % 4 == 0
+    const float4 e = *reinterpret_cast<const float4*>(err_t + i);
+    const float4 q = *reinterpret_cast<const float4*>(quant_t + i);
+    const float o0 = to_f32<T>(orig_t[i]), o1 = to_f32<T>(orig_t[i + 1]), o2 = to_f32<T>(orig_t[i + 2]), o3 = to_f32<T>(orig_t[i + 3]);
+    e2 += e.x * e.x + e.y * e.y + e.z * e.z + e.w * e.w;
+    const float a = q.x - o0, b = q.y - o1, c = q.z - o2, d = q.w - o3;
+    d2 += a * a + b * b + c * c + d * d;
+  }
+  __shared__ float se[32], sd[32];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) { e2 += __shfl_xor_sync(0xffffffffu, e2, o); d2 += __shfl_xor_sync(0xffffffffu, d2, o); }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) { se[warp] = e2; sd[warp] = d2; }
+  __syncthreads();
+  if (warp == 0) {
+    const int nw = blockDim.x >> 5;
+    e2 = lane < nw ? se[lane] : 0.f;
+    d2 = lane < nw ? sd[lane] : 0.f;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) { e2 += __shfl_xor_sync(0xffffffffu, e2, o); d2 += __shfl_xor_sync(0xffffffffu, d2, o); }
+    if (lane == 0) { atomicAdd(out, (double)e2); atomicAdd(out + 1, (double)d2); }
+  }
 }
 
 // ------------------------------------------------------------------ pack / unpack
@@ -87,12 +130,29 @@ __global__ void transpose_pack_kernel(const uint8_t* __restrict__ codes_t, uint8
 
 }  // namespace
 
-int prep_weight_t(const void* W, int fmt, const int64_t* perm, float* Wt, int R, int C, cudaStream_t st) {
+int prep_weight_t(const void* W, int fmt, const int64_t* perm, float* Wt, void* orig_t, float* colsq, int R, int C,
+                  cudaStream_t st) {
   dim3 block(32, 8), grid((R + 31) / 32, (C + 7) / 8);
+  if (colsq && cudaMemsetAsync(colsq, 0, (size_t)C * sizeof(float), st) != cudaSuccess) return GQ_ERR_CUDA;
   GQ_LAUNCHED();
-  if (fmt == 0) prep_weight_t_kernel<__half><<<grid, block, 0, st>>>((const __half*)W, perm, Wt, R, C);
-  else if (fmt == 1) prep_weight_t_kernel<__nv_bfloat16><<<grid, block, 0, st>>>((const __nv_bfloat16*)W, perm, Wt, R, C);
-  else if (fmt == 2) prep_weight_t_kernel<float><<<grid, block, 0, st>>>((const float*)W, perm, Wt, R, C);
+  if (fmt == 0) prep_weight_t_kernel<__half><<<grid, block, 0, st>>>((const __half*)W, perm, Wt, (__half*)orig_t, colsq, R, C);
+  else if (fmt == 1) prep_weight_t_kernel<__nv_bfloat16><<<grid, block, 0, st>>>((const __nv_bfloat16*)W, perm, Wt, (__nv_bfloat16*)orig_t, colsq, R, C);
+  else if (fmt == 2) prep_weight_t_kernel<float><<<grid, block, 0, st>>>((const float*)W, perm, Wt, (float*)orig_t, colsq, R, C);
+  else return GQ_ERR_DTYPE;
+  return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
+}
+
+int solve_metrics(const float* err_t, const float* quant_t, const void* orig_t, int fmt, size_t n, double* out2, cudaStream_t st) {
+  if (n % 4 != 0) return GQ_ERR_SHAPE;
+  if (cudaMemsetAsync(out2, 0, 2 * sizeof(double), st) != cudaSuccess) return GQ_ERR_CUDA;
+  if (n == 0) return GQ_OK;
+  const int threads = 256;
+  size_t blocks = (n / 4 + threads - 1) / threads;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  GQ_LAUNCHED();
+  if (fmt == 0) solve_metrics_kernel<__half><<<(unsigned)blocks, threads, 0, st>>>(err_t, quant_t, (const __half*)orig_t, n, out2);
+  else if (fmt == 1) solve_metrics_kernel<__nv_bfloat16><<<(unsigned)blocks, threads, 0, st>>>(err_t, quant_t, (const __nv_bfloat16*)orig_t, n, out2);
+  else if (fmt == 2) solve_metrics_kernel<float><<<(unsigned)blocks, threads, 0, st>>>(err_t, quant_t, (const float*)orig_t, n, out2);
   else return GQ_ERR_DTYPE;
   return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
 }

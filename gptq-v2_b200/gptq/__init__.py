@@ -14,7 +14,7 @@ import torch
 from . import _cabi
 from ._cabi import GptqB200Error, check, lib, ptr, require_contig, require_cuda, stream_of
 
-__all__ = ['accumulate_hessian', 'gptq_quantize_range', 'hessian_syrk', 'hessian_invert', 'prep_weight_t',
+__all__ = ['accumulate_hessian', 'gptq_quantize_range', 'hessian_syrk', 'hessian_invert', 'prep_weight_t', 'prep_weight_t2', 'solve_metrics',
            'gptq_solve', 'gptq_solve_static', 'pack_int4', 'unpack_int4', 'transpose_pack_int4', 'w4a16_gemm', 'sgemm', 'gemm_tf32x3', 'set_tf32x3', 'set_solve_super',
            'GptqB200Error']
 
@@ -101,6 +101,33 @@ def prep_weight_t(W: torch.Tensor, perm) -> torch.Tensor:
         check(lib.gq_prep_weight_t(ptr(W), _cabi.DTYPE_CODE[W.dtype], ptr(perm), ptr(Wt), R, C_, stream_of(W)),
               'gq_prep_weight_t')
     return Wt
+
+
+def prep_weight_t2(W: torch.Tensor, perm):
+    """prep_weight_t plus what the result metrics need later: orig_t (C, R) in W's dtype (the same elements, kept because
+    the solver consumes Wt) and colsq (C) fp32 = sum_r W[r, perm[c]]^2.  Returns Wt, orig_t, colsq."""
+    dev = require_cuda(W, perm)
+    require_contig(W=W, perm=perm)
+    R, C_ = W.shape
+    Wt = torch.empty(C_, R, dtype=torch.float32, device=dev)
+    orig_t = torch.empty(C_, R, dtype=W.dtype, device=dev)
+    colsq = torch.empty(C_, dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.gq_prep_weight_t2(ptr(W), _cabi.DTYPE_CODE[W.dtype], ptr(perm), ptr(Wt), ptr(orig_t), ptr(colsq), R, C_,
+                                    stream_of(W)), 'gq_prep_weight_t2')
+    return Wt, orig_t, colsq
+
+
+def solve_metrics(err_t: torch.Tensor, quant_t: torch.Tensor, orig_t: torch.Tensor) -> torch.Tensor:
+    """-> float64 tensor [sum err_t^2, sum (quant_t - orig_t)^2] on the device (one pass over the three arrays)."""
+    dev = require_cuda(err_t, quant_t, orig_t)
+    require_contig(err_t=err_t, quant_t=quant_t, orig_t=orig_t)
+    assert err_t.shape == quant_t.shape == orig_t.shape and err_t.dtype == quant_t.dtype == torch.float32
+    out = torch.empty(2, dtype=torch.float64, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.gq_solve_metrics(ptr(err_t), ptr(quant_t), ptr(orig_t), _cabi.DTYPE_CODE[orig_t.dtype], err_t.numel(),
+                                   ptr(out), stream_of(err_t)), 'gq_solve_metrics')
+    return out
 
 
 def gptq_solve(Wt: torch.Tensor, U: torch.Tensor, group: int, maxq: float, want_quant: bool = True):

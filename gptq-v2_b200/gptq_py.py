@@ -130,7 +130,8 @@ def gptq_quant(
     else:
         U = hessian_hook.hessian_inv.contiguous()
 
-    Wt = _ops.prep_weight_t(weight_c, perm)                                    # (C, R) fp32, permuted (ref :90-94,128)
+    # (C, R) fp32, permuted (ref :90-94,128); orig_t / colsq feed the result metrics after the solver has consumed Wt
+    Wt, orig_t, colsq = _ops.prep_weight_t2(weight_c, perm)
     if gptq_use_kernel and hessian_hook is not None:
         # static parameters from the original permuted weights (ref :131-134, quant.py:114-118)
         w3 = Wt.view(n_groups, gs, n_rows)
@@ -152,12 +153,24 @@ def gptq_quant(
     else:
         quant_t, codes_t, err_t, scale_gr, qzero_gr = _ops.gptq_solve(Wt, U, gs, maxq)
 
-    if hessian_hook is None:
-        gptq_error = 0.0
-        gptq_norm = 0.0                                                         # ref :198 (error == 0)
+    # ---- metrics (ref :196-199, :231-237) in one pass over the solver outputs and ONE host sync:
+    #   gptq_error = mean(err^2);  gptq_norm = mean((W / diag(U))^2) with W unpermuted against the permuted-order diag(U),
+    #   reproduced as is (ref :198) = sum_c colsq_orig[c] / diag(U)[c]^2 / (R C);  l2.0_error = mean((quant - W)^2), which
+    #   does not depend on the column order;  l2.0_norm in the weight dtype like the reference.
+    sums = _ops.solve_metrics(err_t, quant_t, orig_t)                            # float64 [sum err^2, sum (quant - W)^2]
+    if perm is not None:
+        colsq_orig = torch.empty_like(colsq)
+        colsq_orig[perm] = colsq
     else:
-        gptq_error = (err_t ** 2.).mean().item()
-        gptq_norm = ((weight / U.diag()) ** 2.).mean().item()                   # ref :198, reproduced as is
+        colsq_orig = colsq
+    norm_sum = (colsq_orig.double() / U.diagonal().double() ** 2).sum()
+    l2_norm = (weight.abs() ** 2.).mean()                                        # ref :237 (fp16 / bf16 arithmetic)
+    n_el = float(n_rows * n_columns)
+    e2, d2, ns, l2n = torch.stack([sums[0], sums[1], norm_sum, l2_norm.double()]).tolist()
+    if hessian_hook is None:
+        gptq_error, gptq_norm = 0.0, 0.0                                         # ref :198 (error == 0)
+    else:
+        gptq_error, gptq_norm = e2 / n_el, ns / n_el
     metrics: dict[str, float] = {'gptq_error': gptq_error, 'gptq_norm': gptq_norm}
 
     qweight, _ = _ops.transpose_pack_int4(codes_t, want_codes=True, want_packed=False)   # (R, C) uint8, permuted order
@@ -169,9 +182,7 @@ def gptq_quant(
         perm16 = torch.arange(n_columns, dtype=torch.int16, device=device)
     perm_inv = perm16.argsort().to(dtype=torch.int16)                           # ref :226
 
-    quant = quant_t.t()[:, perm_inv.to(dtype=torch.int32)]                      # ref :231
-    diff = ((quant - weight.to(dtype=torch.float32)).abs() ** 2.).mean()
-    metrics.update({'l2.0_error': diff.item(), 'l2.0_norm': (weight.abs() ** 2.).mean().item()})
+    metrics.update({'l2.0_error': d2 / n_el, 'l2.0_norm': l2n})
 
     quant_meta: dict[str, torch.Tensor] = {
         'qweight': qweight.to(device=save_device),

@@ -81,6 +81,14 @@ int gq_gptq_solve_static(float* Wt, const float* U, float* quant_t, int16_t* cod
                          const float* qzero_gr, int R, int C, int group, float maxq, void* stream);
 /* Wt[c][r] = (float) W[r][perm[c]]; W (R, C) of dtype GQ_DTYPE_*; perm may be NULL. */
 int gq_prep_weight_t(const void* W, int dtype, const int64_t* perm, float* Wt, int R, int C, void* stream);
+/* Same, plus (each may be NULL) orig_t (C, R): the same elements in W's own dtype, kept for the error metrics after the
+ * solver has consumed Wt; colsq (C) fp32: sum_r W[r][perm[c]]^2 (for gptq_norm, gptq_py.py:198). */
+int gq_prep_weight_t2(const void* W, int dtype, const int64_t* perm, float* Wt, void* orig_t, float* colsq, int R, int C,
+                      void* stream);
+/* Result metrics of one linear in one pass (gptq_py.py:196, 232-233): out2[0] = sum err_t^2, out2[1] = sum (quant_t -
+ * orig_t)^2 over n = R*C elements (n % 4 == 0); out2 is two doubles on the device, overwritten. */
+int gq_solve_metrics(const float* err_t, const float* quant_t, const void* orig_t, int dtype, size_t n, double* out2,
+                     void* stream);
 
 /* ---- K5: int4 storage (new in this build; the reference stores one code per byte, gptq_py.py:217).
  * packed (R, C/8) uint32, column 8k+i in bits [4i, 4i+4) of word k.  C % 8 == 0. */
