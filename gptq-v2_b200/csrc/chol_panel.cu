@@ -12,10 +12,12 @@
 //
 // In-CTA algorithm, 16-column sub-blocks (8 per block), 256 threads:
 //   A  warp 0 factors the 16 x 16 diagonal sub-block on registers: lane k owns column k, every lane
-//      tracks a private copy of the diagonal, so a step costs one shuffle + rsqrt (Newton-refined):
-//      ~70 cycles per column instead of a block-wide barrier per column.
+//      tracks a private copy of the diagonal, so a step costs one shuffle + rsqrt (Newton-refined)
+//      instead of a block-wide barrier per column (~180 clk per column, issue-bound on one warp).
 //   B  one thread per remaining column: 16-row forward substitution on registers.
-//   C  all warps: rank-16 update of the remaining rows (4-row groups per warp, lanes along columns).
+//   C  rank-16 update of the remaining rows (4-row groups per warp, lanes along columns), with
+//      look-ahead: warps 0-3 update the next sub-block's 16 rows first, then warp 0 runs A of the
+//      next sub-block while the other warps finish the update.
 // fp32 FMA throughout (the reference runs LAPACK potrf in fp32; TF32 is off, main.py:12-13).
 #include "gptq_b200_internal.h"
 
@@ -44,58 +46,101 @@ chol_panel_kernel(float* __restrict__ A, int D, int o, int n, int rest, int* __r
   const int pc0 = blockIdx.x * PC;           // first panel column of this CTA (relative to o + n)
   const int pcn = max(0, min(PC, rest - pc0));
 
-  // ---- stage [A_kk (upper) | panel columns]; a partial block is padded with the identity
-  for (int idx = tid; idx < NB * (NB / 4); idx += 256) {
-    const int r = idx / (NB / 4), c4 = (idx - r * (NB / 4)) * 4;
-    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (r < n && c4 < n) v = *reinterpret_cast<const float4*>(A + (size_t)(o + r) * D + o + c4);   // n % 4 == 0
-    if (r >= n) { v.x = (c4 == r) ? 1.f : 0.f; v.y = (c4 + 1 == r) ? 1.f : 0.f; v.z = (c4 + 2 == r) ? 1.f : 0.f; v.w = (c4 + 3 == r) ? 1.f : 0.f; }
-    *reinterpret_cast<float4*>(S + r * W + c4) = v;
-  }
-  if constexpr (PC > 0) {
-    for (int idx = tid; idx < NB * (PC / 4); idx += 256) {
-      const int r = idx / (PC / 4), c4 = (idx - r * (PC / 4)) * 4;
-      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (r < n && c4 < pcn) v = *reinterpret_cast<const float4*>(A + (size_t)(o + r) * D + o + n + pc0 + c4);   // rest % 4 == 0
-      *reinterpret_cast<float4*>(S + r * W + NB + c4) = v;
+  // ---- stage [A_kk (upper) | panel columns]; a partial block is padded with the identity.  All of a thread's loads
+  // are issued before its first store: one global round trip for the whole block row instead of one per float4.
+  {
+    constexpr int ND = NB * (NB / 4) / 256;          // float4 per thread, diagonal block (16)
+    float4 v[ND];
+#pragma unroll
+    for (int k = 0; k < ND; ++k) {
+      const int idx = tid + k * 256;
+      const int r = idx / (NB / 4), c4 = (idx - r * (NB / 4)) * 4;
+      v[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (r < n && c4 < n) v[k] = *reinterpret_cast<const float4*>(A + (size_t)(o + r) * D + o + c4);   // n % 4 == 0
+      if (r >= n) { v[k].x = (c4 == r) ? 1.f : 0.f; v[k].y = (c4 + 1 == r) ? 1.f : 0.f; v[k].z = (c4 + 2 == r) ? 1.f : 0.f; v[k].w = (c4 + 3 == r) ? 1.f : 0.f; }
+    }
+    if constexpr (PC > 0) {
+      constexpr int NP = NB * (PC / 4) / 256;        // float4 per thread, panel (8 for PC = 64)
+      float4 pv[NP];
+#pragma unroll
+      for (int k = 0; k < NP; ++k) {
+        const int idx = tid + k * 256;
+        const int r = idx / (PC / 4), c4 = (idx - r * (PC / 4)) * 4;
+        pv[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (r < n && c4 < pcn) pv[k] = *reinterpret_cast<const float4*>(A + (size_t)(o + r) * D + o + n + pc0 + c4);   // rest % 4 == 0
+      }
+#pragma unroll
+      for (int k = 0; k < NP; ++k) {
+        const int idx = tid + k * 256;
+        const int r = idx / (PC / 4), c4 = (idx - r * (PC / 4)) * 4;
+        *reinterpret_cast<float4*>(S + r * W + NB + c4) = pv[k];
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < ND; ++k) {
+      const int idx = tid + k * 256;
+      const int r = idx / (NB / 4), c4 = (idx - r * (NB / 4)) * 4;
+      *reinterpret_cast<float4*>(S + r * W + c4) = v[k];
     }
   }
   __syncthreads();
 
   bool bad = false;
+  // ---- A: 16 x 16 diagonal sub-block at (so, so), warp 0 only
+  auto factor_sub = [&](int so) {
+    const int k = lane & 15;
+    float a[SBK], dg[SBK];
+#pragma unroll
+    for (int i = 0; i < SBK; ++i) {
+      a[i] = S[(so + i) * W + so + k];
+      dg[i] = S[(so + i) * W + so + i];
+    }
+#pragma unroll
+    for (int j = 0; j < SBK; ++j) {
+      const float p = dg[j];
+      if (!(p > 0.f)) bad = true;                          // also catches NaN
+      const float ri = rsqrt_nr(p);
+      float d = p * ri;
+      d = fmaf(fmaf(-d, d, p), 0.5f * ri, d);              // sqrt(p) refined
+      const float r = (k > j) ? a[j] * ri : (k == j ? d : 0.f);
+      if (lane < 16) {
+        S[(so + j) * W + so + k] = r;
+        if (k == j) rinv[so + j] = ri;
+      }
+#pragma unroll
+      for (int i = j + 1; i < SBK; ++i) {
+        const float rji = __shfl_sync(0xffffffffu, r, i);  // R[j][i]
+        a[i] = fmaf(-rji, r, a[i]);
+        dg[i] = fmaf(-rji, rji, dg[i]);
+      }
+    }
+  };
+  // ---- C: rank-16 update of the 4 rows of group g behind sub-block so:  S[i][c] -= sum_j X[j][i] X[j][c]  (c >= i needed)
+  auto update_group = [&](int so, int g) {
+    const int i0 = so + SBK + 4 * g;
+    float4 xi[SBK];
+#pragma unroll
+    for (int j = 0; j < SBK; ++j) xi[j] = *reinterpret_cast<const float4*>(S + (so + j) * W + i0);
+#pragma unroll 1
+    for (int c = (i0 & ~31) + lane; c < W; c += 32) {
+      float a0 = S[(i0 + 0) * W + c], a1 = S[(i0 + 1) * W + c];
+      float a2 = S[(i0 + 2) * W + c], a3 = S[(i0 + 3) * W + c];
+#pragma unroll
+      for (int j = 0; j < SBK; ++j) {
+        const float xc = S[(so + j) * W + c];
+        a0 = fmaf(-xi[j].x, xc, a0); a1 = fmaf(-xi[j].y, xc, a1);
+        a2 = fmaf(-xi[j].z, xc, a2); a3 = fmaf(-xi[j].w, xc, a3);
+      }
+      S[(i0 + 0) * W + c] = a0; S[(i0 + 1) * W + c] = a1;
+      S[(i0 + 2) * W + c] = a2; S[(i0 + 3) * W + c] = a3;
+    }
+  };
+
+  if (warp == 0) factor_sub(0);
+  __syncthreads();
 #pragma unroll 1
   for (int s = 0; s < NB / SBK; ++s) {
     const int so = s * SBK;
-    // ---- A: 16 x 16 diagonal sub-block on warp 0
-    if (warp == 0) {
-      const int k = lane & 15;
-      float a[SBK], dg[SBK];
-#pragma unroll
-      for (int i = 0; i < SBK; ++i) {
-        a[i] = S[(so + i) * W + so + k];
-        dg[i] = S[(so + i) * W + so + i];
-      }
-#pragma unroll
-      for (int j = 0; j < SBK; ++j) {
-        const float p = dg[j];
-        if (!(p > 0.f)) bad = true;                          // also catches NaN
-        const float ri = rsqrt_nr(p);
-        float d = p * ri;
-        d = fmaf(fmaf(-d, d, p), 0.5f * ri, d);              // sqrt(p) refined
-        const float r = (k > j) ? a[j] * ri : (k == j ? d : 0.f);
-        if (lane < 16) {
-          S[(so + j) * W + so + k] = r;
-          if (k == j) rinv[so + j] = ri;
-        }
-#pragma unroll
-        for (int i = j + 1; i < SBK; ++i) {
-          const float rji = __shfl_sync(0xffffffffu, r, i);  // R[j][i]
-          a[i] = fmaf(-rji, r, a[i]);
-          dg[i] = fmaf(-rji, rji, dg[i]);
-        }
-      }
-    }
-    __syncthreads();
     // ---- B: rows so..so+15 of every later column: forward substitution, one thread per column
     {
       const int c = so + SBK + tid;
@@ -114,30 +159,19 @@ chol_panel_kernel(float* __restrict__ A, int D, int o, int n, int rest, int* __r
       }
     }
     __syncthreads();
-    // ---- C: rank-16 update of rows so+16.. : S[i][c] -= sum_j X[j][i] X[j][c]   (c >= i needed)
-    {
-      const int r0 = so + SBK;
-      const int groups = (NB - r0) / 4;
+    if (s == NB / SBK - 1) break;
+    // ---- C with look-ahead: warps 0-3 first bring the NEXT sub-block's 16 rows up to date (one 4-row group each),
+    // then warp 0 factors the next diagonal sub-block while the other seven warps update the remaining rows
+    const int groups = (NB - so - SBK) / 4;
+    if (warp < 4) {
+      update_group(so, warp);
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+    }
+    if (warp == 0) {
+      factor_sub(so + SBK);
+    } else {
 #pragma unroll 1
-      for (int g = warp; g < groups; g += 8) {
-        const int i0 = r0 + 4 * g;
-        float4 xi[SBK];
-#pragma unroll
-        for (int j = 0; j < SBK; ++j) xi[j] = *reinterpret_cast<const float4*>(S + (so + j) * W + i0);
-#pragma unroll 1
-        for (int c = (i0 & ~31) + lane; c < W; c += 32) {
-          float a0 = S[(i0 + 0) * W + c], a1 = S[(i0 + 1) * W + c];
-          float a2 = S[(i0 + 2) * W + c], a3 = S[(i0 + 3) * W + c];
-#pragma unroll
-          for (int j = 0; j < SBK; ++j) {
-            const float xc = S[(so + j) * W + c];
-            a0 = fmaf(-xi[j].x, xc, a0); a1 = fmaf(-xi[j].y, xc, a1);
-            a2 = fmaf(-xi[j].z, xc, a2); a3 = fmaf(-xi[j].w, xc, a3);
-          }
-          S[(i0 + 0) * W + c] = a0; S[(i0 + 1) * W + c] = a1;
-          S[(i0 + 2) * W + c] = a2; S[(i0 + 3) * W + c] = a3;
-        }
-      }
+      for (int g = 4 + (warp - 1); g < groups; g += 7) update_group(so, g);
     }
     __syncthreads();
   }
