@@ -346,10 +346,11 @@ def gpu_main(args):
         pass
     peak_tf = peaks.get('bf16_tflops_sustained', 1400.0)
     achieved = syrk_f / syrk_s / 1e12
-    # dram__bytes_read.sum + dram__bytes_write.sum per SYRK launch from the committed `ncu --set full` capture
-    # (profiles/r01_v3_ncu_full_summary.txt), weighted over the launches of one layer; tensor-bound kernel, so the
-    # re-reads of X column panels (L2 misses at D = 11008) cost bandwidth headroom, not time.
-    ncu_dram = {4096: 509.3e6, 11008: 12.853e9}
+    # dram__bytes_read.sum + dram__bytes_write.sum per SYRK launch from the committed `ncu --set full` captures
+    # (profiles/r01_v3_ncu_full_summary.txt for D = 4096, r01_v13_ncu_syrk_11008_summary.txt for D = 11008 with the
+    # blocked tile walk: 12.85 -> 6.0 GB), weighted over the launches of one layer; the kernel is tensor-bound (pipe
+    # 97 % active), the remaining re-reads of X panels cost bandwidth headroom, not time.
+    ncu_dram = {4096: 509.3e6, 11008: 6.04e9}
     traffic = None
     if ctx.world == 1 and all(D in ncu_dram for _, _, D in timers['syrk']):
         traffic = sum(ncu_dram[D] for _, _, D in timers['syrk']) / len(timers['syrk'])
@@ -370,7 +371,7 @@ def gpu_main(args):
                      'achieved': achieved, 'peak': peak_tf, 'unit': 'TFLOP/s', 'frac': achieved / peak_tf,
                      'peak_source': 'MEASURED_PEAKS.json bf16_tflops_sustained' if peaks else 'fallback 1.4 PF',
                      'flops_per_launch': syrk_f / n_syrk, 'launch_s': syrk_s / n_syrk, 'traffic': traffic,
-                     'traffic_source': 'ncu --set full, profiles/r01_v3_ncu_full_summary.txt (weighted per launch)',
+                     'traffic_source': 'ncu --set full, profiles/r01_v3_ncu_full_summary.txt + r01_v13_ncu_syrk_11008_summary.txt (weighted per launch)',
                      'gemm_equivalent_tflops': 2 * achieved},
         'detail': {'syrk_s_per_layer': syrk_s / args.steps,
                    'syrk_s_by_D': {str(D): statistics.mean(v) for D, v in per_d.items()},
