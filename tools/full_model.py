@@ -30,6 +30,7 @@ def main():
     ap.add_argument('--seqlen', type=int, default=2048)
     ap.add_argument('--batch', type=int, default=16)
     ap.add_argument('--model', default='7b')
+    ap.add_argument('--bits', type=int, default=4)
     ap.add_argument('--pure', action='store_true', help='fp32 PyTorch-path semantics (gptq_use_kernel=False)')
     ap.add_argument('--eval-seqs', type=int, default=0, help='after quantising: pack the result (checkpoint.py) and run the layer-streamed perplexity of N sequences through K6 and through dense reconstructed weights (rank 0, N=1 only)')
     ap.add_argument('--keep', default='cpu', help='where quant_meta ends up: cpu (as the reference) or cuda')
@@ -53,7 +54,7 @@ def main():
     if world > 1:
         dist.barrier()
     res = L.quantize_llama(shape, lambda i: L.random_block_weights(shape, i, dev), inps, n_global=args.n_seq,
-                           batch_size=args.batch, n_blocks=args.blocks, use_kernel_semantics=not args.pure,
+                           batch_size=args.batch, n_blocks=args.blocks, use_kernel_semantics=not args.pure, bits=args.bits,
                            save_device=torch.device(args.keep if args.keep == 'cpu' else dev),
                            log=(lambda s: print(s, file=sys.stderr, flush=True)))
     secs = torch.tensor([res['seconds']], dtype=torch.float64, device=dev)
@@ -69,7 +70,7 @@ def main():
             'extrapolated_full_model_s': round(float(secs.item()) / nb * shape.layers, 2),
             'phases_rank0_s': {k: round(v, 3) for k, v in sorted(res['timing'].items())},
             'mean_rel_l2_error': sum(errs) / len(errs),
-            'semantics': 'fp32-pure' if args.pure else 'kernel-compat', 'quant_meta_on': args.keep}), flush=True)
+            'bits': args.bits, 'semantics': 'fp32-pure' if args.pure else 'kernel-compat', 'quant_meta_on': args.keep}), flush=True)
     if args.eval_seqs > 0 and world == 1:
         import time
         import checkpoint

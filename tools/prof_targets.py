@@ -9,7 +9,8 @@ import gptq
 dev = torch.device('cuda')
 which = sys.argv[1]
 if which == 'tf32':
-    M, N, K = 3968, 4096, 128
+    # default: one K4 near update; `tf32 9984 4096 1024` = the far update behind a super-block of 8 blocks (down_proj)
+    M, N, K = (int(v) for v in sys.argv[2:5]) if len(sys.argv) >= 5 else (3968, 4096, 128)
     A = torch.randn(K, M, device=dev); B = torch.randn(K, N, device=dev); C = torch.zeros(M, N, device=dev)
     for _ in range(3):
         gptq.gemm_tf32x3(A, B, C, M, N, K, M, N, N, -1.0, False)
