@@ -23,7 +23,9 @@ def _relfro(a, b):
 
 
 @pytest.mark.parametrize('variant', [1, 2])
-@pytest.mark.parametrize('D,T', [(256, 64), (256, 200), (512, 1024), (64, 1), (320, 100), (1024, 4096), (4096, 2048)])
+# (6400, 192) and (11008, 128): 25 / 43 super-tiles per side, the blocked (8 x 8) tile walk of decode_tile
+@pytest.mark.parametrize('D,T', [(256, 64), (256, 200), (512, 1024), (64, 1), (320, 100), (1024, 4096), (4096, 2048),
+                                 (6400, 192), (11008, 128)])
 @pytest.mark.parametrize('dtype', [torch.float16, torch.bfloat16])
 def test_syrk_matches_fp32(variant, D, T, dtype):
     import gptq
