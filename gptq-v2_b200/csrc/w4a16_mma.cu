@@ -32,19 +32,29 @@ namespace {
 constexpr int WM_TILE_N = 128;            // weight rows per unit (UMMA M)
 constexpr int WM_KSTAGE = 256;            // k per TMA box of packed weights (128 B per row)
 constexpr int WM_KHALF = 128;             // k per dequant / MMA step (one A tile: 2 swizzle atoms of 64)
-constexpr int WM_PS = 8;                  // packed-weight ring stages (16 KB each)
 constexpr int WM_AS = 4;                  // dequantised A tiles in tensor memory (64 columns each)
-constexpr int WM_XS = 4;                  // activation tile ring (MPAD * 256 B each)
-constexpr int WM_MPAD_MAX = 64;           // batch columns per pass (UMMA N)
 constexpr int WM_PK_BYTES = WM_TILE_N * 128;
 constexpr int WM_A_COLS = WM_KHALF / 2;   // 32-bit TMEM columns of one A tile (two 16-bit values per column)
-constexpr int WM_X_BYTES_MAX = WM_MPAD_MAX * WM_KHALF * 2;
-constexpr int WM_SMEM = WM_PS * WM_PK_BYTES + WM_XS * WM_X_BYTES_MAX + 1024 + 512;
 constexpr int WM_DQ_WARPS = 16;
 // 24 warps: 0 weight TMA, 1 MMA, 2 TMEM alloc, 3 activation TMA, 4-19 dequant, 20-23 epilogue
 constexpr int WM_THREADS = (4 + WM_DQ_WARPS + 4) * 32;
-constexpr int WM_TMEM_D = 0;              // accumulators: 2 x WM_MPAD_MAX columns
-constexpr int WM_TMEM_A = 2 * WM_MPAD_MAX;   // A tiles: WM_AS x WM_A_COLS columns
+
+// Two shapes of the same kernel.  A tcgen05.mma with M = 128, K = 16 holds the tensor core for ~172 clk whatever its N
+// (tools/micro/umma_small_n.cu), and every pass over the batch dequantises the weights again, so large batches want the
+// widest N: BIG runs 256 batch columns per pass (one fp32 accumulator of 256 TMEM columns + 4 A tiles = all 512
+// columns; 2 x 64 KB activation stages), the small shape keeps 64 columns with two accumulators and deeper rings.
+template <bool BIG> struct WmCfg {
+  static constexpr int PS = BIG ? 4 : 8;                // packed-weight ring stages (16 KB each)
+  static constexpr int XS = BIG ? 2 : 4;                // activation tile ring (MPAD * 256 B each)
+  static constexpr int MPAD_MAX = BIG ? 256 : 64;       // batch columns per pass (UMMA N)
+  static constexpr int NACC = BIG ? 1 : 2;              // fp32 accumulators in tensor memory
+  static constexpr int X_BYTES_MAX = MPAD_MAX * WM_KHALF * 2;
+  static constexpr int SMEM = PS * WM_PK_BYTES + XS * X_BYTES_MAX + 1024 + 512;
+  static constexpr int TMEM_D = 0;                      // accumulators: NACC x MPAD_MAX columns
+  static constexpr int TMEM_A = NACC * MPAD_MAX;        // A tiles: WM_AS x WM_A_COLS columns
+  static_assert(TMEM_A + WM_AS * WM_A_COLS <= 512, "tensor memory");
+  static_assert(SMEM <= 227 * 1024, "shared memory");
+};
 
 struct W4Params {
   const void* scale;        // (G, N) 16-bit, group-major: the 128 rows of a tile are one contiguous 256-byte line
@@ -53,7 +63,7 @@ struct W4Params {
   float* yacc;              // (M, N) fp32 zero-initialised accumulator for split units
   int M, N, K, G, group;
   int m_base;               // first batch row of this pass
-  int mpad;                 // UMMA N: 16, 32, 48 or 64
+  int mpad;                 // UMMA N: a multiple of 16, <= 64 (small shape) or <= 256 (BIG)
   int k_chunk;              // k per unit (multiple of 256)
   int n_tiles, k_chunks;
   int split;                // 1: atomics into yacc, 0: direct store
@@ -148,9 +158,12 @@ template <> struct Dq<__nv_bfloat16> {
     return o;
   }
 };
-template <typename XT>
+template <typename XT, bool BIG>
 __global__ void __launch_bounds__(WM_THREADS, 1)
 w4a16_mma_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant__ CUtensorMap map_x, const W4Params p) {
+  using Cfg = WmCfg<BIG>;
+  constexpr int WM_PS = Cfg::PS, WM_XS = Cfg::XS, WM_MPAD_MAX = Cfg::MPAD_MAX, WM_X_BYTES_MAX = Cfg::X_BYTES_MAX;
+  constexpr int WM_TMEM_D = Cfg::TMEM_D, WM_TMEM_A = Cfg::TMEM_A, NACC = Cfg::NACC;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
@@ -185,7 +198,7 @@ w4a16_mma_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     for (int s = 0; s < WM_PS; ++s) { mbar_init(pk_full(s), 1); mbar_init(pk_empty(s), WM_DQ_WARPS); }
     for (int s = 0; s < WM_AS; ++s) { mbar_init(a_full(s), WM_DQ_WARPS); mbar_init(a_empty(s), 1); }
     for (int s = 0; s < WM_XS; ++s) { mbar_init(x_full(s), 1); mbar_init(x_empty(s), 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(tfull(s), 1); mbar_init(tempty(s), 4); }
+    for (int s = 0; s < NACC; ++s) { mbar_init(tfull(s), 1); mbar_init(tempty(s), 4); }
     fence_mbar_init();
   }
   if (warp == 2) { tmem_alloc<1>(tmem_slot, 512); tmem_relinquish<1>(); }
@@ -236,8 +249,8 @@ w4a16_mma_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
       for (int u = blockIdx.x; u < units; u += gridDim.x, ++it) {
         int n0, k0;
         const int steps = unit_steps(u, n0, k0);
-        const int acc = it & 1;
-        mbar_wait(tempty(acc), ((it >> 1) & 1u) ^ 1u);
+        const int acc = it % NACC;
+        mbar_wait(tempty(acc), ((uint32_t)(it / NACC) & 1u) ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + WM_TMEM_D + acc * WM_MPAD_MAX;
         for (int st = 0; st < steps; ++st) {
@@ -323,8 +336,8 @@ w4a16_mma_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
     for (int u = blockIdx.x; u < units; u += gridDim.x, ++it) {
       int n0, k0;
       unit_steps(u, n0, k0);
-      const int acc = it & 1;
-      mbar_wait_backoff(tfull(acc), (it >> 1) & 1u);
+      const int acc = it % NACC;
+      mbar_wait_backoff(tfull(acc), (uint32_t)(it / NACC) & 1u);
       tc_fence_after();
       const int n = n0 + 32 * we + lane;
       const uint32_t t_row = tmem_base + (uint32_t(32 * we) << 16) + WM_TMEM_D + acc * WM_MPAD_MAX;
@@ -357,13 +370,15 @@ w4a16_mma_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constan
   if (warp == 2) tmem_dealloc<1>(tmem_base, 512);
 }
 
-template <typename XT>
-int run_w4a16_mma(const void* x, const uint32_t* qw, const void* scale, const uint8_t* qzero, const int32_t* perm, void* y,
-                  void* workspace, int M, int N, int K, int group, int fmt, cudaStream_t st) {
+template <typename XT, bool BIG>
+int run_w4a16_mma_cfg(const void* x, const uint32_t* qw, const void* scale, const uint8_t* qzero, const int32_t* perm, void* y,
+                      void* workspace, int M, int N, int K, int group, int fmt, cudaStream_t st) {
+  using Cfg = WmCfg<BIG>;
+  constexpr int WM_MPAD_MAX = Cfg::MPAD_MAX, WM_SMEM = Cfg::SMEM;
   static bool attr_set = false;
   static int n_sms = 0;
   if (!attr_set) {
-    if (cudaFuncSetAttribute(w4a16_mma_kernel<XT>, cudaFuncAttributeMaxDynamicSharedMemorySize, WM_SMEM) != cudaSuccess)
+    if (cudaFuncSetAttribute(w4a16_mma_kernel<XT, BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, WM_SMEM) != cudaSuccess)
       return GQ_ERR_CUDA;
     int dev = 0;
     cudaGetDevice(&dev);
@@ -416,7 +431,7 @@ int run_w4a16_mma(const void* x, const uint32_t* qw, const void* scale, const ui
     const long units = (long)n_tiles * k_chunks;
     const int grid = (int)(units < n_sms ? units : n_sms);
     GQ_LAUNCHED();
-    w4a16_mma_kernel<XT><<<grid, WM_THREADS, WM_SMEM, st>>>(map_w, map_x, p);
+    w4a16_mma_kernel<XT, BIG><<<grid, WM_THREADS, WM_SMEM, st>>>(map_w, map_x, p);
     if (cudaGetLastError() != cudaSuccess) return GQ_ERR_CUDA;
   }
   if (split) {
@@ -425,6 +440,13 @@ int run_w4a16_mma(const void* x, const uint32_t* qw, const void* scale, const ui
     w4a16_finalize_kernel<XT><<<(unsigned)((n + 255) / 256), 256, 0, st>>>(yacc, reinterpret_cast<XT*>(y), n);
   }
   return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
+}
+
+template <typename XT>
+int run_w4a16_mma(const void* x, const uint32_t* qw, const void* scale, const uint8_t* qzero, const int32_t* perm, void* y,
+                  void* workspace, int M, int N, int K, int group, int fmt, cudaStream_t st) {
+  if (M > WmCfg<false>::MPAD_MAX) return run_w4a16_mma_cfg<XT, true>(x, qw, scale, qzero, perm, y, workspace, M, N, K, group, fmt, st);
+  return run_w4a16_mma_cfg<XT, false>(x, qw, scale, qzero, perm, y, workspace, M, N, K, group, fmt, st);
 }
 
 }  // namespace
