@@ -6,7 +6,7 @@ using namespace gq;
 
 static inline cudaStream_t S(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 
-namespace gq { unsigned long long g_launch_count = 0; int g_use_tf32x3 = 1; int g_solve_super = 8; }
+namespace gq { unsigned long long g_launch_count = 0; int g_use_tf32x3 = 1; int g_solve_super = 8; int g_w4a16_path = 0; }
 
 extern "C" {
 
@@ -117,6 +117,11 @@ int gq_sgemm(const float* A, const float* B, float* C, int M, int N, int K, int 
 int gq_set_solve_super(int blocks) {
   int old = gq::g_solve_super;
   if (blocks >= 1 && blocks <= 16) gq::g_solve_super = blocks;
+  return old;
+}
+int gq_set_w4a16_path(int path) {
+  int old = gq::g_w4a16_path;
+  if (path >= 0 && path <= 2) gq::g_w4a16_path = path;
   return old;
 }
 int gq_set_tf32x3(int enable) { int old = gq::g_use_tf32x3; gq::g_use_tf32x3 = enable ? 1 : 0; return old; }

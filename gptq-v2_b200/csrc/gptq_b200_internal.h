@@ -46,6 +46,7 @@ int sgemm(const GemmProblem& pr, float alpha, float beta, int flags, cudaStream_
 int sgemm_batched(const GemmBatch& b, float alpha, float beta, int flags, cudaStream_t st);
 
 // ---- fp32-faithful tensor-core GEMM  C += alpha * A^T B  (3 x TF32 split, tcgen05)
+extern int g_w4a16_path;   // K6 dispatch: 0 auto; 1 never the small-batch mma.sync kernel; 2 the weights-on-N tcgen05 kernel for batch <= 128
 extern int g_solve_super;  // K4: blocks per super-block of the two-level lazy-batch update (1 = update everything after every block)
 extern int g_use_tf32x3;   // 1 (default): K4 / Cholesky updates on tcgen05 3xTF32; 0: fp32 SIMT GEMM (A/B parity hook)
 struct Tf32Maps { CUtensorMap a, b, c; };
@@ -93,6 +94,9 @@ int w4a16_mma(const void* x, const uint32_t* qw, const void* scale_t, const uint
 bool w4a16_smallm_supports(int M, int N, int K, int group);
 int w4a16_smallm(const void* x, const uint32_t* qw, const void* scale_t, const uint8_t* qzero_t, const int32_t* perm,
                  void* y, void* workspace, int M, int N, int K, int group, int fmt, cudaStream_t st);
+bool w4a16_wb_supports(int M, int N, int K, int group);
+int w4a16_wb(const void* x, const uint32_t* qw, const void* scale_t, const uint8_t* qzero_t, const int32_t* perm, void* y,
+             void* workspace, int M, int N, int K, int group, int fmt, cudaStream_t st);
 int w4a16_gemm(const void* x, const uint32_t* qw, const void* scale_t, const uint8_t* qzero_t, const int32_t* perm,
                void* y, void* workspace, int M, int N, int K, int group, int fmt, cudaStream_t st);
 int prep_weight_t(const void* W, int fmt, const int64_t* perm, float* Wt, void* orig_t, float* colsq, int R, int C,

@@ -40,6 +40,7 @@ SIGNATURES = {
     'gq_gemm_tf32x3': (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _f, _i, _vp]),
     'gq_set_tf32x3': (_i, [_i]),
     'gq_set_solve_super': (_i, [_i]),
+    'gq_set_w4a16_path': (_i, [_i]),
     'gq_sgemm': (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _f, _f, _i, _vp]),
 }
 

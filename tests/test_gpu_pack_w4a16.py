@@ -106,3 +106,55 @@ def test_w4a16_small_batch_kernel(M, N, K, group, use_perm, dtype):
     # elementwise: one 16-bit ulp of the result plus 2e-6 of the absolute sum (fp32 accumulation incl. the offset term)
     bound = want.abs() * (2.0 ** -10 if dtype == torch.float16 else 2.0 ** -7) + 2e-6 * (xp.abs() @ w.abs().t())
     assert ((y.double().cpu() - want).abs() <= bound).all()
+
+
+@pytest.mark.parametrize('dtype', [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize('M,N,K,group,use_perm', [(9, 256, 256, 128, True), (16, 200, 320, 64, False), (33, 1000, 1088, 32, True),
+                                                  (64, 4096, 4096, 128, True), (100, 520, 2048, 128, False),
+                                                  (128, 1024, 11008, 128, True), (24, 28672, 512, 128, False)])
+def test_w4a16_weights_on_n_kernel(M, N, K, group, use_perm, dtype):
+    """Weights-on-N tcgen05 kernel (w4a16_wb.cu, opt-in through set_w4a16_path(2)): weight rows not a multiple of 256, K not a multiple of 256, k-split units,
+    zero-filled batch padding; vs the dense reconstruction (a8)."""
+    import gptq
+    g = torch.Generator().manual_seed(M * 17 + N + K + group)
+    G = K // group
+    codes = torch.randint(0, 16, (N, K), generator=g, dtype=torch.uint8)
+    scale = (torch.rand(N, G, generator=g) * 0.01 + 1e-3).to(dtype)
+    qzero = torch.randint(0, 16, (N, G), generator=g, dtype=torch.uint8)
+    perm = torch.randperm(K, generator=g) if use_perm else None
+    x = torch.randn(M, K, generator=g).to(dtype)
+    meta = dict(qweight=codes, scale=scale, qzero=qzero, perm_inv=perm.argsort().to(torch.int16) if use_perm else None,
+                group_sizes=torch.full((G,), group, dtype=torch.int16))
+    want = O.linear_forward_dense(x, meta, dtype)
+    old = gptq.set_w4a16_path(2)
+    try:
+        y = gptq.w4a16_gemm(x.cuda(), gptq.pack_int4(codes.cuda()), scale.t().contiguous().cuda(), qzero.t().contiguous().cuda(),
+                            perm.to(torch.int32).cuda() if use_perm else None, group)
+        torch.cuda.synchronize()
+    finally:
+        gptq.set_w4a16_path(old)
+    rel = ((y.float().cpu() - want).norm() / want.norm()).item()
+    assert rel <= 1e-2, rel
+
+
+@pytest.mark.parametrize('M', [1, 5, 8])
+def test_w4a16_paths_agree(M):
+    """The same small-batch problem through the warp-level mma kernel (default) and through the tcgen05 kernels."""
+    import gptq
+    g = torch.Generator().manual_seed(M)
+    N, K, group = 2048, 4096, 128
+    codes = torch.randint(0, 16, (N, K), generator=g, dtype=torch.uint8)
+    scale = (torch.rand(K // group, N, generator=g) * 0.01 + 1e-3).half().cuda()
+    qzero = torch.randint(0, 16, (K // group, N), generator=g, dtype=torch.uint8).cuda()
+    x = torch.randn(M, K, generator=g).half().cuda()
+    packed = gptq.pack_int4(codes.cuda())
+    ys = []
+    for path in (0, 2, 1):
+        old = gptq.set_w4a16_path(path)
+        try:
+            ys.append(gptq.w4a16_gemm(x, packed, scale, qzero, None, group).float())
+        finally:
+            gptq.set_w4a16_path(old)
+    torch.cuda.synchronize()
+    for y in ys[1:]:
+        assert ((y - ys[0]).norm() / ys[0].norm()).item() <= 5e-3

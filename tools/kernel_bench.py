@@ -119,6 +119,8 @@ def bench_w4a16():
     if os.environ.get('W4_SHAPES'):                       # e.g. W4_SHAPES=28672x8192 W4_MS=1,8 (profiling runs)
         shapes = tuple(tuple(int(v) for v in sh.split('x')) for sh in os.environ['W4_SHAPES'].split(','))
     m_list = (1, 2, 4, 8, 16, 64, 256, 1024)
+    if os.environ.get('W4_PATH'):
+        gptq.set_w4a16_path(int(os.environ['W4_PATH']))
     if os.environ.get('W4_MS'):
         m_list = tuple(int(v) for v in os.environ['W4_MS'].split(','))
     for N, K in shapes:
