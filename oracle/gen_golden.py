@@ -16,6 +16,10 @@ The reference's gptq_use_kernel=True branch needs its CUDA extension and
 cannot run here; its semantics are pinned by the C++/CUDA source restatement
 in oracle.gptq_oracle.quantize_range_ref only ("parity unpinned" for that
 compat mode beyond self-consistency).
+
+`python oracle/gen_golden.py quantizer` writes only the q_*.npz cases: symmetric grids, MSE grid search, EXL2 quantised
+scales and per-group bit widths (quant.py:40-69,99-112,120-165) through the reference's round-to-nearest and fp32
+branches (gptq_py.py:101-124,158-193).
 """
 import os
 import sys
@@ -92,5 +96,65 @@ def main():
         print('wrote', name, {k: f'{v:.4e}' for k, v in res['metrics'].items()})
 
 
+# ---- the remaining Quantizer options, through the reference's own RTN / fp32 branches
+Q_CASES = [
+    # name,            R,  C, bits per group,  branch, sym,  scale_bits, mse, act_order, dtype
+    ('q_sym_b4',       64, 256, [4, 4],        'pure', True,  None, False, True, torch.float16),
+    ('q_mse_b4',       64, 256, [4, 4],        'pure', False, None, True,  True, torch.float16),
+    ('q_mse_sym_b3',   48, 256, [3, 3],        'pure', True,  None, True,  False, torch.float16),
+    ('q_exl2_b4',      64, 256, [4, 4],        'pure', False, 4,    False, True, torch.float16),
+    ('q_exl2_mse_mix', 64, 384, [3, 4, 2],     'pure', False, 4,    True,  True, torch.float16),
+    ('q_mixed_bits',   64, 384, [2, 8, 4],     'pure', False, None, False, True, torch.bfloat16),
+    ('q_rtn_mse_sym',  64, 256, [4, 3],        'rtn',  True,  None, True,  False, torch.float16),
+    ('q_rtn_exl2_mse', 32, 256, [4, 4],        'rtn',  False, 6,    True,  False, torch.bfloat16),
+]
+
+
+def main_quantizer():
+    from oracle import gptq_oracle as O
+    gptq_py, quant = import_reference()
+    torch.set_num_threads(1)
+    out_dir = os.path.join(ROOT, 'tests', 'golden')
+    for name, R, C, bits, branch, sym, sbits, mse, act, dtype in Q_CASES:
+        n_seq, seqlen = 4, 128
+        W, X = O.synth_linear(R, C, n_seq, seqlen, dtype=dtype, seed=500 + R + C + len(name))
+        hook = None
+        if branch != 'rtn':
+            hook = gptq_py.HessianHook()
+            for i in range(0, n_seq, 2):
+                hook.add_batch(X[i:i + 2], use_kernel=False)
+            hook.invert(damp_ratio=1e-2, act_order=act)
+        G = C // 128
+        gs = torch.full([G], 128, dtype=torch.int32)
+        bw = torch.tensor(bits, dtype=torch.int32)
+        res = gptq_py.gptq_quant(weight=W, hessian_hook=hook, group_sizes=gs, group_bit_widths=bw,
+                                 scale_bit_width=(torch.tensor(sbits) if sbits is not None else None),
+                                 gptq_use_kernel=False, gptq_block_sizes=gs, quant_symmetric=sym, quant_mse=mse,
+                                 quant_max_shrink=.8, quant_n_grid=100, quant_norm=2.4, quant_use_kernel=False)
+        lin = quant.reconstruct_nn_linear(res['quant_meta'], dtype=dtype)
+        m = res['quant_meta']
+        to_np = lambda t: t.to(torch.float32).numpy() if t.dtype in (torch.float16, torch.bfloat16) else t.numpy()
+        extra = {}
+        if m['sscale'] is not None:
+            extra = dict(qscale=m['qscale'].numpy(), sscale=to_np(m['sscale']), scale_bit_width=m['scale_bit_width'].numpy())
+        if hook is not None:
+            extra.update(U=hook.hessian_inv.numpy(), perm=(hook.perm.numpy() if hook.perm is not None else np.arange(C)))
+        np.savez_compressed(
+            os.path.join(out_dir, name + '.npz'),
+            R=R, C=C, bits=np.array(bits), branch=branch, sym=int(sym), scale_bits=(-1 if sbits is None else sbits),
+            mse=int(mse), act_order=int(act), dtype=str(dtype).split('.')[-1],
+            W_bits=W.view(torch.int16).numpy(),
+            qweight=m['qweight'].numpy(), scale=to_np(m['scale']), qzero=m['qzero'].numpy(), perm_inv=m['perm_inv'].numpy(),
+            group_bit_widths=m['group_bit_widths'].numpy(),
+            metrics=np.array([res['metrics'][k] for k in ('gptq_error', 'gptq_norm', 'l2.0_error', 'l2.0_norm')],
+                             dtype=np.float64),
+            W_hat=to_np(lin.weight.data), **extra)
+        print('wrote', name, {k: f'{v:.4e}' for k, v in res['metrics'].items()})
+
+
 if __name__ == '__main__':
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == 'quantizer':
+        main_quantizer()
+    else:
+        main()
+        main_quantizer()

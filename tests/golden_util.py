@@ -10,7 +10,28 @@ _DT = {'float16': torch.float16, 'bfloat16': torch.bfloat16}
 
 
 def names():
-    return sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN_DIR, '*.npz')))
+    return sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN_DIR, 'r*.npz')))
+
+
+def qnames():
+    """The Quantizer-option cases."""
+    return sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN_DIR, 'q_*.npz')))
+
+
+def loadq(name):
+    z = np.load(os.path.join(GOLDEN_DIR, name + '.npz'))
+    d = {k: z[k] for k in z.files}
+    dt = _DT[str(d['dtype'])]
+    sb = int(d['scale_bits'])
+    out = dict(name=name, R=int(d['R']), C=int(d['C']), bits=[int(b) for b in d['bits']], branch=str(d['branch']),
+               sym=bool(int(d['sym'])), scale_bits=(None if sb < 0 else sb), mse=bool(int(d['mse'])),
+               act_order=bool(int(d['act_order'])), dtype=dt)
+    out['W'] = torch.from_numpy(d['W_bits'].copy()).view(dt)
+    for k in ('scale', 'W_hat', 'qweight', 'qzero', 'perm_inv', 'group_bit_widths', 'U', 'qscale', 'sscale'):
+        out[k] = torch.from_numpy(d[k].copy()) if k in d else None
+    out['perm'] = torch.from_numpy(d['perm'].copy()).to(torch.int64) if ('perm' in d and out['act_order']) else None
+    out['metrics'] = dict(zip(('gptq_error', 'gptq_norm', 'l2.0_error', 'l2.0_norm'), d['metrics'].tolist()))
+    return out
 
 
 def load(name):
