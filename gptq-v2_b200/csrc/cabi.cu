@@ -79,6 +79,25 @@ int gq_gptq_solve_static(float* Wt, const float* U, float* quant_t, int16_t* cod
                     group, maxq, 3, 0, C, S(stream));
 }
 
+int gq_gptq_solve_ex(float* Wt, const float* U, float* quant_t, void* codes_t, float* err_t, float* scale_gr,
+                     float* qzero_gr, int R, int C, int group, const float* maxq_groups, float maxq, int mode, int a,
+                     int b, void* stream) {
+  if (mode != 0 && mode != 3 && mode != 4) return GQ_ERR_ARG;
+  return gptq_solve(Wt, U, quant_t, codes_t, mode == 3 ? 2 : 1, err_t, scale_gr, qzero_gr, R, C, group, maxq, mode, a, b,
+                    S(stream), maxq_groups);
+}
+
+int gq_find_params(const float* Wt, int R, int group, int n_groups, const float* maxq_groups_dev, int sym,
+                   float* scale_gr, float* qzero_gr, void* stream) {
+  return find_params(Wt, R, group, n_groups, maxq_groups_dev, sym, scale_gr, qzero_gr, S(stream));
+}
+
+int gq_mse_refine(const float* Wt, int R, int group, int n_groups, const float* maxq_groups_dev, const float* grid_dev,
+                  int n_grid, float norm, float* scale_gr, const float* qzero_gr, int32_t* index_gr, void* stream) {
+  return mse_refine(Wt, R, group, n_groups, maxq_groups_dev, grid_dev, n_grid, norm, scale_gr, qzero_gr, index_gr,
+                    S(stream));
+}
+
 int gq_prep_weight_t(const void* W, int dtype, const int64_t* perm, float* Wt, int R, int C, void* stream) {
   return prep_weight_t(W, dtype, perm, Wt, nullptr, nullptr, R, C, S(stream));
 }

@@ -79,7 +79,11 @@ int chol_factor_panel(float* A, int D, int o, int n, int rest, int* info_dev, cu
 // ---- K3/K4
 int gptq_solve(float* Wt, const float* U, float* quant_t, void* codes_t, int codes_elem_size, float* err_t,
                float* scale_gr, float* qzero_gr, int R, int C, int group, float maxq, int mode, int a, int b,
-               cudaStream_t st);
+               cudaStream_t st, const float* maxq_groups = nullptr);
+int find_params(const float* Wt, int R, int group, int n_groups, const float* maxq_groups_dev, int sym, float* scale_gr,
+                float* qzero_gr, cudaStream_t st);
+int mse_refine(const float* Wt, int R, int group, int n_groups, const float* maxq_groups_dev, const float* grid_dev,
+               int n_grid, float norm, float* scale_gr, const float* qzero_gr, int* index_gr, cudaStream_t st);
 
 // ---- K5/K6
 int pack_int4(const uint8_t* codes, uint32_t* packed, int R, int C, cudaStream_t st);

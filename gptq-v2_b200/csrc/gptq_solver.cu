@@ -38,13 +38,17 @@ static int launch_block_nb(int mode, const SolveParams& p, int nb, cudaStream_t 
 // mode 3: mode 1's arithmetic (static parameters, 16-bit-rounded dequant) with the per-group
 // (C/group, R) parameter layout of mode 0: all groups of a linear in ONE call (one tensor-map
 // build, no host round trip per group).
+// mode 4: mode 0's fp32 arithmetic with caller-supplied per-group parameters (symmetric / MSE-refined / EXL2 grids).
+// maxq_groups (host, C/group entries, may be null) overrides maxq per group in modes 0, 3 and 4.
 int gptq_solve(float* Wt, const float* U, float* quant_t, void* codes_t, int codes_elem_size, float* err_t,
                float* scale_gr, float* qzero_gr, int R, int C, int group, float maxq, int mode, int a, int b,
-               cudaStream_t st) {
+               cudaStream_t st, const float* maxq_groups) {
   if (R % 4 != 0 || C % 4 != 0) return GQ_ERR_SHAPE;           // float4 path, as the reference (gptq_cpp_kernel.cu:130)
   if (a < 0 || b > C || a >= b) return GQ_ERR_ARG;
-  const bool per_group = mode == 0 || mode == 3;
+  const bool per_group = mode == 0 || mode == 3 || mode == 4;
+  const int static_params = mode == 4;
   if (mode == 3) mode = 1;
+  if (mode == 4) mode = 0;
   // codes are uint8 in mode 0 (this build's storage type) and int16 in mode 1 (the reference's out_q)
   if (codes_t && codes_elem_size != (mode == 0 ? 1 : 2)) return GQ_ERR_ARG;
   if (per_group && (group != 32 && group != 64 && group != 128)) return GQ_ERR_SHAPE;
@@ -66,8 +70,9 @@ int gptq_solve(float* Wt, const float* U, float* quant_t, void* codes_t, int cod
     int nb = per_group ? group : ((b - c >= 128) ? 128 : (b - c));
     SolveParams p;
     p.Wt = Wt; p.U = U; p.quant_t = quant_t; p.codes_t = codes_t; p.err_t = err_t;
-    p.R = R; p.C = C; p.c0 = c; p.maxq = maxq;
+    p.R = R; p.C = C; p.c0 = c; p.maxq = maxq; p.static_params = static_params;
     if (per_group) {
+      if (maxq_groups) p.maxq = maxq_groups[c / group];
       p.scale = scale_gr + (size_t)(c / group) * R;
       p.qzero = qzero_gr + (size_t)(c / group) * R;
     } else {

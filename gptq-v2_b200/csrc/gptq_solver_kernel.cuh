@@ -193,7 +193,7 @@ __global__ void __launch_bounds__(SOLVE_WARPS * 32, 3) solve_block_kernel(const 
 
   float s = 1.f, z = 0.f;
   if (warp == 0) {
-    if (MODE == 0) {
+    if (MODE == 0 && !p.static_params) {
 #pragma unroll
       for (int i = 1; i < SOLVE_WARPS; ++i) {
         mx = fmaxf(mx, mm[i * ROWS + lane]);

@@ -11,5 +11,6 @@ struct SolveParams {
   int R, C;
   int c0;               // first column of the block
   float maxq;
+  int static_params;    // MODE 0 only: scale/qzero are inputs (symmetric / MSE-refined / EXL2 parameters)
 };
 }  // namespace gq

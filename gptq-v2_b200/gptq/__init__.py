@@ -14,7 +14,7 @@ import torch
 from . import _cabi
 from ._cabi import GptqB200Error, check, lib, ptr, require_contig, require_cuda, stream_of
 
-__all__ = ['accumulate_hessian', 'gptq_quantize_range', 'hessian_syrk', 'hessian_invert', 'prep_weight_t', 'prep_weight_t2', 'solve_metrics',
+__all__ = ['accumulate_hessian', 'gptq_quantize_range', 'hessian_syrk', 'hessian_invert', 'prep_weight_t', 'prep_weight_t2', 'solve_metrics', 'gptq_solve_ex', 'find_params', 'mse_refine',
            'gptq_solve', 'gptq_solve_static', 'pack_int4', 'unpack_int4', 'transpose_pack_int4', 'w4a16_gemm', 'sgemm', 'gemm_tf32x3', 'set_tf32x3', 'set_solve_super', 'set_w4a16_path',
            'GptqB200Error']
 
@@ -163,6 +163,72 @@ def gptq_solve_static(Wt: torch.Tensor, U: torch.Tensor, scale_gr: torch.Tensor,
         check(lib.gq_gptq_solve_static(ptr(Wt), ptr(U), ptr(quant_t), ptr(codes_t), ptr(err_t), ptr(scale_gr),
                                        ptr(qzero_gr), R, C_, int(group), float(maxq), stream_of(Wt)), 'gq_gptq_solve_static')
     return quant_t, codes_t, err_t
+
+
+def gptq_solve_ex(Wt: torch.Tensor, U: torch.Tensor, scale_gr: torch.Tensor, qzero_gr: torch.Tensor, group: int, maxq_groups,
+                  mode: int, a: int = 0, b: int = None, out=None):
+    """K3+K4 over columns [a, b) with per-group maxq (list of C/group floats) -- gq_gptq_solve_ex.
+    mode 0: dynamic asymmetric parameters (scale_gr / qzero_gr written); 3: static, 16-bit dequant, int16 codes;
+    4: static, fp32 arithmetic (symmetric / MSE / EXL2 grids on the fp32 path).  Wt (C, R) is consumed.
+    `out` = (quant_t, codes_t, err_t) from an earlier call over another column range, or None to allocate.
+    Returns quant_t, codes_t, err_t."""
+    import ctypes
+    dev = require_cuda(Wt, U, scale_gr, qzero_gr)
+    require_contig(Wt=Wt, U=U, scale_gr=scale_gr, qzero_gr=qzero_gr)
+    C_, R = Wt.shape
+    G = C_ // group
+    assert scale_gr.shape == (G, R) and qzero_gr.shape == (G, R)
+    assert scale_gr.dtype == torch.float32 and qzero_gr.dtype == torch.float32
+    assert len(maxq_groups) == G
+    if b is None:
+        b = C_
+    if out is None:
+        out = (torch.empty_like(Wt), torch.empty(C_, R, dtype=torch.int16 if mode == 3 else torch.uint8, device=dev),
+               torch.empty_like(Wt))
+    quant_t, codes_t, err_t = out
+    mq = (ctypes.c_float * G)(*[float(v) for v in maxq_groups])
+    with torch.cuda.device(dev):
+        check(lib.gq_gptq_solve_ex(ptr(Wt), ptr(U), ptr(quant_t), ptr(codes_t), ptr(err_t), ptr(scale_gr), ptr(qzero_gr),
+                                   R, C_, int(group), ctypes.cast(mq, ctypes.c_void_p), 0.0, int(mode), int(a), int(b),
+                                   stream_of(Wt)), 'gq_gptq_solve_ex')
+    return quant_t, codes_t, err_t
+
+
+def find_params(Wt: torch.Tensor, group: int, maxq_dev: torch.Tensor, sym: bool, scale_gr: torch.Tensor, qzero_gr: torch.Tensor,
+                g0: int = 0, n_groups: int = None) -> None:
+    """Quantizer.find_params (quant.py:89-118) for groups [g0, g0 + n_groups) of the transposed weights Wt (C, R):
+    writes rows g0.. of scale_gr / qzero_gr (C/group, R) fp32.  maxq_dev: (C/group) fp32 on the device."""
+    dev = require_cuda(Wt, maxq_dev, scale_gr, qzero_gr)
+    require_contig(Wt=Wt, maxq_dev=maxq_dev, scale_gr=scale_gr, qzero_gr=qzero_gr)
+    C_, R = Wt.shape
+    G = C_ // group
+    if n_groups is None:
+        n_groups = G - g0
+    assert 0 <= g0 and g0 + n_groups <= G and scale_gr.shape == (G, R) and qzero_gr.shape == (G, R) and maxq_dev.shape == (G,)
+    assert Wt.dtype == torch.float32 and maxq_dev.dtype == torch.float32 and scale_gr.dtype == torch.float32
+    with torch.cuda.device(dev):
+        check(lib.gq_find_params(ptr(Wt[g0 * group:]), R, int(group), int(n_groups), ptr(maxq_dev[g0:]), int(bool(sym)),
+                                 ptr(scale_gr[g0:]), ptr(qzero_gr[g0:]), stream_of(Wt)), 'gq_find_params')
+
+
+def mse_refine(Wt: torch.Tensor, group: int, maxq_dev: torch.Tensor, grid: torch.Tensor, norm: float, scale_gr: torch.Tensor,
+               qzero_gr: torch.Tensor, g0: int = 0, n_groups: int = None, want_index: bool = False):
+    """Quantizer.mse (quant.py:152-156): scale_gr[g0:g0+n_groups] *= grid[argmin error] per row, in place.
+    grid: (Q) fp32 shrink factors on the device.  Returns the chosen indices (n_groups, R) int32 when asked."""
+    dev = require_cuda(Wt, maxq_dev, grid, scale_gr, qzero_gr)
+    require_contig(Wt=Wt, maxq_dev=maxq_dev, grid=grid, scale_gr=scale_gr, qzero_gr=qzero_gr)
+    C_, R = Wt.shape
+    G = C_ // group
+    if n_groups is None:
+        n_groups = G - g0
+    assert 0 <= g0 and g0 + n_groups <= G and scale_gr.shape == (G, R) and qzero_gr.shape == (G, R) and maxq_dev.shape == (G,)
+    assert grid.dtype == torch.float32 and grid.dim() == 1
+    idx = torch.empty(n_groups, R, dtype=torch.int32, device=dev) if want_index else None
+    with torch.cuda.device(dev):
+        check(lib.gq_mse_refine(ptr(Wt[g0 * group:]), R, int(group), int(n_groups), ptr(maxq_dev[g0:]), ptr(grid), int(grid.numel()),
+                                float(norm), ptr(scale_gr[g0:]), ptr(qzero_gr[g0:]), ptr(idx) if idx is not None else None,
+                                stream_of(Wt)), 'gq_mse_refine')
+    return idx
 
 
 def pack_int4(codes: torch.Tensor) -> torch.Tensor:

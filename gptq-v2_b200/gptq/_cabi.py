@@ -29,6 +29,9 @@ SIGNATURES = {
     'gq_quantize_range': (_i, [_vp, _vp, _vp, _vp, _f, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     'gq_gptq_solve': (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _f, _vp]),
     'gq_gptq_solve_static': (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _f, _vp]),
+    'gq_gptq_solve_ex': (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _f, _i, _i, _i, _vp]),
+    'gq_find_params': (_i, [_vp, _i, _i, _i, _vp, _i, _vp, _vp, _vp]),
+    'gq_mse_refine': (_i, [_vp, _i, _i, _i, _vp, _vp, _i, _f, _vp, _vp, _vp, _vp]),
     'gq_prep_weight_t': (_i, [_vp, _i, _vp, _vp, _i, _i, _vp]),
     'gq_prep_weight_t2': (_i, [_vp, _i, _vp, _vp, _vp, _vp, _i, _i, _vp]),
     'gq_solve_metrics': (_i, [_vp, _vp, _vp, _i, C.c_size_t, _vp, _vp]),

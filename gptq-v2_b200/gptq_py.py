@@ -11,9 +11,10 @@ every arithmetic step is a kernel of libgptq_b200.so:
 
 Host-side torch ops are limited to what the reference also leaves to torch and that is
 O(D) or a single elementwise pass (argsort of the diagonal, metrics).
-Not implemented (outside SURVEY section 8 scope, never exercised by llama.py): quant_mse,
-quant_symmetric, scale_bit_width (EXL2), non-uniform group sizes; they raise
-NotImplementedError instead of silently doing something else.
+The Quantizer options llama.py never sets are supported on all three branches:
+quant_symmetric, quant_mse (grid search, gq_mse_refine), scale_bit_width (EXL2 qscale / sscale), per-group bit widths.
+Still NotImplementedError: non-uniform group sizes, gptq_block_sizes != group_sizes, quant_use_kernel=True (needs
+exllamav2, which the reference itself no longer imports).
 """
 from __future__ import annotations
 
@@ -22,6 +23,7 @@ import torch
 import gptq as _ops
 from gptq import accumulate_hessian as accumulate_hessian_c, gptq_quantize_range  # noqa: F401  (reference names)
 from gptq_triton.accumulate_hessian import accumulate_hessian as accumulate_hessian_t  # noqa: F401
+from quant import exl2_scale_grid, exl2_scale_mse
 
 
 class HessianHook:
@@ -106,21 +108,26 @@ def gptq_quant(
                                 from the un-compensated weights, fp16-rounded dequant (ref :125-157)
        gptq_use_kernel=False -> the reference's fp32 PyTorch semantics: per-group scale/zero from
                                 the error-compensated weights, fp32 dequant (ref :158-193)
-    Both run on the same CUDA block solver."""
-    if quant_mse:
-        raise NotImplementedError('quant_mse=True (MSE grid search, quant.py:120-165) is outside this build\'s scope')
-    if quant_symmetric or (scale_bit_width is not None):
-        raise NotImplementedError('symmetric / EXL2 scale quantisation is outside this build\'s scope')
+       hessian_hook=None     -> round to nearest (ref :101-124)
+    All run on the same CUDA block solver; group parameters come from the solver itself (asymmetric min/max) or from
+    gq_find_params / gq_mse_refine (symmetric, MSE-refined, EXL2 grids)."""
+    if quant_mse and quant_use_kernel:
+        # ref quant.py:131-150 calls exllamav2's ext_c.quantize_err, whose import the reference has commented out (quant.py:4)
+        raise NotImplementedError('quant_use_kernel=True needs exllamav2 (not importable in the reference either)')
     n_rows, n_columns = weight.shape
     dtype = weight.dtype
     device = weight.device
     gs = _uniform(group_sizes, 'group_sizes')
-    bits = _uniform(group_bit_widths, 'group_bit_widths')
+    bits_list = [int(v) for v in group_bit_widths.tolist()]
     if gptq_block_sizes is not None and _uniform(gptq_block_sizes, 'gptq_block_sizes') != gs:
         raise NotImplementedError('gptq_block_sizes must equal group_sizes (as llama.py:155 sets them)')
     n_groups = n_columns // gs
-    assert n_groups * gs == n_columns and len(group_sizes) == n_groups
-    maxq = float(2 ** bits - 1)
+    assert n_groups * gs == n_columns and len(bits_list) == n_groups
+    maxq_list = [float(2 ** b - 1) for b in bits_list]
+    sbits = int(scale_bit_width) if scale_bit_width is not None else None
+    exl2 = sbits is not None and sbits > 0                                  # ref quant.py:99-100,108
+    sym = bool(quant_symmetric) or exl2
+    plain = not (sym or quant_mse)                                          # llama.py's setting: asymmetric min/max, no refinement
     perm = hessian_hook.perm if hessian_hook is not None else None
     weight_c = weight.contiguous()
 
@@ -132,26 +139,67 @@ def gptq_quant(
 
     # (C, R) fp32, permuted (ref :90-94,128); orig_t / colsq feed the result metrics after the solver has consumed Wt
     Wt, orig_t, colsq = _ops.prep_weight_t2(weight_c, perm)
+    solver_ok = gs in (32, 64, 128)
+    qscale_gr = sscale_g = None
+    if not plain or not solver_ok or (gptq_use_kernel and hessian_hook is not None):
+        maxq_dev = torch.tensor(maxq_list, dtype=torch.float32, device=device)
+        scale_gr = torch.empty(n_groups, n_rows, dtype=torch.float32, device=device)
+        qzero_gr = torch.empty_like(scale_gr)
+        if exl2:
+            qscale_gr = torch.empty_like(scale_gr)
+            sscale_g = torch.empty(n_groups, dtype=torch.float32, device=device)
+        grid = (1. - torch.arange(0., quant_max_shrink, 1. / quant_n_grid, device=device)) if quant_mse else None   # ref quant.py:152
+        smaxq = torch.tensor(2. ** sbits - 1., dtype=torch.float32, device=device) if exl2 else None
+
+        def group_params(g0: int, n: int) -> None:
+            """Quantizer.find_params (+ .mse) of groups [g0, g0 + n) from the current Wt (ref quant.py:89-165): the
+            O(R C) and O(R C Q) passes run in the library, the (R)-sized EXL2 scale grid in torch on the device."""
+            _ops.find_params(Wt, gs, maxq_dev, sym, scale_gr, qzero_gr, g0, n)
+            rows = slice(g0, g0 + n)
+            if exl2:
+                qs, ss, sc = exl2_scale_grid(scale_gr[rows].unsqueeze(-1), smaxq)
+                scale_gr[rows] = sc.squeeze(-1)
+            if quant_mse:
+                _ops.mse_refine(Wt, gs, maxq_dev, grid, quant_norm, scale_gr, qzero_gr, g0, n)
+                if exl2:
+                    qs, ss, sc = exl2_scale_mse(scale_gr[rows].unsqueeze(-1), smaxq, grid, quant_norm)
+                    scale_gr[rows] = sc.squeeze(-1)
+            if exl2:
+                qscale_gr[rows] = qs.squeeze(-1)
+                sscale_g[rows] = ss.reshape(-1)
+
     if gptq_use_kernel and hessian_hook is not None:
-        # static parameters from the original permuted weights (ref :131-134, quant.py:114-118)
-        w3 = Wt.view(n_groups, gs, n_rows)
-        xmax = w3.amax(dim=1).relu()
-        xmin = -(-w3.amin(dim=1)).relu()
-        scale_gr = (xmax - xmin) / maxq + 1e-12                               # (G, R)
-        qzero_gr = (-xmin / scale_gr).round()
-        if gs in (32, 64, 128):
-            # the reference's per-group gptq_quantize_range loop (ref :135-139), host loop inside the library
-            quant_t, q_t, err_t = _ops.gptq_solve_static(Wt, U, scale_gr.contiguous(), qzero_gr.contiguous(), gs, maxq)
+        # static parameters from the original permuted weights (ref :131-134), then the reference's per-group
+        # gptq_quantize_range loop (ref :135-139) as one library call
+        group_params(0, n_groups)
+        if solver_ok:
+            quant_t, q_t, err_t = _ops.gptq_solve_ex(Wt, U, scale_gr, qzero_gr, gs, maxq_list, mode=3)
         else:
             quant_t = torch.empty_like(Wt)
             err_t = torch.empty_like(Wt)
             q_t = torch.empty_like(Wt, dtype=torch.int16)
             for g in range(n_groups):
-                gptq_quantize_range(quant_t, scale_gr[g].contiguous(), q_t, qzero_gr[g].contiguous(), maxq, U, Wt, err_t,
-                                    g * gs, (g + 1) * gs)
+                gptq_quantize_range(quant_t, scale_gr[g], q_t, qzero_gr[g], maxq_list[g], U, Wt, err_t, g * gs, (g + 1) * gs)
         codes_t = q_t.to(torch.uint8)
+    elif not solver_ok:
+        raise NotImplementedError('the fp32 path needs group_sizes in {32, 64, 128}')
+    elif plain:
+        # min/max parameters of every group computed by the solver itself on the compensated weights (ref :169-176)
+        scale_gr = torch.empty(n_groups, n_rows, dtype=torch.float32, device=device)
+        qzero_gr = torch.empty_like(scale_gr)
+        quant_t, codes_t, err_t = _ops.gptq_solve_ex(Wt, U, scale_gr, qzero_gr, gs, maxq_list, mode=0)
+    elif hessian_hook is None:
+        # round to nearest with a refined grid: nothing propagates, so every group's parameters come from one pass
+        group_params(0, n_groups)
+        quant_t, codes_t, err_t = _ops.gptq_solve_ex(Wt, U, scale_gr, qzero_gr, gs, maxq_list, mode=4)
     else:
-        quant_t, codes_t, err_t, scale_gr, qzero_gr = _ops.gptq_solve(Wt, U, gs, maxq)
+        # fp32 path with a symmetric / MSE / EXL2 grid: each group's parameters depend on the updates of the groups
+        # before it (ref :171-185), so parameters and solve alternate per group
+        out = None
+        for g in range(n_groups):
+            group_params(g, 1)
+            out = _ops.gptq_solve_ex(Wt, U, scale_gr, qzero_gr, gs, maxq_list, mode=4, a=g * gs, b=(g + 1) * gs, out=out)
+        quant_t, codes_t, err_t = out
 
     # ---- metrics (ref :196-199, :231-237) in one pass over the solver outputs and ONE host sync:
     #   gptq_error = mean(err^2);  gptq_norm = mean((W / diag(U))^2) with W unpermuted against the permuted-order diag(U),
@@ -176,10 +224,24 @@ def gptq_quant(
     qweight, _ = _ops.transpose_pack_int4(codes_t, want_codes=True, want_packed=False)   # (R, C) uint8, permuted order
     scale = scale_gr.t().to(dtype=dtype).contiguous()                           # (R, G)
     qzero = qzero_gr.t().to(dtype=torch.uint8).contiguous()                     # (R, G)
+    qscale = qscale_gr.t().to(dtype=torch.uint8).contiguous() if exl2 else None  # (R, G)   ref :217
+    sscale = sscale_g.to(dtype=dtype) if exl2 else None                          # (G)      ref :218
     if perm is not None:
         perm16 = perm.to(dtype=torch.int16)
     else:
         perm16 = torch.arange(n_columns, dtype=torch.int16, device=device)
+    bits_out = group_bit_widths.to(dtype=torch.uint8)
+    # with EXL2 metadata the groups are stored by descending bit width, ties in ascending position (ref :201-212)
+    order = list(range(n_groups))
+    if scale_bit_width is not None:
+        order.sort(key=lambda g: (bits_list[g], gs, -g), reverse=True)
+    if order != list(range(n_groups)):
+        ig = torch.tensor(order, dtype=torch.int64, device=device)
+        ic = (ig[:, None] * gs + torch.arange(gs, device=device)).reshape(-1)
+        qweight, perm16 = qweight[:, ic].contiguous(), perm16[ic]
+        scale, qzero, bits_out = scale[:, ig].contiguous(), qzero[:, ig].contiguous(), bits_out[ig.to(bits_out.device)]
+        if exl2:
+            qscale, sscale = qscale[:, ig].contiguous(), sscale[ig]
     perm_inv = perm16.argsort().to(dtype=torch.int16)                           # ref :226
 
     metrics.update({'l2.0_error': d2 / n_el, 'l2.0_norm': l2n})
@@ -188,11 +250,11 @@ def gptq_quant(
         'qweight': qweight.to(device=save_device),
         'scale': scale.to(device=save_device),
         'qzero': qzero.to(device=save_device),
-        'qscale': None,
-        'sscale': None,
+        'qscale': qscale.to(device=save_device) if exl2 else None,
+        'sscale': sscale.to(device=save_device) if exl2 else None,
         'perm_inv': perm_inv.to(device=save_device),
         'group_sizes': group_sizes.to(dtype=torch.int16, device=save_device),
-        'group_bit_widths': group_bit_widths.to(dtype=torch.uint8, device=save_device),
-        'scale_bit_width': None,
+        'group_bit_widths': bits_out.to(device=save_device),
+        'scale_bit_width': scale_bit_width.to(dtype=torch.uint8, device=save_device) if scale_bit_width is not None else None,
     }
     return {'quant_meta': quant_meta, 'metrics': metrics}

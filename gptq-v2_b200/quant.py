@@ -32,24 +32,80 @@ def dequantize_quantized(x, scale, qzero, maxq):
     return dequantize(quantize(x, scale, qzero, maxq), scale, qzero)
 
 
-class Quantizer:
-    """Asymmetric min/max quantiser over the last dimension (reference quant.py:72-118).
-    Symmetric / EXL2 / MSE variants are outside this build's scope and raise."""
+def quantize2(x, scale, maxq):
+    """Quadratic grid for a column of scales (EXL2): clamp(round(sqrt(x / scale)), 1, maxq + 1)   (reference quant.py:40-53)"""
+    return torch.clamp(torch.round(torch.sqrt(x / scale)), 1., maxq + 1.)
 
-    def __init__(self, scale=None, qzero=None, maxq=None):
+
+def dequantize2(qx, scale):
+    """qx^2 * scale   (reference quant.py:56-65)"""
+    return qx * qx * scale
+
+
+def dequantize2_quantized2(x, scale, maxq):
+    return dequantize2(quantize2(x, scale, maxq), scale)
+
+
+def exl2_scale_grid(scale, smaxq):
+    """The EXL2 re-quantisation of a group's scales (reference quant.py:109-112).  scale (..., R, 1) fp32.
+    Returns qscale (..., R, 1), sscale (..., 1, 1), dequantised scale."""
+    sscale = scale.amax(dim=-2, keepdim=True) / (smaxq + 1.) ** 2. + EPSILON
+    qscale = quantize2(scale, sscale, smaxq)
+    return qscale, sscale, dequantize2(qscale, sscale)
+
+
+def exl2_scale_mse(scale, smaxq, p, norm):
+    """Second half of Quantizer.mse (reference quant.py:157-165): one shrink factor for the group's sscale.
+    scale (..., R, 1) fp32 (already MSE-refined), p (Q) shrink factors."""
+    sscale = scale.amax(dim=-2, keepdim=True) / (smaxq + 1.) ** 2. + EPSILON
+    cand = sscale[..., None] * p
+    q = dequantize2(quantize2(scale[..., None], cand, smaxq), cand)                                    # (..., R, 1, Q)
+    arg = (q - scale[..., None]).abs().pow(norm).sum(dim=-3).argmin(dim=-1, keepdim=True)              # (..., 1, 1)
+    sscale = sscale * p[arg]
+    qscale = quantize2(scale, sscale, smaxq)
+    return qscale, sscale, dequantize2(qscale, sscale)
+
+
+class Quantizer:
+    """Per-row quantiser over the last dimension with the reference's options (quant.py:72-183): asymmetric min/max or
+    symmetric grid, EXL2 quantised scales (qscale / sscale), MSE refinement of the scale.  Plain torch on whatever device
+    x lives on: this class is the host mirror for callers of the reference API; gptq_quant itself runs the same
+    arithmetic in libgptq_b200.so (gq_find_params / gq_mse_refine) on the solver's transposed layout."""
+
+    def __init__(self, scale=None, qzero=None, maxq=None, qscale=None, sscale=None, smaxq=None):
         self.scale, self.qzero, self.maxq = scale, qzero, maxq
+        self.qscale, self.sscale, self.smaxq = qscale, sscale, smaxq
+        if self.scale is None and self.qscale is not None and self.sscale is not None:
+            self.scale = dequantize2(self.qscale, self.sscale)
+        elif self.qscale is None and self.scale is not None and self.sscale is not None and self.smaxq is not None:
+            self.qscale = quantize2(self.scale, self.sscale, self.smaxq)
 
     def find_params(self, x, bit_width, sym: bool = False, scale_bit_width=None) -> None:
-        if sym or (scale_bit_width is not None and scale_bit_width > 0):
-            raise NotImplementedError('symmetric / EXL2 quantisation is outside gptq_b200\'s scope')
+        exl2 = scale_bit_width is not None and scale_bit_width > 0
         self.maxq = 2. ** bit_width - 1.
-        hi = torch.relu(x.amax(dim=-1, keepdim=True))
-        lo = -torch.relu(-x.amin(dim=-1, keepdim=True))
-        self.scale = (hi - lo) / self.maxq + EPSILON
-        self.qzero = torch.round(-lo / self.scale)
+        if sym or exl2:
+            self.scale = x.abs().amax(dim=-1, keepdim=True) * (2. / self.maxq) + EPSILON
+            mid = (self.maxq + 1.) * .5
+            self.qzero = torch.full_like(self.scale, float(torch.round(torch.as_tensor(mid))))
+            if exl2:
+                self.smaxq = 2. ** scale_bit_width - 1.
+                self.qscale, self.sscale, self.scale = exl2_scale_grid(self.scale, self.smaxq)
+        else:
+            hi = torch.relu(x.amax(dim=-1, keepdim=True))
+            lo = -torch.relu(-x.amin(dim=-1, keepdim=True))
+            self.scale = (hi - lo) / self.maxq + EPSILON
+            self.qzero = torch.round(-lo / self.scale)
 
-    def mse(self, *args, **kwargs) -> None:
-        raise NotImplementedError('MSE grid search is outside gptq_b200\'s scope')
+    def mse(self, x, max_shrink: float = .8, n_grid: int = 100, norm: float = 2.4, use_kernel: bool = False) -> None:
+        if use_kernel:
+            # the reference calls exllamav2's ext_c.quantize_err here, whose import is commented out (quant.py:4)
+            raise NotImplementedError('Quantizer.mse(use_kernel=True) needs exllamav2, which the reference itself does not import')
+        p = 1. - torch.arange(0., max_shrink, 1. / n_grid, device=x.device)
+        q = dequantize_quantized(x[..., None], self.scale[..., None] * p, self.qzero[..., None], self.maxq)
+        best = (q - x[..., None]).abs().pow(norm).sum(dim=-2).argmin(dim=-1, keepdim=True)
+        self.scale = self.scale * p[best]
+        if self.sscale is not None:
+            self.qscale, self.sscale, self.scale = exl2_scale_mse(self.scale, self.smaxq, p, norm)
 
     def quantize(self, x):
         return quantize(x, self.scale, self.qzero, self.maxq)
@@ -78,13 +134,26 @@ def construct_matrix(qweight, scale, qzero, group_sizes):
     return ((q - z) * scale.unsqueeze(-1)).view(R, C)
 
 
+def construct_matrix_2(qweight, qzero, qscale, sscale, group_sizes):
+    """EXL2 metadata (reference quant.py:240-259): scale = qscale^2 (int16) * sscale, evaluated in sscale.dtype."""
+    gs = _uniform_group(group_sizes)
+    R, C = qweight.shape
+    qs = qscale.to(torch.int16)
+    scale = qs * qs * sscale.reshape(1, -1)
+    q = qweight.to(torch.int16).view(R, C // gs, gs)
+    z = qzero.to(torch.int16).expand(scale.shape).unsqueeze(-1)
+    return ((q - z) * scale.unsqueeze(-1)).view(R, C)
+
+
 def reconstruct_nn_linear(quant_meta: dict, dtype: torch.dtype, device: torch.device = torch.device('cpu')) -> nn.Linear:
     """Reference-compatible dense reconstruction (quant.py:262-279)."""
-    if quant_meta.get('sscale') is not None:
-        raise NotImplementedError('EXL2 metadata is outside gptq_b200\'s scope')
     qweight = quant_meta['qweight'].to(device=device)
-    weight = construct_matrix(qweight, quant_meta['scale'].to(dtype=dtype, device=device),
-                              quant_meta['qzero'].to(device=device), quant_meta['group_sizes'])
+    if quant_meta.get('sscale') is not None:
+        weight = construct_matrix_2(qweight, quant_meta['qzero'].to(device=device), quant_meta['qscale'].to(device=device),
+                                    quant_meta['sscale'].to(dtype=dtype, device=device), quant_meta['group_sizes'])
+    else:
+        weight = construct_matrix(qweight, quant_meta['scale'].to(dtype=dtype, device=device),
+                                  quant_meta['qzero'].to(device=device), quant_meta['group_sizes'])
     if quant_meta.get('perm_inv') is not None:
         weight = weight[:, quant_meta['perm_inv'].to(dtype=torch.int32, device=device)]
     lin = nn.Linear(weight.shape[1], weight.shape[0], bias=False, dtype=dtype, device=weight.device)
@@ -93,17 +162,27 @@ def reconstruct_nn_linear(quant_meta: dict, dtype: torch.dtype, device: torch.de
     return lin
 
 
+def _meta_scale(quant_meta: dict, device: torch.device) -> torch.Tensor:
+    """(R, G) 16-bit scale a dense reconstruction would use: quant_meta['scale'], or qscale^2 * sscale for EXL2 metadata."""
+    if quant_meta.get('sscale') is None:
+        return quant_meta['scale'].to(device=device)
+    qs = quant_meta['qscale'].to(device=device, dtype=torch.int16)
+    return qs * qs * quant_meta['sscale'].to(device=device).reshape(1, -1)
+
+
 def pack_quant_meta(quant_meta: dict, device: torch.device) -> dict:
     """quant_meta (one uint8 per code) -> packed storage for K6:
     qweight_packed (R, C/8) int32, scale_t (G, R) and qzero_t (G, R) uint8 (group-major), perm (C) int32."""
     gs = _uniform_group(quant_meta['group_sizes'])
+    if int(quant_meta['group_bit_widths'].max()) > 4:
+        raise NotImplementedError('packed storage / K6 hold one code per nibble: bit widths up to 4 (llama.py:147 uses 4)')
     codes = quant_meta['qweight'].to(device=device).contiguous()
     perm = None
     if quant_meta.get('perm_inv') is not None:
         perm = quant_meta['perm_inv'].to(device=device, dtype=torch.int64).argsort().to(torch.int32).contiguous()
     return {
         'qweight_packed': _ops.pack_int4(codes),
-        'scale_t': quant_meta['scale'].to(device=device).t().contiguous(),
+        'scale_t': _meta_scale(quant_meta, device).t().contiguous(),
         'qzero_t': quant_meta['qzero'].to(device=device).t().contiguous(),
         'perm': perm,
         'group_size': gs,

@@ -87,6 +87,10 @@ def gptq_quant_row_sharded(weight: torch.Tensor, hessian_hook, quant_fn: Optiona
     R = weight.shape[0]
     if world == 1:
         return quant_fn(weight=weight, hessian_hook=hessian_hook, **quant_kwargs)
+    if quant_kwargs.get('scale_bit_width') is not None:
+        # sscale is a maximum over ALL rows of a group (quant.py:110) and reorders the stored groups (gptq_py.py:210):
+        # not a row-local quantity.  Symmetric grids, the MSE search and per-group bit widths are row-local and shard.
+        raise NotImplementedError('EXL2 scale quantisation does not shard by rows; quantise this linear on one rank')
     lo, hi = shard_range(R, world, rank, 4)
     dev = weight.device
     kw = dict(quant_kwargs)

@@ -79,6 +79,28 @@ int gq_gptq_solve(float* Wt, const float* U, float* quant_t, uint8_t* codes_t, f
  * trip per group.  group in {32, 64, 128}. */
 int gq_gptq_solve_static(float* Wt, const float* U, float* quant_t, int16_t* codes_t, float* err_t, const float* scale_gr,
                          const float* qzero_gr, int R, int C, int group, float maxq, void* stream);
+/* ---- The remaining Quantizer options (quant.py:89-165, gptq_py.py:101-193) ----
+ * General form of the two solves above over columns [a, b) (multiples of group; group in {32, 64, 128}):
+ *   mode 0: gq_gptq_solve's semantics (the kernel computes asymmetric min/max parameters, scale_gr/qzero_gr OUT)
+ *   mode 3: gq_gptq_solve_static's semantics (scale_gr/qzero_gr IN, 16-bit-rounded dequant, codes_t int16)
+ *   mode 4: mode 0's fp32 arithmetic with caller-supplied scale_gr/qzero_gr (IN): what gptq_use_kernel=False does
+ *           with a symmetric / MSE-refined / EXL2 Quantizer (gptq_py.py:169-192)
+ * codes_t is uint8 in modes 0 and 4.  scale_gr/qzero_gr are the full (C/group, R) arrays.  maxq_groups: HOST array
+ * of C/group floats (2^bits - 1 per group, gptq_py.py group_bit_widths), or NULL to use maxq for every group. */
+int gq_gptq_solve_ex(float* Wt, const float* U, float* quant_t, void* codes_t, float* err_t, float* scale_gr,
+                     float* qzero_gr, int R, int C, int group, const float* maxq_groups, float maxq, int mode, int a,
+                     int b, void* stream);
+/* Quantizer.find_params (quant.py:89-118) for n_groups consecutive groups of the transposed weights: Wt points at row
+ * c0 of the (C, R) matrix, scale_gr/qzero_gr (OUT) and maxq_groups_dev (DEVICE array) at group c0/group.
+ * sym = 0: min/max grid; sym = 1: scale = absmax * 2 / maxq + 1e-12, zero = round((maxq + 1) / 2). */
+int gq_find_params(const float* Wt, int R, int group, int n_groups, const float* maxq_groups_dev, int sym,
+                   float* scale_gr, float* qzero_gr, void* stream);
+/* Quantizer.mse (quant.py:152-156, use_kernel=False): per row and group, scale *= grid[argmin_i sum_c |deq(q(x_c;
+ * scale * grid[i])) - x_c|^norm] (first minimum).  grid_dev: n_grid shrink factors on the device (the reference's
+ * 1 - arange(0, max_shrink, 1/n_grid)); index_gr (n_groups, R) int32 receives the chosen index (may be NULL).
+ * group <= 1024. */
+int gq_mse_refine(const float* Wt, int R, int group, int n_groups, const float* maxq_groups_dev, const float* grid_dev,
+                  int n_grid, float norm, float* scale_gr, const float* qzero_gr, int32_t* index_gr, void* stream);
 /* Wt[c][r] = (float) W[r][perm[c]]; W (R, C) of dtype GQ_DTYPE_*; perm may be NULL. */
 int gq_prep_weight_t(const void* W, int dtype, const int64_t* perm, float* Wt, int R, int C, void* stream);
 /* Same, plus (each may be NULL) orig_t (C, R): the same elements in W's own dtype, kept for the error metrics after the

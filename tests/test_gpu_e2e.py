@@ -90,13 +90,15 @@ def test_kernel_path_semantics_vs_oracle():
 
 def test_unsupported_options_raise():
     from gptq_py import gptq_quant
-    W = torch.zeros(8, 128, device='cuda', dtype=torch.float16)
-    gs = torch.full([1], 128, dtype=torch.int32)
-    bw = torch.full([1], 4, dtype=torch.int32)
-    with pytest.raises(NotImplementedError):
-        gptq_quant(W, None, gs, bw, quant_mse=True)
-    with pytest.raises(NotImplementedError):
-        gptq_quant(W, None, gs, bw, quant_mse=False, quant_symmetric=True)
+    W = torch.zeros(8, 256, device='cuda', dtype=torch.float16)
+    gs = torch.full([2], 128, dtype=torch.int32)
+    bw = torch.full([2], 4, dtype=torch.int32)
+    with pytest.raises(NotImplementedError):          # exllamav2's quantize_err (quant.py:131-150): absent from the reference too
+        gptq_quant(W, None, gs, bw, quant_mse=True, quant_use_kernel=True)
+    with pytest.raises(NotImplementedError):          # non-uniform group sizes
+        gptq_quant(W, None, torch.tensor([64, 192], dtype=torch.int32), bw, quant_mse=False)
+    with pytest.raises(NotImplementedError):          # GPTQ blocks that are not the quantisation groups
+        gptq_quant(W, None, gs, bw, quant_mse=False, gptq_block_sizes=torch.full([4], 64, dtype=torch.int32))
 
 
 def test_rtn_without_hook():

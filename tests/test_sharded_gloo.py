@@ -72,6 +72,13 @@ def _worker(rank, world, port, R, C, n_seq, ret):
         gs = torch.full([C // 128], 128, dtype=torch.int32)
         bw = torch.full([C // 128], 4, dtype=torch.int32)
         res = sharded.gptq_quant_row_sharded(W, hook, quant_fn=oracle_quant, group_sizes=gs, group_bit_widths=bw)
+        # EXL2 scale quantisation needs a maximum over all rows of a group: the row-sharded path must refuse it
+        try:
+            sharded.gptq_quant_row_sharded(W, hook, quant_fn=oracle_quant, group_sizes=gs, group_bit_widths=bw,
+                                           scale_bit_width=torch.tensor(4))
+            raise AssertionError('EXL2 was accepted by the row-sharded path')
+        except NotImplementedError:
+            pass
         if rank == 0:
             torch.save({'H': H_sum, 'U': hook.hessian_inv, 'perm': hook.perm, 'meta': res['quant_meta'],
                         'metrics': res['metrics']}, ret)

@@ -89,6 +89,45 @@ def bench_solve():
         del X, H, U, W, Wt0
 
 
+def bench_quantizer():
+    """Quantizer.find_params / .mse on the transposed layout, and gptq_quant end to end with each option."""
+    from gptq_py import HessianHook, gptq_quant
+    for R, C in ((4096, 4096), (11008, 4096)):
+        G = C // 128
+        Wt = torch.randn(C, R, device=dev) * 0.02
+        maxq = torch.full([G], 15.0, device=dev)
+        scale = torch.empty(G, R, device=dev)
+        zero = torch.empty_like(scale)
+        grid = 1. - torch.arange(0., .8, .01, device=dev)
+        t = timeit(lambda: gptq.find_params(Wt, 128, maxq, False, scale, zero))
+        print(json.dumps({'k': 'find_params', 'R': R, 'C': C, 'us': t * 1e6, 'GBps': 4 * R * C / t / 1e9}))
+        s0 = scale.clone()
+
+        def mse():
+            scale.copy_(s0)
+            gptq.mse_refine(Wt, 128, maxq, grid, 2.4, scale, zero)
+        t = timeit(mse)
+        print(json.dumps({'k': 'mse_refine', 'R': R, 'C': C, 'grid': int(grid.numel()), 'norm': 2.4, 'ms': t * 1e3,
+                          'G_candidates_per_s': R * C * grid.numel() / t / 1e9}))
+    R = C = 4096
+    X = (torch.randn(8, 2048, C, device=dev) * torch.exp(torch.rand(C, device=dev) * 3 - 1.5)).half()
+    hook = HessianHook()
+    hook.add_batch(X)
+    hook.invert(1e-2, True)
+    W = (torch.randn(R, C, device=dev) * 0.02).half()
+    gs = torch.full([C // 128], 128, dtype=torch.int32, device=dev)
+    bw = torch.full([C // 128], 4, dtype=torch.int32, device=dev)
+    for label, kw in (('plain', {}), ('sym', {'quant_symmetric': True}), ('mse', {'quant_mse': True}),
+                      ('exl2+mse', {'quant_mse': True, 'scale_bit_width': torch.tensor(4)})):
+        for use_kernel in (True, False):
+            args = dict(weight=W, hessian_hook=hook, group_sizes=gs, group_bit_widths=bw, gptq_use_kernel=use_kernel,
+                        gptq_block_sizes=gs, quant_mse=False, save_device=dev)
+            args.update(kw)
+            t = timeit(lambda: gptq_quant(**args), iters=3, warm=1)
+            print(json.dumps({'k': 'gptq_quant', 'R': R, 'C': C, 'options': label,
+                              'branch': 'kernel' if use_kernel else 'fp32', 'ms': t * 1e3}))
+
+
 def bench_sgemm():
     torch.backends.cuda.matmul.allow_tf32 = False
     for M, N, K, flags in ((3968, 4096, 128, 1), (10880, 4096, 128, 1), (4096, 4096, 128, 3), (4096, 4096, 4096, 0)):
