@@ -238,8 +238,11 @@ class _GroupQuantizer:
     """One Hessian group: accumulate -> (all-reduce) -> invert -> quantise each linear -> dense replay weights."""
 
     def __init__(self, n_global: int, timer: PhaseTimer, pgroup, damp: float, act_order: bool, bits: int, gsize: int,
-                 use_kernel_semantics: bool, save_device: torch.device):
+                 use_kernel_semantics: bool, save_device: torch.device, quant_options: Optional[dict] = None):
         self.hook = HessianHook()
+        # the Quantizer options llama.py:152-162 pins (asymmetric, no MSE search, no EXL2 scales) unless overridden
+        self.quant_options = {'scale_bit_width': None, 'quant_symmetric': False, 'quant_mse': False}
+        self.quant_options.update(quant_options or {})
         self.n_global, self.timer, self.pgroup = n_global, timer, pgroup
         self.damp, self.act_order, self.bits, self.gsize = damp, act_order, bits, gsize
         self.use_kernel_semantics, self.save_device = use_kernel_semantics, save_device
@@ -262,9 +265,9 @@ class _GroupQuantizer:
         gb = torch.full([G], self.bits, dtype=torch.int32, device=dev)
         with self.timer('solve'):
             res = sharded.gptq_quant_row_sharded(
-                weight, self.hook, group=self.pgroup, group_sizes=gs, group_bit_widths=gb, scale_bit_width=None,
-                gptq_use_kernel=self.use_kernel_semantics, gptq_block_sizes=gs, quant_symmetric=False, quant_mse=False,
-                save_device=dev)                                                  # llama.py:148-163
+                weight, self.hook, group=self.pgroup, group_sizes=gs, group_bit_widths=gb,
+                gptq_use_kernel=self.use_kernel_semantics, gptq_block_sizes=gs, save_device=dev,
+                **self.quant_options)                                             # llama.py:148-163
         with self.timer('reconstruct'):
             what = reconstruct_nn_linear(res['quant_meta'], dtype=weight.dtype, device=dev).weight.data   # llama.py:172
         meta = res['quant_meta']
@@ -278,7 +281,8 @@ class _GroupQuantizer:
 def quantize_block(shape: LlamaShape, weights: dict, inps: torch.Tensor, n_global: int, batch_size: int = 16,
                    timer: Optional[PhaseTimer] = None, pgroup=None, damp: float = 1e-2, act_order: bool = True,
                    bits: int = 4, gsize: int = 128, use_kernel_semantics: bool = True,
-                   save_device: torch.device = torch.device('cpu')) -> tuple[torch.Tensor, dict, dict]:
+                   save_device: torch.device = torch.device('cpu'),
+                   quant_options: Optional[dict] = None) -> tuple[torch.Tensor, dict, dict]:
     """GPTQ of one decoder block.  inps (n_local, N, hidden) on the GPU -> (next inps, {name: quant_meta},
     {name: metrics}).  Group order and the order inside a group are the reference's (v, k, q / o / up, gate / down:
     the hoisted dependency list of model_utils.py:146-248 on a Llama block)."""
@@ -290,7 +294,8 @@ def quantize_block(shape: LlamaShape, weights: dict, inps: torch.Tensor, n_globa
     cos, sin = rope_tables(N, shape.hidden // shape.heads, shape.rope_theta, dev, dt)
 
     def make_group():
-        return _GroupQuantizer(n_global, timer, pgroup, damp, act_order, bits, gsize, use_kernel_semantics, save_device)
+        return _GroupQuantizer(n_global, timer, pgroup, damp, act_order, bits, gsize, use_kernel_semantics, save_device,
+                               quant_options)
 
     def quantize_into(grp: _GroupQuantizer, name: str) -> torch.Tensor:
         meta, met, what = grp.quantize(weights[name])

@@ -111,3 +111,40 @@ def test_quantize_llama_random_init_gptq_beats_rtn():
     e_rtn = (h1 @ w_rtn.t() - ref).pow(2).mean().item()
     e_gptq = (h1 @ w_gptq.t() - ref).pow(2).mean().item()
     assert e_gptq < e_rtn
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('opts', [{'quant_mse': True}, {'quant_symmetric': True}, {'quant_mse': True, 'scale_bit_width': 4}])
+def test_quantize_llama_with_quantizer_options(opts):
+    """The driver hands the SURVEY 8f rank-4 Quantizer options through to gptq_quant: the block still replays through its
+    quantised weights, EXL2 metadata reconstructs, and the MSE search does not make the weight error worse than the plain
+    grid on round-to-nearest."""
+    from gptq_py import gptq_quant
+    from quant import reconstruct_nn_linear
+    dev = torch.device('cuda:0')
+    shape = L.LlamaShape(hidden=256, inter=512, layers=1, heads=4, vocab=300)
+    inps = L.synthetic_inputs(shape, 16, 128, dev)
+    w = L.random_block_weights(shape, 0, dev)
+    o = dict(opts)
+    if 'scale_bit_width' in o:
+        o['scale_bit_width'] = torch.tensor(o['scale_bit_width'])
+    res = L.quantize_llama(shape, lambda i: w, inps, batch_size=8, quant_options=o)
+    plain = L.quantize_llama(shape, lambda i: w, inps, batch_size=8)
+    assert set(res['data']) == set(plain['data'])
+    for name, meta in res['data'].items():
+        what = reconstruct_nn_linear(meta, torch.float16, dev).weight
+        assert torch.isfinite(what).all()
+        if 'scale_bit_width' in opts:
+            assert meta['qscale'] is not None and meta['sscale'].shape == (meta['scale'].shape[1],)
+            assert int(meta['qscale'].min()) >= 1 and int(meta['qscale'].max()) <= 16
+        rel = res['metrics'][name]['l2.0_error'] / res['metrics'][name]['l2.0_norm']
+        assert rel < 0.05, (name, rel)                       # 4-bit g128: a few percent of the weight energy at most
+    assert torch.isfinite(res['final_hidden']).all()
+    if opts.get('quant_mse') and 'scale_bit_width' not in opts:
+        W = w['mlp.down_proj']
+        G = W.shape[1] // 128
+        gs = torch.full([G], 128, dtype=torch.int32, device=dev)
+        gb = torch.full([G], 4, dtype=torch.int32, device=dev)
+        e0 = gptq_quant(W, None, gs, gb, quant_mse=False, save_device=dev)['metrics']['l2.0_error']
+        e1 = gptq_quant(W, None, gs, gb, quant_mse=True, quant_norm=2.0, save_device=dev)['metrics']['l2.0_error']
+        assert e1 <= e0 * (1 + 1e-6)                         # the grid contains p = 1, and norm 2 is the metric itself

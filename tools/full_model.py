@@ -33,6 +33,8 @@ def main():
     ap.add_argument('--bits', type=int, default=4)
     ap.add_argument('--pure', action='store_true', help='fp32 PyTorch-path semantics (gptq_use_kernel=False)')
     ap.add_argument('--eval-seqs', type=int, default=0, help='after quantising: pack the result (checkpoint.py) and run the layer-streamed perplexity of N sequences through K6 and through dense reconstructed weights (rank 0, N=1 only)')
+    ap.add_argument('--mse', action='store_true', help='Quantizer.mse grid search (quant_mse=True)')
+    ap.add_argument('--sym', action='store_true', help='symmetric grid (quant_symmetric=True)')
     ap.add_argument('--keep', default='cpu', help='where quant_meta ends up: cpu (as the reference) or cuda')
     args = ap.parse_args()
 
@@ -56,6 +58,7 @@ def main():
     res = L.quantize_llama(shape, lambda i: L.random_block_weights(shape, i, dev), inps, n_global=args.n_seq,
                            batch_size=args.batch, n_blocks=args.blocks, use_kernel_semantics=not args.pure, bits=args.bits,
                            save_device=torch.device(args.keep if args.keep == 'cpu' else dev),
+                           quant_options={'quant_mse': args.mse, 'quant_symmetric': args.sym},
                            log=(lambda s: print(s, file=sys.stderr, flush=True)))
     secs = torch.tensor([res['seconds']], dtype=torch.float64, device=dev)
     if world > 1:
@@ -70,7 +73,7 @@ def main():
             'extrapolated_full_model_s': round(float(secs.item()) / nb * shape.layers, 2),
             'phases_rank0_s': {k: round(v, 3) for k, v in sorted(res['timing'].items())},
             'mean_rel_l2_error': sum(errs) / len(errs),
-            'bits': args.bits, 'semantics': 'fp32-pure' if args.pure else 'kernel-compat', 'quant_meta_on': args.keep}), flush=True)
+            'bits': args.bits, 'quant_mse': args.mse, 'quant_symmetric': args.sym, 'semantics': 'fp32-pure' if args.pure else 'kernel-compat', 'quant_meta_on': args.keep}), flush=True)
     if args.eval_seqs > 0 and world == 1:
         import time
         import checkpoint
