@@ -61,18 +61,56 @@ def layer_phase_flops():
 
 
 class ClockSampler:
-    """nvidia-smi clocks/throttle reasons sampled while the timed region runs."""
+    """SM clock and clock-event (throttle) reasons sampled WHILE the timed region runs: an NVML polling thread
+    (nvidia_ml_py, one sample every 10 ms), or `nvidia-smi -lms` when NVML cannot be loaded."""
     Q = ('clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,'
          'clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,'
          'clocks_event_reasons.sw_power_cap')
 
     def __init__(self, index):
         self.index, self.rows, self.proc = index, [], None
+        self.nvml, self.handle, self.thread, self.running = None, None, None, False
+        self.sm, self.mx, self.reasons = [], None, set()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            try:
+                uuid = str(torch.cuda.get_device_properties(index).uuid)
+                uuid = uuid if uuid.startswith('GPU-') else 'GPU-' + uuid
+                self.handle = pynvml.nvmlDeviceGetHandleByUUID(uuid)
+            except Exception:
+                self.handle = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.mx = float(pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM))
+            self.nvml = pynvml
+        except Exception:
+            self.nvml = None
+
+    def _poll(self):
+        nv = self.nvml
+        names = (('hw_slowdown', nv.nvmlClocksEventReasonHwSlowdown),
+                 ('hw_thermal_slowdown', nv.nvmlClocksEventReasonHwThermalSlowdown),
+                 ('sw_thermal_slowdown', nv.nvmlClocksEventReasonSwThermalSlowdown),
+                 ('sw_power_cap', nv.nvmlClocksEventReasonSwPowerCap))
+        while self.running:
+            try:
+                self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.handle, nv.NVML_CLOCK_SM)))
+                mask = nv.nvmlDeviceGetCurrentClocksEventReasons(self.handle)
+                for name, bit in names:
+                    if mask & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            time.sleep(0.01)
 
     def start(self):
+        if self.nvml is not None:
+            self.running = True
+            self.thread = threading.Thread(target=self._poll, daemon=True)
+            self.thread.start()
+            return
         try:
             self.proc = subprocess.Popen(['nvidia-smi', '-i', str(self.index), f'--query-gpu={self.Q}',
-                                          '--format=csv,noheader,nounits', '-lms', '100'],
+                                          '--format=csv,noheader,nounits', '-lms', '50'],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             threading.Thread(target=self._read, daemon=True).start()
         except Exception:
@@ -83,22 +121,27 @@ class ClockSampler:
             self.rows.append([c.strip() for c in line.split(',')])
 
     def stop(self):
-        if self.proc is None:
+        if self.nvml is not None:
+            self.running = False
+            self.thread.join(timeout=1.0)
+            sm, mx, reasons, how = self.sm, self.mx, self.reasons, 'nvml 10 ms'
+        elif self.proc is None:
             return {'sm_mhz': None, 'sm_max_mhz': None, 'reasons': ['nvidia-smi unavailable']}
-        time.sleep(0.15)
-        self.proc.terminate()
-        sm, mx, reasons = [], None, set()
-        for r in self.rows:
-            try:
-                sm.append(float(r[0])); mx = float(r[1])
-            except Exception:
-                continue
-            for name, v in zip(('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap'), r[3:7]):
-                if v.lower().startswith('active'):
-                    reasons.add(name)
+        else:
+            time.sleep(0.15)
+            self.proc.terminate()
+            sm, mx, reasons, how = [], None, set(), 'nvidia-smi -lms 50'
+            for r in self.rows:
+                try:
+                    sm.append(float(r[0])); mx = float(r[1])
+                except Exception:
+                    continue
+                for name, v in zip(('hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap'), r[3:7]):
+                    if v.lower().startswith('active'):
+                        reasons.add(name)
         busy = sorted(sm)[len(sm) // 4:] if sm else []          # drop idle samples at the edges
         return {'sm_mhz': statistics.median(busy) if busy else None, 'sm_max_mhz': mx, 'reasons': sorted(reasons),
-                'samples': len(sm)}
+                'samples': len(sm), 'how': how}
 
 
 # ------------------------------------------------------------------------------------------
@@ -242,7 +285,15 @@ def run_step(ctx, W, X, Wh=None, Xh=None, timers=None):
             timers['syrk'].append((e0, e1, D))
         if ctx.dist is not None:
             sharded.allreduce_hessian(hook, N_SEQ)             # NCCL all-reduce of the partial Hessians
+        if timers is not None:
+            e2 = torch.cuda.Event(enable_timing=True)
+            e2.record(stream)
         hook.invert(damp_ratio=1e-2, act_order=True)
+        if timers is not None:
+            e3 = torch.cuda.Event(enable_timing=True)
+            e3.record(stream)
+            timers['phase'].append(('allreduce', e1, e2))
+            timers['phase'].append(('invert', e2, e3))
         for name, R, C, g in LINEARS:
             if g != gi:
                 continue
@@ -283,6 +334,10 @@ def run_step(ctx, W, X, Wh=None, Xh=None, timers=None):
                     ctx.dist.all_gather_into_tensor(sc, m['scale'])
                     packed = full
             out[name] = (packed, res['metrics'])
+        if timers is not None:
+            e4 = torch.cuda.Event(enable_timing=True)
+            e4.record(stream)
+            timers['phase'].append(('quantize', e3, e4))
         del hook
     if host:
         ctx.d2h_stream.synchronize()                           # the step's results are on the host
@@ -303,7 +358,7 @@ def gpu_main(args):
     sampler = ClockSampler(ctx.local)
     if ctx.rank == 0:
         sampler.start()
-    timers = {'syrk': []}
+    timers = {'syrk': [], 'phase': []}
     l0 = lib.gq_launch_count()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     ev0.record()
@@ -323,6 +378,9 @@ def gpu_main(args):
     per_d = {}
     for a, b, D in timers['syrk']:
         per_d.setdefault(D, []).append(a.elapsed_time(b) / 1e3)
+    phase_s = {}
+    for name, a, b in timers['phase']:
+        phase_s[name] = phase_s.get(name, 0.0) + a.elapsed_time(b) / 1e3 / args.steps
 
     # ---------------- end to end from host buffers
     for _ in range(max(1, args.warmup - 1)):
@@ -376,6 +434,9 @@ def gpu_main(args):
         'detail': {'syrk_s_per_layer': syrk_s / args.steps,
                    'syrk_s_by_D': {str(D): statistics.mean(v) for D, v in per_d.items()},
                    'other_s_per_layer': step_s - syrk_s / args.steps,
+                   'invert_s_per_layer': phase_s.get('invert'),
+                   'quantize_s_per_layer': phase_s.get('quantize'),        # prep + K3/K4 solve + metrics + result assembly + pack
+                   'allreduce_s_per_layer': phase_s.get('allreduce') if ctx.world > 1 else 0.0,
                    'full_model_32_layers_s': 32 * step_s},
     }
     if ctx.world == 1 and not args.no_cpu:

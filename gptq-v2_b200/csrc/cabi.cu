@@ -6,7 +6,7 @@ using namespace gq;
 
 static inline cudaStream_t S(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 
-namespace gq { unsigned long long g_launch_count = 0; int g_use_tf32x3 = 1; int g_solve_super = 8; int g_w4a16_path = 0; }
+namespace gq { unsigned long long g_launch_count = 0; int g_use_tf32x3 = 2; int g_solve_super = 8; int g_w4a16_path = 0; }
 
 extern "C" {
 
@@ -105,6 +105,10 @@ int gq_prep_weight_t2(const void* W, int dtype, const int64_t* perm, float* Wt, 
                       void* stream) {
   return prep_weight_t(W, dtype, perm, Wt, orig_t, colsq, R, C, S(stream));
 }
+int gq_prep_weight_t3(const void* W, int dtype, const int64_t* perm_inv, float* Wt, void* orig_t, float* colsq, int R, int C,
+                      void* stream) {
+  return prep_weight_scatter(W, dtype, perm_inv, Wt, orig_t, colsq, R, C, S(stream));
+}
 int gq_solve_metrics(const float* err_t, const float* quant_t, const void* orig_t, int dtype, size_t n, double* out2,
                      void* stream) {
   return solve_metrics(err_t, quant_t, orig_t, dtype, n, out2, S(stream));
@@ -143,7 +147,7 @@ int gq_set_w4a16_path(int path) {
   if (path >= 0 && path <= 2) gq::g_w4a16_path = path;
   return old;
 }
-int gq_set_tf32x3(int enable) { int old = gq::g_use_tf32x3; gq::g_use_tf32x3 = enable ? 1 : 0; return old; }
+int gq_set_tf32x3(int enable) { int old = gq::g_use_tf32x3; gq::g_use_tf32x3 = enable == 2 ? 2 : (enable ? 1 : 0); return old; }
 
 int gq_gemm_tf32x3(const float* A, const float* B, float* C, int M, int N, int K, int lda, int ldb, int ldc, float alpha,
                    int upper_only, void* stream) {

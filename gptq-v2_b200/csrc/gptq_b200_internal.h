@@ -48,7 +48,7 @@ int sgemm_batched(const GemmBatch& b, float alpha, float beta, int flags, cudaSt
 // ---- fp32-faithful tensor-core GEMM  C += alpha * A^T B  (3 x TF32 split, tcgen05)
 extern int g_w4a16_path;   // K6 dispatch: 0 auto; 1 never the small-batch mma.sync kernel; 2 the weights-on-N tcgen05 kernel for batch <= 128
 extern int g_solve_super;  // K4: blocks per super-block of the two-level lazy-batch update (1 = update everything after every block)
-extern int g_use_tf32x3;   // 1 (default): K4 / Cholesky updates on tcgen05 3xTF32; 0: fp32 SIMT GEMM (A/B parity hook)
+extern int g_use_tf32x3;   // 2 (default): K4 / Cholesky updates on tcgen05 3xTF32 with the truncation split (TF32_RAW_HI); 1: round-to-nearest split; 0: fp32 SIMT GEMM (A/B parity hook)
 struct Tf32Maps { CUtensorMap a, b, c; };
 // one GEMM of a batched launch: windows into the matrices the three tensor maps describe
 struct Tf32Problem {
@@ -63,6 +63,7 @@ enum : int {
   TF32_STORE = 2,          // C = alpha * A^T B (plain TMA store) instead of C += (TMA reduce-add)
   TF32_A_UPPER = 4,        // A (K x M) is upper triangular: k range of a tile ends at m0 + 128
   TF32_B_LOWER = 8,        // B (K x N) is lower triangular: k range of a tile starts at n0
+  TF32_RAW_HI = 16,        // split stage keeps the landed fp32 tile as hi (the MMA truncates it) and writes only lo
 };
 int gemm_tf32x3_batch(const Tf32Maps& maps, const Tf32Problem* probs, int count, float alpha, int flags, cudaStream_t st);
 int gemm_tf32x3_maps(Tf32Maps* maps, const float* A, int a_rows, int a_cols, int lda, const float* B, int b_rows,
@@ -105,6 +106,8 @@ int w4a16_gemm(const void* x, const uint32_t* qw, const void* scale_t, const uin
                void* y, void* workspace, int M, int N, int K, int group, int fmt, cudaStream_t st);
 int prep_weight_t(const void* W, int fmt, const int64_t* perm, float* Wt, void* orig_t, float* colsq, int R, int C,
                   cudaStream_t st);
+int prep_weight_scatter(const void* W, int fmt, const int64_t* perm_inv, float* Wt, void* orig_t, float* colsq, int R, int C,
+                        cudaStream_t st);
 int solve_metrics(const float* err_t, const float* quant_t, const void* orig_t, int fmt, size_t n, double* out2, cudaStream_t st);
 
 }  // namespace gq

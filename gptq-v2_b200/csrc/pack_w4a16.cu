@@ -45,6 +45,58 @@ __global__ void prep_weight_t_kernel(const T* __restrict__ W, const int64_t* __r
   }
 }
 
+// Scatter form of the same pass, used whenever the inverse permutation is at hand (HessianHook.perm_inv):
+//   Wt[pinv[k]][r] = (float) W[r][k]
+// The gather form above reads one 2-byte element per 32-byte sector (a warp touches 32 rows of one permuted column);
+// here W is read in its own order (128 B per warp and row), transposed through shared memory, and every destination row
+// segment Wt[c][r0 .. r0+31] is one full 128-byte line, wherever c = pinv[k] lands.  Tile = 32 rows x 64 source columns.
+template <typename T> struct Pair;
+template <> struct Pair<__half> { using type = __half2; };
+template <> struct Pair<__nv_bfloat16> { using type = __nv_bfloat162; };
+template <> struct Pair<float> { using type = float2; };
+
+template <typename T>
+__global__ void __launch_bounds__(256) prep_weight_scatter_kernel(const T* __restrict__ W, const int64_t* __restrict__ pinv,
+                                                                  float* __restrict__ Wt, T* __restrict__ orig_t,
+                                                                  float* __restrict__ colsq, int R, int C) {
+  using T2 = typename Pair<T>::type;
+  __shared__ T tile[64][34];                       // [source column][row], pitch 34: 2-element stores hit distinct banks
+  const int r0 = blockIdx.x * 32, k0 = blockIdx.y * 64;
+  const int tx = threadIdx.x, ty = threadIdx.y;    // (32, 8)
+  const int k = k0 + 2 * tx;
+#pragma unroll
+  for (int yy = ty; yy < 32; yy += 8) {
+    const int r = r0 + yy;
+    T a = T(0.f), b = T(0.f);
+    if (r < R && k + 1 < C) {                      // C is even (checked by the launcher)
+      const T2 v = *reinterpret_cast<const T2*>(W + (size_t)r * C + k);
+      a = v.x; b = v.y;
+    }
+    tile[2 * tx][yy] = a;
+    tile[2 * tx + 1][yy] = b;
+  }
+  __syncthreads();
+  const int r = r0 + tx;
+#pragma unroll
+  for (int kk = ty; kk < 64; kk += 8) {
+    const int ks = k0 + kk;                        // warp-uniform
+    if (ks >= C) break;
+    const int c = pinv ? (int)pinv[ks] : ks;
+    const T w = tile[kk][tx];
+    const float v = to_f32<T>(w);
+    if (r < R) {
+      Wt[(size_t)c * R + r] = v;
+      if (orig_t) orig_t[(size_t)c * R + r] = w;
+    }
+    if (colsq) {
+      float sq = v * v;                            // rows past R hold zeros
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
+      if (tx == 0) atomicAdd(colsq + c, sq);
+    }
+  }
+}
+
 // out[0] += sum err^2,  out[1] += sum (quant - orig)^2   over n elements of the (C, R) solver outputs
 template <typename T>
 __global__ void solve_metrics_kernel(const float* __restrict__ err_t, const float* __restrict__ quant_t,
@@ -138,6 +190,20 @@ int prep_weight_t(const void* W, int fmt, const int64_t* perm, float* Wt, void* 
   if (fmt == 0) prep_weight_t_kernel<__half><<<grid, block, 0, st>>>((const __half*)W, perm, Wt, (__half*)orig_t, colsq, R, C);
   else if (fmt == 1) prep_weight_t_kernel<__nv_bfloat16><<<grid, block, 0, st>>>((const __nv_bfloat16*)W, perm, Wt, (__nv_bfloat16*)orig_t, colsq, R, C);
   else if (fmt == 2) prep_weight_t_kernel<float><<<grid, block, 0, st>>>((const float*)W, perm, Wt, (float*)orig_t, colsq, R, C);
+  else return GQ_ERR_DTYPE;
+  return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
+}
+
+int prep_weight_scatter(const void* W, int fmt, const int64_t* perm_inv, float* Wt, void* orig_t, float* colsq, int R, int C,
+                        cudaStream_t st) {
+  if (C & 1) return GQ_ERR_SHAPE;
+  if (reinterpret_cast<uintptr_t>(W) & 7) return GQ_ERR_ALIGN;
+  dim3 block(32, 8), grid((R + 31) / 32, (C + 63) / 64);
+  if (colsq && cudaMemsetAsync(colsq, 0, (size_t)C * sizeof(float), st) != cudaSuccess) return GQ_ERR_CUDA;
+  GQ_LAUNCHED();
+  if (fmt == 0) prep_weight_scatter_kernel<__half><<<grid, block, 0, st>>>((const __half*)W, perm_inv, Wt, (__half*)orig_t, colsq, R, C);
+  else if (fmt == 1) prep_weight_scatter_kernel<__nv_bfloat16><<<grid, block, 0, st>>>((const __nv_bfloat16*)W, perm_inv, Wt, (__nv_bfloat16*)orig_t, colsq, R, C);
+  else if (fmt == 2) prep_weight_scatter_kernel<float><<<grid, block, 0, st>>>((const float*)W, perm_inv, Wt, (float*)orig_t, colsq, R, C);
   else return GQ_ERR_DTYPE;
   return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
 }

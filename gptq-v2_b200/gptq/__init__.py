@@ -103,18 +103,29 @@ def prep_weight_t(W: torch.Tensor, perm) -> torch.Tensor:
     return Wt
 
 
-def prep_weight_t2(W: torch.Tensor, perm):
+def prep_weight_t2(W: torch.Tensor, perm, perm_inv=None):
     """prep_weight_t plus what the result metrics need later: orig_t (C, R) in W's dtype (the same elements, kept because
-    the solver consumes Wt) and colsq (C) fp32 = sum_r W[r, perm[c]]^2.  Returns Wt, orig_t, colsq."""
+    the solver consumes Wt) and colsq (C) fp32 = sum_r W[r, perm[c]]^2.  Returns Wt, orig_t, colsq.
+    With perm_inv (HessianHook.perm_inv, or no permutation at all) the scatter-form kernel runs: W read in its own
+    order, 128-byte writes (gq_prep_weight_t3); with perm alone, the gather form (gq_prep_weight_t2)."""
     dev = require_cuda(W, perm)
     require_contig(W=W, perm=perm)
     R, C_ = W.shape
     Wt = torch.empty(C_, R, dtype=torch.float32, device=dev)
     orig_t = torch.empty(C_, R, dtype=W.dtype, device=dev)
     colsq = torch.empty(C_, dtype=torch.float32, device=dev)
+    scatter = (perm is None or perm_inv is not None) and C_ % 2 == 0
     with torch.cuda.device(dev):
-        check(lib.gq_prep_weight_t2(ptr(W), _cabi.DTYPE_CODE[W.dtype], ptr(perm), ptr(Wt), ptr(orig_t), ptr(colsq), R, C_,
-                                    stream_of(W)), 'gq_prep_weight_t2')
+        if scatter:
+            if perm_inv is not None:
+                require_cuda(W, perm_inv)
+                perm_inv = perm_inv.to(torch.int64).contiguous()
+                assert perm_inv.numel() == C_
+            check(lib.gq_prep_weight_t3(ptr(W), _cabi.DTYPE_CODE[W.dtype], ptr(perm_inv) if perm is not None else None,
+                                        ptr(Wt), ptr(orig_t), ptr(colsq), R, C_, stream_of(W)), 'gq_prep_weight_t3')
+        else:
+            check(lib.gq_prep_weight_t2(ptr(W), _cabi.DTYPE_CODE[W.dtype], ptr(perm), ptr(Wt), ptr(orig_t), ptr(colsq), R, C_,
+                                        stream_of(W)), 'gq_prep_weight_t2')
     return Wt, orig_t, colsq
 
 
@@ -313,6 +324,7 @@ def set_solve_super(blocks: int) -> int:
     return int(lib.gq_set_solve_super(int(blocks)))
 
 
-def set_tf32x3(enable: bool) -> bool:
-    """A/B parity hook; returns the previous setting."""
-    return bool(lib.gq_set_tf32x3(int(enable)))
+def set_tf32x3(enable) -> int:
+    """A/B hook: 0 = fp32 SIMT GEMM, 1 = 3xTF32 with the round-to-nearest split, 2 = 3xTF32 with the truncation split
+    (hi is the landed tile itself); returns the previous setting."""
+    return int(lib.gq_set_tf32x3(int(enable)))

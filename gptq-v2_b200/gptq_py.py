@@ -138,7 +138,7 @@ def gptq_quant(
         U = hessian_hook.hessian_inv.contiguous()
 
     # (C, R) fp32, permuted (ref :90-94,128); orig_t / colsq feed the result metrics after the solver has consumed Wt
-    Wt, orig_t, colsq = _ops.prep_weight_t2(weight_c, perm)
+    Wt, orig_t, colsq = _ops.prep_weight_t2(weight_c, perm, getattr(hessian_hook, 'perm_inv', None) if perm is not None else None)
     solver_ok = gs in (32, 64, 128)
     qscale_gr = sscale_g = None
     if not plain or not solver_ok or (gptq_use_kernel and hessian_hook is not None):

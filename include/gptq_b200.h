@@ -107,6 +107,12 @@ int gq_prep_weight_t(const void* W, int dtype, const int64_t* perm, float* Wt, i
  * solver has consumed Wt; colsq (C) fp32: sum_r W[r][perm[c]]^2 (for gptq_norm, gptq_py.py:198). */
 int gq_prep_weight_t2(const void* W, int dtype, const int64_t* perm, float* Wt, void* orig_t, float* colsq, int R, int C,
                       void* stream);
+/* Scatter form of gq_prep_weight_t2 for callers that hold the INVERSE permutation (HessianHook.perm_inv,
+ * gptq_py.py:49): Wt[perm_inv[k]][r] = (float) W[r][k], the same result as gq_prep_weight_t2 with perm, but W is read
+ * in its own order and every write is a full 128-byte line (the gather form reads one element per 32-byte sector).
+ * perm_inv may be NULL (identity); C must be even; orig_t / colsq as above (each may be NULL). */
+int gq_prep_weight_t3(const void* W, int dtype, const int64_t* perm_inv, float* Wt, void* orig_t, float* colsq, int R, int C,
+                      void* stream);
 /* Result metrics of one linear in one pass (gptq_py.py:196, 232-233): out2[0] = sum err_t^2, out2[1] = sum (quant_t -
  * orig_t)^2 over n = R*C elements (n % 4 == 0); out2 is two doubles on the device, overwritten. */
 int gq_solve_metrics(const float* err_t, const float* quant_t, const void* orig_t, int dtype, size_t n, double* out2,
@@ -142,7 +148,8 @@ int gq_sgemm(const float* A, const float* B, float* C, int M, int N, int K, int 
 int gq_gemm_tf32x3(const float* A, const float* B, float* C, int M, int N, int K, int lda, int ldb, int ldc, float alpha,
                    int upper_only, void* stream);
 /* A/B parity hook: 0 routes K4 and the Cholesky trailing update through the fp32 SIMT GEMM instead of the
- * 3xTF32 tensor-core GEMM.  Returns the previous setting. */
+ * 3xTF32 tensor-core GEMM; 1 = 3xTF32 with x = rna_tf32(x) + lo; 2 = 3xTF32 with x = trunc_tf32(x) + lo (the landed
+ * fp32 tile is the hi operand as it is: kind::tf32 reads only the upper 19 bits).  Returns the previous setting. */
 int gq_set_tf32x3(int enable);
 /* Tuning hook: blocks per super-block of K4's two-level lazy-batch update (default 8; 1 = the reference's schedule, one
  * full trailing update per block, gptq_py.py:139).  Returns the previous setting. */

@@ -127,6 +127,30 @@ def test_gemm_tf32x3_is_fp32_faithful(M, N, K, upper):
     assert err <= 4e-6 * scale, (err, scale)
 
 
+@pytest.mark.parametrize('M,N,K', [(128, 256, 128), (3968, 4096, 128), (1024, 768, 1024)])
+def test_gemm_tf32x3_truncation_split(M, N, K):
+    """Mode 2: the landed fp32 tile is the hi operand as it is (the tensor core reads its upper 19 bits) and only
+    lo = rna_tf32(x - trunc_tf32(x)) is written.  Same fp32-faithful bound as the round-to-nearest split."""
+    import gptq
+    g = torch.Generator(device='cuda').manual_seed(M + N + K + 1)
+    A = torch.randn(K, M, device='cuda', generator=g)
+    B = torch.randn(K, N, device='cuda', generator=g)
+    C0 = torch.randn(M, N, device='cuda', generator=g)
+    want = C0.double() - A.double().t() @ B.double()
+    scale = (A.abs().double().t() @ B.abs().double()).max().item()
+    errs = {}
+    for mode in (1, 2):
+        prev = gptq.set_tf32x3(mode)
+        try:
+            C = C0.clone()
+            gptq.gemm_tf32x3(A, B, C, M, N, K, M, N, N, -1.0, False)
+            torch.cuda.synchronize()
+        finally:
+            gptq.set_tf32x3(prev)
+        errs[mode] = (C.double() - want).abs().max().item()
+    assert errs[1] <= 4e-6 * scale and errs[2] <= 4e-6 * scale, (errs, scale)
+
+
 def test_tf32x3_switch_gives_same_codes():
     """K4 on tensor cores (3xTF32) vs fp32 SIMT: the quantisation codes must agree to >= 99.9%."""
     import gptq
@@ -135,7 +159,7 @@ def test_tf32x3_switch_gives_same_codes():
     inv = O.hessian_invert(H, n, 1e-2, True)
     U = inv['U'].cuda().contiguous()
     outs = []
-    for enable in (True, False):
+    for enable in (1, 0, 2):
         prev = gptq.set_tf32x3(enable)
         try:
             Wt = gptq.prep_weight_t(W.cuda().contiguous(), inv['perm'].cuda())
@@ -144,3 +168,4 @@ def test_tf32x3_switch_gives_same_codes():
         finally:
             gptq.set_tf32x3(prev)
     assert (outs[0] == outs[1]).float().mean().item() >= 0.999
+    assert (outs[2] == outs[1]).float().mean().item() >= 0.999

@@ -158,3 +158,28 @@ def test_w4a16_paths_agree(M):
     torch.cuda.synchronize()
     for y in ys[1:]:
         assert ((y - ys[0]).norm() / ys[0].norm()).item() <= 5e-3
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('dtype', [torch.float16, torch.bfloat16, torch.float32])
+@pytest.mark.parametrize('R,C', [(64, 128), (100, 200), (4096, 4096), (36, 1030)])
+def test_prep_weight_scatter_form_matches_gather_form(dtype, R, C):
+    """gq_prep_weight_t3 (inverse permutation, coalesced scatter) == gq_prep_weight_t2 (permutation, gather): Wt and
+    orig_t bit for bit, colsq to fp32 summation order; and both equal W[:, perm].t()."""
+    import gptq
+    g = torch.Generator(device='cuda').manual_seed(R * 7 + C)
+    W = (torch.randn(R, C, device='cuda', generator=g) * 0.02).to(dtype)
+    perm = torch.randperm(C, device='cuda', generator=g)
+    pinv = torch.argsort(perm)
+    Wt_g, o_g, sq_g = gptq.prep_weight_t2(W, perm)
+    Wt_s, o_s, sq_s = gptq.prep_weight_t2(W, perm, pinv)
+    torch.cuda.synchronize()
+    want = W[:, perm].t().contiguous()
+    assert torch.equal(Wt_s, want.float()) and torch.equal(Wt_g, Wt_s)
+    assert torch.equal(o_s, want) and torch.equal(o_g, o_s)
+    ref_sq = (want.double() ** 2).sum(dim=1)
+    assert torch.allclose(sq_s.double(), ref_sq, rtol=1e-5, atol=1e-12)
+    assert torch.allclose(sq_g.double(), ref_sq, rtol=1e-5, atol=1e-12)
+    # no permutation: identity scatter
+    Wt_i, o_i, sq_i = gptq.prep_weight_t2(W, None)
+    assert torch.equal(Wt_i, W.t().float().contiguous()) and torch.equal(o_i, W.t().contiguous())

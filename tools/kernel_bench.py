@@ -128,6 +128,19 @@ def bench_quantizer():
                               'branch': 'kernel' if use_kernel else 'fp32', 'ms': t * 1e3}))
 
 
+def bench_prep():
+    """transposing / permuting weight prep: gather form (perm) vs scatter form (perm_inv)"""
+    for R, C in ((4096, 4096), (11008, 4096), (4096, 11008)):
+        W = (torch.randn(R, C, device=dev) * 0.02).half()
+        perm = torch.randperm(C, device=dev)
+        pinv = torch.argsort(perm)
+        tg = timeit(lambda: gptq.prep_weight_t2(W, perm))
+        ts = timeit(lambda: gptq.prep_weight_t2(W, perm, pinv))
+        byts = R * C * (2 + 4 + 2)
+        print(json.dumps({'k': 'prep_weight', 'R': R, 'C': C, 'gather_us': tg * 1e6, 'scatter_us': ts * 1e6,
+                          'scatter_GBps': byts / ts / 1e9}))
+
+
 def bench_sgemm():
     torch.backends.cuda.matmul.allow_tf32 = False
     for M, N, K, flags in ((3968, 4096, 128, 1), (10880, 4096, 128, 1), (4096, 4096, 128, 3), (4096, 4096, 4096, 0)):
@@ -234,6 +247,8 @@ def bench_refext():
 
 
 if __name__ == '__main__':
+    if os.environ.get('GQ_TF32_MODE'):
+        gptq.set_tf32x3(int(os.environ['GQ_TF32_MODE']))
     which = sys.argv[1:] or ['syrk', 'invert', 'solve', 'sgemm', 'tf32', 'w4a16', 'refext']
     for w in which:
         globals()['bench_' + w]()
