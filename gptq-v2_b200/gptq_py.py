@@ -71,7 +71,7 @@ class HessianHook:
             tries += 1
             # cumulative damping: try k factors H + k*damp*I (ref :58)
             Hp, U, info = _ops.hessian_invert(H, self.perm, scale, damp * tries)
-            if int(info.item()) == 0 and bool(torch.isfinite(U.diagonal()).all()):
+            if not bool((info != 0) | ~torch.isfinite(U.diagonal()).all()):         # one host sync per try (ref :63)
                 break
         assert max_try >= 0
         self.invert_tries = tries
@@ -214,12 +214,7 @@ def gptq_quant(
     norm_sum = (colsq_orig.double() / U.diagonal().double() ** 2).sum()
     l2_norm = (weight.abs() ** 2.).mean()                                        # ref :237 (fp16 / bf16 arithmetic)
     n_el = float(n_rows * n_columns)
-    e2, d2, ns, l2n = torch.stack([sums[0], sums[1], norm_sum, l2_norm.double()]).tolist()
-    if hessian_hook is None:
-        gptq_error, gptq_norm = 0.0, 0.0                                         # ref :198 (error == 0)
-    else:
-        gptq_error, gptq_norm = e2 / n_el, ns / n_el
-    metrics: dict[str, float] = {'gptq_error': gptq_error, 'gptq_norm': gptq_norm}
+    stats = torch.stack([sums[0], sums[1], norm_sum, l2_norm.double()])          # read back AFTER the result assembly is queued
 
     qweight, _ = _ops.transpose_pack_int4(codes_t, want_codes=True, want_packed=False)   # (R, C) uint8, permuted order
     scale = scale_gr.t().to(dtype=dtype).contiguous()                           # (R, G)
@@ -244,8 +239,6 @@ def gptq_quant(
             qscale, sscale = qscale[:, ig].contiguous(), sscale[ig]
     perm_inv = perm16.argsort().to(dtype=torch.int16)                           # ref :226
 
-    metrics.update({'l2.0_error': d2 / n_el, 'l2.0_norm': l2n})
-
     quant_meta: dict[str, torch.Tensor] = {
         'qweight': qweight.to(device=save_device),
         'scale': scale.to(device=save_device),
@@ -257,4 +250,12 @@ def gptq_quant(
         'group_bit_widths': bits_out.to(device=save_device),
         'scale_bit_width': scale_bit_width.to(dtype=torch.uint8, device=save_device) if scale_bit_width is not None else None,
     }
+    # the one host sync of the call, after every kernel of the result assembly has been queued behind the solver
+    e2, d2, ns, l2n = stats.tolist()
+    if hessian_hook is None:
+        gptq_error, gptq_norm = 0.0, 0.0                                         # ref :198 (error == 0)
+    else:
+        gptq_error, gptq_norm = e2 / n_el, ns / n_el
+    metrics: dict[str, float] = {'gptq_error': gptq_error, 'gptq_norm': gptq_norm,
+                                 'l2.0_error': d2 / n_el, 'l2.0_norm': l2n}
     return {'quant_meta': quant_meta, 'metrics': metrics}
