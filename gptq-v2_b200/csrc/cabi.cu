@@ -61,6 +61,14 @@ int gq_hessian_invert(const float* H, int D, const int64_t* perm, float scale, f
   return chol_inverse_upper(A, D, U, Wb, tmp, info_dev, S(stream));
 }
 
+size_t gq_upper_packed_floats(int D) { return D > 0 ? upper_packed_floats(D) : 0; }
+int gq_pack_upper(const float* H, int D, float* packed, void* stream) {
+  return upper_tiles(const_cast<float*>(H), packed, D, 1, S(stream));
+}
+int gq_unpack_upper(const float* packed, int D, float* H, void* stream) {
+  return upper_tiles(H, const_cast<float*>(packed), D, 0, S(stream));
+}
+
 int gq_quantize_range(float* quant, const float* scale, int16_t* out_q, const float* qzero, float maxq,
                       const float* hessian_inv, float* weights, float* error, int C, int R, int a, int b,
                       void* stream) {

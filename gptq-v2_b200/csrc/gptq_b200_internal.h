@@ -75,6 +75,8 @@ int gemm_tf32x3(const Tf32Maps& maps, int M, int N, int K, int a_row0, int a_col
 int hessian_gather(const float* H, int D, const int64_t* perm, float scale, float damp, float* Hp, float* Arev,
                    cudaStream_t st);
 int chol_inverse_upper(float* A, int D, float* U, float* Wb, float* tmp, int* info_dev, cudaStream_t st);
+size_t upper_packed_floats(int D);
+int upper_tiles(float* H, float* packed, int D, int pack, cudaStream_t st);
 int chol_factor_panel(float* A, int D, int o, int n, int rest, int* info_dev, cudaStream_t st);
 
 // ---- K3/K4

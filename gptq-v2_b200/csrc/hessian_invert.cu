@@ -121,7 +121,43 @@ __global__ void reverse_lower_kernel(const float* __restrict__ Wb, float* __rest
   U[(size_t)i * D + j] = (i <= j) ? Wb[(size_t)(D - 1 - i) * D + (D - 1 - j)] : 0.f;
 }
 
+// ---------------------------------------------------------------- packed upper triangle (multi-GPU reduction payload)
+// Tile (bi, bj >= bi) of 128 x 128 floats -> packed[t], t = bi*nb - bi*(bi-1)/2 + (bj - bi); edge tiles are zero-padded.
+template <bool PACK>
+__global__ void __launch_bounds__(256) upper_tiles_kernel(float* __restrict__ H, float* __restrict__ packed, int D, int nb) {
+  const int bj = blockIdx.x, bi = blockIdx.y;
+  if (bj < bi) return;
+  const size_t t = (size_t)bi * nb - (size_t)bi * (bi - 1) / 2 + (bj - bi);
+  float* tile = packed + t * (size_t)(NB * NB);
+  const int r0 = bi * NB, c0 = bj * NB;
+  for (int idx = threadIdx.x; idx < NB * (NB / 4); idx += 256) {
+    const int r = idx >> 5, c4 = (idx & 31) * 4;
+    const bool in = (r0 + r < D) && (c0 + c4 < D);          // D % 4 == 0
+    float* h = H + (size_t)(r0 + r) * D + c0 + c4;
+    float4* pk = reinterpret_cast<float4*>(tile + r * NB + c4);
+    if (PACK) *pk = in ? *reinterpret_cast<const float4*>(h) : make_float4(0.f, 0.f, 0.f, 0.f);
+    else if (in) *reinterpret_cast<float4*>(h) = *pk;
+  }
+}
+
 }  // namespace
+
+size_t upper_packed_floats(int D) {
+  const size_t nb = (size_t)(D + NB - 1) / NB;
+  return nb * (nb + 1) / 2 * (size_t)(NB * NB);
+}
+
+// pack = 1: H's upper 128 x 128 tiles -> packed; pack = 0: packed -> the same tiles of H (everything else untouched)
+int upper_tiles(float* H, float* packed, int D, int pack, cudaStream_t st) {
+  if (D <= 0 || (D & 3)) return GQ_ERR_SHAPE;
+  if ((reinterpret_cast<uintptr_t>(H) | reinterpret_cast<uintptr_t>(packed)) & 15) return GQ_ERR_ALIGN;
+  const int nb = (D + NB - 1) / NB;
+  dim3 grid(nb, nb);
+  GQ_LAUNCHED();
+  if (pack) upper_tiles_kernel<true><<<grid, 256, 0, st>>>(H, packed, D, nb);
+  else upper_tiles_kernel<false><<<grid, 256, 0, st>>>(H, packed, D, nb);
+  return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
+}
 
 int hessian_gather(const float* H, int D, const int64_t* perm, float scale, float damp, float* Hp, float* Arev,
                    cudaStream_t st) {

@@ -14,7 +14,7 @@ import torch
 from . import _cabi
 from ._cabi import GptqB200Error, check, lib, ptr, require_contig, require_cuda, stream_of
 
-__all__ = ['accumulate_hessian', 'gptq_quantize_range', 'hessian_syrk', 'hessian_invert', 'prep_weight_t', 'prep_weight_t2', 'solve_metrics', 'gptq_solve_ex', 'find_params', 'mse_refine',
+__all__ = ['accumulate_hessian', 'gptq_quantize_range', 'hessian_syrk', 'hessian_invert', 'pack_upper', 'unpack_upper', 'prep_weight_t', 'prep_weight_t2', 'solve_metrics', 'gptq_solve_ex', 'find_params', 'mse_refine',
            'gptq_solve', 'gptq_solve_static', 'pack_int4', 'unpack_int4', 'transpose_pack_int4', 'w4a16_gemm', 'sgemm', 'gemm_tf32x3', 'set_tf32x3', 'set_solve_super', 'set_w4a16_path',
            'GptqB200Error']
 
@@ -89,6 +89,28 @@ def hessian_invert(H: torch.Tensor, perm, scale: float, damp: float, want_hp: bo
         check(lib.gq_hessian_invert(ptr(H), D, ptr(perm), float(scale), float(damp), ptr(Hp), ptr(U), ptr(work),
                                     ptr(info), stream_of(H)), 'gq_hessian_invert')
     return Hp, U, info
+
+
+def pack_upper(H: torch.Tensor) -> torch.Tensor:
+    """Upper 128 x 128 tiles of H (D, D) fp32 -> one contiguous fp32 buffer (the all-reduce payload of sharded.py)."""
+    dev = require_cuda(H)
+    require_contig(H=H)
+    D = H.shape[0]
+    assert H.dtype == torch.float32 and H.shape == (D, D)
+    packed = torch.empty(lib.gq_upper_packed_floats(D), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.gq_pack_upper(ptr(H), D, ptr(packed), stream_of(H)), 'gq_pack_upper')
+    return packed
+
+
+def unpack_upper(packed: torch.Tensor, H: torch.Tensor) -> None:
+    """Inverse of pack_upper, in place: the upper tiles of H are overwritten, the rest is left alone."""
+    dev = require_cuda(packed, H)
+    require_contig(packed=packed, H=H)
+    D = H.shape[0]
+    assert packed.dtype == H.dtype == torch.float32 and packed.numel() == lib.gq_upper_packed_floats(D)
+    with torch.cuda.device(dev):
+        check(lib.gq_unpack_upper(ptr(packed), D, ptr(H), stream_of(H)), 'gq_unpack_upper')
 
 
 def prep_weight_t(W: torch.Tensor, perm) -> torch.Tensor:

@@ -26,6 +26,9 @@ SIGNATURES = {
     'accumulate_hessian_bf16_fp32_cuda': (_i, [_vp, _vp, _i, _i]),
     'gq_invert_workspace_floats': (C.c_size_t, [_i]),
     'gq_hessian_invert': (_i, [_vp, _i, _vp, _f, _f, _vp, _vp, _vp, _vp, _vp]),
+    'gq_upper_packed_floats': (C.c_size_t, [_i]),
+    'gq_pack_upper': (_i, [_vp, _i, _vp, _vp]),
+    'gq_unpack_upper': (_i, [_vp, _i, _vp, _vp]),
     'gq_quantize_range': (_i, [_vp, _vp, _vp, _vp, _f, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     'gq_gptq_solve': (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _f, _vp]),
     'gq_gptq_solve_static': (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _f, _vp]),

@@ -5,7 +5,7 @@ One process per GPU (`torch.distributed`, backend nccl on the box, gloo in the C
 two ways the algebra allows:
 
   1. H = sum over calibration sequences of X^T X  ->  rank p accumulates sequences [p*n/P, (p+1)*n/P) with K1,
-     then ONE all_reduce(sum, fp32) of H per Hessian group.  `n_samples` becomes the global sequence count, so the
+     then ONE all_reduce(sum, fp32) of H's packed upper triangle per Hessian group.  `n_samples` becomes the global sequence count, so the
      2/n scale of invert() (gptq_py.py:41) is unchanged.
   2. Given U = chol(H^-1), the rows of W are independent (gptq_py.py:187-193, quant.py:114-118 are per row) ->
      rank p solves rows [p*R/P, (p+1)*R/P) of every linear of the group; codes / scales / zeros are all-gathered.
@@ -50,7 +50,16 @@ def allreduce_hessian(hook, n_samples_global: Optional[int] = None, group=None) 
         if n_samples_global is not None:
             hook.n_samples = n_samples_global
         return
-    dist.all_reduce(hook.hessian, op=dist.ReduceOp.SUM, group=group)
+    H = hook.hessian
+    if H.is_cuda and getattr(hook, 'upper_only', True) and H.shape[0] % 4 == 0:
+        # K1 keeps only the upper triangle (HessianHook.add_batch, mode 0) and invert() reads nothing else: reduce the
+        # upper 128 x 128 tiles as ONE contiguous message of about half the bytes (242 MB instead of 485 MB at D = 11008)
+        import gptq as _ops
+        packed = _ops.pack_upper(H)
+        dist.all_reduce(packed, op=dist.ReduceOp.SUM, group=group)
+        _ops.unpack_upper(packed, H)
+    else:
+        dist.all_reduce(H, op=dist.ReduceOp.SUM, group=group)
     if n_samples_global is None:
         t = torch.tensor([hook.n_samples], dtype=torch.int64, device=hook.hessian.device)
         dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)

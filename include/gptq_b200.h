@@ -56,6 +56,15 @@ size_t gq_invert_workspace_floats(int D);
 int gq_hessian_invert(const float* H, int D, const int64_t* perm, float scale, float damp, float* Hp, float* U,
                       float* work, int* info_dev, void* stream);
 
+/* ---- multi-GPU reduction payload (no reference counterpart: the reference is single-GPU).
+ * K1 mode 0 maintains only the upper triangle of H, so only that is summed over ranks: the upper 128 x 128 tiles of
+ * H (D, D) are copied into a contiguous buffer of gq_upper_packed_floats(D) floats (tile (bi, bj >= bi) at index
+ * bi*nb - bi*(bi-1)/2 + bj - bi, nb = ceil(D/128), edge tiles zero-padded), all-reduced by NCCL as ONE message of about
+ * half the bytes of H, and copied back.  gq_unpack_upper leaves everything outside those tiles untouched.  D % 4 == 0. */
+size_t gq_upper_packed_floats(int D);
+int gq_pack_upper(const float* H, int D, float* packed, void* stream);
+int gq_unpack_upper(const float* packed, int D, float* H, void* stream);
+
 /* ---- K3+K4, compat: quantize_range (gptq_cpp.cpp:33-84) on raw pointers.
  * Layout is the reference's transposed one: weights/quant/error/out_q are (C, R) row-major
  * with R = number of weight rows ("columns" in the reference's naming), hessian_inv (C, C).

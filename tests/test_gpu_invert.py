@@ -169,3 +169,29 @@ def test_tf32x3_switch_gives_same_codes():
             gptq.set_tf32x3(prev)
     assert (outs[0] == outs[1]).float().mean().item() >= 0.999
     assert (outs[2] == outs[1]).float().mean().item() >= 0.999
+
+
+@pytest.mark.parametrize('D', [128, 200, 1000, 4096])
+def test_pack_unpack_upper_tiles(D):
+    """The multi-GPU reduction payload: upper 128 x 128 tiles of H packed into one contiguous buffer and back, bit for
+    bit; everything outside those tiles is left alone; a sum over two 'ranks' done on the packed buffers equals the sum
+    done on the matrices wherever invert() reads (the upper triangle)."""
+    import gptq
+    g = torch.Generator(device='cuda').manual_seed(D)
+    H1 = torch.randn(D, D, device='cuda', generator=g)
+    H2 = torch.randn(D, D, device='cuda', generator=g)
+    nb = (D + 127) // 128
+    p1, p2 = gptq.pack_upper(H1), gptq.pack_upper(H2)
+    assert p1.numel() == nb * (nb + 1) // 2 * 128 * 128
+    out = torch.full((D, D), -7.0, device='cuda')
+    gptq.unpack_upper(p1, out)
+    torch.cuda.synchronize()
+    tile_mask = torch.zeros(D, D, dtype=torch.bool, device='cuda')
+    for bi in range(nb):
+        tile_mask[bi * 128:(bi + 1) * 128, bi * 128:] = True
+    assert torch.equal(out[tile_mask], H1[tile_mask])
+    assert (out[~tile_mask] == -7.0).all()
+    Hs = H1.clone()
+    gptq.unpack_upper(p1 + p2, Hs)
+    triu = torch.ones(D, D, dtype=torch.bool, device='cuda').triu()
+    assert torch.equal(Hs[triu], (H1 + H2)[triu])
