@@ -17,9 +17,10 @@ The transformer forward that produces the activations is outside the hot path (S
   cpu_baseline / --impl reference : the oracle port of gptq_py.py's fp32 path on the host cores,
           on a bounded sample, extrapolated to one layer by the flop counts of each phase.
 
-N > 1 (torchrun): calibration sequences are sharded over ranks, partial Hessians are summed by an
-NCCL all-reduce, the factorisation is replicated, the rows of every linear are sharded over
-ranks and the codes all-gathered ("strong" scaling of one layer).
+N > 1 (torchrun): calibration sequences are sharded over ranks, partial Hessians (packed upper triangle)
+are summed by an NCCL all-reduce, the factorisation is replicated, the linears of each Hessian group
+are spread over the ranks (rows sharded only inside a linear's own ranks, sharded.plan_group) and the
+codes all-gathered, one message per group ("strong" scaling of one layer).
 """
 import argparse
 import json
@@ -195,6 +196,13 @@ class Ctx:
             self.dist.barrier()
         torch.cuda.synchronize()
 
+    def sum_over_ranks(self, v):
+        if self.dist is None:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device=self.dev)
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
+        return float(t.item())
+
     def max_over_ranks(self, v):
         if self.dist is None:
             return v
@@ -240,6 +248,9 @@ def run_step(ctx, W, X, Wh=None, Xh=None, timers=None):
     stream = torch.cuda.current_stream()
     h2d = d2h = 0
     out = {}
+    # the linears of a Hessian group are spread over the ranks first, rows only inside a linear's own ranks
+    groups = [[l for l in LINEARS if l[3] == gi] for gi in range(len(GROUP_D))]
+    plans = [sharded.plan_group([l[1] for l in grp], ctx.world, 4) for grp in groups]
     if host:
         if not hasattr(ctx, 'h2d_stream'):
             ctx.h2d_stream, ctx.d2h_stream = torch.cuda.Stream(), torch.cuda.Stream()
@@ -254,15 +265,15 @@ def run_step(ctx, W, X, Wh=None, Xh=None, timers=None):
                     ev.record(ctx.h2d_stream)
                     xdev[gi, ci], xready[gi, ci] = buf, ev
                     h2d += buf.numel() * 2
-                for name, R, C, g in LINEARS:
-                    if g != gi:
+                for i, lo, hi, r in plans[gi]:
+                    if r != ctx.rank:
                         continue
-                    r0, r1 = sharded.shard_range(R, ctx.world, ctx.rank, 4)
-                    w = torch.empty(r1 - r0, C, device=ctx.dev, dtype=torch.float16)
-                    w.copy_(Wh[name][r0:r1], non_blocking=True)
+                    name, _, C, _ = groups[gi][i]
+                    w = torch.empty(hi - lo, C, device=ctx.dev, dtype=torch.float16)
+                    w.copy_(Wh[name][lo:hi], non_blocking=True)
                     ev = torch.cuda.Event()
                     ev.record(ctx.h2d_stream)
-                    wdev[name], wready[name] = w, ev
+                    wdev[gi, i, lo, hi], wready[gi, i, lo, hi] = w, ev
                     h2d += w.numel() * 2
     for gi, D in enumerate(GROUP_D):
         hook = HessianHook()
@@ -294,45 +305,43 @@ def run_step(ctx, W, X, Wh=None, Xh=None, timers=None):
             e3.record(stream)
             timers['phase'].append(('allreduce', e1, e2))
             timers['phase'].append(('invert', e2, e3))
-        for name, R, C, g in LINEARS:
-            if g != gi:
-                continue
-            r0, r1 = sharded.shard_range(R, ctx.world, ctx.rank, 4)
+        grp = groups[gi]
+        C = grp[0][2]
+        gs = torch.full([C // GROUP], GROUP, dtype=torch.int32)
+        bw = torch.full([C // GROUP], BITS, dtype=torch.int32)
+
+        def shard_of(i, lo, hi, gi=gi, grp=grp):
+            if not host:
+                return W[grp[i][0]][lo:hi]
+            stream.wait_event(wready[gi, i, lo, hi])
+            w = wdev.pop((gi, i, lo, hi))
+            w.record_stream(stream)                            # allocated on the copy stream, consumed here
+            return w
+
+        metas = [torch.empty(l[1], l[2], dtype=torch.float16, device='meta') for l in grp]
+        results = sharded.gptq_quant_group_sharded(
+            metas, hook, shard_of=shard_of, group_sizes=gs, group_bit_widths=bw, scale_bit_width=None,
+            gptq_use_kernel=False, gptq_block_sizes=gs, quant_symmetric=False, quant_mse=False, save_device=ctx.dev)
+        for (name, R, C, _), res in zip(grp, results):
+            m = res['quant_meta']                              # complete on every rank (all-gathered for N > 1)
             if host:
-                stream.wait_event(wready[name])
-                w = wdev.pop(name)
-                w.record_stream(stream)
-            else:
-                w = W[name][r0:r1]
-            gs = torch.full([C // GROUP], GROUP, dtype=torch.int32)
-            bw = torch.full([C // GROUP], BITS, dtype=torch.int32)
-            res = gptq_quant(weight=w, hessian_hook=hook, group_sizes=gs, group_bit_widths=bw, scale_bit_width=None,
-                             gptq_use_kernel=False, gptq_block_sizes=gs, quant_symmetric=False, quant_mse=False,
-                             save_device=ctx.dev)
-            m = res['quant_meta']
-            if host:
-                # quant_meta -> pinned host buffers on the result stream (joined at the end of the step)
-                done = torch.cuda.Event()
-                done.record(stream)
-                with torch.cuda.stream(ctx.d2h_stream):
-                    ctx.d2h_stream.wait_event(done)
-                    for key in ('qweight', 'scale', 'qzero', 'perm_inv'):
-                        t = m[key]
-                        hb = ctx.pinned_out.get((name, key))
-                        if hb is None or hb.shape != t.shape:
-                            hb = ctx.pinned_out[name, key] = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
-                        hb.copy_(t, non_blocking=True)
-                        t.record_stream(ctx.d2h_stream)
-                        d2h += t.numel() * t.element_size()
                 packed = None
+                if ctx.rank == 0:
+                    # quant_meta -> pinned host buffers on the result stream (joined at the end of the step)
+                    done = torch.cuda.Event()
+                    done.record(stream)
+                    with torch.cuda.stream(ctx.d2h_stream):
+                        ctx.d2h_stream.wait_event(done)
+                        for key in ('qweight', 'scale', 'qzero', 'perm_inv'):
+                            t = m[key]
+                            hb = ctx.pinned_out.get((name, key))
+                            if hb is None or hb.shape != t.shape:
+                                hb = ctx.pinned_out[name, key] = torch.empty(t.shape, dtype=t.dtype, pin_memory=True)
+                            hb.copy_(t, non_blocking=True)
+                            t.record_stream(ctx.d2h_stream)
+                            d2h += t.numel() * t.element_size()
             else:
                 packed = pack_int4(m['qweight'])
-                if ctx.dist is not None:
-                    full = torch.empty(R, C // 8, dtype=torch.int32, device=ctx.dev)
-                    ctx.dist.all_gather_into_tensor(full, packed)
-                    sc = torch.empty(R, C // GROUP, dtype=m['scale'].dtype, device=ctx.dev)
-                    ctx.dist.all_gather_into_tensor(sc, m['scale'])
-                    packed = full
             out[name] = (packed, res['metrics'])
         if timers is not None:
             e4 = torch.cuda.Event(enable_timing=True)
@@ -394,6 +403,8 @@ def gpu_main(args):
     e1.record()
     ctx.barrier()
     e2e_s = ctx.max_over_ranks(max(e0.elapsed_time(e1) / 1e3, time.perf_counter() - t0) / args.steps)
+    h2d_all = int(ctx.sum_over_ranks(h2d))                     # every rank stages its own sequences and weight rows
+    d2h_all = int(ctx.sum_over_ranks(d2h))                     # rank 0 reads the complete quant_meta back
 
     if ctx.rank != 0:
         return
@@ -420,10 +431,10 @@ def gpu_main(args):
         'config': {'workload': WORKLOAD, 'tokens': N_SEQ * SEQLEN, 'bits': BITS, 'group': GROUP,
                    'l2': 'inputs larger than L2 (2.1 GB / 5.8 GB of activations per Hessian)',
                    'parallelism': ('single GPU' if ctx.world == 1 else
-                                   f'sequences sharded x{ctx.world} + NCCL all-reduce of H; rows of each linear sharded')},
+                                   f'sequences sharded x{ctx.world} + NCCL all-reduce of the packed upper triangle of H; the linears of a '
+                                   'Hessian group spread over ranks, rows sharded inside a linear\'s ranks; one all-gather per group')},
         'clocks': clocks,
-        'e2e': {'value': e2e_s, 'unit': 's/layer', 'h2d_bytes_per_step': h2d * ctx.world,
-                'd2h_bytes_per_step': d2h * ctx.world},
+        'e2e': {'value': e2e_s, 'unit': 's/layer', 'h2d_bytes_per_step': h2d_all, 'd2h_bytes_per_step': d2h_all},
         'gpu_launches': int(launches),
         'roofline': {'bound': 'tensor', 'kernel': 'syrk_upper_kernel<2> (K1, tcgen05 cta_group::2)',
                      'achieved': achieved, 'peak': peak_tf, 'unit': 'TFLOP/s', 'frac': achieved / peak_tf,

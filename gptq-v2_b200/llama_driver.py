@@ -259,22 +259,38 @@ class _GroupQuantizer:
 
     def quantize(self, weight: torch.Tensor) -> tuple[dict, dict, torch.Tensor]:
         """-> (quant_meta on save_device, metrics, dense reconstructed weight on the GPU)."""
-        dev = weight.device
-        G = weight.shape[1] // self.gsize
+        return self.quantize_many([weight])[0]
+
+    def quantize_many(self, weights: list) -> list[tuple[dict, dict, torch.Tensor]]:
+        """All linears that share this group's Hessian (v/k/q, up/gate, or one): spread over the ranks by
+        sharded.plan_group (whole linears first, rows inside a linear's own ranks), one all-gather for the group."""
+        dev = weights[0].device
+        G = weights[0].shape[1] // self.gsize
         gs = torch.full([G], self.gsize, dtype=torch.int32, device=dev)          # llama.py:146-147
         gb = torch.full([G], self.bits, dtype=torch.int32, device=dev)
         with self.timer('solve'):
-            res = sharded.gptq_quant_row_sharded(
-                weight, self.hook, group=self.pgroup, group_sizes=gs, group_bit_widths=gb,
-                gptq_use_kernel=self.use_kernel_semantics, gptq_block_sizes=gs, save_device=dev,
-                **self.quant_options)                                             # llama.py:148-163
-        with self.timer('reconstruct'):
-            what = reconstruct_nn_linear(res['quant_meta'], dtype=weight.dtype, device=dev).weight.data   # llama.py:172
-        meta = res['quant_meta']
-        if self.save_device != dev:
-            with self.timer('offload'):
-                meta = {k: (v.to(self.save_device) if torch.is_tensor(v) else v) for k, v in meta.items()}
-        return meta, res['metrics'], what
+            if self.quant_options.get('scale_bit_width') is not None:
+                # EXL2 scales are a maximum over all rows (quant.py:110): row sharding refuses them, one rank's worth of
+                # work on every rank instead
+                from gptq_py import gptq_quant
+                results = [gptq_quant(weight=w, hessian_hook=self.hook, group_sizes=gs, group_bit_widths=gb,
+                                      gptq_use_kernel=self.use_kernel_semantics, gptq_block_sizes=gs, save_device=dev,
+                                      **self.quant_options) for w in weights]
+            else:
+                results = sharded.gptq_quant_group_sharded(
+                    weights, self.hook, group=self.pgroup, group_sizes=gs, group_bit_widths=gb,
+                    gptq_use_kernel=self.use_kernel_semantics, gptq_block_sizes=gs, save_device=dev,
+                    **self.quant_options)                                         # llama.py:148-163
+        out = []
+        for weight, res in zip(weights, results):
+            with self.timer('reconstruct'):
+                what = reconstruct_nn_linear(res['quant_meta'], dtype=weight.dtype, device=dev).weight.data   # llama.py:172
+            meta = res['quant_meta']
+            if self.save_device != dev:
+                with self.timer('offload'):
+                    meta = {k: (v.to(self.save_device) if torch.is_tensor(v) else v) for k, v in meta.items()}
+            out.append((meta, res['metrics'], what))
+        return out
 
 
 @torch.no_grad()
@@ -297,10 +313,12 @@ def quantize_block(shape: LlamaShape, weights: dict, inps: torch.Tensor, n_globa
         return _GroupQuantizer(n_global, timer, pgroup, damp, act_order, bits, gsize, use_kernel_semantics, save_device,
                                quant_options)
 
-    def quantize_into(grp: _GroupQuantizer, name: str) -> torch.Tensor:
-        meta, met, what = grp.quantize(weights[name])
-        data[name], metrics[name] = meta, met
-        return what
+    def quantize_into(grp: _GroupQuantizer, *names: str):
+        whats = []
+        for name, (meta, met, what) in zip(names, grp.quantize_many([weights[n] for n in names])):
+            data[name], metrics[name] = meta, met
+            whats.append(what)
+        return whats[0] if len(whats) == 1 else whats
 
     # ---- group 1: v, k, q on input_layernorm(x)
     grp = make_group()
@@ -311,9 +329,7 @@ def quantize_block(shape: LlamaShape, weights: dict, inps: torch.Tensor, n_globa
     for b in _batches(n, batch_size):
         grp.add(h1[b])
     grp.finish()
-    wv = quantize_into(grp, 'self_attn.v_proj')
-    wk = quantize_into(grp, 'self_attn.k_proj')
-    wq = quantize_into(grp, 'self_attn.q_proj')
+    wv, wk, wq = quantize_into(grp, 'self_attn.v_proj', 'self_attn.k_proj', 'self_attn.q_proj')
     del grp
     # ---- group 2: o on the attention output (computed from the QUANTISED q/k/v, llama.py:176-177)
     grp = make_group()
@@ -340,8 +356,7 @@ def quantize_block(shape: LlamaShape, weights: dict, inps: torch.Tensor, n_globa
     for b in _batches(n, batch_size):
         grp.add(h3[b])
     grp.finish()
-    wu = quantize_into(grp, 'mlp.up_proj')
-    wg = quantize_into(grp, 'mlp.gate_proj')
+    wu, wg = quantize_into(grp, 'mlp.up_proj', 'mlp.gate_proj')
     del grp
     # ---- group 4: down on silu(gate) * up
     grp = make_group()

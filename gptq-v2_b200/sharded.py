@@ -9,7 +9,9 @@ two ways the algebra allows:
      2/n scale of invert() (gptq_py.py:41) is unchanged.
   2. Given U = chol(H^-1), the rows of W are independent (gptq_py.py:187-193, quant.py:114-118 are per row) ->
      rank p solves rows [p*R/P, (p+1)*R/P) of every linear of the group; codes / scales / zeros are all-gathered.
-     Alternatively the linears of one Hessian group go to different ranks ("modules" mode, the north_star wording).
+     The linears of one Hessian group are independent too ("modules" mode, the north_star wording): gptq_quant_group_sharded
+     spreads a group's linears over the ranks first and shards rows only inside a linear's own ranks (plan_group),
+     because the column loop of a linear is a serial chain that does not get shorter with fewer rows.
 
 The factorisation (K2) is replicated on every rank: no broadcast of U (67-765 MB), lowest wall time.
 The compute objects (`HessianHook`, `gptq_quant`) are parameters so that the CPU tests can drive the same host
@@ -138,6 +140,132 @@ def gptq_quant_row_sharded(weight: torch.Tensor, hessian_hook, quant_fn: Optiona
                  'group_bit_widths': quant_kwargs['group_bit_widths'].to(dtype=torch.uint8, device=save_device),
                  'scale_bit_width': None})
     return {'quant_meta': full, 'metrics': metrics}
+
+
+def plan_group(rows: Sequence[int], world: int, multiple: int = 4) -> list[tuple[int, int, int, int]]:
+    """Work plan for the L linears of ONE Hessian group (they share U and are independent of each other) on `world`
+    ranks: a list of (linear index, row lo, row hi, rank).  The column loop of a linear is a serial chain whose length
+    does not shrink with the rows (C / 128 dependent block solves), so linears are spread over ranks FIRST and rows
+    only inside a linear's own ranks: with world >= L every linear gets a contiguous set of ranks (sizes as even as
+    possible, extra ranks to the linears with more rows) and its rows are split over them with shard_range; with
+    world < L whole linears are dealt to the least-loaded rank, longest first.  Deterministic, identical on every rank."""
+    L = len(rows)
+    plan: list[tuple[int, int, int, int]] = []
+    if L == 0:
+        return plan
+    if world >= L:
+        base, extra = divmod(world, L)
+        order = sorted(range(L), key=lambda i: (-rows[i], i))
+        n_ranks = [base] * L
+        for i in order[:extra]:
+            n_ranks[i] += 1
+        r0 = 0
+        for i in range(L):
+            for j in range(n_ranks[i]):
+                lo, hi = shard_range(rows[i], n_ranks[i], j, multiple)
+                if hi > lo:
+                    plan.append((i, lo, hi, r0 + j))
+            r0 += n_ranks[i]
+    else:
+        load = [0] * world
+        for i in sorted(range(L), key=lambda i: (-rows[i], i)):
+            r = min(range(world), key=lambda q: (load[q], q))
+            plan.append((i, 0, rows[i], r))
+            load[r] += rows[i]
+        plan.sort()
+    return plan
+
+
+def gptq_quant_group_sharded(weights: Sequence[torch.Tensor], hessian_hook, quant_fn: Optional[Callable] = None, group=None,
+                             shard_of: Optional[Callable[[int, int, int], torch.Tensor]] = None,
+                             **quant_kwargs) -> list[dict]:
+    """gptq_quant of all linears that share one Hessian (q/k/v, up/gate, or a single o / down), spread over the ranks
+    by plan_group.  weights: the FULL (R_i, C) weights, replicated on every rank.  Returns one {'quant_meta',
+    'metrics'} dict per linear, complete on every rank: the shards travel as ONE all_gather of a per-rank byte blob
+    (codes, scales and zero points of everything the rank solved, padded to the largest blob) and one all_reduce of
+    the metric sums.
+    shard_of(i, lo, hi): optional source of rows [lo, hi) of linear i for callers that stage only the rows a rank solves
+    (bench.py's host-fed step); `weights` may then be meta tensors (shape and dtype only)."""
+    if quant_fn is None:
+        from gptq_py import gptq_quant as quant_fn
+    rank, world = world_info(group)
+    L = len(weights)
+    if shard_of is None:
+        def shard_of(i, lo, hi):
+            return weights[i][lo:hi]
+    if world == 1:
+        return [quant_fn(weight=shard_of(i, 0, w.shape[0]), hessian_hook=hessian_hook, **quant_kwargs)
+                for i, w in enumerate(weights)]
+    if quant_kwargs.get('scale_bit_width') is not None:
+        raise NotImplementedError('EXL2 scale quantisation does not shard by rows; quantise this linear on one rank')
+    dev = hessian_hook.hessian_inv.device
+    dtype = weights[0].dtype
+    C = weights[0].shape[1]
+    assert all(w.shape[1] == C and w.dtype == dtype for w in weights)
+    gs = quant_kwargs['group_sizes']
+    G = len(gs)
+    save_device = quant_kwargs.get('save_device', torch.device('cpu'))
+    kw = dict(quant_kwargs)
+    kw['save_device'] = dev
+    plan = plan_group([w.shape[0] for w in weights], world, 4)
+    esz = torch.empty(0, dtype=dtype).element_size()
+    fields = (('qweight', C, torch.uint8), ('scale', G * esz, dtype), ('qzero', G, torch.uint8))   # bytes per row
+
+    def padded(nbytes: int) -> int:
+        return (nbytes + 15) & ~15                              # every field starts 16-byte aligned (typed views)
+
+    def shard_bytes(n: int) -> int:
+        return sum(padded(n * width) for _, width, _ in fields)
+
+    blob_bytes = [0] * world
+    for i, lo, hi, r in plan:
+        blob_bytes[r] += shard_bytes(hi - lo)
+    mx = max(max(blob_bytes), 1)
+    blob = torch.zeros(mx, dtype=torch.uint8, device=dev)
+    keys = ('gptq_error', 'gptq_norm', 'l2.0_error', 'l2.0_norm')
+    msum = torch.zeros(L, len(keys), dtype=torch.float64, device=dev)
+    off = 0
+    for i, lo, hi, r in plan:
+        if r != rank:
+            continue
+        res = quant_fn(weight=shard_of(i, lo, hi), hessian_hook=hessian_hook, **kw)
+        meta, met = res['quant_meta'], res['metrics']
+        for k, width, _ in fields:
+            b = meta[k].to(dev).contiguous().view(torch.uint8).reshape(-1)
+            assert b.numel() == (hi - lo) * width
+            blob[off:off + b.numel()] = b
+            off += padded(b.numel())
+        msum[i] = torch.tensor([met[k] * (hi - lo) for k in keys], dtype=torch.float64, device=dev)
+    out = torch.empty(world * mx, dtype=torch.uint8, device=dev)
+    dist.all_gather_into_tensor(out, blob, group=group)
+    dist.all_reduce(msum, group=group)
+    # reassemble: every rank walks the same plan
+    pieces: list[dict[str, list]] = [{'qweight': [], 'scale': [], 'qzero': []} for _ in range(L)]
+    offs = [0] * world
+    for i, lo, hi, r in plan:
+        n = hi - lo
+        base = r * mx + offs[r]
+        for k, width, dt in fields:
+            chunk = out[base:base + n * width]
+            pieces[i][k].append(chunk.view(dt).reshape(n, -1) if dt != torch.uint8 else chunk.reshape(n, -1))
+            base += padded(n * width)
+        offs[r] += shard_bytes(n)
+    perm = getattr(hessian_hook, 'perm', None)
+    if perm is not None:
+        perm_inv = perm.to(torch.int16).argsort().to(torch.int16)
+    else:
+        perm_inv = torch.arange(C, dtype=torch.int16, device=dev)
+    msum = msum.tolist()
+    results = []
+    for i in range(L):
+        R = weights[i].shape[0]
+        meta = {k: torch.cat(v, dim=0).to(save_device) for k, v in pieces[i].items()}
+        meta.update({'qscale': None, 'sscale': None, 'perm_inv': perm_inv.to(save_device),
+                     'group_sizes': gs.to(dtype=torch.int16, device=save_device),
+                     'group_bit_widths': quant_kwargs['group_bit_widths'].to(dtype=torch.uint8, device=save_device),
+                     'scale_bit_width': None})
+        results.append({'quant_meta': meta, 'metrics': {k: v / R for k, v in zip(keys, msum[i])}})
+    return results
 
 
 def assign_modules(names: Sequence[str], world: int) -> dict[str, int]:

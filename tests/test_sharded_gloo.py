@@ -127,6 +127,83 @@ def test_sequence_and_row_sharding_world2(R, C, n_seq, tmp_path):
     assert O.code_match(got['meta']['qweight'], full['result']['quant_meta']['qweight']) >= 0.999
 
 
+def _group_worker(rank, world, port, rows, C, ret):
+    for p in (ROOT, os.path.join(ROOT, 'gptq-v2_b200'), os.path.join(ROOT, 'tests')):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    os.environ['MASTER_ADDR'] = '127.0.0.1'
+    os.environ['MASTER_PORT'] = str(port)
+    torch.set_num_threads(2)
+    dist.init_process_group('gloo', rank=rank, world_size=world)
+    try:
+        import sharded
+        from oracle import gptq_oracle as O
+        _, X = O.synth_linear(8, C, 4, 64, seed=9)
+        hook = OracleHook()
+        hook.add_batch(X)
+        hook.invert(1e-2, True)
+        Ws = [O.synth_linear(R, C, 1, 8, seed=20 + i)[0] for i, R in enumerate(rows)]
+        gs = torch.full([C // 128], 128, dtype=torch.int32)
+        bw = torch.full([C // 128], 4, dtype=torch.int32)
+        res = sharded.gptq_quant_group_sharded(Ws, hook, quant_fn=oracle_quant, group_sizes=gs, group_bit_widths=bw)
+        assert len(res) == len(rows)
+        for W, r in zip(Ws, res):                              # every rank holds every linear, bit for bit
+            want = oracle_quant(W, hook, gs, bw)
+            for k in ('qweight', 'scale', 'qzero', 'perm_inv', 'group_sizes', 'group_bit_widths'):
+                assert torch.equal(r['quant_meta'][k], want['quant_meta'][k]), (rank, k)
+            for k, v in want['metrics'].items():
+                assert r['metrics'][k] == pytest.approx(v, rel=2e-3 if k == 'l2.0_norm' else 1e-5), (rank, k)
+        if rank == 0:
+            torch.save({'ok': True}, ret)
+        dist.barrier()
+    except Exception:
+        import traceback
+        with open(ret + f'.err{rank}', 'w') as f:
+            f.write(traceback.format_exc())
+        raise
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize('rows', [(64, 64, 64), (36,), (40, 24)])
+def test_group_sharding_world2(rows, tmp_path):
+    """Linears of one Hessian group spread over ranks (whole linears when world < L, rows inside a linear's own ranks
+    otherwise), one blob all_gather: every rank ends with every linear's full quant_meta, identical to the
+    single-process result."""
+    ctx = mp.get_context('spawn')
+    ret = os.path.join(str(tmp_path), 'rank0.pt')
+    port = _free_port()
+    procs = [ctx.Process(target=_group_worker, args=(r, 2, port, rows, 128, ret)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(240)
+        if p.is_alive():
+            p.kill()
+    errs = [open(ret + f'.err{r}').read() for r in range(2) if os.path.exists(ret + f'.err{r}')]
+    assert [p.exitcode for p in procs] == [0, 0], ([p.exitcode for p in procs], errs)
+    assert torch.load(ret)['ok']
+
+
+def test_plan_group_properties():
+    import sharded
+    for rows, world in (([4096] * 3, 8), ([4096] * 3, 2), ([11008] * 2, 8), ([4096], 8), ([4096] * 3, 4), ([4096, 1024, 1024], 8),
+                        ([12] * 3, 8), ([5120] * 3, 1), ([8], 4)):
+        plan = sharded.plan_group(rows, world, 4)
+        cover = [[] for _ in rows]
+        for i, lo, hi, r in plan:
+            assert 0 <= r < world and 0 <= lo < hi <= rows[i] and lo % 4 == 0 and hi % 4 == 0
+            cover[i].append((lo, hi))
+        for i, R in enumerate(rows):                           # every row of every linear exactly once
+            segs = sorted(cover[i])
+            assert segs[0][0] == 0 and segs[-1][1] == R
+            assert all(a[1] == b[0] for a, b in zip(segs, segs[1:]))
+        if world >= len(rows):                                 # a rank never works on two linears
+            owners = {}
+            for i, lo, hi, r in plan:
+                assert owners.setdefault(r, i) == i
+
+
 def test_shard_range_properties():
     import sharded
     for n, world, mult in ((128, 8, 1), (4096, 8, 4), (11008, 8, 4), (36, 2, 4), (12, 8, 4), (0, 4, 1)):
