@@ -387,9 +387,17 @@ def gpu_main(args):
     per_d = {}
     for a, b, D in timers['syrk']:
         per_d.setdefault(D, []).append(a.elapsed_time(b) / 1e3)
-    phase_s = {}
+    phase_s = {'syrk': syrk_s / args.steps}
     for name, a, b in timers['phase']:
         phase_s[name] = phase_s.get(name, 0.0) + a.elapsed_time(b) / 1e3 / args.steps
+    phase_by_rank = None
+    if ctx.dist is not None:
+        # this rank's view of each phase (a collective's phase includes waiting for the slowest rank to arrive)
+        names = ('syrk', 'allreduce', 'invert', 'quantize')
+        t = torch.tensor([phase_s.get(k, 0.0) for k in names], dtype=torch.float64, device=ctx.dev)
+        allt = torch.empty(ctx.world, len(names), dtype=torch.float64, device=ctx.dev)
+        ctx.dist.all_gather_into_tensor(allt, t)
+        phase_by_rank = {k: [round(v, 5) for v in allt[:, i].tolist()] for i, k in enumerate(names)}
 
     # ---------------- end to end from host buffers
     for _ in range(max(1, args.warmup - 1)):
@@ -448,6 +456,7 @@ def gpu_main(args):
                    'invert_s_per_layer': phase_s.get('invert'),
                    'quantize_s_per_layer': phase_s.get('quantize'),        # prep + K3/K4 solve + metrics + result assembly + pack
                    'allreduce_s_per_layer': phase_s.get('allreduce') if ctx.world > 1 else 0.0,
+                   'phase_s_by_rank': phase_by_rank,
                    'full_model_32_layers_s': 32 * step_s},
     }
     if ctx.world == 1 and not args.no_cpu:
