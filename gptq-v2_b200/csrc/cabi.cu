@@ -132,6 +132,10 @@ int gq_transpose_pack_int4(const uint8_t* codes_t, uint8_t* codes, uint32_t* pac
   return transpose_pack_int4(codes_t, codes, packed, R, C, S(stream));
 }
 
+int gq_w4a16_dequant(const uint32_t* qweight, const void* scale_t, const uint8_t* qzero_t, void* dense, int N, int K, int group,
+                     int dtype, void* stream) {
+  return w4a16_dequant(qweight, scale_t, qzero_t, dense, N, K, group, dtype, S(stream));
+}
 size_t gq_w4a16_workspace_bytes(int M, int N, int K) { return w4a16_workspace_bytes(M, N, K); }
 int gq_w4a16_gemm(const void* x, const uint32_t* qweight, const void* scale_t, const uint8_t* qzero_t,
                   const int32_t* perm, void* y, void* workspace, int M, int N, int K, int group, int dtype,

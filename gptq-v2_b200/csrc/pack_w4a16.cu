@@ -156,6 +156,32 @@ __global__ void unpack_kernel(const uint32_t* __restrict__ packed, uint8_t* __re
   *reinterpret_cast<uint2*>(codes + i * 8) = v;
 }
 
+// Dense 16-bit reconstruction from the packed format, for batches large enough to be compute-bound (the W4A16 GEMM
+// re-dequantises the weights for every 256 batch columns; past a few hundred rows one dequantisation + a dense GEMM is
+// cheaper):  out[n][k] = T( float(q[n][k] - z[g][n]) * float(s[g][n]) ), one rounding, exactly what the reference's
+// construct_matrix stores (quant.py:222-237: int16 subtract, multiply in the 16-bit dtype); permuted column order kept
+// (the caller permutes x instead, like K6).  One thread per packed word: 4-byte loads and 16-byte stores, both coalesced.
+template <typename T> __device__ __forceinline__ T from_f32(float v);
+template <> __device__ __forceinline__ __half from_f32<__half>(float v) { return __float2half_rn(v); }
+template <> __device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+
+template <typename T>
+__global__ void dequant_w4_kernel(const uint32_t* __restrict__ qw, const T* __restrict__ scale_t,
+                                  const uint8_t* __restrict__ qzero_t, T* __restrict__ out, int N, int K, int group) {
+  const int kw = K >> 3;
+  const size_t idx = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (idx >= (size_t)N * kw) return;
+  const int n = (int)(idx / kw), w = (int)(idx - (size_t)n * kw);
+  const int g = (w << 3) / group;
+  const float s = to_f32<T>(scale_t[(size_t)g * N + n]);
+  const int z = qzero_t[(size_t)g * N + n];
+  const uint32_t word = qw[idx];
+  __align__(16) T v[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) v[i] = from_f32<T>((float)((int)((word >> (4 * i)) & 0xFu) - z) * s);
+  *reinterpret_cast<uint4*>(out + idx * 8) = *reinterpret_cast<const uint4*>(v);
+}
+
 // codes_t (C, R) uint8 -> codes (R, C) uint8 (optional) and packed (R, C/8) (optional)
 __global__ void transpose_pack_kernel(const uint8_t* __restrict__ codes_t, uint8_t* __restrict__ codes,
                                       uint32_t* __restrict__ packed, int R, int C) {
@@ -204,6 +230,20 @@ int prep_weight_scatter(const void* W, int fmt, const int64_t* perm_inv, float* 
   if (fmt == 0) prep_weight_scatter_kernel<__half><<<grid, block, 0, st>>>((const __half*)W, perm_inv, Wt, (__half*)orig_t, colsq, R, C);
   else if (fmt == 1) prep_weight_scatter_kernel<__nv_bfloat16><<<grid, block, 0, st>>>((const __nv_bfloat16*)W, perm_inv, Wt, (__nv_bfloat16*)orig_t, colsq, R, C);
   else if (fmt == 2) prep_weight_scatter_kernel<float><<<grid, block, 0, st>>>((const float*)W, perm_inv, Wt, (float*)orig_t, colsq, R, C);
+  else return GQ_ERR_DTYPE;
+  return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
+}
+
+int w4a16_dequant(const uint32_t* qw, const void* scale_t, const uint8_t* qzero_t, void* out, int N, int K, int group, int fmt,
+                  cudaStream_t st) {
+  if (N <= 0 || K <= 0) return GQ_OK;
+  if ((K & 7) || group < 8 || (group & 7) || (K % group)) return GQ_ERR_SHAPE;   // a packed word never straddles two groups
+  if (reinterpret_cast<uintptr_t>(out) & 15) return GQ_ERR_ALIGN;
+  const size_t words = (size_t)N * (K / 8);
+  const unsigned grid = (unsigned)((words + 255) / 256);
+  GQ_LAUNCHED();
+  if (fmt == 0) dequant_w4_kernel<__half><<<grid, 256, 0, st>>>(qw, (const __half*)scale_t, qzero_t, (__half*)out, N, K, group);
+  else if (fmt == 1) dequant_w4_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(qw, (const __nv_bfloat16*)scale_t, qzero_t, (__nv_bfloat16*)out, N, K, group);
   else return GQ_ERR_DTYPE;
   return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
 }

@@ -14,7 +14,7 @@ import torch
 from . import _cabi
 from ._cabi import GptqB200Error, check, lib, ptr, require_contig, require_cuda, stream_of
 
-__all__ = ['accumulate_hessian', 'gptq_quantize_range', 'hessian_syrk', 'hessian_invert', 'pack_upper', 'unpack_upper', 'prep_weight_t', 'prep_weight_t2', 'solve_metrics', 'gptq_solve_ex', 'find_params', 'mse_refine',
+__all__ = ['accumulate_hessian', 'gptq_quantize_range', 'hessian_syrk', 'hessian_invert', 'w4a16_dequant', 'pack_upper', 'unpack_upper', 'prep_weight_t', 'prep_weight_t2', 'solve_metrics', 'gptq_solve_ex', 'find_params', 'mse_refine',
            'gptq_solve', 'gptq_solve_static', 'pack_int4', 'unpack_int4', 'transpose_pack_int4', 'w4a16_gemm', 'sgemm', 'gemm_tf32x3', 'set_tf32x3', 'set_solve_super', 'set_w4a16_path',
            'GptqB200Error']
 
@@ -318,6 +318,22 @@ def w4a16_gemm(x: torch.Tensor, qweight: torch.Tensor, scale_t: torch.Tensor, qz
         check(lib.gq_w4a16_gemm(ptr(x), ptr(qweight), ptr(scale_t), ptr(qzero_t), ptr(perm), ptr(y), ptr(work), M, N, K,
                                 int(group), _cabi.DTYPE_CODE[x.dtype], stream_of(x)), 'gq_w4a16_gemm')
     return y
+
+
+def w4a16_dequant(qweight: torch.Tensor, scale_t: torch.Tensor, qzero_t: torch.Tensor, group: int = 128) -> torch.Tensor:
+    """Dense (N, K) reconstruction in scale_t.dtype from the packed format, permuted column order kept:
+    dense[n, k] = ((q - z) * s) with the reference's rounding (quant.py:222-237)."""
+    dev = require_cuda(qweight, scale_t, qzero_t)
+    require_contig(qweight=qweight, scale_t=scale_t, qzero_t=qzero_t)
+    N, K = qweight.shape[0], qweight.shape[1] * 8
+    G = K // int(group)
+    if qzero_t.dtype != torch.uint8 or tuple(scale_t.shape) != (G, N) or tuple(qzero_t.shape) != (G, N):
+        raise GptqB200Error('w4a16_dequant: scale_t / qzero_t must be (K/group, N)')
+    dense = torch.empty(N, K, dtype=scale_t.dtype, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.gq_w4a16_dequant(ptr(qweight), ptr(scale_t), ptr(qzero_t), ptr(dense), N, K, int(group),
+                                   _cabi.DTYPE_CODE[scale_t.dtype], stream_of(qweight)), 'gq_w4a16_dequant')
+    return dense
 
 
 def sgemm(A, B, C_, M, N, K, lda, ldb, ldc, alpha, beta, flags) -> None:

@@ -190,7 +190,17 @@ def pack_quant_meta(quant_meta: dict, device: torch.device) -> dict:
 
 
 class W4A16Linear(nn.Module):
-    """y = x W_hat^T straight from packed int4 codes (K6); no dense copy of W_hat exists."""
+    """y = x W_hat^T from packed int4 codes.  Batches below `dense_rows(N, K)` rows run K6 (dequantisation fused into the
+    GEMM, no dense copy of W_hat exists).  Larger batches are compute-bound and K6 would dequantise the weights again
+    for every 256 batch columns: there the packed weights are dequantised ONCE into a transient 16-bit matrix
+    (gq_w4a16_dequant, the reference's construct_matrix rounding) and multiplied by a dense GEMM -- what the reference
+    does for every batch size (quant.py:262-279 + nn.Linear), but from 4x fewer resident bytes.  Crossovers measured on
+    B200 (profiles/r01_v29_w4a16_sweep.jsonl): 128 rows for N*K <= 2^26 (all Llama-2-7B shapes), 512 rows above."""
+    dense_route = True
+
+    @staticmethod
+    def dense_rows(N: int, K: int) -> int:
+        return 128 if N * K <= (1 << 26) else 512
 
     def __init__(self, packed: dict):
         super().__init__()
@@ -210,5 +220,10 @@ class W4A16Linear(nn.Module):
         lead = x.shape[:-1]
         x2 = x.reshape(-1, self.in_features).contiguous()
         scale_t = self.scale_t if self.scale_t.dtype == x2.dtype else self.scale_t.to(x2.dtype)
-        y = _ops.w4a16_gemm(x2, self.qweight_packed, scale_t, self.qzero_t, self.perm, self.group_size)
+        if self.dense_route and x2.shape[0] >= self.dense_rows(self.out_features, self.in_features):
+            dense = _ops.w4a16_dequant(self.qweight_packed, scale_t, self.qzero_t, self.group_size)   # transient
+            xp = x2.index_select(1, self.perm) if self.perm is not None else x2
+            y = xp @ dense.t()
+        else:
+            y = _ops.w4a16_gemm(x2, self.qweight_packed, scale_t, self.qzero_t, self.perm, self.group_size)
         return y.view(*lead, self.out_features)

@@ -134,6 +134,12 @@ int gq_unpack_int4(const uint32_t* packed, uint8_t* codes, int R, int C, void* s
 /* codes_t (C, R) -> codes (R, C) (may be NULL) and packed (R, C/8) (may be NULL) */
 int gq_transpose_pack_int4(const uint8_t* codes_t, uint8_t* codes, uint32_t* packed, int R, int C, void* stream);
 
+/* Dense 16-bit reconstruction from the packed format (quant.py:222-237 semantics: dense[n][k] = T(float(q - z) * float(s)),
+ * one rounding; permuted column order kept, i.e. no perm_inv gather): the large-batch route of W4A16Linear (one
+ * dequantisation + a dense GEMM once the batch is compute-bound).  dense (N, K) of dtype GQ_DTYPE_F16 / BF16, 16-byte
+ * aligned; K % 8 == 0, group % 8 == 0, K % group == 0. */
+int gq_w4a16_dequant(const uint32_t* qweight, const void* scale_t, const uint8_t* qzero_t, void* dense, int N, int K, int group,
+                     int dtype, void* stream);
 /* ---- K6: y (M, N) = x[:, perm] (M, K) * dequant(qweight)^T, replacing reconstruct_nn_linear +
  * nn.Linear (quant.py:262-279, llama.py:172-177).  x, y, scale_t share `dtype` (f16/bf16).  scale_t and
  * qzero_t are GROUP-MAJOR: (K/group, N) 16-bit and (K/group, N) uint8 (the transposes of quant_meta's scale /

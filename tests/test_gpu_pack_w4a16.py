@@ -183,3 +183,48 @@ def test_prep_weight_scatter_form_matches_gather_form(dtype, R, C):
     # no permutation: identity scatter
     Wt_i, o_i, sq_i = gptq.prep_weight_t2(W, None)
     assert torch.equal(Wt_i, W.t().float().contiguous()) and torch.equal(o_i, W.t().contiguous())
+
+
+@pytest.mark.parametrize('dtype', [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize('N,K,group', [(64, 128, 128), (100, 384, 64), (4096, 4096, 128), (24, 1024, 32)])
+def test_w4a16_dequant_matches_reference_construct_matrix(N, K, group, dtype):
+    """gq_w4a16_dequant == the reference's construct_matrix (quant.py:222-237: int16 subtract, multiply in the 16-bit
+    dtype) bit for bit, in the permuted column order of quant_meta."""
+    import gptq
+    import quant
+    g = torch.Generator().manual_seed(N + K + group)
+    G = K // group
+    codes = torch.randint(0, 16, (N, K), generator=g, dtype=torch.uint8)
+    scale = (torch.rand(N, G, generator=g) * 0.01 + 1e-3).to(dtype)
+    qzero = torch.randint(0, 16, (N, G), generator=g, dtype=torch.uint8)
+    want = quant.construct_matrix(codes, scale, qzero, torch.full([G], group, dtype=torch.int16))
+    got = gptq.w4a16_dequant(gptq.pack_int4(codes.cuda()), scale.t().contiguous().cuda(), qzero.t().contiguous().cuda(), group)
+    torch.cuda.synchronize()
+    assert got.dtype == dtype and torch.equal(got.cpu(), want)
+
+
+@pytest.mark.parametrize('M', [128, 600])
+def test_w4a16_linear_large_batch_route(M):
+    """W4A16Linear switches to one dequantisation + a dense GEMM for compute-bound batches; both routes agree with the
+    dense reconstruction of the reference (a8) within the 1e-2 of BASELINE.json, and with each other far tighter."""
+    import quant
+    R, C, group = 512, 1024, 128
+    g = torch.Generator().manual_seed(M)
+    G = C // group
+    meta = {'qweight': torch.randint(0, 16, (R, C), generator=g, dtype=torch.uint8),
+            'scale': (torch.rand(R, G, generator=g) * 0.01 + 1e-3).half(),
+            'qzero': torch.randint(0, 16, (R, G), generator=g, dtype=torch.uint8),
+            'perm_inv': torch.randperm(C, generator=g).to(torch.int16),
+            'group_sizes': torch.full([G], group, dtype=torch.int16), 'qscale': None, 'sscale': None,
+            'group_bit_widths': torch.full([G], 4, dtype=torch.uint8), 'scale_bit_width': None}
+    lin = quant.W4A16Linear.from_quant_meta(meta, torch.device('cuda'))
+    assert M >= lin.dense_rows(R, C)
+    x = torch.randn(M, C, generator=g).half().cuda()
+    y_dense_route = lin(x).float()
+    lin.dense_route = False
+    y_fused = lin(x).float()
+    ref = quant.reconstruct_nn_linear(meta, torch.float16, torch.device('cuda'))
+    want = ref(x).float()
+    for y in (y_dense_route, y_fused):
+        assert ((y - want).norm() / want.norm()).item() <= 1e-2
+    assert ((y_dense_route - want).norm() / want.norm()).item() <= 2e-3     # same 16-bit weights, fp32 accumulation

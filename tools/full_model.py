@@ -97,7 +97,12 @@ def main():
                 out[n] = reconstruct_nn_linear(res['data'][f'model.layers.{i}.{n}'], torch.float16, dev).weight.data
             return out
         out = {}
-        for label, bw in (('packed_k6', L.packed_block_weights(packed, lambda i: ones, dev, torch.float16)), ('dense', dense_block)):
+        from quant import W4A16Linear
+        pbw = L.packed_block_weights(packed, lambda i: ones, dev, torch.float16)
+        # 'packed': W4A16Linear as shipped (2048-row batches take the dequantise-once + dense GEMM route);
+        # 'packed_k6_only': the fused K6 kernel for every batch size; 'dense': the reference's reconstructed fp16 weights
+        for label, bw in (('packed', pbw), ('packed_k6_only', pbw), ('dense', dense_block)):
+            W4A16Linear.dense_route = label != 'packed_k6_only'
             L.evaluate_llama(shape, bw, emb, fnorm, head, tok[:1], batch_size=1, n_blocks=1)      # warm-up
             torch.cuda.synchronize()
             t0 = time.perf_counter()
@@ -105,6 +110,7 @@ def main():
             torch.cuda.synchronize()
             dt = time.perf_counter() - t0
             out[label] = {'ppl': ppl, 'seconds': round(dt, 3), 'tokens_per_s': round(args.eval_seqs * args.seqlen / dt, 1)}
+        W4A16Linear.dense_route = True
         raw = sum(v.numel() * v.element_size() for m in res['data'].values() for v in m.values() if torch.is_tensor(v))
         print(json.dumps({'what': 'packed checkpoint + layer-streamed eval', 'blocks': nb, 'eval_seqs': args.eval_seqs,
                           'pack_seconds': round(t_pack, 3), 'packed_bytes': checkpoint.packed_bytes(packed),

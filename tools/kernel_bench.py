@@ -13,6 +13,11 @@ import torch  # noqa: E402
 import gptq  # noqa: E402
 
 dev = torch.device('cuda')
+try:
+    _pk = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
+    PEAK_HBM, PEAK_BF16 = _pk['hbm_gbs'] * 1e9, _pk['bf16_tflops'] * 1e12
+except Exception:
+    PEAK_HBM, PEAK_BF16 = 6560.6e9, 1626.9e12
 
 
 def timeit(fn, iters=5, warm=2):
@@ -167,10 +172,11 @@ def bench_tf32():
 def bench_w4a16():
     """Weights rotate through > 4x L2 of distinct buffers; the launches of one rotation are captured in
     a CUDA graph so that the host (ctypes + allocator) is out of the timed region."""
-    shapes = ((4096, 4096), (11008, 4096), (4096, 11008), (8192, 8192), (28672, 8192), (8192, 28672))
+    # BASELINE.json configs[4]: Llama-2-7B and 70B layer shapes (N = out, K = in), incl. the 70B k/v projection
+    shapes = ((4096, 4096), (11008, 4096), (4096, 11008), (8192, 8192), (1024, 8192), (28672, 8192), (8192, 28672))
     if os.environ.get('W4_SHAPES'):                       # e.g. W4_SHAPES=28672x8192 W4_MS=1,8 (profiling runs)
         shapes = tuple(tuple(int(v) for v in sh.split('x')) for sh in os.environ['W4_SHAPES'].split(','))
-    m_list = (1, 2, 4, 8, 16, 64, 256, 1024)
+    m_list = (1, 2, 4, 8, 16, 32, 64, 128, 256, 512, 1024, 2048, 4096)
     if os.environ.get('W4_PATH'):
         gptq.set_w4a16_path(int(os.environ['W4_PATH']))
     if os.environ.get('W4_MS'):
@@ -182,10 +188,9 @@ def bench_w4a16():
         sc = (torch.rand(G, N, device=dev) * 0.01 + 1e-3).half()
         qz = torch.randint(0, 16, (G, N), device=dev, dtype=torch.uint8)
         perm = torch.randperm(K, device=dev).to(torch.int32)
+        dense = [(torch.randn(N, K, device=dev) * 0.02).half() for _ in range(max(2, min(nbuf, int(2e9 // (N * K * 2)))))]
         for variant, Ms in ((2, m_list),):
             for M in Ms:
-                if M > 16 and nbuf > 8:
-                    continue                              # large M only on the big (HBM-resident) shapes
                 x = torch.randn(M, K, device=dev).half()
                 gptq.w4a16_gemm(x, qs[0], sc, qz, perm, 128)
                 torch.cuda.synchronize()
@@ -194,12 +199,23 @@ def bench_w4a16():
                     for q in qs:
                         gptq.w4a16_gemm(x, q, sc, qz, perm, 128)
                 t = timeit(graph.replay, iters=7, warm=2) / nbuf
+                del graph
+                # a8: the reference evaluates through a dense 16-bit reconstruction + cuBLAS (quant.py:262-279,
+                # llama.py:172-177); the GEMM alone (reconstruction not timed), dense weights rotated the same way
+                g2 = torch.cuda.CUDAGraph()
+                torch.matmul(x, dense[0].t())
+                torch.cuda.synchronize()
+                with torch.cuda.graph(g2):
+                    for wd in dense:
+                        torch.matmul(x, wd.t())
+                td = timeit(g2.replay, iters=7, warm=2) / len(dense)
+                del g2
                 byts = N * K / 2 + N * G * 3 + 2 * M * K + 2 * M * N
                 print(json.dumps({'k': 'w4a16', 'variant': variant, 'M': M, 'N': N, 'K': K, 'us': t * 1e6,
                                   'GBps': byts / t / 1e9, 'tflops': 2.0 * M * N * K / t / 1e12,
-                                  'frac_hbm': byts / t / 6560.6e9, 'frac_bf16_peak': 2.0 * M * N * K / t / 1626.9e12}))
-                del graph
-        del qs
+                                  'frac_hbm': byts / t / PEAK_HBM, 'frac_bf16_peak': 2.0 * M * N * K / t / PEAK_BF16,
+                                  'dense_cublas_us': td * 1e6, 'speedup_vs_dense_cublas': td / t}))
+        del qs, dense
 
 
 def bench_refext():
