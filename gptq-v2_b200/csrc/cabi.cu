@@ -6,7 +6,7 @@ using namespace gq;
 
 static inline cudaStream_t S(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 
-namespace gq { unsigned long long g_launch_count = 0; int g_use_tf32x3 = 2; int g_solve_super = 8; int g_w4a16_path = 0; }
+namespace gq { unsigned long long g_launch_count = 0; int g_use_tf32x3 = 3; int g_solve_super = 8; int g_w4a16_path = 0; }
 
 extern "C" {
 
@@ -159,7 +159,7 @@ int gq_set_w4a16_path(int path) {
   if (path >= 0 && path <= 2) gq::g_w4a16_path = path;
   return old;
 }
-int gq_set_tf32x3(int enable) { int old = gq::g_use_tf32x3; gq::g_use_tf32x3 = enable == 2 ? 2 : (enable ? 1 : 0); return old; }
+int gq_set_tf32x3(int enable) { int old = gq::g_use_tf32x3; gq::g_use_tf32x3 = (enable >= 0 && enable <= 3) ? enable : 1; return old; }
 
 int gq_gemm_tf32x3(const float* A, const float* B, float* C, int M, int N, int K, int lda, int ldb, int ldc, float alpha,
                    int upper_only, void* stream) {

@@ -10,7 +10,7 @@
 //   A^T B ~= hi^T hi + hi^T lo + lo^T hi        (3 x kind::tf32, fp32 accumulation in TMEM)
 // whose relative error (~2^-21) is below what reordering an fp32 sum already causes.
 //
-// Pipeline per CTA (persistent over 128 x 256 output tiles, 384 threads):
+// Pipeline per CTA (persistent over 128 x 256 output tiles, or CTA pairs over 256 x 256 tiles: Cfg<2>; 384 threads):
 //   warp 0      TMA producer: [16 k][32 cols] fp32 boxes, SWIZZLE_128B_ATOM_32B (both operands MN-major)
 //   warps 8-11  split: read the landed tile, write hi back in place and lo next to it
 //               (element-wise on identical swizzled addresses, so no layout knowledge needed)
@@ -24,15 +24,23 @@
 namespace gq {
 namespace {
 
-constexpr int TM = 128, TN = 256, BK = 16;
+constexpr int TN = 256, BK = 16;
 constexpr int SUB = BK * 128;                       // one [16 k][32 fp32] box = 2 KB
-constexpr int A_SUBS = TM / 32, B_SUBS = TN / 32;   // 4, 8
-constexpr int HI_BYTES = (A_SUBS + B_SUBS) * SUB;   // 24 KB
-constexpr int STAGE_BYTES = 2 * HI_BYTES;           // hi + lo
-constexpr int STAGES = 4;
 constexpr int SPLIT_THREADS = 128;                  // warps 8..11 split the landed tile into hi / lo
 constexpr int EPI_BUF = 32 * 128;                   // one 32 x 32 fp32 staging tile
-constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 4 * 2 * EPI_BUF + 1024 + 256;
+// CG = 1: one CTA per 128 x 256 output tile.  CG = 2: a CTA pair (cluster of 2, tcgen05 cta_group::2) per 256 x 256
+// tile: each CTA stages its own 128 rows of A and only HALF of B (128 columns), so the shared-memory traffic per flop
+// -- what bounds this kernel -- drops by a third (per 16-deep k-block and CTA: 16 KB landed by TMA, 16 + 16 KB through
+// the split stage, 48 KB read by the MMAs = 96 KB instead of 144 KB for the same 768 tensor-core clocks).
+template <int CG> struct Cfg {
+  static constexpr int TM = 128 * CG;                             // rows of the tile (128 per CTA)
+  static constexpr int A_SUBS = 4;                                // 128 rows per CTA
+  static constexpr int B_SUBS = (TN / 32) / CG;                   // 8, or this CTA's half: 4
+  static constexpr int HI_BYTES = (A_SUBS + B_SUBS) * SUB;        // 24 KB / 16 KB
+  static constexpr int STAGE_BYTES = 2 * HI_BYTES;                // hi + lo
+  static constexpr int STAGES = (CG == 2) ? 6 : 4;                // 192 KB either way
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 4 * 2 * EPI_BUF + 1024 + 256;
+};
 
 struct GemmTf32Params {
   int count;               // problems in this launch (identical tile grid, individually clipped)
@@ -44,7 +52,9 @@ struct GemmTf32Params {
 
 struct TileInfo { int m0, n0, kb0, kb1, prob; bool skip; };
 
+template <int CG>
 __device__ __forceinline__ TileInfo decode_tile(const GemmTf32Params& P, int t) {
+  constexpr int TM = Cfg<CG>::TM;
   TileInfo ti;
   const int per = P.tiles_m * P.tiles_n;
   ti.prob = t / per;
@@ -77,9 +87,13 @@ __device__ __forceinline__ float rna_tf32(float x) {
   return __uint_as_float(r);
 }
 
+template <int CG>
 __global__ void __launch_bounds__(256 + SPLIT_THREADS, 1)
 gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                    const __grid_constant__ CUtensorMap map_c, const GemmTf32Params p) {
+  using C = Cfg<CG>;
+  constexpr int TM = C::TM, A_SUBS = C::A_SUBS, B_SUBS = C::B_SUBS, HI_BYTES = C::HI_BYTES, STAGE_BYTES = C::STAGE_BYTES,
+                STAGES = C::STAGES;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
@@ -96,27 +110,35 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n_tiles = p.count * p.tiles_m * p.tiles_n;
+  // CG = 2: CTA `rank` of the pair owns rows [128 rank, 128 rank + 128) of the tile and stages columns
+  // [128 rank, 128 rank + 128) of B; the pair walks the tile list together
+  const int rank = (CG == 2) ? (int)cluster_ctarank() : 0;
+  const int walker = (CG == 2) ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int n_walkers = (CG == 2) ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  const int row_off = 128 * rank;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&map_a); tma_prefetch_desc(&map_b); tma_prefetch_desc(&map_c);
-    for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(ready_bar(s), SPLIT_THREADS); mbar_init(empty_bar(s), 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 4); }
+    // full: this CTA's own TMA bytes (its split warps wait on it); ready: one arrival per CTA of the pair (after its split warps have
+    // synchronised) on the leader's barrier; empty / tfull: the leader's tcgen05.commit, multicast to both CTAs; tempty: 4 epilogue warps per CTA
+    for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(ready_bar(s), CG == 2 ? 2 : SPLIT_THREADS); mbar_init(empty_bar(s), 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 4 * CG); }
     fence_mbar_init();
   }
-  if (warp == 2) { tmem_alloc<1>(tmem_slot, 512); tmem_relinquish<1>(); }
+  if (warp == 2) { tmem_alloc<CG>(tmem_slot, 512); tmem_relinquish<CG>(); }
   tc_fence_before();
-  __syncthreads();
+  if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
 
   if (warp == 0) {
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
-      for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-        const TileInfo ti = decode_tile(p, t);
+      for (int t = walker; t < n_tiles; t += n_walkers) {
+        const TileInfo ti = decode_tile<CG>(p, t);
         if (ti.skip) continue;
         const Tf32Problem& q = p.p[ti.prob];
-        const int m0 = ti.m0, n0 = ti.n0;
+        const int m0 = ti.m0 + row_off, n0 = ti.n0 + (CG == 2 ? row_off : 0);
         for (int kb = ti.kb0; kb < ti.kb1; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t sa = smem_base + stage * STAGE_BYTES;
@@ -132,12 +154,12 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (rank == 0 && lane == 0) {                      // CG = 2: the leader issues for the pair
       const uint32_t idesc = umma_idesc(2u /*tf32*/, 1u, 1u, TM, TN);
       int stage = 0; uint32_t phase = 0;
       int it = 0;
-      for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-        const TileInfo ti = decode_tile(p, t);
+      for (int t = walker; t < n_tiles; t += n_walkers) {
+        const TileInfo ti = decode_tile<CG>(p, t);
         if (ti.skip) continue;
         const int acc = it & 1;
         const uint32_t acc_phase = (it >> 1) & 1u;
@@ -160,22 +182,23 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
             const uint64_t bh = umma_smem_desc(b_hi + k8 * 1024, SUB, 512, 1u);
             const uint64_t al = umma_smem_desc(a_lo + k8 * 1024, SUB, 512, 1u);
             const uint64_t bl = umma_smem_desc(b_lo + k8 * 1024, SUB, 512, 1u);
-            mma_tf32<1>(d_tmem, al, bh, idesc, ((kb - ti.kb0) | k8) ? 1u : 0u);     // small terms first
-            mma_tf32<1>(d_tmem, ah, bl, idesc, 1u);
-            mma_tf32<1>(d_tmem, ah, bh, idesc, 1u);
+            mma_tf32<CG>(d_tmem, al, bh, idesc, ((kb - ti.kb0) | k8) ? 1u : 0u);     // small terms first
+            mma_tf32<CG>(d_tmem, ah, bl, idesc, 1u);
+            mma_tf32<CG>(d_tmem, ah, bh, idesc, 1u);
           }
-          tc_commit_cg1(empty_bar(stage));
+          if constexpr (CG == 2) tc_commit_cg2_mcast(empty_bar(stage), 0x3); else tc_commit_cg1(empty_bar(stage));
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
-        tc_commit_cg1(tfull_bar(acc));
+        if constexpr (CG == 2) tc_commit_cg2_mcast(tfull_bar(acc), 0x3); else tc_commit_cg1(tfull_bar(acc));
       }
     }
   } else if (warp >= 8) {
     // ---- split hi / lo, element-wise over the 24 KB that just landed
     const int tid = threadIdx.x - 256;                 // 0..SPLIT_THREADS-1
     int stage = 0; uint32_t phase = 0;
-    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-      const TileInfo ti = decode_tile(p, t);
+    const uint32_t lead_ready0 = (CG == 2) ? mapa(ready_bar(0), 0) : 0u;     // the leader's ready barriers
+    for (int t = walker; t < n_tiles; t += n_walkers) {
+      const TileInfo ti = decode_tile<CG>(p, t);
       if (ti.skip) continue;
       for (int kb = ti.kb0; kb < ti.kb1; ++kb) {
         mbar_wait(full_bar(stage), phase);
@@ -209,7 +232,18 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
           }
         }
         fence_proxy_async();                            // generic-proxy writes -> visible to the tensor core
-        mbar_arrive(ready_bar(stage));
+        if constexpr (CG == 2) {
+          // one remote arrival per CTA and stage (128 cluster-scope arrivals per k-block cost more than the split itself)
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          // default semantics (.release.cta) on the leader's barrier, the form CUTLASS' ClusterBarrier::arrive(cta_id)
+          // uses: the data this signals is read by THIS SM's tensor core (async proxy, ordered by the fence above), not
+          // by the leader's threads; a .release.cluster arrive here costs a cluster-scope fence per k-block and halves
+          // the kernel's throughput (measured: 120 vs 247 TFLOP/s at K = 4096)
+          if (tid == 0)
+            asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" :: "r"(lead_ready0 + 8u * stage) : "memory");
+        } else {
+          mbar_arrive(ready_bar(stage));
+        }
         if (++stage == STAGES) { stage = 0; phase ^= 1u; }
       }
     }
@@ -219,11 +253,11 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
     const uint32_t stg0 = epi_base + we * 2 * EPI_BUF;
     int it = 0;
     int buf = 0;
-    for (int t = blockIdx.x; t < n_tiles; t += gridDim.x) {
-      const TileInfo ti = decode_tile(p, t);
+    for (int t = walker; t < n_tiles; t += n_walkers) {
+      const TileInfo ti = decode_tile<CG>(p, t);
       if (ti.skip) continue;
       const Tf32Problem& pq = p.p[ti.prob];
-      const int m0 = ti.m0, n0 = ti.n0;
+      const int m0 = ti.m0 + row_off, n0 = ti.n0;
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1u;
       ++it;
@@ -239,7 +273,10 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
         if (c == TN / 32 - 1) {
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(tempty_bar(acc));
+          if (lane == 0) {
+            if constexpr (CG == 2) mbar_arrive_cluster(mapa(tempty_bar(acc), 0));
+            else mbar_arrive(tempty_bar(acc));
+          }
         }
         if (rows_live && n0 + c * 32 < pq.N) {
           const uint32_t stg = stg0 + buf * EPI_BUF;
@@ -271,8 +308,8 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
   }
 
   tc_fence_before();
-  __syncthreads();
-  if (warp == 2) tmem_dealloc<1>(tmem_base, 512);
+  if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();
+  if (warp == 2) tmem_dealloc<CG>(tmem_base, 512);
 }
 
 int make_map_f32(CUtensorMap* out, const float* base, int rows, int cols, int ld, int box_cols, int box_rows,
@@ -295,21 +332,47 @@ int gemm_tf32x3_maps(Tf32Maps* maps, const float* A, int a_rows, int a_cols, int
   return GQ_OK;
 }
 
+template <int CG>
+static int launch_gemm(const Tf32Maps& maps, const GemmTf32Params& p, int n_sms, cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    if (cudaFuncSetAttribute(gemm_tf32x3_kernel<CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<CG>::SMEM_BYTES) !=
+        cudaSuccess)
+      return GQ_ERR_CUDA;
+    attr_set = true;
+  }
+  const int tiles = p.count * p.tiles_m * p.tiles_n;
+  int walkers = n_sms / CG;
+  if (walkers > tiles) walkers = tiles;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(CG * walkers);
+  cfg.blockDim = dim3(256 + SPLIT_THREADS);
+  cfg.dynamicSmemBytes = Cfg<CG>::SMEM_BYTES;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = CG;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  GQ_LAUNCHED();
+  return cudaLaunchKernelEx(&cfg, gemm_tf32x3_kernel<CG>, maps.a, maps.b, maps.c, p) == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
+}
+
 int gemm_tf32x3_batch(const Tf32Maps& maps, const Tf32Problem* probs, int count, float alpha, int flags, cudaStream_t st) {
   if (count <= 0) return GQ_OK;
   if (count > TF32_MAX_BATCH) return GQ_ERR_ARG;
-  static bool attr_set = false;
   static int n_sms = 0;
-  if (!attr_set) {
-    if (cudaFuncSetAttribute(gemm_tf32x3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BYTES) != cudaSuccess)
-      return GQ_ERR_CUDA;
+  if (n_sms == 0) {
     int dev = 0;
     cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev);
-    attr_set = true;
+    if (cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n_sms <= 0) n_sms = 148;
   }
   GemmTf32Params p;
-  p.count = 0; p.tiles_m = 0; p.tiles_n = 0; p.alpha = alpha; p.flags = flags | (g_use_tf32x3 == 2 ? TF32_RAW_HI : 0);
+  p.count = 0; p.tiles_m = 0; p.tiles_n = 0; p.alpha = alpha;
+  p.flags = flags | (g_use_tf32x3 >= 2 ? TF32_RAW_HI : 0);
+  int max_m = 0, max_n = 0;
   for (int i = 0; i < count; ++i) {
     const Tf32Problem& q = probs[i];
     if (q.M <= 0 || q.N <= 0 || q.K <= 0) continue;
@@ -317,15 +380,20 @@ int gemm_tf32x3_batch(const Tf32Maps& maps, const Tf32Problem* probs, int count,
     // the tensor maps clip at the edge of the WHOLE matrix, not of the window: a store-mode window must be tile-exact
     // in N (32-column boxes) and M (32-row boxes) unless it ends at the matrix edge -- callers guarantee % 32 == 0
     p.p[p.count++] = q;
-    p.tiles_m = max(p.tiles_m, (q.M + TM - 1) / TM);
-    p.tiles_n = max(p.tiles_n, (q.N + TN - 1) / TN);
+    max_m = max(max_m, q.M);
+    max_n = max(max_n, q.N);
   }
   if (p.count == 0) return GQ_OK;
-  const int tiles = p.count * p.tiles_m * p.tiles_n;
-  const int grid = tiles < n_sms ? tiles : n_sms;
-  GQ_LAUNCHED();
-  gemm_tf32x3_kernel<<<grid, 256 + SPLIT_THREADS, SMEM_BYTES, st>>>(maps.a, maps.b, maps.c, p);
-  return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
+  p.tiles_n = (max_n + TN - 1) / TN;
+  // CTA pairs (256-row tiles) once there is more than one wave of 128-row tiles: below that a pair would leave SMs idle
+  const int tiles1 = p.count * ((max_m + 127) / 128) * p.tiles_n;
+  const bool pair = g_use_tf32x3 == 3 && tiles1 > n_sms;
+  if (pair) {
+    p.tiles_m = (max_m + 255) / 256;
+    return launch_gemm<2>(maps, p, n_sms, st);
+  }
+  p.tiles_m = (max_m + 127) / 128;
+  return launch_gemm<1>(maps, p, n_sms, st);
 }
 
 int gemm_tf32x3(const Tf32Maps& maps, int M, int N, int K, int a_row0, int a_col0, int b_row0, int b_col0, int c_row0,

@@ -364,5 +364,6 @@ def set_solve_super(blocks: int) -> int:
 
 def set_tf32x3(enable) -> int:
     """A/B hook: 0 = fp32 SIMT GEMM, 1 = 3xTF32 with the round-to-nearest split, 2 = 3xTF32 with the truncation split
-    (hi is the landed tile itself); returns the previous setting."""
+    (hi is the landed tile itself), 3 (default) = 2 plus CTA-pair 256 x 256 tiles for multi-wave launches; returns the
+    previous setting."""
     return int(lib.gq_set_tf32x3(int(enable)))

@@ -164,7 +164,9 @@ int gq_gemm_tf32x3(const float* A, const float* B, float* C, int M, int N, int K
                    int upper_only, void* stream);
 /* A/B parity hook: 0 routes K4 and the Cholesky trailing update through the fp32 SIMT GEMM instead of the
  * 3xTF32 tensor-core GEMM; 1 = 3xTF32 with x = rna_tf32(x) + lo; 2 = 3xTF32 with x = trunc_tf32(x) + lo (the landed
- * fp32 tile is the hi operand as it is: kind::tf32 reads only the upper 19 bits).  Returns the previous setting. */
+ * fp32 tile is the hi operand as it is: kind::tf32 reads only the upper 19 bits); 3 (default) = 2 plus 256 x 256 tiles on
+ * CTA pairs (tcgen05 cta_group::2, each CTA stages half of B) when a launch has more than one wave of tiles.  Returns the
+ * previous setting. */
 int gq_set_tf32x3(int enable);
 /* Tuning hook: blocks per super-block of K4's two-level lazy-batch update (default 8; 1 = the reference's schedule, one
  * full trailing update per block, gptq_py.py:139).  Returns the previous setting. */

@@ -127,6 +127,65 @@ def test_gemm_tf32x3_is_fp32_faithful(M, N, K, upper):
     assert err <= 4e-6 * scale, (err, scale)
 
 
+@pytest.mark.parametrize('M,N,K,upper', [(3968, 4096, 128, False), (2200, 2560, 192, False), (4096, 4096, 1024, False),
+                                         (10880, 10880, 128, True), (2304, 2304, 64, True)])
+def test_gemm_tf32x3_cta_pair(M, N, K, upper):
+    """Mode 3: 256 x 256 tiles on CTA pairs (tcgen05 cta_group::2, each CTA stages half of B) whenever there is more than
+    one wave of tiles.  Same fp32-faithful bound; ragged M (the second CTA of the last pair partly or wholly past the
+    edge), upper-only tile skipping on 256-row tiles."""
+    import gptq
+    g = torch.Generator(device='cuda').manual_seed(M + N + K + 3)
+    A = torch.randn(K, M, device='cuda', generator=g)
+    B = torch.randn(K, N, device='cuda', generator=g)
+    C0 = torch.randn(M, N, device='cuda', generator=g)
+    prev = gptq.set_tf32x3(3)
+    try:
+        C = C0.clone()
+        gptq.gemm_tf32x3(A, B, C, M, N, K, M, N, N, -1.0, upper)
+        torch.cuda.synchronize()
+    finally:
+        gptq.set_tf32x3(prev)
+    want = C0.double() - A.double().t() @ B.double()
+    scale = (A.abs().double().t() @ B.abs().double()).max().item()
+    if upper:
+        mask = torch.zeros(M, N, dtype=torch.bool, device='cuda')
+        for m0 in range(0, M, 256):
+            for n0 in range(0, N, 256):
+                if not (m0 >= n0 + 256):
+                    mask[m0:m0 + 256, n0:n0 + 256] = True
+        assert torch.equal(C[~mask], C0[~mask])
+        triu = torch.ones(M, N, dtype=torch.bool, device='cuda').triu()
+        assert (mask | ~triu).all()                           # everything on or above the diagonal is computed
+        err = ((C.double() - want)[mask]).abs().max().item()
+    else:
+        err = (C.double() - want).abs().max().item()
+    assert err <= 4e-6 * scale, (err, scale)
+
+
+def test_invert_cta_pair_mode_matches():
+    """hessian_invert with the CTA-pair GEMM (far updates of the Cholesky and the triangular products) == the
+    single-CTA GEMM up to fp32 summation order."""
+    import gptq
+    D = 4096
+    g = torch.Generator(device='cuda').manual_seed(5)
+    X = torch.randn(2 * D, D, device='cuda', generator=g) * torch.exp(torch.rand(D, device='cuda', generator=g) * 3 - 1.5)
+    H = X.t() @ X
+    perm = torch.argsort(H.diagonal(), descending=True)
+    damp = 0.01 * float(H.diagonal().mean())
+    outs = {}
+    for mode in (2, 3):
+        prev = gptq.set_tf32x3(mode)
+        try:
+            _, U, info = gptq.hessian_invert(H, perm, 1.0, damp)
+            torch.cuda.synchronize()
+        finally:
+            gptq.set_tf32x3(prev)
+        assert int(info.item()) == 0
+        outs[mode] = U
+    rel = ((outs[3] - outs[2]).norm() / outs[2].norm()).item()
+    assert rel <= 1e-5, rel
+
+
 @pytest.mark.parametrize('M,N,K', [(128, 256, 128), (3968, 4096, 128), (1024, 768, 1024)])
 def test_gemm_tf32x3_truncation_split(M, N, K):
     """Mode 2: the landed fp32 tile is the hi operand as it is (the tensor core reads its upper 19 bits) and only

@@ -8,6 +8,8 @@ import torch
 import gptq
 dev = torch.device('cuda')
 which = sys.argv[1]
+if os.environ.get('GQ_TF32_MODE'):
+    gptq.set_tf32x3(int(os.environ['GQ_TF32_MODE']))
 if which == 'tf32':
     # default: one K4 near update; `tf32 9984 4096 1024` = the far update behind a super-block of 8 blocks (down_proj)
     M, N, K = (int(v) for v in sys.argv[2:5]) if len(sys.argv) >= 5 else (3968, 4096, 128)
