@@ -376,6 +376,12 @@ def gpu_main(args):
     ev1.record()
     ctx.barrier()
     launches = lib.gq_launch_count() - l0
+    # sanity of what was timed: every linear of the last step must be a usable 4-bit quantisation (relative squared
+    # error of a g128 4-bit grid on these weights is ~1e-2; garbage from a broken kernel is >= 1)
+    for name, (_, met) in out.items():
+        rel = met['l2.0_error'] / max(met['l2.0_norm'], 1e-30)
+        if not (rel == rel and rel < 0.1 and met['gptq_error'] == met['gptq_error']):
+            raise RuntimeError(f'bench: {name} came out wrong (relative squared error {rel}, metrics {met})')
     clocks = sampler.stop() if ctx.rank == 0 else None
     step_s = ctx.max_over_ranks(ev0.elapsed_time(ev1) / 1e3 / args.steps)
 

@@ -91,6 +91,19 @@ __global__ void __launch_bounds__(256) trtri_diag_kernel(float* __restrict__ A, 
   }
 }
 
+// Zero every 128 x 128 block of A strictly below the block diagonal.  After the factorisation that region still holds the
+// input matrix; the triangular products read A-operand windows with TF32_A_UPPER, and on CTA-pair tiles (256 rows, one
+// shared k range) the first CTA of a pair reads 128 k-rows below its own diagonal block, which must be zeros.
+__global__ void __launch_bounds__(256) zero_block_lower_kernel(float* __restrict__ A, int D) {
+  const int bj = blockIdx.x, bi = blockIdx.y;
+  if (bi <= bj) return;
+  const int r0 = bi * NB, c0 = bj * NB;
+  for (int idx = threadIdx.x; idx < NB * (NB / 4); idx += 256) {
+    const int r = idx >> 5, c4 = (idx & 31) * 4;
+    if (r0 + r < D && c0 + c4 < D) *reinterpret_cast<float4*>(A + (size_t)(r0 + r) * D + c0 + c4) = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+}
+
 // V12 = W21^T for every pair of a doubling level: Wb[c0 + j][r0 + i] -> A[r0 + i][c0 + j]
 struct TransposeBatch {
   int count;
@@ -217,6 +230,11 @@ int chol_inverse_upper(float* A, int D, float* U, float* Wb, float* tmp, int* in
   GQ_LAUNCHED();
   trtri_diag_kernel<<<nb, 256, trtri_smem, st>>>(A, Wb, D);
   if (cudaGetLastError() != cudaSuccess) return GQ_ERR_CUDA;
+  if (nb > 1) {
+    GQ_LAUNCHED();
+    zero_block_lower_kernel<<<dim3(nb, nb), 256, 0, st>>>(A, D);
+    if (cudaGetLastError() != cudaSuccess) return GQ_ERR_CUDA;
+  }
   // ---- V = R^-1 by recursive doubling over diagonal blocks
   for (int w = 1; w < nb; w *= 2) {
     const int n1 = w * NB;

@@ -162,11 +162,11 @@ def test_gemm_tf32x3_cta_pair(M, N, K, upper):
     assert err <= 4e-6 * scale, (err, scale)
 
 
-def test_invert_cta_pair_mode_matches():
-    """hessian_invert with the CTA-pair GEMM (far updates of the Cholesky and the triangular products) == the
-    single-CTA GEMM up to fp32 summation order."""
+@pytest.mark.parametrize('D', [4096, 11008])
+def test_invert_cta_pair_mode_matches(D):
+    """hessian_invert with the CTA-pair GEMM (far updates of the Cholesky and, from D = 11008 on, the batched triangular
+    products with their clipped k ranges) == the single-CTA GEMM up to fp32 summation order, and U^T U H = I."""
     import gptq
-    D = 4096
     g = torch.Generator(device='cuda').manual_seed(5)
     X = torch.randn(2 * D, D, device='cuda', generator=g) * torch.exp(torch.rand(D, device='cuda', generator=g) * 3 - 1.5)
     H = X.t() @ X
@@ -182,8 +182,16 @@ def test_invert_cta_pair_mode_matches():
             gptq.set_tf32x3(prev)
         assert int(info.item()) == 0
         outs[mode] = U
-    rel = ((outs[3] - outs[2]).norm() / outs[2].norm()).item()
+    rel = ((outs[3].double() - outs[2].double()).norm() / outs[2].double().norm()).item()
     assert rel <= 1e-5, rel
+    # independent check of the pair-mode result on a slice: rows of (U^T U) (H_perm + damp I) = I
+    Hp = (H[perm][:, perm] + damp * torch.eye(D, device='cuda')).double()
+    Ud = outs[3].double()
+    rows = torch.arange(0, D, max(1, D // 64), device='cuda')
+    got = (Ud.t()[rows] @ Ud) @ Hp
+    want = torch.zeros_like(got)
+    want[torch.arange(len(rows), device='cuda'), rows] = 1.0
+    assert (got - want).abs().max().item() <= 2e-2
 
 
 @pytest.mark.parametrize('M,N,K', [(128, 256, 128), (3968, 4096, 128), (1024, 768, 1024)])
