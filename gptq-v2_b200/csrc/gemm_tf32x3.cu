@@ -79,7 +79,7 @@ __device__ __forceinline__ void tma_store_2d(const void* tmap, uint32_t src, int
                :: "l"(reinterpret_cast<uint64_t>(tmap)), "r"(src), "r"(c0), "r"(c1) : "memory");
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ float rna_tf32(float x) {
   uint32_t r;
@@ -280,8 +280,9 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
         }
         if (rows_live && n0 + c * 32 < pq.N) {
           const uint32_t stg = stg0 + buf * EPI_BUF;
-          // the previous reduce from this buffer must have finished reading it
-          if (lane == 0) bulk_wait_read0();
+          // the reduce issued from THIS buffer two chunks ago must have finished reading it; the one issued from the
+          // other buffer one chunk ago may still be in flight (one bulk group per chunk, so "at most 1 pending")
+          if (lane == 0) bulk_wait_read1();
           __syncwarp();
 #pragma unroll
           for (int q = 0; q < 8; ++q) {
@@ -385,9 +386,12 @@ int gemm_tf32x3_batch(const Tf32Maps& maps, const Tf32Problem* probs, int count,
   }
   if (p.count == 0) return GQ_OK;
   p.tiles_n = (max_n + TN - 1) / TN;
-  // CTA pairs (256-row tiles) once there is more than one wave of 128-row tiles: below that a pair would leave SMs idle
+  // CTA pairs (256-row tiles) whenever they need no more waves than single CTAs would: a pair's main loop moves a third
+  // less through shared memory per flop, which also shortens the one-tile-per-CTA near updates on the critical path
   const int tiles1 = p.count * ((max_m + 127) / 128) * p.tiles_n;
-  const bool pair = g_use_tf32x3 == 3 && tiles1 > n_sms;
+  const int tiles2 = p.count * ((max_m + 255) / 256) * p.tiles_n;
+  const int waves1 = (tiles1 + n_sms - 1) / n_sms, waves2 = (tiles2 + n_sms / 2 - 1) / (n_sms / 2);
+  const bool pair = g_use_tf32x3 == 3 && max_m > 128 && waves2 <= waves1;
   if (pair) {
     p.tiles_m = (max_m + 255) / 256;
     return launch_gemm<2>(maps, p, n_sms, st);
