@@ -20,6 +20,8 @@ compat mode beyond self-consistency).
 `python oracle/gen_golden.py quantizer` writes only the q_*.npz cases: symmetric grids, MSE grid search, EXL2 quantised
 scales and per-group bit widths (quant.py:40-69,99-112,120-165) through the reference's round-to-nearest and fp32
 branches (gptq_py.py:101-124,158-193).
+`python oracle/gen_golden.py blocks` writes only the b_*.npz cases: GPTQ blocks larger / smaller than the quantisation
+groups and non-uniform group sizes through the reference's fp32 branch (gptq_py.py:158-193).
 """
 import os
 import sys
@@ -152,9 +154,53 @@ def main_quantizer():
         print('wrote', name, {k: f'{v:.4e}' for k, v in res['metrics'].items()})
 
 
+# ---- GPTQ blocks that differ from the quantisation groups, non-uniform group sizes (gptq_py.py:158-193, fp32 branch)
+B_CASES = [
+    # name,                R,  C,  group sizes,          bits,            block sizes,            act_order, dtype
+    ('b_blk256_g128',      64, 512, [128] * 4,           [4] * 4,         [256, 256],             True,  torch.float16),
+    ('b_blk64_g128',       64, 256, [128, 128],          [4, 4],          [64] * 4,               True,  torch.float16),
+    ('b_blk128_g32',       48, 256, [32] * 8,            [3] * 8,         [128, 128],             False, torch.bfloat16),
+    ('b_groups_64_128_64', 64, 256, [64, 128, 64],       [4, 3, 4],       [128, 128],             True,  torch.float16),
+]
+
+
+def main_blocks():
+    from oracle import gptq_oracle as O
+    gptq_py, quant = import_reference()
+    torch.set_num_threads(1)
+    out_dir = os.path.join(ROOT, 'tests', 'golden')
+    for name, R, C, gsz, bits, bsz, act, dtype in B_CASES:
+        n_seq, seqlen = 4, 128
+        W, X = O.synth_linear(R, C, n_seq, seqlen, dtype=dtype, seed=900 + R + C + len(name))
+        hook = gptq_py.HessianHook()
+        for i in range(0, n_seq, 2):
+            hook.add_batch(X[i:i + 2], use_kernel=False)
+        hook.invert(damp_ratio=1e-2, act_order=act)
+        res = gptq_py.gptq_quant(weight=W, hessian_hook=hook, group_sizes=torch.tensor(gsz, dtype=torch.int32),
+                                 group_bit_widths=torch.tensor(bits, dtype=torch.int32), scale_bit_width=None,
+                                 gptq_use_kernel=False, gptq_block_sizes=torch.tensor(bsz, dtype=torch.int32),
+                                 quant_symmetric=False, quant_mse=False)
+        lin = quant.reconstruct_nn_linear(res['quant_meta'], dtype=dtype)
+        m = res['quant_meta']
+        to_np = lambda t: t.to(torch.float32).numpy() if t.dtype in (torch.float16, torch.bfloat16) else t.numpy()
+        np.savez_compressed(
+            os.path.join(out_dir, name + '.npz'),
+            R=R, C=C, group_sizes=np.array(gsz), bits=np.array(bits), block_sizes=np.array(bsz), act_order=int(act),
+            dtype=str(dtype).split('.')[-1], W_bits=W.view(torch.int16).numpy(), U=hook.hessian_inv.numpy(),
+            perm=(hook.perm.numpy() if hook.perm is not None else np.arange(C)),
+            qweight=m['qweight'].numpy(), scale=to_np(m['scale']), qzero=m['qzero'].numpy(), perm_inv=m['perm_inv'].numpy(),
+            metrics=np.array([res['metrics'][k] for k in ('gptq_error', 'gptq_norm', 'l2.0_error', 'l2.0_norm')],
+                             dtype=np.float64),
+            W_hat=to_np(lin.weight.data))
+        print('wrote', name, {k: f'{v:.4e}' for k, v in res['metrics'].items()})
+
+
 if __name__ == '__main__':
     if len(sys.argv) > 1 and sys.argv[1] == 'quantizer':
         main_quantizer()
+    elif len(sys.argv) > 1 and sys.argv[1] == 'blocks':
+        main_blocks()
     else:
         main()
         main_quantizer()
+        main_blocks()

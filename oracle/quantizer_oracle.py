@@ -153,6 +153,69 @@ def solve_general(weight: torch.Tensor, U: Optional[torch.Tensor], perm: Optiona
     return out
 
 
+def solve_blocks(weight: torch.Tensor, U: torch.Tensor, perm: Optional[torch.Tensor], group_sizes: Sequence[int],
+                 bits: Sequence[int], block_sizes: Sequence[int]) -> dict:
+    """The fp32 branch of gptq_quant (gptq_py.py:158-193) with GPTQ blocks that differ from the quantisation groups and
+    group sizes that need not be uniform (asymmetric min/max grid, no MSE search), exactly as the reference walks it:
+    the parameters of a group are computed when the column loop reaches the group's first column, from the GLOBAL
+    weight matrix (:175-176) -- which holds the lazy-batch updates of the finished blocks but NOT the in-block updates
+    of the current one -- while the columns themselves are quantised from the error-compensated block copy (:186);
+    a quantiser stays in force across block ends (:167,171)."""
+    W = weight.to(torch.float32).clone()
+    if perm is not None:
+        W = W[:, perm]
+    R, C = W.shape
+    assert sum(group_sizes) == C and sum(block_sizes) == C and len(bits) == len(group_sizes)
+    gid = [0]
+    for n in group_sizes:
+        gid.append(gid[-1] + int(n))
+    bid = [0]
+    for n in block_sizes:
+        bid.append(bid[-1] + int(n))
+    quant, qweight, error = torch.empty_like(W), torch.empty_like(W), torch.empty_like(W)
+    params = []
+    cur, P = 0, None
+    for i1, i2 in zip(bid[:-1], bid[1:]):
+        blk = W[:, i1:i2].clone()
+        eblk = torch.empty_like(blk)
+        for j in range(i1, i2):
+            if cur < len(group_sizes) and j == gid[cur]:
+                P = find_params(W[:, j:j + int(group_sizes[cur])], int(bits[cur]))          # :172-177
+                params.append(P)
+                cur += 1
+            w = blk[:, j - i1:j - i1 + 1]
+            qw = G.quantize(w, P['scale'], P['qzero'], P['maxq'])
+            q = G.dequantize(qw, P['scale'], P['qzero'])
+            err = (w - q) / U[j, j]
+            qweight[:, j:j + 1], quant[:, j:j + 1] = qw, q
+            error[:, j:j + 1] = eblk[:, j - i1:j - i1 + 1] = err
+            blk[:, j - i1 + 1:] -= err @ U[j:j + 1, j + 1:i2]
+        W[:, i2:] -= eblk @ U[i1:i2, i2:]
+    out = dict(quant=quant, qweight=qweight, error=error, mse_index=None)
+    out.update(_collect(params))
+    return out
+
+
+def assemble_blocks(weight_ref: torch.Tensor, solved: dict, U: torch.Tensor, perm: Optional[torch.Tensor],
+                    group_sizes: Sequence[int], bits: Sequence[int]) -> dict:
+    """gptq_py.py:195-251 for solve_blocks (no EXL2 metadata, so the groups keep their order)."""
+    R, C = weight_ref.shape
+    dtype = weight_ref.dtype
+    err = solved['error']
+    metrics = {'gptq_error': (err ** 2.0).mean().item(),
+               'gptq_norm': ((weight_ref / U.diag()) ** 2.0).mean().item()}
+    p16 = perm.to(torch.int16) if perm is not None else torch.arange(C, dtype=torch.int16)
+    perm_inv = p16.argsort().to(torch.int16)
+    quant = solved['quant'][:, perm_inv.to(torch.int32)]
+    metrics['l2.0_error'] = ((quant.to(torch.float32) - weight_ref.to(torch.float32)).abs() ** 2.0).mean().item()
+    metrics['l2.0_norm'] = (weight_ref.abs() ** 2.0).mean().item()
+    meta = {'qweight': solved['qweight'].to(torch.uint8), 'scale': solved['scale'].to(dtype),
+            'qzero': solved['qzero'].to(torch.uint8), 'qscale': None, 'sscale': None, 'perm_inv': perm_inv,
+            'group_sizes': torch.tensor([int(n) for n in group_sizes], dtype=torch.int16),
+            'group_bit_widths': torch.tensor(list(bits), dtype=torch.uint8), 'scale_bit_width': None}
+    return {'quant_meta': meta, 'metrics': metrics}
+
+
 def group_order(bits: Sequence[int], group_size: int, scale_bits: Optional[int]):
     """gptq_py.py:201-212: with EXL2 metadata the groups are stored by descending bit width (ties: ascending index)."""
     order = list(range(len(bits)))

@@ -50,3 +50,23 @@ def load(name):
     out['perm_inv'] = torch.from_numpy(d['perm_inv'].copy())
     out['metrics'] = dict(zip(('gptq_error', 'gptq_norm', 'l2.0_error', 'l2.0_norm'), d['metrics'].tolist()))
     return out
+
+
+def bnames():
+    """GPTQ blocks != quantisation groups, non-uniform group sizes (fp32 branch of the reference)."""
+    return sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(GOLDEN_DIR, 'b_*.npz')))
+
+
+def loadb(name):
+    z = np.load(os.path.join(GOLDEN_DIR, name + '.npz'))
+    d = {k: z[k] for k in z.files}
+    dt = _DT[str(d['dtype'])]
+    out = dict(name=name, R=int(d['R']), C=int(d['C']), group_sizes=[int(v) for v in d['group_sizes']],
+               bits=[int(v) for v in d['bits']], block_sizes=[int(v) for v in d['block_sizes']],
+               act_order=bool(int(d['act_order'])), dtype=dt)
+    out['W'] = torch.from_numpy(d['W_bits'].copy()).view(dt)
+    for k in ('U', 'scale', 'W_hat', 'qweight', 'qzero', 'perm_inv'):
+        out[k] = torch.from_numpy(d[k].copy())
+    out['perm'] = torch.from_numpy(d['perm'].copy()).to(torch.int64) if out['act_order'] else None
+    out['metrics'] = dict(zip(('gptq_error', 'gptq_norm', 'l2.0_error', 'l2.0_norm'), d['metrics'].tolist()))
+    return out
