@@ -13,8 +13,10 @@ Host-side torch ops are limited to what the reference also leaves to torch and t
 O(D) or a single elementwise pass (argsort of the diagonal, metrics).
 The Quantizer options llama.py never sets are supported on all three branches:
 quant_symmetric, quant_mse (grid search, gq_mse_refine), scale_bit_width (EXL2 qscale / sscale), per-group bit widths.
-Still NotImplementedError: non-uniform group sizes, gptq_block_sizes != group_sizes, quant_use_kernel=True (needs
-exllamav2, which the reference itself no longer imports).
+gptq_block_sizes != group_sizes runs on the fp32 branch when the two nest (blocks of whole groups or groups of whole
+blocks, the smaller one in {32, 64, 128}) without the MSE search / EXL2 scales.
+Still NotImplementedError: non-uniform group sizes, quant_use_kernel=True (needs exllamav2, which the reference itself
+no longer imports).
 """
 from __future__ import annotations
 
@@ -119,8 +121,11 @@ def gptq_quant(
     device = weight.device
     gs = _uniform(group_sizes, 'group_sizes')
     bits_list = [int(v) for v in group_bit_widths.tolist()]
-    if gptq_block_sizes is not None and _uniform(gptq_block_sizes, 'gptq_block_sizes') != gs:
-        raise NotImplementedError('gptq_block_sizes must equal group_sizes (as llama.py:155 sets them)')
+    # GPTQ blocks matter only to the fp32 branch (ref :161): the round-to-nearest branch has no blocks and the kernel
+    # branch "assume[s] gptq_block_sizes is the same as quantization group_sizes" (ref :126)
+    blk = gs
+    if gptq_block_sizes is not None and hessian_hook is not None and not gptq_use_kernel:
+        blk = _uniform(gptq_block_sizes, 'gptq_block_sizes')
     n_groups = n_columns // gs
     assert n_groups * gs == n_columns and len(bits_list) == n_groups
     maxq_list = [float(2 ** b - 1) for b in bits_list]
@@ -168,7 +173,44 @@ def gptq_quant(
                 qscale_gr[rows] = qs.squeeze(-1)
                 sscale_g[rows] = ss.reshape(-1)
 
-    if gptq_use_kernel and hessian_hook is not None:
+    if blk != gs:
+        # ---- fp32 branch with GPTQ blocks that differ from the quantisation groups (ref :161-193).  The reference
+        # computes a group's parameters when its column loop reaches the group's first column, from the GLOBAL weights:
+        # they hold the lazy-batch updates of the finished blocks but not the in-block updates of the current one.
+        #   blk > gs: the parameters of every group of a block come from the weights as they are at the block's start;
+        #             the block is then solved group by group (mode 4, supplied parameters) -- the same updates as the
+        #             reference's in-block propagation, applied in a different order (fp32 reordering only);
+        #   blk < gs: the parameters come from the weights at the group's start (= a block start), then the group is
+        #             solved in blocks of blk columns that all use them.
+        if quant_mse or exl2:
+            # ref :178-184 runs Quantizer.mse over the BLOCK's columns, not the group's: not reproduced
+            raise NotImplementedError('gptq_block_sizes != group_sizes is supported without quant_mse / scale_bit_width')
+        step = min(gs, blk)
+        if step not in (32, 64, 128) or max(gs, blk) % step != 0 or n_columns % blk != 0:
+            raise NotImplementedError('gptq_block_sizes / group_sizes must nest, the smaller one in {32, 64, 128}')
+        maxq_dev = torch.tensor(maxq_list, dtype=torch.float32, device=device)
+        scale_gr = torch.empty(n_groups, n_rows, dtype=torch.float32, device=device)
+        qzero_gr = torch.empty_like(scale_gr)
+        out = None
+        if blk > gs:
+            per = blk // gs
+            for g0 in range(0, n_groups, per):
+                _ops.find_params(Wt, gs, maxq_dev, sym, scale_gr, qzero_gr, g0, per)
+                for g in range(g0, g0 + per):
+                    out = _ops.gptq_solve_ex(Wt, U, scale_gr, qzero_gr, gs, maxq_list, mode=4, a=g * gs, b=(g + 1) * gs, out=out)
+        else:
+            per = gs // blk
+            n_steps = n_columns // blk
+            scale_st = torch.empty(n_steps, n_rows, dtype=torch.float32, device=device)
+            qzero_st = torch.empty_like(scale_st)
+            maxq_st = [maxq_list[i // per] for i in range(n_steps)]
+            for g in range(n_groups):
+                _ops.find_params(Wt, gs, maxq_dev, sym, scale_gr, qzero_gr, g, 1)
+                scale_st[g * per:(g + 1) * per] = scale_gr[g]
+                qzero_st[g * per:(g + 1) * per] = qzero_gr[g]
+                out = _ops.gptq_solve_ex(Wt, U, scale_st, qzero_st, blk, maxq_st, mode=4, a=g * gs, b=(g + 1) * gs, out=out)
+        quant_t, codes_t, err_t = out
+    elif gptq_use_kernel and hessian_hook is not None:
         # static parameters from the original permuted weights (ref :131-134), then the reference's per-group
         # gptq_quantize_range loop (ref :135-139) as one library call
         group_params(0, n_groups)

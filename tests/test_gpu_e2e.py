@@ -97,8 +97,18 @@ def test_unsupported_options_raise():
         gptq_quant(W, None, gs, bw, quant_mse=True, quant_use_kernel=True)
     with pytest.raises(NotImplementedError):          # non-uniform group sizes
         gptq_quant(W, None, torch.tensor([64, 192], dtype=torch.int32), bw, quant_mse=False)
-    with pytest.raises(NotImplementedError):          # GPTQ blocks that are not the quantisation groups
-        gptq_quant(W, None, gs, bw, quant_mse=False, gptq_block_sizes=torch.full([4], 64, dtype=torch.int32))
+    import types
+    hook = types.SimpleNamespace(hessian_inv=torch.eye(256, device='cuda'), perm=None, perm_inv=None, hessian=None)
+    with pytest.raises(NotImplementedError):          # GPTQ blocks that do not nest with the quantisation groups
+        gptq_quant(W, hook, gs, bw, gptq_use_kernel=False, quant_mse=False,
+                   gptq_block_sizes=torch.full([2], 96, dtype=torch.int32))
+    with pytest.raises(NotImplementedError):          # differing blocks with the MSE search (ref :178-184 searches over the block)
+        gptq_quant(W, hook, gs, bw, gptq_use_kernel=False, quant_mse=True,
+                   gptq_block_sizes=torch.full([4], 64, dtype=torch.int32))
+    # the round-to-nearest branch has no blocks (ref :101-124): gptq_block_sizes is ignored there, as in the reference
+    a = gptq_quant(W, None, gs, bw, quant_mse=False, gptq_block_sizes=torch.full([4], 64, dtype=torch.int32), save_device=W.device)
+    b = gptq_quant(W, None, gs, bw, quant_mse=False, gptq_block_sizes=gs, save_device=W.device)
+    assert torch.equal(a['quant_meta']['qweight'], b['quant_meta']['qweight'])
 
 
 def test_rtn_without_hook():

@@ -198,3 +198,34 @@ def test_solve_ex_mode4_equals_mode0_on_asymmetric_parameters():
     finally:
         ops.set_solve_super(8)
     assert torch.equal(out[1], c0) and torch.equal(out[0], q0) and torch.equal(out[2], e0)
+
+
+@pytest.mark.parametrize('name', [n for n in GU.bnames() if 'groups_' not in n])
+def test_gptq_quant_blocks_differ_from_groups(name):
+    """gptq_block_sizes != group_sizes on the fp32 branch (gptq_py.py:161-193) against the outputs of the real reference
+    (tests/golden/b_*.npz): group parameters from the global weights at the block / group start, blocks nested in
+    groups or groups nested in blocks.  Blocks smaller than groups repeat the reference's own blocking; blocks larger
+    than groups apply the same updates in another order (fp32 reordering: rounding ties may move)."""
+    from gptq_py import gptq_quant
+    g = GU.loadb(name)
+    hook = types.SimpleNamespace(hessian_inv=g['U'].to(DEV), perm=(g['perm'].to(DEV) if g['perm'] is not None else None),
+                                 perm_inv=(torch.argsort(g['perm']).to(DEV) if g['perm'] is not None else None), hessian=None)
+    res = gptq_quant(weight=g['W'].to(DEV), hessian_hook=hook,
+                     group_sizes=torch.tensor(g['group_sizes'], dtype=torch.int32),
+                     group_bit_widths=torch.tensor(g['bits'], dtype=torch.int32), scale_bit_width=None,
+                     gptq_use_kernel=False, gptq_block_sizes=torch.tensor(g['block_sizes'], dtype=torch.int32),
+                     quant_symmetric=False, quant_mse=False)
+    m = res['quant_meta']
+    assert torch.equal(m['perm_inv'], g['perm_inv'])
+    match = O.code_match(m['qweight'], g['qweight'])
+    assert match >= 0.999, match
+    assert (m['qzero'].float() - g['qzero'].float()).abs().max().item() <= 1
+    assert (m['qzero'] == g['qzero']).float().mean().item() >= 0.995
+    assert torch.allclose(m['scale'].float(), g['scale'], rtol=2e-3, atol=0)
+    for k in ('gptq_error', 'l2.0_error'):
+        assert res['metrics'][k] == pytest.approx(g['metrics'][k], rel=1e-2), k
+    # MSE search and EXL2 scales with differing blocks are refused, as are sizes that do not nest
+    with pytest.raises(NotImplementedError):
+        gptq_quant(weight=g['W'].to(DEV), hessian_hook=hook, group_sizes=torch.tensor(g['group_sizes'], dtype=torch.int32),
+                   group_bit_widths=torch.tensor(g['bits'], dtype=torch.int32), gptq_use_kernel=False,
+                   gptq_block_sizes=torch.tensor(g['block_sizes'], dtype=torch.int32), quant_mse=True)
