@@ -266,24 +266,3 @@ def gptq_quant_group_sharded(weights: Sequence[torch.Tensor], hessian_hook, quan
                      'scale_bit_width': None})
         results.append({'quant_meta': meta, 'metrics': {k: v / R for k, v in zip(keys, msum[i])}})
     return results
-
-
-def assign_modules(names: Sequence[str], world: int) -> dict[str, int]:
-    """"modules" mode: the linears of one Hessian group go round-robin to ranks (q,k,v -> 3 ranks; up,gate -> 2)."""
-    return {n: i % world for i, n in enumerate(names)}
-
-
-def broadcast_quant_meta(meta: Optional[dict], src: int, R: int, C: int, G: int, scale_dtype: torch.dtype,
-                         device: torch.device, group=None) -> dict:
-    """"modules" mode: the owner of a linear broadcasts its quant_meta tensors to every rank."""
-    out = {}
-    rank, world = world_info(group)
-    spec = (('qweight', (R, C), torch.uint8), ('scale', (R, G), scale_dtype), ('qzero', (R, G), torch.uint8),
-            ('perm_inv', (C,), torch.int16), ('group_sizes', (G,), torch.int16), ('group_bit_widths', (G,), torch.uint8))
-    for k, shape, dt in spec:
-        t = meta[k].to(device).contiguous() if rank == src else torch.empty(shape, dtype=dt, device=device)
-        if world > 1:
-            dist.broadcast(t, src=src, group=group)
-        out[k] = t
-    out.update({'qscale': None, 'sscale': None, 'scale_bit_width': None})
-    return out

@@ -215,4 +215,3 @@ def test_shard_range_properties():
         assert max(sizes) - min(sizes) <= mult
     with pytest.raises(ValueError):
         sharded.shard_range(10, 2, 0, 4)
-    assert sharded.assign_modules(['v', 'k', 'q'], 2) == {'v': 0, 'k': 1, 'q': 0}
