@@ -100,6 +100,11 @@ int gq_find_params(const float* Wt, int R, int group, int n_groups, const float*
   return find_params(Wt, R, group, n_groups, maxq_groups_dev, sym, scale_gr, qzero_gr, S(stream));
 }
 
+int gq_rtn_quantize(const float* Wt, int R, int group, int n_groups, const float* maxq_groups_dev, const float* scale_gr,
+                    const float* qzero_gr, float* quant_t, uint8_t* codes_t, void* stream) {
+  return rtn_quantize(Wt, R, group, n_groups, maxq_groups_dev, scale_gr, qzero_gr, quant_t, codes_t, S(stream));
+}
+
 int gq_mse_refine(const float* Wt, int R, int group, int n_groups, const float* maxq_groups_dev, const float* grid_dev,
                   int n_grid, float norm, float* scale_gr, const float* qzero_gr, int32_t* index_gr, void* stream) {
   return mse_refine(Wt, R, group, n_groups, maxq_groups_dev, grid_dev, n_grid, norm, scale_gr, qzero_gr, index_gr,

@@ -207,7 +207,7 @@ chol_panel_kernel(float* __restrict__ A, int D, int o, int n, int rest, int* __r
 template <int PC>
 int launch_cp(float* A, int D, int o, int n, int rest, int* info, cudaStream_t st) {
   const int smem = (NB * (NB + PC) + NB) * (int)sizeof(float);
-  static bool attr_set = false;
+  static PerDeviceFlag attr_set;   // function attributes are per device
   if (!attr_set) {
     if (cudaFuncSetAttribute(chol_panel_kernel<PC>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess)
       return GQ_ERR_CUDA;

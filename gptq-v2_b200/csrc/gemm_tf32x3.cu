@@ -335,7 +335,7 @@ int gemm_tf32x3_maps(Tf32Maps* maps, const float* A, int a_rows, int a_cols, int
 
 template <int CG>
 static int launch_gemm(const Tf32Maps& maps, const GemmTf32Params& p, int n_sms, cudaStream_t st) {
-  static bool attr_set = false;
+  static PerDeviceFlag attr_set;   // function attributes are per device
   if (!attr_set) {
     if (cudaFuncSetAttribute(gemm_tf32x3_kernel<CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<CG>::SMEM_BYTES) !=
         cudaSuccess)

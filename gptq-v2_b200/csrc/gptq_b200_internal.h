@@ -14,7 +14,24 @@
 #define GQ_ERR_NOT_SPD 7     // Cholesky met a non-positive pivot (caller adds damping and retries)
 #define GQ_ERR_ARG 8
 
+#include <atomic>
+
 namespace gq {
+
+// cudaFuncSetAttribute is per DEVICE: "done once" flags are indexed by the current device (a process may drive several
+// GPUs, e.g. an HF device_map) and atomic (llama_driver.py runs worker threads).
+constexpr int GQ_MAX_DEVICES = 64;
+struct PerDeviceInt {
+  std::atomic<int> v[GQ_MAX_DEVICES];
+  PerDeviceInt() { for (auto& x : v) x.store(0, std::memory_order_relaxed); }
+  static int dev() { int d = 0; cudaGetDevice(&d); return (d >= 0 && d < GQ_MAX_DEVICES) ? d : 0; }
+  int get() const { return v[dev()].load(std::memory_order_acquire); }
+  void set(int x) { v[dev()].store(x, std::memory_order_release); }
+};
+struct PerDeviceFlag : PerDeviceInt {
+  bool operator!() const { return get() == 0; }
+  PerDeviceFlag& operator=(bool b) { set(b ? 1 : 0); return *this; }
+};
 
 // number of kernels this library has launched (bench.py reports it as gpu_launches)
 extern unsigned long long g_launch_count;
@@ -85,6 +102,8 @@ int gptq_solve(float* Wt, const float* U, float* quant_t, void* codes_t, int cod
                cudaStream_t st, const float* maxq_groups = nullptr);
 int find_params(const float* Wt, int R, int group, int n_groups, const float* maxq_groups_dev, int sym, float* scale_gr,
                 float* qzero_gr, cudaStream_t st);
+int rtn_quantize(const float* Wt, int R, int group, int n_groups, const float* maxq_groups_dev, const float* scale_gr,
+                 const float* qzero_gr, float* quant_t, uint8_t* codes_t, cudaStream_t st);
 int mse_refine(const float* Wt, int R, int group, int n_groups, const float* maxq_groups_dev, const float* grid_dev,
                int n_grid, float norm, float* scale_gr, const float* qzero_gr, int* index_gr, cudaStream_t st);
 

@@ -1,6 +1,8 @@
 // Host driver for K3 + K4 (see gptq_solver_kernel.cuh for the kernel and its design notes).
 // The six kernel instantiations live in gptq_solver_inst_*.cu so they compile in parallel
 // (each is ~10k fully unrolled instructions).
+#include <algorithm>
+#include <vector>
 #include "gptq_b200_internal.h"
 
 namespace gq {
@@ -54,20 +56,36 @@ int gptq_solve(float* Wt, const float* U, float* quant_t, void* codes_t, int cod
   if (per_group && (group != 32 && group != 64 && group != 128)) return GQ_ERR_SHAPE;
   if (per_group && ((a % group) || (b % group))) return GQ_ERR_SHAPE;
   if ((a % 4) != 0) return GQ_ERR_SHAPE;                        // 16-byte aligned U row starts
+  // ---- plan the blocks BEFORE the first launch: an unsupported range must not leave half-updated tensors behind.
+  // Per-group modes walk `group`-sized blocks; the quantize_range contract (mode 1) takes any [a, b) whose length is a
+  // multiple of 32 and is cut greedily into 128 / 64 / 32-column blocks (same updates as the reference's per-column
+  // loop, applied in block order).
+  std::vector<int> blocks;
+  for (int c = a; c < b;) {
+    int nb = group;
+    if (!per_group) {
+      const int left = b - c;
+      nb = left >= 128 ? 128 : left >= 64 ? 64 : left >= 32 ? 32 : 0;
+      if (nb == 0) return GQ_ERR_SHAPE;
+    }
+    blocks.push_back(nb);
+    c += nb;
+  }
   Tf32Maps maps;
   const bool tc = g_use_tf32x3 != 0;
   if (tc) {
     int rcm = gemm_tf32x3_maps(&maps, U, C, C, C, err_t, C, R, R, Wt, C, R, R);
     if (rcm != GQ_OK) return rcm;
   }
-  // Two-level lazy batching: inside a super-block of `super` blocks the update only runs over the super-block's own
-  // later columns (they are needed next); the columns behind it get ONE rank-(super x nb) update when the
+  // Two-level lazy batching: inside a super-block of `super` x 128 columns the update only runs over the super-block's
+  // own later columns (they are needed next); the columns behind it get ONE rank-(super-block width) update when the
   // super-block is finished: a quarter of the read-modify-write passes over W and a deeper, more efficient GEMM.
-  const int super = tc ? g_solve_super : 1;
+  // The end of a super-block is fixed when it opens (blocks of different widths may share one).
+  const int super_cols = (tc ? g_solve_super : 1) * 128;
   int c = a;
-  int sb_start = a, sb_blocks = 0;
-  while (c < b) {
-    int nb = per_group ? group : ((b - c >= 128) ? 128 : (b - c));
+  int sb_start = a, sb_end = std::min(std::min(a + super_cols, b), C);
+  for (size_t bi = 0; bi < blocks.size(); ++bi) {
+    const int nb = blocks[bi];
     SolveParams p;
     p.Wt = Wt; p.U = U; p.quant_t = quant_t; p.codes_t = codes_t; p.err_t = err_t;
     p.R = R; p.C = C; p.c0 = c; p.maxq = maxq; p.static_params = static_params;
@@ -81,31 +99,21 @@ int gptq_solve(float* Wt, const float* U, float* quant_t, void* codes_t, int cod
     int rc = launch_block_nb(mode, p, nb, st);
     if (rc != GQ_OK) return rc;
     const int e = c + nb;
-    ++sb_blocks;
-    const bool two_level = tc && nb % 16 == 0 && super > 1;
-    const bool close_super = !two_level || sb_blocks == super || e >= b;
+    const bool close_super = !tc || e >= sb_end;
     if (e < C) {
-      if (two_level) {
-        if (close_super) {
-          // near part of the last block, then everything behind the super-block at once
-          // (rows [e, C) all take U[sb_start:e, .]^T E[sb_start:e, :]; the blocks before this one already reached
-          //  rows [., e) through their near updates, so only this block's near range is empty)
-          const int k = e - sb_start;
-          if ((rc = gemm_tf32x3(maps, C - e, R, k, sb_start, e, sb_start, 0, e, 0, -1.f, 0, st)) != GQ_OK) return rc;
-        } else {
-          // W[e:se, :] -= U[c:e, e:se]^T E[c:e, :]   with se = end of the super-block
-          const int se = std::min(std::min(sb_start + super * nb, b), C);
-          if (se > e && (rc = gemm_tf32x3(maps, se - e, R, nb, c, e, c, 0, e, 0, -1.f, 0, st)) != GQ_OK) return rc;
-        }
-      } else if (tc && nb % 16 == 0) {
-        // W[e:, :] -= U[c:e, e:]^T * E[c:e, :]
-        if ((rc = gemm_tf32x3(maps, C - e, R, nb, c, e, c, 0, e, 0, -1.f, 0, st)) != GQ_OK) return rc;
-      } else {
+      if (!tc) {
         GemmProblem g{U + (size_t)c * C + e, err_t + (size_t)c * R, Wt + (size_t)e * R, C - e, R, nb, C, R, R};
         if ((rc = sgemm(g, -1.f, 1.f, GEMM_TRANS_A, st)) != GQ_OK) return rc;
+      } else if (close_super) {
+        // everything behind the super-block at once: rows [e, C) all take U[sb_start:e, .]^T E[sb_start:e, :] (the
+        // blocks before this one already reached rows [., e) through their near updates)
+        if ((rc = gemm_tf32x3(maps, C - e, R, e - sb_start, sb_start, e, sb_start, 0, e, 0, -1.f, 0, st)) != GQ_OK) return rc;
+      } else {
+        // W[e:sb_end, :] -= U[c:e, e:sb_end]^T E[c:e, :]
+        if ((rc = gemm_tf32x3(maps, sb_end - e, R, nb, c, e, c, 0, e, 0, -1.f, 0, st)) != GQ_OK) return rc;
       }
     }
-    if (close_super) { sb_start = e; sb_blocks = 0; }
+    if (close_super) { sb_start = e; sb_end = std::min(std::min(e + super_cols, b), C); }
     c = e;
   }
   return GQ_OK;

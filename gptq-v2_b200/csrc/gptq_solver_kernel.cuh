@@ -275,7 +275,7 @@ __global__ void __launch_bounds__(SOLVE_WARPS * 32, 3) solve_block_kernel(const 
 template <int MODE, int NB, typename CodeT>
 int launch_block(const SolveParams& p, cudaStream_t st) {
   const int smem = SOLVE_SMEM_FLOATS<NB> * 4 + 16;
-  static bool attr_set = false;
+  static PerDeviceFlag attr_set;   // function attributes are per device
   if (!attr_set) {
     if (cudaFuncSetAttribute(solve_block_kernel<MODE, NB, CodeT>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) !=
         cudaSuccess)

@@ -184,7 +184,7 @@ int hessian_gather(const float* H, int D, const int64_t* perm, float scale, floa
 // Wb: (D x D) scratch for W = V^T.  tmp: >= D*D/2 + 32*D floats.  info_dev: device int, set to 1 on a bad pivot.
 int chol_inverse_upper(float* A, int D, float* U, float* Wb, float* tmp, int* info_dev, cudaStream_t st) {
   if (D % 16 != 0) return GQ_ERR_SHAPE;
-  static bool attr_set = false;
+  static PerDeviceFlag attr_set;   // function attributes are per device
   const int trtri_smem = 2 * NB * PITCH * (int)sizeof(float);
   if (!attr_set) {
     if (cudaFuncSetAttribute(trtri_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, trtri_smem) != cudaSuccess)

@@ -12,6 +12,7 @@
 //
 // The EXL2 step that follows in the reference (quant.py:109-112, 157-165) works on the (R, G) scales only; the host
 // mirror does it with a handful of torch calls on the device (gptq_py.py of this package).
+#include <algorithm>
 #include "gptq_b200_internal.h"
 
 namespace gq {
@@ -132,7 +133,52 @@ __global__ void __launch_bounds__(QP_ROWS * QP_WARPS) mse_refine_kernel(const fl
   if (index_gr) index_gr[(size_t)g * R + r] = bi;
 }
 
+// Round to nearest with given parameters (gptq_py.py:101-124: Quantizer.quantize / dequantize of every group, nothing
+// propagates): q = clamp(round(w / s) + z, 0, maxq), w_hat = (q - z) * s, element-wise on the (C, R) layout.
+__global__ void __launch_bounds__(256) rtn_quantize_kernel(const float* __restrict__ Wt, int R, int group, int n_cols,
+                                                           const float* __restrict__ maxq_g, const float* __restrict__ scale_gr,
+                                                           const float* __restrict__ qzero_gr, float* __restrict__ quant_t,
+                                                           uint8_t* __restrict__ codes_t) {
+  const int r4 = R >> 2;
+  const size_t n = (size_t)n_cols * r4;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i / r4), r = (int)(i - (size_t)c * r4) * 4;
+    const int g = c / group;
+    const float maxq = maxq_g[g];
+    const float4 w = *reinterpret_cast<const float4*>(Wt + (size_t)c * R + r);
+    const float4 s = *reinterpret_cast<const float4*>(scale_gr + (size_t)g * R + r);
+    const float4 z = *reinterpret_cast<const float4*>(qzero_gr + (size_t)g * R + r);
+    const float wv[4] = {w.x, w.y, w.z, w.w}, sv[4] = {s.x, s.y, s.z, s.w}, zv[4] = {z.x, z.y, z.z, z.w};
+    float dq[4];
+    uint32_t codes = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      float q = __fadd_rn(rintf(__fdiv_rn(wv[k], sv[k])), zv[k]);          // quant.py:19
+      q = fminf(fmaxf(q, 0.f), maxq);
+      dq[k] = __fmul_rn(__fsub_rn(q, zv[k]), sv[k]);                       // quant.py:30
+      codes |= (uint32_t)(int)q << (8 * k);
+    }
+    if (quant_t) *reinterpret_cast<float4*>(quant_t + (size_t)c * R + r) = make_float4(dq[0], dq[1], dq[2], dq[3]);
+    if (codes_t) *reinterpret_cast<uint32_t*>(codes_t + (size_t)c * R + r) = codes;
+  }
+}
+
 }  // namespace
+
+// n_groups groups of `group` columns each, starting where Wt / quant_t / codes_t / scale_gr / qzero_gr / maxq_groups_dev point.
+int rtn_quantize(const float* Wt, int R, int group, int n_groups, const float* maxq_groups_dev, const float* scale_gr,
+                 const float* qzero_gr, float* quant_t, uint8_t* codes_t, cudaStream_t st) {
+  if (R <= 0 || (R & 3) || group <= 0 || n_groups <= 0) return GQ_ERR_SHAPE;
+  if (!Wt || !maxq_groups_dev || !scale_gr || !qzero_gr) return GQ_ERR_ARG;
+  if ((reinterpret_cast<uintptr_t>(Wt) | reinterpret_cast<uintptr_t>(quant_t) | reinterpret_cast<uintptr_t>(scale_gr) |
+       reinterpret_cast<uintptr_t>(qzero_gr)) & 15) return GQ_ERR_ALIGN;
+  if (reinterpret_cast<uintptr_t>(codes_t) & 3) return GQ_ERR_ALIGN;
+  const size_t n = (size_t)group * n_groups * (R >> 2);
+  const int grid = (int)std::min<size_t>((n + 255) / 256, 148 * 16);
+  GQ_LAUNCHED();
+  rtn_quantize_kernel<<<grid, 256, 0, st>>>(Wt, R, group, group * n_groups, maxq_groups_dev, scale_gr, qzero_gr, quant_t, codes_t);
+  return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
+}
 
 // Wt points at the first row of the first group; scale_gr / qzero_gr / maxq_groups_dev at that group's entries.
 int find_params(const float* Wt, int R, int group, int n_groups, const float* maxq_groups_dev, int sym, float* scale_gr,
@@ -150,11 +196,11 @@ int mse_refine(const float* Wt, int R, int group, int n_groups, const float* max
   if (R <= 0 || group <= 0 || group > 1024 || n_groups <= 0 || n_groups > 65535 || n_grid <= 0) return GQ_ERR_SHAPE;
   if (!Wt || !maxq_groups_dev || !grid_dev || !scale_gr || !qzero_gr) return GQ_ERR_ARG;
   const int smem = (group * QP_ROWS + 2 * QP_WARPS * QP_ROWS) * 4;
-  static int smem_set = 0;
-  if (smem > 48 * 1024 && smem > smem_set) {
+  static PerDeviceInt smem_set;          // function attributes are per device
+  if (smem > 48 * 1024 && smem > smem_set.get()) {
     if (cudaFuncSetAttribute(mse_refine_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess)
       return GQ_ERR_CUDA;
-    smem_set = smem;
+    smem_set.set(smem);
   }
   dim3 grid((R + QP_ROWS - 1) / QP_ROWS, n_groups);
   GQ_LAUNCHED();

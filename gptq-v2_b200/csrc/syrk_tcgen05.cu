@@ -326,7 +326,7 @@ int make_tmap_2d_raw(CUtensorMap* out, const void* base, int cu_dtype, uint64_t 
 template <int CG>
 static int launch_syrk(const CUtensorMap& tmap, const SyrkParams& p, int n_sms, cudaStream_t st) {
   using C = SyrkCfg<CG>;
-  static bool attr_set = false;
+  static PerDeviceFlag attr_set;   // function attributes are per device
   if (!attr_set) {
     if (cudaFuncSetAttribute(syrk_upper_kernel<CG>, cudaFuncAttributeMaxDynamicSharedMemorySize, C::SMEM_BYTES) !=
         cudaSuccess)

@@ -288,7 +288,7 @@ int run_w4a16_mma_cfg(const void* x, const uint32_t* qw, const void* scale, cons
                       void* workspace, int M, int N, int K, int group, int fmt, cudaStream_t st) {
   using Cfg = WmCfg<BIG>;
   constexpr int WM_MPAD_MAX = Cfg::MPAD_MAX, WM_SMEM = Cfg::SMEM;
-  static bool attr_set = false;
+  static PerDeviceFlag attr_set;   // function attributes are per device
   static int n_sms = 0;
   if (!attr_set) {
     if (cudaFuncSetAttribute(w4a16_mma_kernel<XT, BIG>, cudaFuncAttributeMaxDynamicSharedMemorySize, WM_SMEM) != cudaSuccess)

@@ -262,7 +262,7 @@ w4a16_wb_kernel(const __grid_constant__ CUtensorMap map_w, const __grid_constant
 template <typename XT>
 int run_w4a16_wb(const void* x, const uint32_t* qw, const void* scale, const uint8_t* qzero, const int32_t* perm, void* y,
                  void* workspace, int M, int N, int K, int group, int fmt, cudaStream_t st) {
-  static bool attr_set = false;
+  static PerDeviceFlag attr_set;   // function attributes are per device
   static int n_sms = 0;
   if (!attr_set) {
     if (cudaFuncSetAttribute(w4a16_wb_kernel<XT>, cudaFuncAttributeMaxDynamicSharedMemorySize, WB_SMEM) != cudaSuccess)

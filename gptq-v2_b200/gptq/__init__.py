@@ -14,7 +14,7 @@ import torch
 from . import _cabi
 from ._cabi import GptqB200Error, check, lib, ptr, require_contig, require_cuda, stream_of
 
-__all__ = ['accumulate_hessian', 'gptq_quantize_range', 'hessian_syrk', 'hessian_invert', 'w4a16_dequant', 'pack_upper', 'unpack_upper', 'prep_weight_t', 'prep_weight_t2', 'solve_metrics', 'gptq_solve_ex', 'find_params', 'mse_refine',
+__all__ = ['accumulate_hessian', 'gptq_quantize_range', 'hessian_syrk', 'hessian_invert', 'w4a16_dequant', 'pack_upper', 'unpack_upper', 'prep_weight_t', 'prep_weight_t2', 'solve_metrics', 'gptq_solve_ex', 'find_params', 'mse_refine', 'find_params_cols', 'mse_refine_cols', 'rtn_quantize',
            'gptq_solve', 'gptq_solve_static', 'pack_int4', 'unpack_int4', 'transpose_pack_int4', 'w4a16_gemm', 'sgemm', 'gemm_tf32x3', 'set_tf32x3', 'set_solve_super', 'set_w4a16_path',
            'GptqB200Error']
 
@@ -262,6 +262,60 @@ def mse_refine(Wt: torch.Tensor, group: int, maxq_dev: torch.Tensor, grid: torch
                                 float(norm), ptr(scale_gr[g0:]), ptr(qzero_gr[g0:]), ptr(idx) if idx is not None else None,
                                 stream_of(Wt)), 'gq_mse_refine')
     return idx
+
+
+def _group_args(Wt, maxq_dev, scale_gr, qzero_gr, c0, ncols, n_groups, g0):
+    dev = require_cuda(Wt, maxq_dev, scale_gr, qzero_gr)
+    require_contig(Wt=Wt, maxq_dev=maxq_dev, scale_gr=scale_gr, qzero_gr=qzero_gr)
+    C_, R = Wt.shape
+    G = scale_gr.shape[0]
+    if not (0 <= c0 and ncols > 0 and n_groups > 0 and c0 + ncols * n_groups <= C_ and 0 <= g0 and g0 + n_groups <= G):
+        raise GptqB200Error('column / group range out of bounds')
+    if scale_gr.shape != (G, R) or qzero_gr.shape != (G, R) or maxq_dev.shape != (G,):
+        raise GptqB200Error('scale_gr / qzero_gr must be (G, R) and maxq_dev (G)')
+    if not (Wt.dtype == maxq_dev.dtype == scale_gr.dtype == qzero_gr.dtype == torch.float32):
+        raise GptqB200Error('float32 tensors expected')
+    return dev, R
+
+
+def find_params_cols(Wt: torch.Tensor, c0: int, ncols: int, n_groups: int, maxq_dev: torch.Tensor, g0: int, sym: bool,
+                     scale_gr: torch.Tensor, qzero_gr: torch.Tensor) -> None:
+    """Quantizer.find_params (quant.py:89-118) for n_groups consecutive groups of `ncols` columns each starting at column
+    c0 of Wt (C, R); the parameters go to rows g0.. of scale_gr / qzero_gr (G, R) and use maxq_dev[g0..].  Any group size
+    (the groups of a linear need not be uniform: one call per run of equal sizes)."""
+    dev, R = _group_args(Wt, maxq_dev, scale_gr, qzero_gr, c0, ncols, n_groups, g0)
+    with torch.cuda.device(dev):
+        check(lib.gq_find_params(ptr(Wt[c0:]), R, int(ncols), int(n_groups), ptr(maxq_dev[g0:]), int(bool(sym)),
+                                 ptr(scale_gr[g0:]), ptr(qzero_gr[g0:]), stream_of(Wt)), 'gq_find_params')
+
+
+def mse_refine_cols(Wt: torch.Tensor, c0: int, ncols: int, n_groups: int, maxq_dev: torch.Tensor, g0: int,
+                    grid: torch.Tensor, norm: float, scale_gr: torch.Tensor, qzero_gr: torch.Tensor) -> None:
+    """Quantizer.mse (quant.py:152-156) with the error summed over columns [c0 + i * ncols, c0 + (i + 1) * ncols) for
+    group g0 + i: the group's own columns, or -- gptq_py.py:178-184 -- the columns of the GPTQ block the group starts in
+    (n_groups = 1 then).  ncols <= 1024."""
+    dev, R = _group_args(Wt, maxq_dev, scale_gr, qzero_gr, c0, ncols, n_groups, g0)
+    require_cuda(Wt, grid)
+    require_contig(grid=grid)
+    if grid.dtype != torch.float32 or grid.dim() != 1:
+        raise GptqB200Error('grid must be a 1-d float32 tensor')
+    with torch.cuda.device(dev):
+        check(lib.gq_mse_refine(ptr(Wt[c0:]), R, int(ncols), int(n_groups), ptr(maxq_dev[g0:]), ptr(grid), int(grid.numel()),
+                                float(norm), ptr(scale_gr[g0:]), ptr(qzero_gr[g0:]), None, stream_of(Wt)), 'gq_mse_refine')
+
+
+def rtn_quantize(Wt: torch.Tensor, c0: int, ncols: int, n_groups: int, maxq_dev: torch.Tensor, g0: int,
+                 scale_gr: torch.Tensor, qzero_gr: torch.Tensor, quant_t: torch.Tensor, codes_t: torch.Tensor) -> None:
+    """Round to nearest with the given parameters (gptq_py.py:120-123) for n_groups groups of `ncols` columns from
+    column c0: codes_t (C, R) uint8 and quant_t (C, R) fp32 are written for those columns."""
+    dev, R = _group_args(Wt, maxq_dev, scale_gr, qzero_gr, c0, ncols, n_groups, g0)
+    require_cuda(Wt, quant_t, codes_t)
+    require_contig(quant_t=quant_t, codes_t=codes_t)
+    if quant_t.shape != Wt.shape or codes_t.shape != Wt.shape or quant_t.dtype != torch.float32 or codes_t.dtype != torch.uint8:
+        raise GptqB200Error('quant_t (C, R) float32 and codes_t (C, R) uint8 expected')
+    with torch.cuda.device(dev):
+        check(lib.gq_rtn_quantize(ptr(Wt[c0:]), R, int(ncols), int(n_groups), ptr(maxq_dev[g0:]), ptr(scale_gr[g0:]),
+                                  ptr(qzero_gr[g0:]), ptr(quant_t[c0:]), ptr(codes_t[c0:]), stream_of(Wt)), 'gq_rtn_quantize')
 
 
 def pack_int4(codes: torch.Tensor) -> torch.Tensor:

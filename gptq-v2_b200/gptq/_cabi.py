@@ -34,6 +34,7 @@ SIGNATURES = {
     'gq_gptq_solve_static': (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _f, _vp]),
     'gq_gptq_solve_ex': (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp, _f, _i, _i, _i, _vp]),
     'gq_find_params': (_i, [_vp, _i, _i, _i, _vp, _i, _vp, _vp, _vp]),
+    'gq_rtn_quantize': (_i, [_vp, _i, _i, _i, _vp, _vp, _vp, _vp, _vp, _vp]),
     'gq_mse_refine': (_i, [_vp, _i, _i, _i, _vp, _vp, _i, _f, _vp, _vp, _vp, _vp]),
     'gq_prep_weight_t': (_i, [_vp, _i, _vp, _vp, _i, _i, _vp]),
     'gq_prep_weight_t2': (_i, [_vp, _i, _vp, _vp, _vp, _vp, _i, _i, _vp]),

@@ -13,10 +13,10 @@ Host-side torch ops are limited to what the reference also leaves to torch and t
 O(D) or a single elementwise pass (argsort of the diagonal, metrics).
 The Quantizer options llama.py never sets are supported on all three branches:
 quant_symmetric, quant_mse (grid search, gq_mse_refine), scale_bit_width (EXL2 qscale / sscale), per-group bit widths.
-gptq_block_sizes != group_sizes runs on the fp32 branch when the two nest (blocks of whole groups or groups of whole
-blocks, the smaller one in {32, 64, 128}) without the MSE search / EXL2 scales.
-Still NotImplementedError: non-uniform group sizes, quant_use_kernel=True (needs exllamav2, which the reference itself
-no longer imports).
+Group sizes need not be uniform (any sizes on the round-to-nearest branch, multiples of 32 on the two GPTQ branches), and
+on the fp32 branch gptq_block_sizes may differ from group_sizes in any way (nested either way or not at all, multiples of
+32), with every Quantizer option: the MSE search then runs over the block's columns as in ref :178-184.
+Still NotImplementedError: quant_use_kernel=True (needs exllamav2, which the reference itself no longer imports).
 """
 from __future__ import annotations
 
@@ -82,11 +82,23 @@ class HessianHook:
         return self.hessian_inv
 
 
-def _uniform(t: torch.Tensor, what: str) -> int:
-    v = t.tolist()
-    if len(set(v)) != 1:
-        raise NotImplementedError(f'{what} must be uniform across groups in gptq_b200 (got {sorted(set(v))})')
-    return int(v[0])
+def _int_list(t) -> list[int]:
+    """group_sizes / group_bit_widths / gptq_block_sizes as Python ints.  Pass CPU tensors (or lists): a CUDA tensor costs a
+    device synchronisation here, like the reference's own .tolist() (gptq_py.py:98)."""
+    return [int(v) for v in (t.tolist() if isinstance(t, torch.Tensor) else t)]
+
+
+def _runs(sizes: list[int]):
+    """Consecutive groups of equal size as (first group, number of groups, group size, first column)."""
+    out, g, c = [], 0, 0
+    while g < len(sizes):
+        n = 1
+        while g + n < len(sizes) and sizes[g + n] == sizes[g]:
+            n += 1
+        out.append((g, n, sizes[g], c))
+        c += n * sizes[g]
+        g += n
+    return out
 
 
 @torch.no_grad()
@@ -111,23 +123,24 @@ def gptq_quant(
        gptq_use_kernel=False -> the reference's fp32 PyTorch semantics: per-group scale/zero from
                                 the error-compensated weights, fp32 dequant (ref :158-193)
        hessian_hook=None     -> round to nearest (ref :101-124)
-    All run on the same CUDA block solver; group parameters come from the solver itself (asymmetric min/max) or from
-    gq_find_params / gq_mse_refine (symmetric, MSE-refined, EXL2 grids)."""
+    Group sizes need not be uniform (ref :98 walks a cumsum); on the fp32 branch GPTQ blocks may differ from the groups
+    (ref :161-193).  Group parameters come from the solver itself (asymmetric min/max) or from gq_find_params /
+    gq_mse_refine (symmetric, MSE-refined, EXL2 grids)."""
     if quant_mse and quant_use_kernel:
         # ref quant.py:131-150 calls exllamav2's ext_c.quantize_err, whose import the reference has commented out (quant.py:4)
         raise NotImplementedError('quant_use_kernel=True needs exllamav2 (not importable in the reference either)')
     n_rows, n_columns = weight.shape
     dtype = weight.dtype
     device = weight.device
-    gs = _uniform(group_sizes, 'group_sizes')
-    bits_list = [int(v) for v in group_bit_widths.tolist()]
-    # GPTQ blocks matter only to the fp32 branch (ref :161): the round-to-nearest branch has no blocks and the kernel
-    # branch "assume[s] gptq_block_sizes is the same as quantization group_sizes" (ref :126)
-    blk = gs
-    if gptq_block_sizes is not None and hessian_hook is not None and not gptq_use_kernel:
-        blk = _uniform(gptq_block_sizes, 'gptq_block_sizes')
-    n_groups = n_columns // gs
-    assert n_groups * gs == n_columns and len(bits_list) == n_groups
+    sizes = _int_list(group_sizes)
+    bits_list = _int_list(group_bit_widths)
+    n_groups = len(sizes)
+    offs = [0]
+    for n in sizes:
+        offs.append(offs[-1] + n)
+    assert offs[-1] == n_columns and len(bits_list) == n_groups and min(sizes) > 0
+    uniform = len(set(sizes)) == 1
+    gs = sizes[0] if uniform else None
     maxq_list = [float(2 ** b - 1) for b in bits_list]
     sbits = int(scale_bit_width) if scale_bit_width is not None else None
     exl2 = sbits is not None and sbits > 0                                  # ref quant.py:99-100,108
@@ -135,37 +148,42 @@ def gptq_quant(
     plain = not (sym or quant_mse)                                          # llama.py's setting: asymmetric min/max, no refinement
     perm = hessian_hook.perm if hessian_hook is not None else None
     weight_c = weight.contiguous()
-
-    if hessian_hook is None:
-        # round-to-nearest (ref :101-124): the block solver with U = I propagates nothing
-        U = torch.eye(n_columns, dtype=torch.float32, device=device)
-    else:
-        U = hessian_hook.hessian_inv.contiguous()
+    U = hessian_hook.hessian_inv.contiguous() if hessian_hook is not None else None
 
     # (C, R) fp32, permuted (ref :90-94,128); orig_t / colsq feed the result metrics after the solver has consumed Wt
     Wt, orig_t, colsq = _ops.prep_weight_t2(weight_c, perm, getattr(hessian_hook, 'perm_inv', None) if perm is not None else None)
-    solver_ok = gs in (32, 64, 128)
+    scale_gr = torch.empty(n_groups, n_rows, dtype=torch.float32, device=device)
+    qzero_gr = torch.empty_like(scale_gr)
     qscale_gr = sscale_g = None
-    if not plain or not solver_ok or (gptq_use_kernel and hessian_hook is not None):
+    solver_gs = uniform and gs in (32, 64, 128)
+    fast = (hessian_hook is not None and not gptq_use_kernel and plain and solver_gs
+            and (gptq_block_sizes is None or _int_list(gptq_block_sizes) == sizes))
+    if not fast:
         maxq_dev = torch.tensor(maxq_list, dtype=torch.float32, device=device)
-        scale_gr = torch.empty(n_groups, n_rows, dtype=torch.float32, device=device)
-        qzero_gr = torch.empty_like(scale_gr)
         if exl2:
             qscale_gr = torch.empty_like(scale_gr)
             sscale_g = torch.empty(n_groups, dtype=torch.float32, device=device)
         grid = (1. - torch.arange(0., quant_max_shrink, 1. / quant_n_grid, device=device)) if quant_mse else None   # ref quant.py:152
         smaxq = torch.tensor(2. ** sbits - 1., dtype=torch.float32, device=device) if exl2 else None
 
-        def group_params(g0: int, n: int) -> None:
-            """Quantizer.find_params (+ .mse) of groups [g0, g0 + n) from the current Wt (ref quant.py:89-165): the
-            O(R C) and O(R C Q) passes run in the library, the (R)-sized EXL2 scale grid in torch on the device."""
-            _ops.find_params(Wt, gs, maxq_dev, sym, scale_gr, qzero_gr, g0, n)
+        def group_params(g0: int, n: int, mse_cols=None) -> None:
+            """Quantizer.find_params (+ .mse) of the equal-sized groups [g0, g0 + n) from the current Wt (ref quant.py:89-165):
+            the O(R C) and O(R C Q) passes run in the library, the (R)-sized EXL2 scale grid in torch on the device.
+            mse_cols = (i1, i2): the MSE search sums the error over those columns (the GPTQ block, ref :178-184) instead
+            of the group's own (n == 1 then)."""
+            size, c0 = sizes[g0], offs[g0]
+            _ops.find_params_cols(Wt, c0, size, n, maxq_dev, g0, sym, scale_gr, qzero_gr)
             rows = slice(g0, g0 + n)
             if exl2:
                 qs, ss, sc = exl2_scale_grid(scale_gr[rows].unsqueeze(-1), smaxq)
                 scale_gr[rows] = sc.squeeze(-1)
             if quant_mse:
-                _ops.mse_refine(Wt, gs, maxq_dev, grid, quant_norm, scale_gr, qzero_gr, g0, n)
+                if mse_cols is None:
+                    _ops.mse_refine_cols(Wt, c0, size, n, maxq_dev, g0, grid, quant_norm, scale_gr, qzero_gr)
+                else:
+                    assert n == 1
+                    _ops.mse_refine_cols(Wt, mse_cols[0], mse_cols[1] - mse_cols[0], 1, maxq_dev, g0, grid, quant_norm,
+                                         scale_gr, qzero_gr)
                 if exl2:
                     qs, ss, sc = exl2_scale_mse(scale_gr[rows].unsqueeze(-1), smaxq, grid, quant_norm)
                     scale_gr[rows] = sc.squeeze(-1)
@@ -173,87 +191,83 @@ def gptq_quant(
                 qscale_gr[rows] = qs.squeeze(-1)
                 sscale_g[rows] = ss.reshape(-1)
 
-    if blk != gs:
-        # ---- fp32 branch with GPTQ blocks that differ from the quantisation groups (ref :161-193).  The reference
-        # computes a group's parameters when its column loop reaches the group's first column, from the GLOBAL weights:
-        # they hold the lazy-batch updates of the finished blocks but not the in-block updates of the current one.
-        #   blk > gs: the parameters of every group of a block come from the weights as they are at the block's start;
-        #             the block is then solved group by group (mode 4, supplied parameters) -- the same updates as the
-        #             reference's in-block propagation, applied in a different order (fp32 reordering only);
-        #   blk < gs: the parameters come from the weights at the group's start (= a block start), then the group is
-        #             solved in blocks of blk columns that all use them.
-        if quant_mse or exl2:
-            # ref :178-184 runs Quantizer.mse over the BLOCK's columns, not the group's: not reproduced
-            raise NotImplementedError('gptq_block_sizes != group_sizes is supported without quant_mse / scale_bit_width')
-        step = min(gs, blk)
-        if step not in (32, 64, 128) or max(gs, blk) % step != 0 or n_columns % blk != 0:
-            raise NotImplementedError('gptq_block_sizes / group_sizes must nest, the smaller one in {32, 64, 128}')
-        maxq_dev = torch.tensor(maxq_list, dtype=torch.float32, device=device)
-        scale_gr = torch.empty(n_groups, n_rows, dtype=torch.float32, device=device)
-        qzero_gr = torch.empty_like(scale_gr)
-        out = None
-        if blk > gs:
-            per = blk // gs
-            for g0 in range(0, n_groups, per):
-                _ops.find_params(Wt, gs, maxq_dev, sym, scale_gr, qzero_gr, g0, per)
-                for g in range(g0, g0 + per):
-                    out = _ops.gptq_solve_ex(Wt, U, scale_gr, qzero_gr, gs, maxq_list, mode=4, a=g * gs, b=(g + 1) * gs, out=out)
-        else:
-            per = gs // blk
-            n_steps = n_columns // blk
-            scale_st = torch.empty(n_steps, n_rows, dtype=torch.float32, device=device)
-            qzero_st = torch.empty_like(scale_st)
-            maxq_st = [maxq_list[i // per] for i in range(n_steps)]
-            for g in range(n_groups):
-                _ops.find_params(Wt, gs, maxq_dev, sym, scale_gr, qzero_gr, g, 1)
-                scale_st[g * per:(g + 1) * per] = scale_gr[g]
-                qzero_st[g * per:(g + 1) * per] = qzero_gr[g]
-                out = _ops.gptq_solve_ex(Wt, U, scale_st, qzero_st, blk, maxq_st, mode=4, a=g * gs, b=(g + 1) * gs, out=out)
-        quant_t, codes_t, err_t = out
-    elif gptq_use_kernel and hessian_hook is not None:
-        # static parameters from the original permuted weights (ref :131-134), then the reference's per-group
-        # gptq_quantize_range loop (ref :135-139) as one library call
-        group_params(0, n_groups)
-        if solver_ok:
+    err_t = None
+    if hessian_hook is None:
+        # ---- round to nearest (ref :101-124): parameters from the weights as they are, element-wise quantisation; no U,
+        # no propagation, any group sizes
+        quant_t = torch.empty_like(Wt)
+        codes_t = torch.empty(n_columns, n_rows, dtype=torch.uint8, device=device)
+        for g0, n, size, c0 in _runs(sizes):
+            group_params(g0, n)
+            _ops.rtn_quantize(Wt, c0, size, n, maxq_dev, g0, scale_gr, qzero_gr, quant_t, codes_t)
+    elif gptq_use_kernel:
+        # ---- static parameters from the original permuted weights (ref :131-134), then the reference's per-group
+        # gptq_quantize_range loop (ref :135-139): one library call when the groups are uniform
+        if any(n % 32 for n in sizes):
+            raise NotImplementedError('the kernel branch needs group sizes that are multiples of 32')
+        for g0, n, size, c0 in _runs(sizes):
+            group_params(g0, n)
+        if solver_gs:
             quant_t, q_t, err_t = _ops.gptq_solve_ex(Wt, U, scale_gr, qzero_gr, gs, maxq_list, mode=3)
         else:
             quant_t = torch.empty_like(Wt)
             err_t = torch.empty_like(Wt)
             q_t = torch.empty_like(Wt, dtype=torch.int16)
             for g in range(n_groups):
-                gptq_quantize_range(quant_t, scale_gr[g], q_t, qzero_gr[g], maxq_list[g], U, Wt, err_t, g * gs, (g + 1) * gs)
+                gptq_quantize_range(quant_t, scale_gr[g], q_t, qzero_gr[g], maxq_list[g], U, Wt, err_t, offs[g], offs[g + 1])
         codes_t = q_t.to(torch.uint8)
-    elif not solver_ok:
-        raise NotImplementedError('the fp32 path needs group_sizes in {32, 64, 128}')
-    elif plain:
-        # min/max parameters of every group computed by the solver itself on the compensated weights (ref :169-176)
-        scale_gr = torch.empty(n_groups, n_rows, dtype=torch.float32, device=device)
-        qzero_gr = torch.empty_like(scale_gr)
+    elif fast:
+        # ---- min/max parameters of every group computed by the solver itself on the compensated weights (ref :169-176)
         quant_t, codes_t, err_t = _ops.gptq_solve_ex(Wt, U, scale_gr, qzero_gr, gs, maxq_list, mode=0)
-    elif hessian_hook is None:
-        # round to nearest with a refined grid: nothing propagates, so every group's parameters come from one pass
-        group_params(0, n_groups)
-        quant_t, codes_t, err_t = _ops.gptq_solve_ex(Wt, U, scale_gr, qzero_gr, gs, maxq_list, mode=4)
     else:
-        # fp32 path with a symmetric / MSE / EXL2 grid: each group's parameters depend on the updates of the groups
-        # before it (ref :171-185), so parameters and solve alternate per group
-        out = None
-        for g in range(n_groups):
-            group_params(g, 1)
-            out = _ops.gptq_solve_ex(Wt, U, scale_gr, qzero_gr, gs, maxq_list, mode=4, a=g * gs, b=(g + 1) * gs, out=out)
+        # ---- fp32 branch, general form (ref :161-193).  The reference computes a group's parameters when its column loop
+        # reaches the group's first column, from the GLOBAL weights: they hold the lazy-batch updates of the finished
+        # blocks but not the in-block updates of the current one.  So: at every block start the parameters of all groups
+        # that begin inside the block are computed from Wt as it is (the MSE search over the block's columns, ref
+        # :178-184), then the block is solved in steps of `step` columns with supplied parameters (mode 4), every step
+        # pushing its update to all later columns -- the reference's in-block propagation applied in another order
+        # (fp32 reordering only).  Blocks and groups may nest either way or not at all; every boundary must be a
+        # multiple of step = gcd(all sizes, 128) in {32, 64, 128}.
+        import math
+        blocks = _int_list(gptq_block_sizes) if gptq_block_sizes is not None else sizes
+        assert sum(blocks) == n_columns and min(blocks) > 0
+        step = math.gcd(128, *sizes, *blocks)
+        if step not in (32, 64, 128):
+            raise NotImplementedError('group sizes and gptq_block_sizes must be multiples of 32 on the fp32 branch')
+        n_steps = n_columns // step
+        direct = uniform and gs == step                                     # the per-step layout IS the per-group layout
+        scale_st = scale_gr if direct else torch.empty(n_steps, n_rows, dtype=torch.float32, device=device)
+        qzero_st = qzero_gr if direct else torch.empty_like(scale_st)
+        grp_of_step = [g for g in range(n_groups) for _ in range(sizes[g] // step)]
+        maxq_st = [maxq_list[g] for g in grp_of_step]
+        out, gi, i1 = None, 0, 0
+        for bsz in blocks:
+            i2 = i1 + bsz
+            while gi < n_groups and offs[gi] < i2:
+                group_params(gi, 1, mse_cols=(i1, i2) if (quant_mse and (i1, i2) != (offs[gi], offs[gi + 1])) else None)
+                if not direct:
+                    s0, s1 = offs[gi] // step, offs[gi + 1] // step
+                    scale_st[s0:s1] = scale_gr[gi]
+                    qzero_st[s0:s1] = qzero_gr[gi]
+                gi += 1
+            out = _ops.gptq_solve_ex(Wt, U, scale_st, qzero_st, step, maxq_st, mode=4, a=i1, b=i2, out=out)
+            i1 = i2
         quant_t, codes_t, err_t = out
 
     # ---- metrics (ref :196-199, :231-237) in one pass over the solver outputs and ONE host sync:
     #   gptq_error = mean(err^2);  gptq_norm = mean((W / diag(U))^2) with W unpermuted against the permuted-order diag(U),
     #   reproduced as is (ref :198) = sum_c colsq_orig[c] / diag(U)[c]^2 / (R C);  l2.0_error = mean((quant - W)^2), which
     #   does not depend on the column order;  l2.0_norm in the weight dtype like the reference.
-    sums = _ops.solve_metrics(err_t, quant_t, orig_t)                            # float64 [sum err^2, sum (quant - W)^2]
-    if perm is not None:
-        colsq_orig = torch.empty_like(colsq)
-        colsq_orig[perm] = colsq
+    sums = _ops.solve_metrics(err_t if err_t is not None else quant_t, quant_t, orig_t)   # float64 [sum err^2, sum (quant - W)^2]
+    if hessian_hook is None:
+        norm_sum = torch.zeros((), dtype=torch.float64, device=device)
     else:
-        colsq_orig = colsq
-    norm_sum = (colsq_orig.double() / U.diagonal().double() ** 2).sum()
+        if perm is not None:
+            colsq_orig = torch.empty_like(colsq)
+            colsq_orig[perm] = colsq
+        else:
+            colsq_orig = colsq
+        norm_sum = (colsq_orig.double() / U.diagonal().double() ** 2).sum()
     l2_norm = (weight.abs() ** 2.).mean()                                        # ref :237 (fp16 / bf16 arithmetic)
     n_el = float(n_rows * n_columns)
     stats = torch.stack([sums[0], sums[1], norm_sum, l2_norm.double()])          # read back AFTER the result assembly is queued
@@ -268,13 +282,15 @@ def gptq_quant(
     else:
         perm16 = torch.arange(n_columns, dtype=torch.int16, device=device)
     bits_out = group_bit_widths.to(dtype=torch.uint8)
-    # with EXL2 metadata the groups are stored by descending bit width, ties in ascending position (ref :201-212)
+    # with EXL2 metadata the groups are stored by descending (bit width, group size), ties in ascending position (ref :201-212)
     order = list(range(n_groups))
     if scale_bit_width is not None:
-        order.sort(key=lambda g: (bits_list[g], gs, -g), reverse=True)
+        order.sort(key=lambda g: (bits_list[g], sizes[g], -g), reverse=True)
+    sizes_out = torch.tensor(sizes, dtype=torch.int16)
     if order != list(range(n_groups)):
         ig = torch.tensor(order, dtype=torch.int64, device=device)
-        ic = (ig[:, None] * gs + torch.arange(gs, device=device)).reshape(-1)
+        ic = torch.cat([torch.arange(offs[g], offs[g + 1], device=device) for g in order])
+        sizes_out = sizes_out[ig.cpu()]
         qweight, perm16 = qweight[:, ic].contiguous(), perm16[ic]
         scale, qzero, bits_out = scale[:, ig].contiguous(), qzero[:, ig].contiguous(), bits_out[ig.to(bits_out.device)]
         if exl2:
@@ -288,7 +304,7 @@ def gptq_quant(
         'qscale': qscale.to(device=save_device) if exl2 else None,
         'sscale': sscale.to(device=save_device) if exl2 else None,
         'perm_inv': perm_inv.to(device=save_device),
-        'group_sizes': group_sizes.to(dtype=torch.int16, device=save_device),
+        'group_sizes': sizes_out.to(device=save_device),
         'group_bit_widths': bits_out.to(device=save_device),
         'scale_bit_width': scale_bit_width.to(dtype=torch.uint8, device=save_device) if scale_bit_width is not None else None,
     }

@@ -120,29 +120,36 @@ class Quantizer:
 def _uniform_group(group_sizes: torch.Tensor) -> int:
     v = set(group_sizes.tolist())
     if len(v) != 1:
-        raise NotImplementedError('non-uniform group sizes are outside gptq_b200\'s scope')
+        raise NotImplementedError('the packed int4 format / K6 take one group size per linear (llama.py:146 uses 128 everywhere); '
+                                  'reconstruct_nn_linear handles non-uniform groups densely')
     return int(v.pop())
+
+
+def _expand_groups(per_group: torch.Tensor, group_sizes: torch.Tensor) -> torch.Tensor:
+    """(R, G) per-group values -> (R, C) per-column values for any group sizes (the reference loops over the groups,
+    quant.py:230-236)."""
+    sizes = group_sizes.to(device=per_group.device, dtype=torch.int64)
+    if int(sizes.min()) == int(sizes.max()):
+        gs = int(sizes[0])
+        return per_group.unsqueeze(-1).expand(*per_group.shape, gs).reshape(per_group.shape[0], -1)
+    return per_group.repeat_interleave(sizes, dim=1)
 
 
 def construct_matrix(qweight, scale, qzero, group_sizes):
     """Dense (R, C) matrix in scale.dtype from codes (permuted column order kept).
-    int16 subtract, then multiply in the 16-bit dtype, as reference quant.py:222-237."""
-    gs = _uniform_group(group_sizes)
-    R, C = qweight.shape
-    q = qweight.to(torch.int16).view(R, C // gs, gs)
-    z = qzero.to(torch.int16).expand(scale.shape).unsqueeze(-1)
-    return ((q - z) * scale.unsqueeze(-1)).view(R, C)
+    int16 subtract, then multiply in the 16-bit dtype, as reference quant.py:222-237.  Any group sizes."""
+    q = qweight.to(torch.int16)
+    z = _expand_groups(qzero.to(torch.int16), group_sizes)
+    return (q - z) * _expand_groups(scale, group_sizes)
 
 
 def construct_matrix_2(qweight, qzero, qscale, sscale, group_sizes):
     """EXL2 metadata (reference quant.py:240-259): scale = qscale^2 (int16) * sscale, evaluated in sscale.dtype."""
-    gs = _uniform_group(group_sizes)
-    R, C = qweight.shape
     qs = qscale.to(torch.int16)
     scale = qs * qs * sscale.reshape(1, -1)
-    q = qweight.to(torch.int16).view(R, C // gs, gs)
-    z = qzero.to(torch.int16).expand(scale.shape).unsqueeze(-1)
-    return ((q - z) * scale.unsqueeze(-1)).view(R, C)
+    q = qweight.to(torch.int16)
+    z = _expand_groups(qzero.to(torch.int16), group_sizes)
+    return (q - z) * _expand_groups(scale, group_sizes)
 
 
 def reconstruct_nn_linear(quant_meta: dict, dtype: torch.dtype, device: torch.device = torch.device('cpu')) -> nn.Linear:

@@ -70,7 +70,7 @@ int gq_unpack_upper(const float* packed, int D, float* H, void* stream);
  * with R = number of weight rows ("columns" in the reference's naming), hessian_inv (C, C).
  * scale/qzero (R) are static for the range; dequant is rounded through fp16.  out_q may be
  * NULL (the reference skips it for meta tensors).  Preconditions: R % 4 == 0, a % 4 == 0,
- * (b - a) a multiple of 128 plus an optional tail of 32 or 64. */
+ * (b - a) a multiple of 32 (checked before anything is written; GQ_ERR_SHAPE otherwise). */
 int gq_quantize_range(float* quant, const float* scale, int16_t* out_q, const float* qzero, float maxq,
                       const float* hessian_inv, float* weights, float* error, int C, int R, int a, int b,
                       void* stream);
@@ -104,6 +104,12 @@ int gq_gptq_solve_ex(float* Wt, const float* U, float* quant_t, void* codes_t, f
  * sym = 0: min/max grid; sym = 1: scale = absmax * 2 / maxq + 1e-12, zero = round((maxq + 1) / 2). */
 int gq_find_params(const float* Wt, int R, int group, int n_groups, const float* maxq_groups_dev, int sym,
                    float* scale_gr, float* qzero_gr, void* stream);
+/* Round to nearest with given parameters (gptq_py.py:101-124, the hessian_hook=None branch: Quantizer.quantize /
+ * dequantize per group, no error propagation): n_groups groups of `group` columns starting at row c0 of the (C, R)
+ * arrays; every pointer is at that row / group.  q = clamp(round(w / scale) + zero, 0, maxq) -> codes_t (uint8, may be
+ * NULL), (q - zero) * scale -> quant_t (may be NULL).  Any group size; R % 4 == 0. */
+int gq_rtn_quantize(const float* Wt, int R, int group, int n_groups, const float* maxq_groups_dev, const float* scale_gr,
+                    const float* qzero_gr, float* quant_t, uint8_t* codes_t, void* stream);
 /* Quantizer.mse (quant.py:152-156, use_kernel=False): per row and group, scale *= grid[argmin_i sum_c |deq(q(x_c;
  * scale * grid[i])) - x_c|^norm] (first minimum).  grid_dev: n_grid shrink factors on the device (the reference's
  * 1 - arange(0, max_shrink, 1/n_grid)); index_gr (n_groups, R) int32 receives the chosen index (may be NULL).

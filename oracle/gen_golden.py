@@ -154,44 +154,66 @@ def main_quantizer():
         print('wrote', name, {k: f'{v:.4e}' for k, v in res['metrics'].items()})
 
 
-# ---- GPTQ blocks that differ from the quantisation groups, non-uniform group sizes (gptq_py.py:158-193, fp32 branch)
+# ---- GPTQ blocks that differ from the quantisation groups, non-uniform group sizes (gptq_py.py:101-124, 158-193)
 B_CASES = [
-    # name,                R,  C,  group sizes,          bits,            block sizes,            act_order, dtype
-    ('b_blk256_g128',      64, 512, [128] * 4,           [4] * 4,         [256, 256],             True,  torch.float16),
-    ('b_blk64_g128',       64, 256, [128, 128],          [4, 4],          [64] * 4,               True,  torch.float16),
-    ('b_blk128_g32',       48, 256, [32] * 8,            [3] * 8,         [128, 128],             False, torch.bfloat16),
-    ('b_groups_64_128_64', 64, 256, [64, 128, 64],       [4, 3, 4],       [128, 128],             True,  torch.float16),
+    # name,                R,  C,  group sizes,          bits,            block sizes (None = round to nearest), act_order, dtype, options
+    ('b_blk256_g128',      64, 512, [128] * 4,           [4] * 4,         [256, 256],             True,  torch.float16, {}),
+    ('b_blk64_g128',       64, 256, [128, 128],          [4, 4],          [64] * 4,               True,  torch.float16, {}),
+    ('b_blk128_g32',       48, 256, [32] * 8,            [3] * 8,         [128, 128],             False, torch.bfloat16, {}),
+    ('b_groups_64_128_64', 64, 256, [64, 128, 64],       [4, 3, 4],       [128, 128],             True,  torch.float16, {}),
+    # round 2: the MSE search over the BLOCK's columns (:178-184), EXL2 scales, sizes that do not nest, any sizes on the
+    # round-to-nearest branch, EXL2 group ordering by (bit width, group size)
+    ('b_blk256_g128_mse',  64, 512, [128] * 4,           [4, 3, 4, 4],    [256, 256],             True,  torch.float16, {'mse': True}),
+    ('b_blk64_g128_exl2',  48, 256, [128, 128],          [4, 4],          [64] * 4,               True,  torch.float16, {'scale_bits': 4, 'mse': True}),
+    ('b_nonnest_96_160',   64, 256, [96, 160],           [4, 4],          [128, 128],             True,  torch.float16, {}),
+    ('b_groups_sym_mse',   48, 320, [64, 128, 32, 96],   [4, 3, 4, 2],    [64, 128, 32, 96],      True,  torch.float16, {'sym': True, 'mse': True}),
+    ('b_rtn_48_80_128',    40, 256, [48, 80, 128],       [4, 3, 4],       None,                   False, torch.float16, {'mse': True}),
+    ('b_rtn_exl2_order',   40, 320, [64, 128, 64, 64],   [3, 4, 4, 3],    None,                   False, torch.bfloat16, {'scale_bits': 4}),
 ]
 
 
-def main_blocks():
+def main_blocks(only_new: bool = False):
     from oracle import gptq_oracle as O
     gptq_py, quant = import_reference()
     torch.set_num_threads(1)
     out_dir = os.path.join(ROOT, 'tests', 'golden')
-    for name, R, C, gsz, bits, bsz, act, dtype in B_CASES:
+    for name, R, C, gsz, bits, bsz, act, dtype, opt in B_CASES:
+        if only_new and os.path.exists(os.path.join(out_dir, name + '.npz')):
+            continue
         n_seq, seqlen = 4, 128
         W, X = O.synth_linear(R, C, n_seq, seqlen, dtype=dtype, seed=900 + R + C + len(name))
-        hook = gptq_py.HessianHook()
-        for i in range(0, n_seq, 2):
-            hook.add_batch(X[i:i + 2], use_kernel=False)
-        hook.invert(damp_ratio=1e-2, act_order=act)
-        res = gptq_py.gptq_quant(weight=W, hessian_hook=hook, group_sizes=torch.tensor(gsz, dtype=torch.int32),
-                                 group_bit_widths=torch.tensor(bits, dtype=torch.int32), scale_bit_width=None,
-                                 gptq_use_kernel=False, gptq_block_sizes=torch.tensor(bsz, dtype=torch.int32),
-                                 quant_symmetric=False, quant_mse=False)
+        sbits = opt.get('scale_bits')
+        kw = dict(group_sizes=torch.tensor(gsz, dtype=torch.int32), group_bit_widths=torch.tensor(bits, dtype=torch.int32),
+                  scale_bit_width=(torch.tensor(sbits, dtype=torch.int32) if sbits is not None else None),
+                  gptq_use_kernel=False, quant_symmetric=bool(opt.get('sym', False)), quant_mse=bool(opt.get('mse', False)))
+        if bsz is None:
+            hook = None
+            res = gptq_py.gptq_quant(weight=W, hessian_hook=None, **kw)
+        else:
+            hook = gptq_py.HessianHook()
+            for i in range(0, n_seq, 2):
+                hook.add_batch(X[i:i + 2], use_kernel=False)
+            hook.invert(damp_ratio=1e-2, act_order=act)
+            res = gptq_py.gptq_quant(weight=W, hessian_hook=hook, gptq_block_sizes=torch.tensor(bsz, dtype=torch.int32), **kw)
         lin = quant.reconstruct_nn_linear(res['quant_meta'], dtype=dtype)
         m = res['quant_meta']
         to_np = lambda t: t.to(torch.float32).numpy() if t.dtype in (torch.float16, torch.bfloat16) else t.numpy()
+        extra = {}
+        if m['qscale'] is not None:
+            extra = dict(qscale=m['qscale'].numpy(), sscale=to_np(m['sscale']))
         np.savez_compressed(
             os.path.join(out_dir, name + '.npz'),
-            R=R, C=C, group_sizes=np.array(gsz), bits=np.array(bits), block_sizes=np.array(bsz), act_order=int(act),
-            dtype=str(dtype).split('.')[-1], W_bits=W.view(torch.int16).numpy(), U=hook.hessian_inv.numpy(),
-            perm=(hook.perm.numpy() if hook.perm is not None else np.arange(C)),
+            R=R, C=C, group_sizes=np.array(gsz), bits=np.array(bits), block_sizes=np.array(bsz if bsz is not None else []),
+            rtn=int(bsz is None), act_order=int(act and hook is not None),
+            sym=int(bool(opt.get('sym', False))), mse=int(bool(opt.get('mse', False))), scale_bits=(-1 if sbits is None else sbits),
+            dtype=str(dtype).split('.')[-1], W_bits=W.view(torch.int16).numpy(),
+            U=(hook.hessian_inv.numpy() if hook is not None else np.zeros((0, 0), dtype=np.float32)),
+            perm=(hook.perm.numpy() if hook is not None and hook.perm is not None else np.arange(C)),
             qweight=m['qweight'].numpy(), scale=to_np(m['scale']), qzero=m['qzero'].numpy(), perm_inv=m['perm_inv'].numpy(),
+            group_sizes_out=m['group_sizes'].numpy(), group_bit_widths_out=m['group_bit_widths'].numpy(),
             metrics=np.array([res['metrics'][k] for k in ('gptq_error', 'gptq_norm', 'l2.0_error', 'l2.0_norm')],
                              dtype=np.float64),
-            W_hat=to_np(lin.weight.data))
+            W_hat=to_np(lin.weight.data), **extra)
         print('wrote', name, {k: f'{v:.4e}' for k, v in res['metrics'].items()})
 
 
@@ -200,6 +222,8 @@ if __name__ == '__main__':
         main_quantizer()
     elif len(sys.argv) > 1 and sys.argv[1] == 'blocks':
         main_blocks()
+    elif len(sys.argv) > 1 and sys.argv[1] == 'blocks-new':
+        main_blocks(only_new=True)                     # add cases without touching the fixtures already committed
     else:
         main()
         main_quantizer()

@@ -154,13 +154,14 @@ def solve_general(weight: torch.Tensor, U: Optional[torch.Tensor], perm: Optiona
 
 
 def solve_blocks(weight: torch.Tensor, U: torch.Tensor, perm: Optional[torch.Tensor], group_sizes: Sequence[int],
-                 bits: Sequence[int], block_sizes: Sequence[int]) -> dict:
+                 bits: Sequence[int], block_sizes: Sequence[int], **opts) -> dict:
     """The fp32 branch of gptq_quant (gptq_py.py:158-193) with GPTQ blocks that differ from the quantisation groups and
-    group sizes that need not be uniform (asymmetric min/max grid, no MSE search), exactly as the reference walks it:
+    group sizes that need not be uniform, exactly as the reference walks it:
     the parameters of a group are computed when the column loop reaches the group's first column, from the GLOBAL
     weight matrix (:175-176) -- which holds the lazy-batch updates of the finished blocks but NOT the in-block updates
     of the current one -- while the columns themselves are quantised from the error-compensated block copy (:186);
-    a quantiser stays in force across block ends (:167,171)."""
+    a quantiser stays in force across block ends (:167,171).  opts: sym, scale_bits, mse (+ max_shrink, n_grid, norm);
+    the MSE search runs over the columns of the current BLOCK of the global matrix (:178-184), not over the group's."""
     W = weight.to(torch.float32).clone()
     if perm is not None:
         W = W[:, perm]
@@ -180,7 +181,11 @@ def solve_blocks(weight: torch.Tensor, U: torch.Tensor, perm: Optional[torch.Ten
         eblk = torch.empty_like(blk)
         for j in range(i1, i2):
             if cur < len(group_sizes) and j == gid[cur]:
-                P = find_params(W[:, j:j + int(group_sizes[cur])], int(bits[cur]))          # :172-177
+                P = find_params(W[:, j:j + int(group_sizes[cur])], int(bits[cur]), opts.get('sym', False),
+                                opts.get('scale_bits'))                                      # :172-177
+                if opts.get('mse', False):
+                    mse_refine(P, W[:, i1:i2], opts.get('max_shrink', 0.8), opts.get('n_grid', 100),
+                               opts.get('norm', 2.4))                                        # :178-184
                 params.append(P)
                 cur += 1
             w = blk[:, j - i1:j - i1 + 1]
@@ -194,6 +199,64 @@ def solve_blocks(weight: torch.Tensor, U: torch.Tensor, perm: Optional[torch.Ten
     out = dict(quant=quant, qweight=qweight, error=error, mse_index=None)
     out.update(_collect(params))
     return out
+
+
+def solve_rtn_groups(weight: torch.Tensor, group_sizes: Sequence[int], bits: Sequence[int], **opts) -> dict:
+    """Round to nearest (gptq_py.py:101-124) with group sizes that need not be uniform."""
+    W = weight.to(torch.float32).clone()
+    quant, qweight = torch.empty_like(W), torch.empty_like(W)
+    params, i1 = [], 0
+    for n, b in zip(group_sizes, bits):
+        i2 = i1 + int(n)
+        P = _group_params(W[:, i1:i2], int(b), opts)
+        params.append(P)
+        qweight[:, i1:i2] = qw = G.quantize(W[:, i1:i2], P['scale'], P['qzero'], P['maxq'])
+        quant[:, i1:i2] = G.dequantize(qw, P['scale'], P['qzero'])
+        i1 = i2
+    out = dict(quant=quant, qweight=qweight, error=None, mse_index=None)
+    out.update(_collect(params))
+    return out
+
+
+def assemble_groups(weight_ref: torch.Tensor, solved: dict, U: Optional[torch.Tensor], perm: Optional[torch.Tensor],
+                    group_sizes: Sequence[int], bits: Sequence[int], scale_bits: Optional[int] = None) -> dict:
+    """gptq_py.py:195-251 for any group sizes, with every optional key: with EXL2 metadata the groups are stored by
+    descending (bit width, group size), ties in ascending position (:201-212)."""
+    R, C = weight_ref.shape
+    dtype = weight_ref.dtype
+    sizes = [int(n) for n in group_sizes]
+    err = solved['error']
+    if err is None:
+        metrics = {'gptq_error': 0.0, 'gptq_norm': 0.0}
+    else:
+        metrics = {'gptq_error': (err ** 2.0).mean().item(),
+                   'gptq_norm': ((weight_ref / U.diag()) ** 2.0).mean().item()}
+    order = list(range(len(sizes)))
+    if scale_bits is not None:
+        order.sort(key=lambda g: (int(bits[g]), sizes[g], -g), reverse=True)
+    offs = [0]
+    for n in sizes:
+        offs.append(offs[-1] + n)
+    ic = torch.cat([torch.arange(offs[g], offs[g + 1]) for g in order])
+    ig = torch.tensor(order)
+    p16 = (perm.to(torch.int16) if perm is not None else torch.arange(C, dtype=torch.int16))[ic]
+    perm_inv = p16.argsort().to(torch.int16)
+    quant = solved['quant'][:, ic][:, perm_inv.to(torch.int32)]
+    metrics['l2.0_error'] = ((quant.to(torch.float32) - weight_ref.to(torch.float32)).abs() ** 2.0).mean().item()
+    metrics['l2.0_norm'] = (weight_ref.abs() ** 2.0).mean().item()
+    has_s = 'sscale' in solved
+    meta = {
+        'qweight': solved['qweight'].to(torch.uint8)[:, ic],
+        'scale': solved['scale'].to(dtype)[:, ig],
+        'qzero': solved['qzero'].to(torch.uint8)[:, ig],
+        'qscale': solved['qscale'].to(torch.uint8)[:, ig] if has_s else None,
+        'sscale': solved['sscale'].to(dtype)[0, ig] if has_s else None,
+        'perm_inv': perm_inv,
+        'group_sizes': torch.tensor(sizes, dtype=torch.int16)[ig],
+        'group_bit_widths': torch.tensor([int(b) for b in bits], dtype=torch.uint8)[ig],
+        'scale_bit_width': torch.tensor(scale_bits, dtype=torch.uint8) if scale_bits is not None else None,
+    }
+    return {'quant_meta': meta, 'metrics': metrics}
 
 
 def assemble_blocks(weight_ref: torch.Tensor, solved: dict, U: torch.Tensor, perm: Optional[torch.Tensor],

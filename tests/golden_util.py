@@ -61,12 +61,18 @@ def loadb(name):
     z = np.load(os.path.join(GOLDEN_DIR, name + '.npz'))
     d = {k: z[k] for k in z.files}
     dt = _DT[str(d['dtype'])]
+    sb = int(d['scale_bits']) if 'scale_bits' in d else -1
     out = dict(name=name, R=int(d['R']), C=int(d['C']), group_sizes=[int(v) for v in d['group_sizes']],
                bits=[int(v) for v in d['bits']], block_sizes=[int(v) for v in d['block_sizes']],
-               act_order=bool(int(d['act_order'])), dtype=dt)
+               act_order=bool(int(d['act_order'])), dtype=dt, rtn=bool(int(d['rtn'])) if 'rtn' in d else False,
+               sym=bool(int(d['sym'])) if 'sym' in d else False, mse=bool(int(d['mse'])) if 'mse' in d else False,
+               scale_bits=(None if sb < 0 else sb))
     out['W'] = torch.from_numpy(d['W_bits'].copy()).view(dt)
-    for k in ('U', 'scale', 'W_hat', 'qweight', 'qzero', 'perm_inv'):
-        out[k] = torch.from_numpy(d[k].copy())
+    for k in ('U', 'scale', 'W_hat', 'qweight', 'qzero', 'perm_inv', 'qscale', 'sscale', 'group_sizes_out',
+              'group_bit_widths_out'):
+        out[k] = torch.from_numpy(d[k].copy()) if k in d else None
+    if out['rtn']:
+        out['U'] = None
     out['perm'] = torch.from_numpy(d['perm'].copy()).to(torch.int64) if out['act_order'] else None
     out['metrics'] = dict(zip(('gptq_error', 'gptq_norm', 'l2.0_error', 'l2.0_norm'), d['metrics'].tolist()))
     return out

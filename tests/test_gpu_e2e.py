@@ -95,16 +95,13 @@ def test_unsupported_options_raise():
     bw = torch.full([2], 4, dtype=torch.int32)
     with pytest.raises(NotImplementedError):          # exllamav2's quantize_err (quant.py:131-150): absent from the reference too
         gptq_quant(W, None, gs, bw, quant_mse=True, quant_use_kernel=True)
-    with pytest.raises(NotImplementedError):          # non-uniform group sizes
-        gptq_quant(W, None, torch.tensor([64, 192], dtype=torch.int32), bw, quant_mse=False)
     import types
     hook = types.SimpleNamespace(hessian_inv=torch.eye(256, device='cuda'), perm=None, perm_inv=None, hessian=None)
-    with pytest.raises(NotImplementedError):          # GPTQ blocks that do not nest with the quantisation groups
+    with pytest.raises(NotImplementedError):          # sizes that are not multiples of 32 on the GPTQ branches
         gptq_quant(W, hook, gs, bw, gptq_use_kernel=False, quant_mse=False,
-                   gptq_block_sizes=torch.full([2], 96, dtype=torch.int32))
-    with pytest.raises(NotImplementedError):          # differing blocks with the MSE search (ref :178-184 searches over the block)
-        gptq_quant(W, hook, gs, bw, gptq_use_kernel=False, quant_mse=True,
-                   gptq_block_sizes=torch.full([4], 64, dtype=torch.int32))
+                   gptq_block_sizes=torch.tensor([100, 156], dtype=torch.int32))
+    with pytest.raises(NotImplementedError):
+        gptq_quant(W, hook, torch.tensor([72, 184], dtype=torch.int32), bw, gptq_use_kernel=True, quant_mse=False)
     # the round-to-nearest branch has no blocks (ref :101-124): gptq_block_sizes is ignored there, as in the reference
     a = gptq_quant(W, None, gs, bw, quant_mse=False, gptq_block_sizes=torch.full([4], 64, dtype=torch.int32), save_device=W.device)
     b = gptq_quant(W, None, gs, bw, quant_mse=False, gptq_block_sizes=gs, save_device=W.device)
