@@ -11,10 +11,31 @@ struct SolveParams;
 #define GQ_DECL(MODE, NB) int launch_solve_block_m##MODE##_nb##NB(const SolveParams& p, cudaStream_t st);
 GQ_DECL(0, 32) GQ_DECL(0, 64) GQ_DECL(0, 128) GQ_DECL(1, 32) GQ_DECL(1, 64) GQ_DECL(1, 128)
 #undef GQ_DECL
+struct SuperParams;
+#define GQ_DECL(MODE, NQ) int launch_solve_super_m##MODE##_nq##NQ(const CUtensorMap& map_u, const SuperParams& p, cudaStream_t st);
+GQ_DECL(0, 1) GQ_DECL(0, 2) GQ_DECL(0, 4) GQ_DECL(1, 1) GQ_DECL(1, 2) GQ_DECL(1, 4)
+#undef GQ_DECL
 
 }  // namespace gq
 #include "gptq_solver_params.h"
 namespace gq {
+
+// rows per CTA of the fused super-block kernel: the smallest tile that still fits the linear into one wave of CTAs
+static int launch_super_nq(int mode, const CUtensorMap& map_u, const SuperParams& p, int n_sms, cudaStream_t st) {
+  const int nq = (p.R + 31) / 32 <= n_sms ? 1 : (p.R + 63) / 64 <= n_sms ? 2 : 4;
+  if (mode == 0) {
+    switch (nq) {
+      case 1: return launch_solve_super_m0_nq1(map_u, p, st);
+      case 2: return launch_solve_super_m0_nq2(map_u, p, st);
+      default: return launch_solve_super_m0_nq4(map_u, p, st);
+    }
+  }
+  switch (nq) {
+    case 1: return launch_solve_super_m1_nq1(map_u, p, st);
+    case 2: return launch_solve_super_m1_nq2(map_u, p, st);
+    default: return launch_solve_super_m1_nq4(map_u, p, st);
+  }
+}
 
 static int launch_block_nb(int mode, const SolveParams& p, int nb, cudaStream_t st) {
   if (mode == 0) {
@@ -76,6 +97,39 @@ int gptq_solve(float* Wt, const float* U, float* quant_t, void* codes_t, int cod
   if (tc) {
     int rcm = gemm_tf32x3_maps(&maps, U, C, C, C, err_t, C, R, R, Wt, C, R, R);
     if (rcm != GQ_OK) return rcm;
+  }
+  // ---- fused path (gptq_solver_super.cuh): 128-column blocks only.  One launch solves a super-block of up to four blocks
+  // and keeps their mutual updates in tensor memory; the columns behind it get one rank-(super-block) update.
+  bool all128 = tc && g_solve_fused && g_solve_super > 1;
+  for (int nb : blocks) all128 = all128 && nb == 128;
+  if (all128) {
+    static int n_sms = 0;
+    if (n_sms == 0) {
+      int dev = 0;
+      cudaGetDevice(&dev);
+      if (cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n_sms <= 0) n_sms = 148;
+    }
+    CUtensorMap map_u;
+    int rc = make_tmap_2d(&map_u, U, 2, (uint64_t)C, (uint64_t)C, (uint64_t)C * 4, 32, 8, 1);
+    if (rc != GQ_OK) return rc;
+    const int per = std::min(g_solve_super, (int)SUP_MAXBLK);
+    const int n_blocks = (int)blocks.size();
+    for (int b0 = 0; b0 < n_blocks; b0 += per) {
+      SuperParams sp;
+      sp.Wt = Wt; sp.U = U; sp.quant_t = quant_t; sp.codes_t = codes_t; sp.err_t = err_t;
+      sp.R = R; sp.C = C; sp.c0 = a + 128 * b0; sp.nblk = std::min(per, n_blocks - b0); sp.static_params = static_params;
+      for (int i = 0; i < SUP_MAXBLK; ++i)
+        sp.maxq[i] = (per_group && maxq_groups && i < sp.nblk) ? maxq_groups[sp.c0 / 128 + i] : maxq;
+      if (per_group) {
+        sp.scale = scale_gr + (size_t)(sp.c0 / 128) * R; sp.qzero = qzero_gr + (size_t)(sp.c0 / 128) * R; sp.param_stride = R;
+      } else {
+        sp.scale = scale_gr; sp.qzero = qzero_gr; sp.param_stride = 0;
+      }
+      if ((rc = launch_super_nq(mode, map_u, sp, n_sms, st)) != GQ_OK) return rc;
+      const int e = sp.c0 + 128 * sp.nblk;
+      if (e < C && (rc = gemm_tf32x3(maps, C - e, R, e - sp.c0, sp.c0, e, sp.c0, 0, e, 0, -1.f, 0, st)) != GQ_OK) return rc;
+    }
+    return GQ_OK;
   }
   // Two-level lazy batching: inside a super-block of `super` x 128 columns the update only runs over the super-block's
   // own later columns (they are needed next); the columns behind it get ONE rank-(super-block width) update when the

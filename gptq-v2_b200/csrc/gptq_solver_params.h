@@ -13,4 +13,21 @@ struct SolveParams {
   float maxq;
   int static_params;    // MODE 0 only: scale/qzero are inputs (symmetric / MSE-refined / EXL2 parameters)
 };
+constexpr int SUP_MAXBLK = 4;   // blocks per fused super-block launch: 3 accumulator regions of 128 TMEM columns
+struct SuperParams {
+  float* Wt;            // (C, R) in (and out in MODE 1)
+  const float* U;       // (C, C)
+  float* quant_t;       // (C, R) out, may be null
+  void* codes_t;        // (C, R) out, may be null
+  float* err_t;         // (C, R) out
+  float* scale;         // parameters of the first block; block b at scale + b * param_stride
+  float* qzero;
+  int param_stride;     // R for per-group parameters, 0 when one (R) vector serves the whole range (quantize_range)
+  int R, C;
+  int c0;               // first column of the super-block
+  int nblk;             // 1..SUP_MAXBLK blocks of 128 columns
+  float maxq[SUP_MAXBLK];
+  int static_params;    // MODE 0 only: scale / qzero are inputs
+};
+
 }  // namespace gq

@@ -49,6 +49,7 @@ SIGNATURES = {
     'gq_gemm_tf32x3': (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _f, _i, _vp]),
     'gq_set_tf32x3': (_i, [_i]),
     'gq_set_solve_super': (_i, [_i]),
+    'gq_set_solve_fused': (_i, [_i]),
     'gq_set_w4a16_path': (_i, [_i]),
     'gq_sgemm': (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _f, _f, _i, _vp]),
 }
@@ -68,6 +69,8 @@ def _load():
         fn.argtypes = args
     if lib.gq_abi_version() != 1:
         raise ImportError('libgptq_b200.so ABI version mismatch')
+    if os.environ.get('GQ_SOLVE_FUSED', '') == '0':
+        lib.gq_set_solve_fused(0)
     return lib
 
 

@@ -177,6 +177,10 @@ int gq_set_tf32x3(int enable);
 /* Tuning hook: blocks per super-block of K4's two-level lazy-batch update (default 8; 1 = the reference's schedule, one
  * full trailing update per block, gptq_py.py:139).  Returns the previous setting. */
 int gq_set_solve_super(int blocks);
+/* A/B hook: 1 (default) = 128-column blocks are solved by the fused super-block kernel (one launch per up to four blocks, their
+ * mutual updates accumulated in tensor memory); 0 = one launch per block plus near-update GEMM launches (round 1's schedule).
+ * The environment variable GQ_SOLVE_FUSED=0 selects 0 at load time.  Returns the previous setting. */
+int gq_set_solve_fused(int on);
 /* A/B hook for K6's dispatch: 0 = automatic (batch <= 8: warp-level mma kernel; otherwise tcgen05 with the weights on the M
  * side through tensor memory, 64 or 256 batch columns per pass), 1 = never the small-batch kernel, 2 = batch <= 128 through
  * the experimental tcgen05 kernel with the weights on the N side (w4a16_wb.cu; correct, not yet faster).  Returns the
