@@ -153,7 +153,7 @@ int gptq_solve(float* Wt, const float* U, float* quant_t, void* codes_t, int cod
     int rc = launch_block_nb(mode, p, nb, st);
     if (rc != GQ_OK) return rc;
     const int e = c + nb;
-    const bool close_super = !tc || e >= sb_end;
+    const bool close_super = !tc || g_solve_super <= 1 || e >= sb_end;   // super = 1: the reference's schedule, one full trailing update per block
     if (e < C) {
       if (!tc) {
         GemmProblem g{U + (size_t)c * C + e, err_t + (size_t)c * R, Wt + (size_t)e * R, C - e, R, nb, C, R, R};
