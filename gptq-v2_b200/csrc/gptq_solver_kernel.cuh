@@ -66,45 +66,68 @@ __device__ __forceinline__ float dequant_code(float q, float s, float z, __half 
   return __half2float(__hmul(__hsub(__float2half_rn(q), hz), hs));           // gptq_cpp_kernel.cu:57-65
 }
 
-// One column step inside a 16-column sub-block; J is a compile-time index so w[] stays in registers.
-// Straight-line: everything it leaves behind goes to shared memory.
+// Shared-memory store the compiler may move OTHER shared-memory loads across (no "memory" clobber).  The recurrence below
+// stores an error and a code per column; as plain C++ stores they fence every later load of the U rows (the compiler
+// cannot prove that es / qs do not alias Upk), which put an exposed LDS latency on each of the 128 dependent column
+// steps.  Readers of es / qs / xs sit behind a barrier (a compiler memory barrier), or add their own.
+__device__ __forceinline__ void sts_noalias(float* p, float v) {
+  asm volatile("st.shared.f32 [%0], %1;" :: "r"(smem_u32(p)), "f"(v));
+}
+
+// The dependent column recurrence of one 16-column sub-block, straight-line (fully unrolled, w[] in registers);
+// everything it leaves behind goes to shared memory.  Software-pipelined by hand: row J + 1 of the U sub-block (the
+// multipliers of column J + 1's error), its diagonal entry and reciprocal are loaded BEFORE column J is computed and
+// stored.  Left to the compiler, the loads of a row sit behind the stores of the previous column (it cannot prove that
+// es / qs do not alias Upk) and every one of the 128 column steps of a block waits for a shared-memory round trip.
 template <int MODE, int J>
 struct SubSteps {
-  static __device__ __forceinline__ void run(float (&w)[SB], const float* Urow0, int ld, const float* rdg, float* es,
-                                             float* qs, float* xs, float s, float rs, float z, float maxq, __half hs,
-                                             __half hz, int lane) {
+  static __device__ __forceinline__ void load_row(float (&u)[SB], float& d, float& rd, const float* Urow0, int ld, const float* rdg) {
     const float* Urow = Urow0 + J * ld;               // packed row (col0 + J) of the diagonal block, starting at column col0
-    const float d = Urow[J];
-    const float rd = rdg[J];                          // RN(1 / d), precomputed in the prologue
+    d = Urow[J];
+    rd = rdg[J];                                      // RN(1 / d), precomputed in the prologue
+#pragma unroll
+    for (int k4 = (J + 1) / 4; k4 < SB / 4; ++k4) {
+      const float4 v = *reinterpret_cast<const float4*>(Urow + k4 * 4);
+      u[k4 * 4 + 0] = v.x; u[k4 * 4 + 1] = v.y; u[k4 * 4 + 2] = v.z; u[k4 * 4 + 3] = v.w;
+    }
+  }
+  // uc / d / rd: row J, loaded one step ago
+  static __device__ __forceinline__ void run(float (&w)[SB], const float (&uc)[SB], float d, float rd, const float* Urow0, int ld,
+                                             const float* rdg, float* es, float* qs, float* xs, float s, float rs, float z,
+                                             float maxq, __half hs, __half hz, int lane) {
+    float un[SB], dn = 0.f, rdn = 0.f;
+    if (J + 1 < SB) SubSteps<MODE, (J + 1 < SB ? J + 1 : J)>::load_row(un, dn, rdn, Urow0, ld, rdg);
     const float x = w[J];
     float q = rint_magic(div_by(x, s, rs));
     q = __fadd_rn(q, z);
     q = fminf(fmaxf(q, 0.f), maxq);
     const float deq = dequant_code<MODE>(q, s, z, hs, hz);
     const float e = div_by(__fsub_rn(x, deq), d, rd);
+    // the next column first: the chain waits for it
+#pragma unroll
+    for (int k = J + 1; k < SB; ++k) {
+      if (MODE == 0) w[k] = __fsub_rn(w[k], __fmul_rn(e, uc[k]));
+      else w[k] = __fmaf_rn(-e, uc[k], w[k]);
+    }
     es[J * ROWS + lane] = e;
     qs[J * ROWS + lane] = q;
     if (MODE == 1) xs[J * ROWS + lane] = x;           // the reference leaves the updated weight in place
-#pragma unroll
-    for (int k4 = (J + 1) / 4; k4 < SB / 4; ++k4) {
-      const float4 u = *reinterpret_cast<const float4*>(Urow + k4 * 4);
-      const float uu[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-      for (int t = 0; t < 4; ++t) {
-        const int k = k4 * 4 + t;
-        if (k > J) {
-          if (MODE == 0) w[k] = __fsub_rn(w[k], __fmul_rn(e, uu[t]));
-          else w[k] = __fmaf_rn(-e, uu[t], w[k]);
-        }
-      }
-    }
-    SubSteps<MODE, J + 1>::run(w, Urow0, ld, rdg, es, qs, xs, s, rs, z, maxq, hs, hz, lane);
+    SubSteps<MODE, J + 1>::run(w, un, dn, rdn, Urow0, ld, rdg, es, qs, xs, s, rs, z, maxq, hs, hz, lane);
+  }
+  // entry point: loads row 0 itself
+  static __device__ __forceinline__ void run(float (&w)[SB], const float* Urow0, int ld, const float* rdg, float* es,
+                                             float* qs, float* xs, float s, float rs, float z, float maxq, __half hs,
+                                             __half hz, int lane) {
+    static_assert(J == 0, "entry point");
+    float u0[SB], d0, rd0;
+    load_row(u0, d0, rd0, Urow0, ld, rdg);
+    run(w, u0, d0, rd0, Urow0, ld, rdg, es, qs, xs, s, rs, z, maxq, hs, hz, lane);
   }
 };
 template <int MODE>
 struct SubSteps<MODE, SB> {
-  static __device__ __forceinline__ void run(float (&)[SB], const float*, int, const float*, float*, float*, float*, float,
-                                             float, float, float, __half, __half, int) {}
+  static __device__ __forceinline__ void run(float (&)[SB], const float (&)[SB], float, float, const float*, int, const float*,
+                                             float*, float*, float*, float, float, float, float, __half, __half, int) {}
 };
 
 // packed upper-triangular storage of the diagonal block: sub-block sb (rows 16 sb .. 16 sb + 15) keeps columns

@@ -64,7 +64,37 @@ def factor_ref(Hp, dtype, device):
     return torch.linalg.cholesky_ex(Hi, upper=True)[0]
 
 
+def factor_sweep(D):
+    """Distance of K2's factor from the fp64 one under the library's A/B hooks: which part of K2 loses the digits?"""
+    import gptq
+    from gptq_py import HessianHook
+    dev = torch.device('cuda:0')
+    g = torch.Generator(device=dev).manual_seed(D)
+    cs = torch.exp(torch.rand(D, device=dev, generator=g) * 3.0 - 1.5)
+    X = (torch.randn(16 * 2048, D, device=dev, generator=g) * cs).half()
+    hook = HessianHook()
+    hook.add_batch(X.view(16, 2048, D))
+    del X
+    H0 = hook.hessian.clone()
+    res = {}
+    U64 = None
+    for tf32, sup in ((3, 8), (3, 4), (3, 2), (3, 1), (1, 8), (0, 8)):
+        gptq.set_tf32x3(tf32)
+        gptq.set_solve_super(sup)
+        h = HessianHook()
+        h.hessian, h.n_samples = H0.clone(), 16
+        h.invert(1e-2, True)
+        if U64 is None:
+            U64 = factor_ref(h.hessian, torch.float64, dev)
+        res[f'tf32x3={tf32} super={sup}'] = float((h.hessian_inv.double() - U64).norm() / U64.norm())
+    gptq.set_tf32x3(3)
+    gptq.set_solve_super(8)
+    print(json.dumps({'D': D, 'U_rel_fro_vs_fp64': res}))
+
+
 def main():
+    if len(sys.argv) > 2 and sys.argv[2] == 'factor':
+        return factor_sweep(int(sys.argv[1]))
     D = int(sys.argv[1]) if len(sys.argv) > 1 else 11008
     bits = int(sys.argv[2]) if len(sys.argv) > 2 else 4
     rows = int(sys.argv[3]) if len(sys.argv) > 3 else 256
