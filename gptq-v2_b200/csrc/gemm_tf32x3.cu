@@ -47,6 +47,8 @@ struct GemmTf32Params {
   int tiles_m, tiles_n;    // tile grid of the largest problem
   float alpha;
   int flags;               // TF32_* (gptq_b200_internal.h)
+  int kchunk;              // 16-deep k-blocks accumulated in tensor memory before the partial sum leaves through the epilogue
+                           // (0 = the whole k range at once)
   Tf32Problem p[TF32_MAX_BATCH];
 };
 
@@ -161,13 +163,20 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
       for (int t = walker; t < n_tiles; t += n_walkers) {
         const TileInfo ti = decode_tile<CG>(p, t);
         if (ti.skip) continue;
+        // Deep k ranges leave tensor memory in chunks: the tensor core adds every MMA into the fp32 accumulator with
+        // truncation, a bias that grows with the number of accumulations (measured: 2e-5 relative on the 5504-deep
+        // products of the triangular inverse at D = 11008); a chunk's partial sum is added to C by the epilogue's
+        // reduce-add in L2, which rounds to nearest, while the next chunk accumulates in the other TMEM buffer.
+        const int kstep = p.kchunk > 0 ? p.kchunk : (ti.kb1 - ti.kb0 > 0 ? ti.kb1 - ti.kb0 : 1);
+        for (int kc = ti.kb0; kc < ti.kb1 || kc == ti.kb0; kc += kstep) {
+        const int kce = min(kc + kstep, ti.kb1);
         const int acc = it & 1;
         const uint32_t acc_phase = (it >> 1) & 1u;
         ++it;
         mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * TN;
-        for (int kb = ti.kb0; kb < ti.kb1; ++kb) {
+        for (int kb = kc; kb < kce; ++kb) {
           mbar_wait(ready_bar(stage), phase);
           tc_fence_after();
           const uint32_t a_hi = smem_base + stage * STAGE_BYTES;
@@ -182,7 +191,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
             const uint64_t bh = umma_smem_desc(b_hi + k8 * 1024, SUB, 512, 1u);
             const uint64_t al = umma_smem_desc(a_lo + k8 * 1024, SUB, 512, 1u);
             const uint64_t bl = umma_smem_desc(b_lo + k8 * 1024, SUB, 512, 1u);
-            mma_tf32<CG>(d_tmem, al, bh, idesc, ((kb - ti.kb0) | k8) ? 1u : 0u);     // small terms first
+            mma_tf32<CG>(d_tmem, al, bh, idesc, ((kb - kc) | k8) ? 1u : 0u);     // small terms first
             mma_tf32<CG>(d_tmem, ah, bl, idesc, 1u);
             mma_tf32<CG>(d_tmem, ah, bh, idesc, 1u);
           }
@@ -190,6 +199,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
         if constexpr (CG == 2) tc_commit_cg2_mcast(tfull_bar(acc), 0x3); else tc_commit_cg1(tfull_bar(acc));
+        }
       }
     }
   } else if (warp >= 8) {
@@ -258,6 +268,14 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
       if (ti.skip) continue;
       const Tf32Problem& pq = p.p[ti.prob];
       const int m0 = ti.m0 + row_off, n0 = ti.n0;
+      const int kstep = p.kchunk > 0 ? p.kchunk : (ti.kb1 - ti.kb0 > 0 ? ti.kb1 - ti.kb0 : 1);
+      for (int kc = ti.kb0; kc < ti.kb1 || kc == ti.kb0; kc += kstep) {
+      // the first chunk of a store-mode tile is stored, the others are added to it: the store must have completed
+      const bool plain_store = (p.flags & TF32_STORE) && kc == ti.kb0;
+      if ((p.flags & TF32_STORE) && kc == ti.kb0 + kstep) {
+        if (lane == 0) bulk_wait_all();
+        __syncwarp();
+      }
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1u;
       ++it;
@@ -297,12 +315,13 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
           fence_proxy_async();
           __syncwarp();
           if (lane == 0) {
-            if (p.flags & TF32_STORE) tma_store_2d(&map_c, stg, pq.c_col0 + n0 + c * 32, pq.c_row0 + m0 + 32 * we);
+            if (plain_store) tma_store_2d(&map_c, stg, pq.c_col0 + n0 + c * 32, pq.c_row0 + m0 + 32 * we);
             else tma_reduce_add_2d(&map_c, stg, pq.c_col0 + n0 + c * 32, pq.c_row0 + m0 + 32 * we);
             bulk_commit();
           }
           buf ^= 1;
         }
+      }
       }
     }
     if (lane == 0) bulk_wait_all();
@@ -373,6 +392,7 @@ int gemm_tf32x3_batch(const Tf32Maps& maps, const Tf32Problem* probs, int count,
   GemmTf32Params p;
   p.count = 0; p.tiles_m = 0; p.tiles_n = 0; p.alpha = alpha;
   p.flags = flags | (g_use_tf32x3 >= 2 ? TF32_RAW_HI : 0);
+  p.kchunk = g_tf32_kchunk;
   int max_m = 0, max_n = 0;
   for (int i = 0; i < count; ++i) {
     const Tf32Problem& q = probs[i];

@@ -78,17 +78,26 @@ def factor_sweep(D):
     H0 = hook.hessian.clone()
     res = {}
     U64 = None
-    for tf32, sup in ((3, 8), (3, 4), (3, 2), (3, 1), (1, 8), (0, 8)):
+    import time
+    for tf32, sup, kch in ((3, 8, 0), (3, 8, 64), (3, 8, 32), (3, 8, 16), (3, 8, 8), (3, 8, 4), (3, 1, 16), (0, 8, 16)):
         gptq.set_tf32x3(tf32)
         gptq.set_solve_super(sup)
-        h = HessianHook()
-        h.hessian, h.n_samples = H0.clone(), 16
-        h.invert(1e-2, True)
+        gptq.set_tf32_kchunk(kch)
+        for rep in range(2):
+            h = HessianHook()
+            h.hessian, h.n_samples = H0.clone(), 16
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            h.invert(1e-2, True)
+            torch.cuda.synchronize()
+            dt = time.perf_counter() - t0
         if U64 is None:
             U64 = factor_ref(h.hessian, torch.float64, dev)
-        res[f'tf32x3={tf32} super={sup}'] = float((h.hessian_inv.double() - U64).norm() / U64.norm())
+        res[f'tf32x3={tf32} super={sup} kchunk={kch}'] = {'U_err': float((h.hessian_inv.double() - U64).norm() / U64.norm()),
+                                                          'invert_ms': round(dt * 1e3, 3)}
     gptq.set_tf32x3(3)
     gptq.set_solve_super(8)
+    gptq.set_tf32_kchunk(16)
     print(json.dumps({'D': D, 'U_rel_fro_vs_fp64': res}))
 
 
