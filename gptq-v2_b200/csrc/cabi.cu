@@ -6,7 +6,7 @@ using namespace gq;
 
 static inline cudaStream_t S(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 
-namespace gq { unsigned long long g_launch_count = 0; int g_use_tf32x3 = 3; int g_solve_super = 8; int g_solve_fused = 1; int g_tf32_kchunk = 16; int g_w4a16_path = 0; }
+namespace gq { unsigned long long g_launch_count = 0; int g_use_tf32x3 = 3; int g_solve_super = 8; int g_solve_fused = 1; int g_tf32_kchunk = 8; long long* g_solve_dbg = nullptr; int g_w4a16_path = 0; }
 
 extern "C" {
 
@@ -162,6 +162,11 @@ int gq_set_solve_super(int blocks) {
 int gq_set_tf32_kchunk(int kblocks) {
   int old = gq::g_tf32_kchunk;
   if (kblocks >= 0 && kblocks <= 4096) gq::g_tf32_kchunk = kblocks;
+  return old;
+}
+void* gq_set_solve_debug(void* dev_buffer) {
+  void* old = gq::g_solve_dbg;
+  gq::g_solve_dbg = static_cast<long long*>(dev_buffer);
   return old;
 }
 int gq_set_solve_fused(int on) {

@@ -64,7 +64,8 @@ int sgemm_batched(const GemmBatch& b, float alpha, float beta, int flags, cudaSt
 
 // ---- fp32-faithful tensor-core GEMM  C += alpha * A^T B  (3 x TF32 split, tcgen05)
 extern int g_w4a16_path;   // K6 dispatch: 0 auto; 1 never the small-batch mma.sync kernel; 2 the weights-on-N tcgen05 kernel for batch <= 128
-extern int g_tf32_kchunk;  // 3xTF32 GEMM: 16-deep k-blocks accumulated in tensor memory per partial sum (default 16 = 256 deep; 0 = unlimited)
+extern int g_tf32_kchunk;  // 3xTF32 GEMM: 16-deep k-blocks accumulated in tensor memory per partial sum (default 8 = 128 deep; 0 = unlimited)
+extern long long* g_solve_dbg;  // profiling hook: device buffer for the fused solver's clock64 stamps (first super-block of a call), or null
 extern int g_solve_fused;  // K3/K4: 1 (default) = 128-column blocks run through the fused super-block kernel (near updates in tensor memory); 0 = one launch per block + near-update GEMMs
 extern int g_solve_super;  // K4: blocks per super-block of the two-level lazy-batch update (1 = update everything after every block)
 extern int g_use_tf32x3;   // 3 (default): K4 / Cholesky updates on tcgen05 3xTF32, truncation split (TF32_RAW_HI), 256 x 256 tiles on CTA pairs (cta_group::2) when there is more than one wave of tiles; 2: truncation split, single-CTA tiles only; 1: round-to-nearest split; 0: fp32 SIMT GEMM (A/B parity hook)

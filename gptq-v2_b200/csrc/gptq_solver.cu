@@ -117,6 +117,7 @@ int gptq_solve(float* Wt, const float* U, float* quant_t, void* codes_t, int cod
     for (int b0 = 0; b0 < n_blocks; b0 += per) {
       SuperParams sp;
       sp.Wt = Wt; sp.U = U; sp.quant_t = quant_t; sp.codes_t = codes_t; sp.err_t = err_t;
+      sp.dbg = (b0 == 0) ? g_solve_dbg : nullptr;
       sp.R = R; sp.C = C; sp.c0 = a + 128 * b0; sp.nblk = std::min(per, n_blocks - b0); sp.static_params = static_params;
       for (int i = 0; i < SUP_MAXBLK; ++i)
         sp.maxq[i] = (per_group && maxq_groups && i < sp.nblk) ? maxq_groups[sp.c0 / 128 + i] : maxq;

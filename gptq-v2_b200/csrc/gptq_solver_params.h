@@ -28,6 +28,7 @@ struct SuperParams {
   int nblk;             // 1..SUP_MAXBLK blocks of 128 columns
   float maxq[SUP_MAXBLK];
   int static_params;    // MODE 0 only: scale / qzero are inputs
+  long long* dbg;       // profiling hook (gq_set_solve_debug): clock64 stamps of CTA 0's first chain warp, or null
 };
 
 }  // namespace gq

@@ -205,13 +205,19 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
     constexpr int OFF_MM = (MODE == 1 ? OFF_XS + 2 * SB * 32 : OFF_XS), OFF_SZ = OFF_MM + 2 * 4 * 32;
     CodeT* codes = reinterpret_cast<CodeT*>(p.codes_t);
     constexpr int NH = SUP_COMPUTE_WARPS - NQ;                  // helper warps
+    // profiling hook: time stamps of CTA 0's chain warp (transition / chain / barriers), 4 + 8 x 4 per block
+    long long* dbg = (p.dbg && blockIdx.x == 0 && threadIdx.x == 0) ? p.dbg : nullptr;
+    int di = 0;
+    auto stamp = [&]() { if (dbg) dbg[di++] = clock64(); };
 
 #pragma unroll 1
     for (int b = 0; b < p.nblk; ++b) {
       const int cb = p.c0 + SUP_NB * b;
       float* rdg_b = rdg + (b & 1) * SUP_NB;
       // ---- stage block b.  Everyone is done with the previous block's Upk / ws / es.
+      stamp();
       named_bar_sync(1, SUP_COMPUTE_THREADS);
+      stamp();
       if (warp == SUP_COMPUTE_WARPS - 1) {
         if (lane == 0) mbar_expect_tx(ubar, SUP_UPK_BYTES);
         __syncwarp();
@@ -253,6 +259,7 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
         ws_q[OFF_MM + part * 32 + lane] = mx;
         ws_q[OFF_MM + (4 + part) * 32 + lane] = mn;
       }
+      stamp();
       named_bar_sync(1, SUP_COMPUTE_THREADS);
       const float maxq = b == 0 ? p.maxq[0] : b == 1 ? p.maxq[1] : b == 2 ? p.maxq[2] : p.maxq[3];   // no dynamic indexing of the parameter space
       float s = 1.f, z = 0.f;
@@ -284,6 +291,7 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
       if (MODE == 1) { hs = __float2half_rn(s); hz = __float2half_rn(z); }
       mbar_wait(ubar, b & 1u);                                   // the diagonal block of U has landed
       named_bar_sync(1, SUP_COMPUTE_THREADS);                    // ... and scale / zero / rdg are published
+      stamp();
 
       // write-out of one finished column of one quarter (coalesced 128-byte rows)
       auto store_col = [&](int sb, int rq, int j) {
@@ -306,6 +314,7 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
         const int ld = SUP_NB - col0;
         const float* Usb = Upk + upk_base<SUP_NB>(sb);
         const int par = (sb & 1) * SB * 32;
+        stamp();
         if (warp < NQ) {
           float* ws_q = Qp(warp);
           float w[SB];
@@ -313,6 +322,7 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
           for (int j = 0; j < SB; ++j) w[j] = ws_q[(col0 + j) * 32 + lane];
           SubSteps<MODE, 0>::run(w, Usb, ld, rdg_b + col0, ws_q + OFF_ES + par, ws_q + OFF_QS + par, ws_q + OFF_XS + par, s, rs,
                                  z, maxq, hs, hz, lane);
+          stamp();
           if (b + 1 < p.nblk) {
             // the 16 errors of this sub-block -> tensor memory (A operand of the near update)
             const int u = b * (SUP_NB / SB) + sb, abuf = u & 1;
@@ -334,7 +344,9 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
             if (lane == 0) mbar_arrive(aready(abuf));
           }
         }
+        stamp();
         named_bar_sync(1, SUP_COMPUTE_THREADS);                  // errors / codes of sub-block sb published
+        stamp();
         if (sb + 1 == SUP_NB / SB) break;
         // the next sub-block's 16 columns first (4 column groups x NQ quarters): the recurrence waits only for these
         if (warp < 4 * NQ) {

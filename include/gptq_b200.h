@@ -179,9 +179,12 @@ int gq_set_tf32x3(int enable);
 int gq_set_solve_super(int blocks);
 /* Accuracy / speed hook of the 3xTF32 GEMM: the tensor core adds every MMA into its fp32 accumulator with truncation, so a
  * k range is accumulated in tensor memory in chunks of `kblocks` x 16 and each chunk's partial sum is added to C by a
- * round-to-nearest reduce-add (default 16 = 256-deep chunks; 0 = the whole range at once, round 1's behaviour).
+ * round-to-nearest reduce-add (default 8 = 128-deep chunks; 0 = the whole range at once, round 1's behaviour).
  * Returns the previous setting. */
 int gq_set_tf32_kchunk(int kblocks);
+/* Profiling hook: a device buffer of >= 256 int64 that receives clock64() stamps of the first chain warp of CTA 0 for the first
+ * super-block of every following fused solve (tools/solve_timeline.py decodes them); NULL switches it off.  Returns the old pointer. */
+void* gq_set_solve_debug(void* dev_buffer);
 /* A/B hook: 1 (default) = 128-column blocks are solved by the fused super-block kernel (one launch per up to four blocks, their
  * mutual updates accumulated in tensor memory); 0 = one launch per block plus near-update GEMM launches (round 1's schedule).
  * The environment variable GQ_SOLVE_FUSED=0 selects 0 at load time.  Returns the previous setting. */
