@@ -170,28 +170,52 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
           tc_fence_after();
           const uint32_t a_hi = tmem_base + SUP_TMEM_A + abuf * 32, a_lo = a_hi + 16;
           const uint32_t first = (b == 0 && sb == 0) ? 0u : 1u;
-          // the next block's 128 columns first: the chain waits for these
-#pragma unroll
-          for (int k8 = 0; k8 < 2; ++k8) {
-            const uint32_t bh = ring + (k8 ? st1 : st0) * SUP_STAGE_BYTES, bl = bh + SUP_STAGE_HI;
-            // MN-major tf32, SWIZZLE_128B_BASE32B: atoms of [4 k][32 fp32] (SBO = 512 B), 32-column groups one box apart
-            const uint64_t dh = umma_smem_desc(bh, SUP_SUBTILE, 512, 1u), dl = umma_smem_desc(bl, SUP_SUBTILE, 512, 1u);
-            const uint32_t d = tmem_base + SUP_NB * b;
-            mma_tf32_ts(d, a_lo + 8 * k8, dh, idesc128, k8 ? 1u : first);      // small terms first
-            mma_tf32_ts(d, a_hi + 8 * k8, dl, idesc128, 1u);
-            mma_tf32_ts(d, a_hi + 8 * k8, dh, idesc128, 1u);
-          }
-          if (sb == SUP_NB / SB - 1) tc_commit_cg1(accfull(b));
-          if (nreg >= 2) {
-            const uint32_t idesc = nreg == 3 ? idesc256 : idesc128;
+          const uint32_t idesc384a = idesc256;                 // three regions = one N = 256 MMA + one N = 128 MMA
+          if (sb == SUP_NB / SB - 1) {
+            // last sub-block: the next block's 128 columns first (the chain waits for them), then the rest
 #pragma unroll
             for (int k8 = 0; k8 < 2; ++k8) {
-              const uint32_t bh = ring + (k8 ? st1 : st0) * SUP_STAGE_BYTES + 4 * SUP_SUBTILE, bl = bh + SUP_STAGE_HI;
+              const uint32_t bh = ring + (k8 ? st1 : st0) * SUP_STAGE_BYTES, bl = bh + SUP_STAGE_HI;
+              // MN-major tf32, SWIZZLE_128B_BASE32B: atoms of [4 k][32 fp32] (SBO = 512 B), 32-column groups one box apart
               const uint64_t dh = umma_smem_desc(bh, SUP_SUBTILE, 512, 1u), dl = umma_smem_desc(bl, SUP_SUBTILE, 512, 1u);
-              const uint32_t d = tmem_base + SUP_NB * (b + 1);
+              const uint32_t d = tmem_base + SUP_NB * b;
+              mma_tf32_ts(d, a_lo + 8 * k8, dh, idesc128, k8 ? 1u : first);      // small terms first
+              mma_tf32_ts(d, a_hi + 8 * k8, dl, idesc128, 1u);
+              mma_tf32_ts(d, a_hi + 8 * k8, dh, idesc128, 1u);
+            }
+            tc_commit_cg1(accfull(b));
+            if (nreg >= 2) {
+              const uint32_t idesc = nreg == 3 ? idesc256 : idesc128;
+#pragma unroll
+              for (int k8 = 0; k8 < 2; ++k8) {
+                const uint32_t bh = ring + (k8 ? st1 : st0) * SUP_STAGE_BYTES + 4 * SUP_SUBTILE, bl = bh + SUP_STAGE_HI;
+                const uint64_t dh = umma_smem_desc(bh, SUP_SUBTILE, 512, 1u), dl = umma_smem_desc(bl, SUP_SUBTILE, 512, 1u);
+                const uint32_t d = tmem_base + SUP_NB * (b + 1);
+                mma_tf32_ts(d, a_lo + 8 * k8, dh, idesc, k8 ? 1u : first);
+                mma_tf32_ts(d, a_hi + 8 * k8, dl, idesc, 1u);
+                mma_tf32_ts(d, a_hi + 8 * k8, dh, idesc, 1u);
+              }
+            }
+          } else {
+            // every other sub-block: as few MMAs as the N <= 256 limit allows (an MMA holds the tensor core ~172 cycles
+            // whatever its N): regions [b, b + 2) in one N = 256 (or N = 128) MMA, a third region in a second one
+#pragma unroll
+            for (int k8 = 0; k8 < 2; ++k8) {
+              const uint32_t bh = ring + (k8 ? st1 : st0) * SUP_STAGE_BYTES, bl = bh + SUP_STAGE_HI;
+              const uint64_t dh = umma_smem_desc(bh, SUP_SUBTILE, 512, 1u), dl = umma_smem_desc(bl, SUP_SUBTILE, 512, 1u);
+              const uint32_t d = tmem_base + SUP_NB * b;
+              const uint32_t idesc = nreg >= 2 ? idesc384a : idesc128;
               mma_tf32_ts(d, a_lo + 8 * k8, dh, idesc, k8 ? 1u : first);
               mma_tf32_ts(d, a_hi + 8 * k8, dl, idesc, 1u);
               mma_tf32_ts(d, a_hi + 8 * k8, dh, idesc, 1u);
+              if (nreg == 3) {
+                const uint64_t dh2 = umma_smem_desc(bh + 8 * SUP_SUBTILE, SUP_SUBTILE, 512, 1u);
+                const uint64_t dl2 = umma_smem_desc(bl + 8 * SUP_SUBTILE, SUP_SUBTILE, 512, 1u);
+                const uint32_t d2 = tmem_base + SUP_NB * (b + 2);
+                mma_tf32_ts(d2, a_lo + 8 * k8, dh2, idesc128, k8 ? 1u : first);
+                mma_tf32_ts(d2, a_hi + 8 * k8, dl2, idesc128, 1u);
+                mma_tf32_ts(d2, a_hi + 8 * k8, dh2, idesc128, 1u);
+              }
             }
           }
           tc_commit_cg1(bempty(st0));
@@ -205,10 +229,12 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
     // Roles among the 16 compute warps (quarter q = 32 rows = TMEM lanes 32 q ..):
     //   chain q          warp q (q < NQ): the column recurrence; after publishing a sub-block's errors it also hands them
     //                    to the tensor core (tcgen05.st) while the look-ahead warps update the next 16 columns
-    //   stagers of q     warps q + 4, q + 8, q + 12 (the other warps that may touch quarter q's TMEM lanes): they prefetch
-    //                    their 48 / 40 / 40 columns of the NEXT block's weights into registers during the last sub-block and
-    //                    turn them into W - acc at the block boundary
-    //   look-ahead       every non-chain warp: the rank-16 update of the next sub-block's 16 columns, split evenly
+    //   stagers of q     warps q + 4, q + 8, q + 12 (the other warps that may touch quarter q's TMEM lanes): at a block
+    //                    boundary they load their 48 / 40 / 40 columns of the block's weights (in flight while the previous
+    //                    block's last MMAs finish) and turn them into W - acc
+    //   look-ahead       the rank-16 update of the next sub-block's 16 columns, four 4-column items per quarter: on four
+    //                    non-chain warps of different SM sub-partitions (NQ <= 2), or on the quarter's chain warp + its three
+    //                    stagers (NQ = 4, where there are no other warps)
     //   far / write-out  warps that do not share an SM sub-partition with a chain warp (all non-chain warps when NQ = 4):
     //                    the rest of the block's columns and the global stores, while the chain runs its next sub-block
     const int row0 = blockIdx.x * 32 * NQ;
@@ -222,9 +248,10 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
     const int part = (warp >> 2) - 1;                            // stagers: 0, 1, 2
     const int part_c0 = part == 0 ? 0 : part == 1 ? 48 : 88;
     const int part_w = part == 0 ? 48 : 40;
-    // look-ahead workers of quarter rq: non-chain warps dealt round-robin to the quarters, at most 8 per quarter
-    constexpr int LA_PER_Q = (SUP_COMPUTE_WARPS - NQ) / NQ > 8 ? 8 : (SUP_COMPUTE_WARPS - NQ) / NQ;     // 8, 7, 3
-    const int la_q = is_chain ? -1 : (warp - NQ) % NQ, la_i = is_chain ? -1 : (warp - NQ) / NQ;
+    // look-ahead item of this warp: (quarter la_q, column group la_g) or none (la_q < 0)
+    int la_q = -1, la_g = 0;
+    if (NQ == 4) { la_q = my_q; la_g = warp >> 2; }
+    else if (warp >= NQ && warp < NQ + 4 * NQ) { la_q = (warp - NQ) >> 2; la_g = (warp - NQ) & 3; }
     // far-update / write-out helpers
     constexpr int NH = NQ == 4 ? 12 : 4 * (4 - NQ);
     const bool is_far = NQ == 4 ? warp >= 4 : my_q >= NQ;
@@ -245,9 +272,17 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
                      p.U + (size_t)(cb + j) * p.C + cb + cs, (SUP_NB - cs) * 4, ubar(b & 1));
       }
     };
-    auto load_rdg = [&](int b) {                                 // threads 128..255: reciprocals of diag(U) of block b
+    // reciprocals of diag(U) of block b by threads 128..255: the load is issued at one point and consumed sub-blocks
+    // later (a strided global load per thread; its latency must not sit in front of a barrier the chain waits behind)
+    float rdg_u = 1.f;
+    auto issue_rdg = [&](int b) {
       const int cb = p.c0 + SUP_NB * b, t = threadIdx.x - 128;
-      if (t >= 0 && t < SUP_NB) rdg[(b & 1) * SUP_NB + t] = __frcp_rn(p.U[(size_t)(cb + t) * p.C + cb + t]);
+      if (t >= 0 && t < SUP_NB)
+        asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(rdg_u) : "l"(p.U + (size_t)(cb + t) * p.C + cb + t));
+    };
+    auto finish_rdg = [&](int b) {
+      const int t = threadIdx.x - 128;
+      if (t >= 0 && t < SUP_NB) rdg[(b & 1) * SUP_NB + t] = __frcp_rn(rdg_u);
     };
     // stagers: their columns of block b's weights, global -> registers (issued early, consumed at the block boundary)
     float wv[48];
@@ -260,8 +295,8 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
     };
 
     if (warp == SUP_COMPUTE_WARPS - 1) load_upk(0);
-    load_rdg(0);
-    if (is_stager) prefetch_w(0);
+    issue_rdg(0);
+    finish_rdg(0);
 
 #pragma unroll 1
     for (int b = 0; b < p.nblk; ++b) {
@@ -274,7 +309,9 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
       stamp();
       if (NUPK == 1 && b > 0 && warp == SUP_COMPUTE_WARPS - 1) load_upk(b);
       if (is_stager) {
-        // W_global (prefetched) - (updates of the super-block's earlier blocks, accumulated in tensor memory)
+        // W_global - (updates of the super-block's earlier blocks, accumulated in tensor memory); the global loads are in
+        // flight while the last MMAs of the previous block finish
+        prefetch_w(b);
         float* ws_q = Qp(my_q);
         if (b > 0) {
           mbar_wait(accfull(b - 1), 0);
@@ -305,7 +342,7 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
       // the NEXT block's diagonal block of U and reciprocals start travelling now
       if (b + 1 < p.nblk) {
         if (NUPK == 2 && warp == SUP_COMPUTE_WARPS - 1) load_upk(b + 1);
-        load_rdg(b + 1);
+        issue_rdg(b + 1);
       }
       const float maxq = b == 0 ? p.maxq[0] : b == 1 ? p.maxq[1] : b == 2 ? p.maxq[2] : p.maxq[3];   // no dynamic indexing of the parameter space
       float s = 1.f, z = 0.f;
@@ -368,58 +405,40 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
           for (int j = 0; j < SB; ++j) w[j] = ws_q[(col0 + j) * 32 + lane];
           SubSteps<MODE, 0>::run(w, Usb, ld, rdg_b + col0, ws_q + OFF_ES + par, ws_q + OFF_QS + par, ws_q + OFF_XS + par, s, rs,
                                  z, maxq, hs, hz, lane);
-        } else if (last_sb && is_stager && b + 1 < p.nblk) {
-          prefetch_w(b + 1);                                     // lands while the chain runs the block's last 16 columns
         }
+        if (sb == 4 && b + 1 < p.nblk) finish_rdg(b + 1);        // issued at the block's start: long landed
         stamp();
         stamp();
         named_bar_sync(1, SUP_COMPUTE_THREADS);                  // errors / codes of sub-block sb published
         stamp();
-        if (is_chain) {
-          if (b + 1 < p.nblk) {
-            // the 16 errors of this sub-block -> tensor memory (A operand of the near update), off the look-ahead's path
-            float* ws_q = Qp(warp);
-            const int u = b * (SUP_NB / SB) + sb, abuf = u & 1;
-            if (u >= 2) mbar_wait(aempty(abuf), ((u >> 1) - 1) & 1u);     // the MMAs that read this buffer are done
-            tc_fence_after();
-            uint32_t hi[SB], lo[SB];
-#pragma unroll
-            for (int j = 0; j < SB; ++j) {
-              const float e = ws_q[OFF_ES + par + j * 32 + lane];
-              hi[j] = __float_as_uint(e);
-              lo[j] = __float_as_uint(sup_lo(e));
-            }
-            const uint32_t t = tmem_base + (uint32_t(32 * warp) << 16) + SUP_TMEM_A + abuf * 32;
-            tmem_st_32x16(t, hi);
-            tmem_st_32x16(t + 16, lo);
-            tmem_st_wait();
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(aready(abuf));
-          }
-        } else if (!last_sb && la_i < LA_PER_Q) {
-          // the next sub-block's 16 columns first: the recurrence waits only for these.  Columns [c_lo, c_hi) of the 16.
-          const int c_lo = (SB * la_i) / LA_PER_Q, c_hi = (SB * (la_i + 1)) / LA_PER_Q;
+        if (!last_sb && la_q >= 0) {
+          // the next sub-block's 16 columns first: the recurrence waits only for these
           float* ws_q = Qp(la_q);
-          const float* e_ = ws_q + OFF_ES + par;
-          constexpr int MAXC = (SB + LA_PER_Q - 1) / LA_PER_Q;   // 2, 3, 6
-          float wn[MAXC];
+          float e[SB];
 #pragma unroll
-          for (int i = 0; i < MAXC; ++i) wn[i] = (c_lo + i < c_hi) ? ws_q[(col0 + SB + c_lo + i) * 32 + lane] : 0.f;
+          for (int j = 0; j < SB; ++j) e[j] = ws_q[OFF_ES + par + j * 32 + lane];
+          update4<MODE>(ws_q, e, Usb, ld, col0, col0 + SB + 4 * la_g, lane);
+        }
+        if (is_chain && b + 1 < p.nblk) {
+          // the 16 errors of this sub-block -> tensor memory (A operand of the near update), off the look-ahead's path
+          float* ws_q = Qp(warp);
+          const int u = b * (SUP_NB / SB) + sb, abuf = u & 1;
+          if (u >= 2) mbar_wait(aempty(abuf), ((u >> 1) - 1) & 1u);       // the MMAs that read this buffer are done
+          tc_fence_after();
+          uint32_t hi[SB], lo[SB];
 #pragma unroll
           for (int j = 0; j < SB; ++j) {
-            const float e = e_[j * 32 + lane];
-            const float* ur = Usb + j * ld + SB + c_lo;
-#pragma unroll
-            for (int i = 0; i < MAXC; ++i) {
-              const float uu = (c_lo + i < c_hi) ? ur[i] : 0.f;
-              if (MODE == 0) wn[i] = __fsub_rn(wn[i], __fmul_rn(e, uu));
-              else wn[i] = __fmaf_rn(-e, uu, wn[i]);
-            }
+            const float e = ws_q[OFF_ES + par + j * 32 + lane];
+            hi[j] = __float_as_uint(e);
+            lo[j] = __float_as_uint(sup_lo(e));
           }
-#pragma unroll
-          for (int i = 0; i < MAXC; ++i)
-            if (c_lo + i < c_hi) ws_q[(col0 + SB + c_lo + i) * 32 + lane] = wn[i];
+          const uint32_t t = tmem_base + (uint32_t(32 * warp) << 16) + SUP_TMEM_A + abuf * 32;
+          tmem_st_32x16(t, hi);
+          tmem_st_32x16(t + 16, lo);
+          tmem_st_wait();
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(aready(abuf));
         }
         if (last_sb) break;
         named_bar_sync(1, SUP_COMPUTE_THREADS);
