@@ -6,7 +6,7 @@ using namespace gq;
 
 static inline cudaStream_t S(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 
-namespace gq { unsigned long long g_launch_count = 0; int g_use_tf32x3 = 3; int g_solve_super = 8; int g_solve_fused = 1; int g_tf32_kchunk = 8; long long* g_solve_dbg = nullptr; int g_w4a16_path = 0; }
+namespace gq { unsigned long long g_launch_count = 0; int g_use_tf32x3 = 3; int g_solve_super = 8; int g_solve_fused = 1; int g_tf32_kchunk = 8; int g_syrk_kchunk = 128; long long* g_solve_dbg = nullptr; int g_w4a16_path = 0; }
 
 extern "C" {
 
@@ -157,6 +157,11 @@ int gq_sgemm(const float* A, const float* B, float* C, int M, int N, int K, int 
 int gq_set_solve_super(int blocks) {
   int old = gq::g_solve_super;
   if (blocks >= 1 && blocks <= 16) gq::g_solve_super = blocks;
+  return old;
+}
+int gq_set_syrk_kchunk(int kblocks) {
+  int old = gq::g_syrk_kchunk;
+  if (kblocks >= 0 && kblocks <= (1 << 20)) gq::g_syrk_kchunk = kblocks;
   return old;
 }
 int gq_set_tf32_kchunk(int kblocks) {

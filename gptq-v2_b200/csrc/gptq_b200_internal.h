@@ -64,6 +64,7 @@ int sgemm_batched(const GemmBatch& b, float alpha, float beta, int flags, cudaSt
 
 // ---- fp32-faithful tensor-core GEMM  C += alpha * A^T B  (3 x TF32 split, tcgen05)
 extern int g_w4a16_path;   // K6 dispatch: 0 auto; 1 never the small-batch mma.sync kernel; 2 the weights-on-N tcgen05 kernel for batch <= 128
+extern int g_syrk_kchunk;  // K1: 64-token k-blocks accumulated in tensor memory per partial sum (default 128 = 8192 tokens; 0 = a whole call)
 extern int g_tf32_kchunk;  // 3xTF32 GEMM: 16-deep k-blocks accumulated in tensor memory per partial sum (default 8 = 128 deep; 0 = unlimited)
 extern long long* g_solve_dbg;  // profiling hook: device buffer for the fused solver's clock64 stamps (first super-block of a call), or null
 extern int g_solve_fused;  // K3/K4: 1 (default) = 128-column blocks run through the fused super-block kernel (near updates in tensor memory); 0 = one launch per block + near-update GEMMs

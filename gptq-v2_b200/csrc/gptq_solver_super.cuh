@@ -257,9 +257,11 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
     const bool is_far = NQ == 4 ? warp >= 4 : my_q >= NQ;
     const int far_i = NQ == 4 ? warp - 4 : (warp >> 2) * (4 - NQ) + (my_q - NQ);
     // profiling hook: time stamps of CTA 0's chain warp
-    long long* dbg = (p.dbg && blockIdx.x == 0 && threadIdx.x == 0) ? p.dbg : nullptr;
+    // (reporters: lane 0 of warps 0, 1, 4 and 15 of CTA 0, 256 slots each)
+    const int rep = warp == 0 ? 0 : warp == 1 ? 1 : warp == 4 ? 2 : warp == 15 ? 3 : -1;
+    long long* dbg = (p.dbg && blockIdx.x == 0 && lane == 0 && rep >= 0) ? p.dbg + 256 * rep : nullptr;
     int di = 0;
-    auto stamp = [&]() { if (dbg) dbg[di++] = clock64(); };
+    auto stamp = [&]() { if (dbg && di < 256) dbg[di++] = clock64(); };
 
     auto load_upk = [&](int b) {                                 // one warp: the packed diagonal block of block b
       const int cb = p.c0 + SUP_NB * b;
@@ -441,6 +443,7 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
           if (lane == 0) mbar_arrive(aready(abuf));
         }
         if (last_sb) break;
+        stamp();
         named_bar_sync(1, SUP_COMPUTE_THREADS);
         if (is_far) {
           // write-out + far columns of the block while the chain warps run the next sub-block

@@ -48,6 +48,7 @@ struct SyrkParams {
   int fmt;        // 0 fp16, 1 bf16
   int NT;         // ceil(D / 256)
   int n_tiles;    // NT (NT + 1) / 2
+  int kchunk;     // 64-token k-blocks accumulated in tensor memory before the partial sum is added to H (0 = all of T)
 };
 
 // Tile order.  Super-tiles that run at the same time should share operand panels: the 74 CTA pairs walk the upper
@@ -172,13 +173,20 @@ syrk_upper_kernel(const __grid_constant__ CUtensorMap tmap, const SyrkParams p) 
       const uint32_t idesc = umma_idesc((uint32_t)p.fmt, 1u, 1u, C::UMMA_M, C::UMMA_N);
       int stage = 0; uint32_t phase = 0;
       int it = 0;
-      for (int s = pair; s < p.n_tiles; s += n_pairs, ++it) {
+      // The tensor core adds every MMA into the fp32 accumulator with truncation: over the 2048 MMAs of a 32768-token
+      // call the sums come out ~5e-6 low (relative), which the inverse factor amplifies by the condition number.  The
+      // token range therefore leaves tensor memory in chunks; the epilogue adds each partial sum to H in fp32
+      // round-to-nearest while the next chunk accumulates in the other TMEM buffer.
+      const int kstep = p.kchunk > 0 ? p.kchunk : num_kb;
+      for (int s = pair; s < p.n_tiles; s += n_pairs)
+      for (int kc = 0; kc < num_kb; kc += kstep, ++it) {
+        const int kce = min(kc + kstep, num_kb);
         const int acc = it & 1;
         const uint32_t acc_phase = (it >> 1) & 1u;
         mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * 256;
-        for (int kb = 0; kb < num_kb; ++kb) {
+        for (int kb = kc; kb < kce; ++kb) {
           mbar_wait(full_bar(stage), phase);
           tc_fence_after();
           const uint32_t sa = smem_base + stage * C::STAGE_BYTES;
@@ -188,7 +196,7 @@ syrk_upper_kernel(const __grid_constant__ CUtensorMap tmap, const SyrkParams p) 
             // MN-major SW128: 16 tokens = 2 swizzle atoms of 8 rows x 128 B -> +2048 B per MMA
             const uint64_t ad = umma_smem_desc_sw128(sa + k4 * 2048, C::SUB_BYTES, 1024);
             const uint64_t bd = umma_smem_desc_sw128(sb + k4 * 2048, C::SUB_BYTES, 1024);
-            mma_f16<CG>(d_tmem, ad, bd, idesc, (kb | k4) ? 1u : 0u);
+            mma_f16<CG>(d_tmem, ad, bd, idesc, ((kb - kc) | k4) ? 1u : 0u);
           }
           if constexpr (CG == 2) tc_commit_cg2_mcast(empty_bar(stage), 0x3); else tc_commit_cg1(empty_bar(stage));
           if (++stage == C::STAGES) { stage = 0; phase ^= 1u; }
@@ -201,7 +209,9 @@ syrk_upper_kernel(const __grid_constant__ CUtensorMap tmap, const SyrkParams p) 
     const int we = warp - 4;                       // TMEM lane quarter this warp may access
     const int D = p.D;
     int it = 0;
-    for (int s = pair; s < p.n_tiles; s += n_pairs, ++it) {
+    const int kstep = p.kchunk > 0 ? p.kchunk : num_kb;
+    for (int s = pair; s < p.n_tiles; s += n_pairs)
+    for (int kc = 0; kc < num_kb; kc += kstep, ++it) {
       int a, nj; decode_tile(s, p.NT, a, nj);
       const int acc = it & 1;
       const uint32_t acc_phase = (it >> 1) & 1u;
@@ -364,6 +374,7 @@ int syrk_upper(float* H, const void* X, int D, int T, int fmt, int mode, int var
   p.H = H; p.D = D; p.T = T; p.mode = mode; p.fmt = fmt;
   p.NT = (D + 255) / 256;
   p.n_tiles = p.NT * (p.NT + 1) / 2;
+  p.kchunk = g_syrk_kchunk;
   int dev = 0, n_sms = 0;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev);

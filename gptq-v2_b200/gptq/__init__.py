@@ -15,7 +15,7 @@ from . import _cabi
 from ._cabi import GptqB200Error, check, lib, ptr, require_contig, require_cuda, stream_of
 
 __all__ = ['accumulate_hessian', 'gptq_quantize_range', 'hessian_syrk', 'hessian_invert', 'w4a16_dequant', 'pack_upper', 'unpack_upper', 'prep_weight_t', 'prep_weight_t2', 'solve_metrics', 'gptq_solve_ex', 'find_params', 'mse_refine', 'find_params_cols', 'mse_refine_cols', 'rtn_quantize',
-           'gptq_solve', 'gptq_solve_static', 'pack_int4', 'unpack_int4', 'transpose_pack_int4', 'w4a16_gemm', 'sgemm', 'gemm_tf32x3', 'set_tf32x3', 'set_solve_super', 'set_solve_fused', 'set_tf32_kchunk', 'set_w4a16_path',
+           'gptq_solve', 'gptq_solve_static', 'pack_int4', 'unpack_int4', 'transpose_pack_int4', 'w4a16_gemm', 'sgemm', 'gemm_tf32x3', 'set_tf32x3', 'set_solve_super', 'set_solve_fused', 'set_tf32_kchunk', 'set_syrk_kchunk', 'set_w4a16_path',
            'GptqB200Error']
 
 
@@ -409,6 +409,11 @@ def gemm_tf32x3(A, B, C_, M, N, K, lda, ldb, ldc, alpha, upper_only=0) -> None:
 def set_w4a16_path(path: int) -> int:
     """K6 dispatch hook (0 auto, 1 never the small-batch kernel, 2 the experimental weights-on-N tcgen05 kernel for batch <= 128); returns the old value."""
     return int(lib.gq_set_w4a16_path(int(path)))
+
+
+def set_syrk_kchunk(kblocks: int) -> int:
+    """K1: 64-token k-blocks accumulated in tensor memory per partial sum (0 = a whole call); returns the old value."""
+    return int(lib.gq_set_syrk_kchunk(int(kblocks)))
 
 
 def set_tf32_kchunk(kblocks: int) -> int:

@@ -51,6 +51,7 @@ SIGNATURES = {
     'gq_set_solve_super': (_i, [_i]),
     'gq_set_solve_fused': (_i, [_i]),
     'gq_set_tf32_kchunk': (_i, [_i]),
+    'gq_set_syrk_kchunk': (_i, [_i]),
     'gq_set_solve_debug': (_vp, [_vp]),
     'gq_set_w4a16_path': (_i, [_i]),
     'gq_sgemm': (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _f, _f, _i, _vp]),

@@ -177,6 +177,9 @@ int gq_set_tf32x3(int enable);
 /* Tuning hook: blocks per super-block of K4's two-level lazy-batch update (default 8; 1 = the reference's schedule, one
  * full trailing update per block, gptq_py.py:139).  Returns the previous setting. */
 int gq_set_solve_super(int blocks);
+/* Accuracy / speed hook of K1: token range (in 64-token k-blocks) accumulated in tensor memory before the partial sum is added
+ * to H in fp32 round-to-nearest (default 128 = 8192 tokens; 0 = the whole call, round 1's behaviour).  Returns the old value. */
+int gq_set_syrk_kchunk(int kblocks);
 /* Accuracy / speed hook of the 3xTF32 GEMM: the tensor core adds every MMA into its fp32 accumulator with truncation, so a
  * k range is accumulated in tensor memory in chunks of `kblocks` x 16 and each chunk's partial sum is added to C by a
  * round-to-nearest reduce-add (default 8 = 128-deep chunks; 0 = the whole range at once, round 1's behaviour).

@@ -101,9 +101,54 @@ def factor_sweep(D):
     print(json.dumps({'D': D, 'U_rel_fro_vs_fp64': res}))
 
 
+def syrk_sweep(D):
+    """K1 against the exact (float64) X^T X for several accumulation chunk lengths, beside torch's fp32 GEMM."""
+    import gptq
+    dev = torch.device('cuda:0')
+    torch.backends.cuda.matmul.allow_tf32 = False
+    g = torch.Generator(device=dev).manual_seed(D)
+    cs = torch.exp(torch.rand(D, device=dev, generator=g) * 3.0 - 1.5)
+    T = 16 * 2048
+    X = (torch.randn(T, D, device=dev, generator=g) * cs).half()
+    H64 = torch.zeros(D, D, dtype=torch.float64, device=dev)
+    for i in range(0, T, 4096):
+        xb = X[i:i + 4096].double()
+        H64.addmm_(xb.t(), xb)
+    del xb
+    up = torch.triu(torch.ones(D, D, dtype=torch.bool, device=dev))
+    n64 = float(H64[up].norm())
+    res = {}
+    Hf = torch.zeros(D, D, device=dev)
+    for i in range(0, T, 8192):
+        xb = X[i:i + 8192].float()
+        Hf.addmm_(xb.t(), xb)
+    del xb
+    res['torch_fp32_addmm'] = {'rel_fro': float((Hf.double() - H64)[up].norm()) / n64,
+                               'diag_mean_rel': float(((Hf.diagonal().double() - H64.diagonal()) / H64.diagonal()).mean())}
+    del Hf
+    for kch in (0, 256, 128, 64, 32):
+        gptq.set_syrk_kchunk(kch)
+        H = torch.zeros(D, D, device=dev)
+        gptq.hessian_syrk(H, X, mode=0)
+        torch.cuda.synchronize()
+        ts = []
+        for _ in range(3):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            Hs = torch.zeros(D, D, device=dev)
+            a.record(); gptq.hessian_syrk(Hs, X, mode=0); b.record(); torch.cuda.synchronize()
+            ts.append(a.elapsed_time(b))
+        res[f'K1 kchunk={kch}'] = {'rel_fro': float((H.double() - H64)[up].norm()) / n64,
+                                   'diag_mean_rel': float(((H.diagonal().double() - H64.diagonal()) / H64.diagonal()).mean()),
+                                   'ms': sorted(ts)[1], 'tflops_tri': T * D * (D + 1) / sorted(ts)[1] / 1e9}
+    gptq.set_syrk_kchunk(128)
+    print(json.dumps({'D': D, 'T': T, 'H_vs_fp64_upper': res}))
+
+
 def main():
     if len(sys.argv) > 2 and sys.argv[2] == 'factor':
         return factor_sweep(int(sys.argv[1]))
+    if len(sys.argv) > 2 and sys.argv[2] == 'syrk':
+        return syrk_sweep(int(sys.argv[1]))
     D = int(sys.argv[1]) if len(sys.argv) > 1 else 11008
     bits = int(sys.argv[2]) if len(sys.argv) > 2 else 4
     rows = int(sys.argv[3]) if len(sys.argv) > 3 else 256
