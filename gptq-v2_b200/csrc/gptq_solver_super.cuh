@@ -93,9 +93,10 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
   auto aempty = [&](int i) { return bar0 + 8u * (3 * STAGES + 2 + i); };
   auto accfull = [&](int r) { return bar0 + 8u * (3 * STAGES + 4 + r); };
   auto ubar = [&](int i) { return bar0 + 8u * (3 * STAGES + 7 + i); };
-  const uint32_t tmem_slot = bar0 + 8u * (3 * STAGES + 9);
+  const uint32_t ufree = bar0 + 8u * (3 * STAGES + 9);       // one arrival per block boundary: the previous block's U buffer is free
+  const uint32_t tmem_slot = bar0 + 8u * (3 * STAGES + 10);
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(
-      reinterpret_cast<uint8_t*>(qbase + NQ * Cfg::Q_FLOATS) + 8u * (3 * STAGES + 9));
+      reinterpret_cast<uint8_t*>(qbase + NQ * Cfg::Q_FLOATS) + 8u * (3 * STAGES + 10));
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int R = p.R;
@@ -105,7 +106,7 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
     for (int s = 0; s < STAGES; ++s) { mbar_init(bfull(s), 1); mbar_init(bready(s), SUP_SPLIT_THREADS); mbar_init(bempty(s), 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(aready(i), NQ); mbar_init(aempty(i), 1); }
     for (int r = 0; r < 3; ++r) mbar_init(accfull(r), 1);
-    mbar_init(ubar(0), 1); mbar_init(ubar(1), 1);
+    mbar_init(ubar(0), 1); mbar_init(ubar(1), 1); mbar_init(ufree, 1);
     fence_mbar_init();
     fence_proxy_async();
   }
@@ -116,19 +117,58 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
   const uint32_t tmem_base = *tmem_slot_ptr;
 
   if (warp == 16) {
-    // ------------------------------------------------------------ TMA producer: U[block rows, later columns]
-    if (lane == 0) {
+    // ------------------------------------------------------------ TMA producer: U[block rows, later columns] through the ring
+    // (lane 0) and the packed diagonal block of U of every block (all lanes, one row copy each: 128 bulk copies take the
+    // TMA unit ~7000 cycles, so they are issued here -- not by a warp the chain meets at a barrier -- in batches of 32
+    // rows between ring stages, one block ahead where the buffer is double)
+    {
+      auto upk_begin = [&](int t) {
+        if (lane == 0) mbar_expect_tx(ubar(t & 1), SUP_UPK_BYTES);
+        __syncwarp();
+      };
+      auto upk_rows = [&](int t, int r0) {                       // rows r0 .. r0 + 31 of block t's diagonal block
+        const int cb = p.c0 + SUP_NB * t;
+        float* Upk = Upk0 + (t % NUPK) * UPK_FLOATS<SUP_NB>;
+        const int jr = r0 + lane, sbj = jr / SB, cs = sbj * SB;  // first column kept for this row
+        bulk_load_1d(smem_u32(Upk + upk_base<SUP_NB>(sbj) + (jr - cs) * (SUP_NB - cs)),
+                     p.U + (size_t)(cb + jr) * p.C + cb + cs, (SUP_NB - cs) * 4, ubar(t & 1));
+      };
+      auto wait_free = [&](int bnd) {                            // boundary `bnd` passed: everyone is done with block bnd - 1
+        if (lane == 0) mbar_wait(ufree, bnd & 1u);
+        __syncwarp();
+      };
+      upk_begin(0);
+      for (int r0 = 0; r0 < SUP_NB; r0 += 32) upk_rows(0, r0);
       int stage = 0; uint32_t phase = 0;
       for (int b = 0; b + 1 < p.nblk; ++b) {
         const int nsub = 4 * (p.nblk - 1 - b);
         const int col = p.c0 + SUP_NB * (b + 1), row = p.c0 + SUP_NB * b;
-        for (int k8 = 0; k8 < SUP_NB / 8; ++k8) {
-          mbar_wait(bempty(stage), phase ^ 1u);
-          mbar_expect_tx(bfull(stage), nsub * SUP_SUBTILE);
-          const uint32_t dst = ring + stage * SUP_STAGE_BYTES;
-          for (int j = 0; j < nsub; ++j) tma_load_2d(dst + j * SUP_SUBTILE, &map_u, bfull(stage), col + 32 * j, row + 8 * k8);
-          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+        const int t = NUPK == 2 ? b + 1 : b;                     // the diagonal block fetched during this block's ring loop
+        if (NUPK == 1 && t >= 1) {                               // single buffer: needed at once
+          wait_free(t);
+          upk_begin(t);
+          for (int r0 = 0; r0 < SUP_NB; r0 += 32) upk_rows(t, r0);
         }
+        for (int k8 = 0; k8 < SUP_NB / 8; ++k8) {
+          if (lane == 0) {
+            mbar_wait(bempty(stage), phase ^ 1u);
+            mbar_expect_tx(bfull(stage), nsub * SUP_SUBTILE);
+            const uint32_t dst = ring + stage * SUP_STAGE_BYTES;
+            for (int j = 0; j < nsub; ++j) tma_load_2d(dst + j * SUP_SUBTILE, &map_u, bfull(stage), col + 32 * j, row + 8 * k8);
+          }
+          __syncwarp();
+          if (++stage == STAGES) { stage = 0; phase ^= 1u; }
+          if (NUPK == 2 && k8 >= 3 && k8 <= 9 && (k8 & 1)) {     // after k-slices 3, 5, 7, 9: 32 rows each
+            if (k8 == 3) { wait_free(b); upk_begin(t); }
+            upk_rows(t, 16 * (k8 - 3));
+          }
+        }
+      }
+      if (NUPK == 1 && p.nblk >= 2) {                            // the last block has no ring loop of its own
+        const int t = p.nblk - 1;
+        wait_free(t);
+        upk_begin(t);
+        for (int r0 = 0; r0 < SUP_NB; r0 += 32) upk_rows(t, r0);
       }
     }
   } else if (warp == 17 || warp == 18) {
@@ -263,17 +303,6 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
     int di = 0;
     auto stamp = [&]() { if (dbg && di < 256) dbg[di++] = clock64(); };
 
-    auto load_upk = [&](int b) {                                 // one warp: the packed diagonal block of block b
-      const int cb = p.c0 + SUP_NB * b;
-      float* Upk = Upk0 + (b % NUPK) * UPK_FLOATS<SUP_NB>;
-      if (lane == 0) mbar_expect_tx(ubar(b & 1), SUP_UPK_BYTES);
-      __syncwarp();
-      for (int j = lane; j < SUP_NB; j += 32) {
-        const int sbj = j / SB, cs = sbj * SB;                   // first column kept for this row
-        bulk_load_1d(smem_u32(Upk + upk_base<SUP_NB>(sbj) + (j - cs) * (SUP_NB - cs)),
-                     p.U + (size_t)(cb + j) * p.C + cb + cs, (SUP_NB - cs) * 4, ubar(b & 1));
-      }
-    };
     // reciprocals of diag(U) of block b by threads 128..255: the load is issued at one point and consumed sub-blocks
     // later (a strided global load per thread; its latency must not sit in front of a barrier the chain waits behind)
     float rdg_u = 1.f;
@@ -296,7 +325,6 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
       for (int i = 0; i < 48; ++i) wv[i] = (act && i < part_w) ? p.Wt[(size_t)(cb + part_c0 + i) * R + r] : 0.f;
     };
 
-    if (warp == SUP_COMPUTE_WARPS - 1) load_upk(0);
     issue_rdg(0);
     finish_rdg(0);
 
@@ -309,7 +337,7 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
       stamp();
       named_bar_sync(1, SUP_COMPUTE_THREADS);
       stamp();
-      if (NUPK == 1 && b > 0 && warp == SUP_COMPUTE_WARPS - 1) load_upk(b);
+      if (threadIdx.x == 0) mbar_arrive(ufree);                 // the producer may overwrite the previous block's U buffer
       if (is_stager) {
         // W_global - (updates of the super-block's earlier blocks, accumulated in tensor memory); the global loads are in
         // flight while the last MMAs of the previous block finish
@@ -343,7 +371,6 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
       named_bar_sync(1, SUP_COMPUTE_THREADS);                    // the block's weights and min / max partials are in place
       // the NEXT block's diagonal block of U and reciprocals start travelling now
       if (b + 1 < p.nblk) {
-        if (NUPK == 2 && warp == SUP_COMPUTE_WARPS - 1) load_upk(b + 1);
         issue_rdg(b + 1);
       }
       const float maxq = b == 0 ? p.maxq[0] : b == 1 ? p.maxq[1] : b == 2 ? p.maxq[2] : p.maxq[3];   // no dynamic indexing of the parameter space
