@@ -74,7 +74,10 @@ def bench_invert():
 
 
 def bench_solve():
-    for R, C in ((4096, 4096), (11008, 4096), (4096, 11008)):
+    shapes = ((4096, 4096), (11008, 4096), (4096, 11008))
+    if os.environ.get('GQ_SHAPES'):
+        shapes = tuple(tuple(int(v) for v in sh.split('x')) for sh in os.environ['GQ_SHAPES'].split(','))
+    for R, C in shapes:
         X = torch.randn(2 * C, C, device=dev) * torch.exp(torch.rand(C, device=dev) * 3 - 1.5)
         H = X.t() @ X
         _, U, _ = gptq.hessian_invert(H, None, 1.0, 0.01 * float(H.diagonal().mean()), want_hp=False)
@@ -89,7 +92,7 @@ def bench_solve():
             old = gptq.set_solve_super(sup)
             t = timeit(run, iters=3, warm=1)
             gptq.set_solve_super(old)
-            print(json.dumps({'k': 'solve', 'R': R, 'C': C, 'super': sup, 'ms': (t - tc) * 1e3,
+            print(json.dumps({'k': 'solve', 'R': R, 'C': C, 'super': sup, 'fused': os.environ.get('GQ_SOLVE_FUSED', '1'), 'ms': (t - tc) * 1e3,
                               'trailing_tflops': R * C * C / (t - tc) / 1e12, 'us_per_block': (t - tc) / (C / 128) * 1e6}))
         del X, H, U, W, Wt0
 
