@@ -48,7 +48,7 @@ LINEARS = [('v', HIDDEN, HIDDEN, 0), ('k', HIDDEN, HIDDEN, 0), ('q', HIDDEN, HID
            ('up', INTER, HIDDEN, 2), ('gate', INTER, HIDDEN, 2), ('down', HIDDEN, INTER, 3)]
 GROUP_D = [HIDDEN, HIDDEN, HIDDEN, INTER]
 # relative squared error of each linear of the synthetic layer at N = 1 (see gpu_main); filled from profiles/r02_bench_*.json
-EXPECTED_REL = {}
+EXPECTED_REL = {'v': 0.011144, 'k': 0.011146, 'q': 0.011153, 'o': 0.011151, 'up': 0.011150, 'gate': 0.011146, 'down': 0.012897}
 WORKLOAD = ('llama2-7b decoder layer: 4 Hessians (D=4096 x3, 11008) over 128x2048 tokens + invert + '
             'GPTQ 4-bit g128 act-order solve of 7 linears + int4 pack')
 
@@ -457,12 +457,12 @@ def gpu_main(args):
     # error of a g128 4-bit grid on these weights is ~1e-2; garbage from a broken kernel is >= 1)
     # EXPECTED_REL: relative squared error l2.0_error / l2.0_norm of every linear of this synthetic layer, measured at N = 1
     # with results that match the oracle code for code (tools/multi_gpu_parity.py, tests/test_gpu_config_shapes.py).  The
-    # sequences differ between rank counts (every rank draws its own), so the bound is the N = 1 value + 2 %.
+    # sequences differ between rank counts (every rank draws its own), so the bound is the N = 1 value + 2 % (+ 5 % for N > 1).
     rel_by_linear = {}
     for name, (_, met) in out.items():
         rel = met['l2.0_error'] / max(met['l2.0_norm'], 1e-30)
         rel_by_linear[name] = rel
-        bound = EXPECTED_REL.get(name, 0.1) * 1.02
+        bound = EXPECTED_REL.get(name, 0.1) * (1.02 if ctx.world == 1 else 1.05)
         if not (rel == rel and rel < bound and met['gptq_error'] == met['gptq_error']):
             raise RuntimeError(f'bench: {name} came out wrong (relative squared error {rel} > {bound}, metrics {met})')
     clocks = sampler.stop() if ctx.rank == 0 else None

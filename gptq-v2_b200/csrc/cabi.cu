@@ -141,6 +141,9 @@ int gq_w4a16_dequant(const uint32_t* qweight, const void* scale_t, const uint8_t
                      int dtype, void* stream) {
   return w4a16_dequant(qweight, scale_t, qzero_t, dense, N, K, group, dtype, S(stream));
 }
+int gq_gemm_f16_nt(const void* x, const void* w, void* y, int M, int N, int K, int dtype, void* stream) {
+  return gemm_f16_nt(x, w, y, M, N, K, dtype, S(stream));
+}
 size_t gq_w4a16_workspace_bytes(int M, int N, int K) { return w4a16_workspace_bytes(M, N, K); }
 int gq_w4a16_gemm(const void* x, const uint32_t* qweight, const void* scale_t, const uint8_t* qzero_t,
                   const int32_t* perm, void* y, void* workspace, int M, int N, int K, int group, int dtype,

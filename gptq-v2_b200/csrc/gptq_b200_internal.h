@@ -115,6 +115,7 @@ int mse_refine(const float* Wt, int R, int group, int n_groups, const float* max
 int pack_int4(const uint8_t* codes, uint32_t* packed, int R, int C, cudaStream_t st);
 int unpack_int4(const uint32_t* packed, uint8_t* codes, int R, int C, cudaStream_t st);
 int transpose_pack_int4(const uint8_t* codes_t, uint8_t* codes, uint32_t* packed, int R, int C, cudaStream_t st);
+int gemm_f16_nt(const void* x, const void* w, void* y, int M, int N, int K, int fmt, cudaStream_t st);
 int w4a16_dequant(const uint32_t* qw, const void* scale_t, const uint8_t* qzero_t, void* out, int N, int K, int group, int fmt,
                   cudaStream_t st);
 size_t w4a16_workspace_bytes(int M, int N, int K);

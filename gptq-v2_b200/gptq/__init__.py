@@ -15,7 +15,7 @@ from . import _cabi
 from ._cabi import GptqB200Error, check, lib, ptr, require_contig, require_cuda, stream_of
 
 __all__ = ['accumulate_hessian', 'gptq_quantize_range', 'hessian_syrk', 'hessian_invert', 'w4a16_dequant', 'pack_upper', 'unpack_upper', 'prep_weight_t', 'prep_weight_t2', 'solve_metrics', 'gptq_solve_ex', 'find_params', 'mse_refine', 'find_params_cols', 'mse_refine_cols', 'rtn_quantize',
-           'gptq_solve', 'gptq_solve_static', 'pack_int4', 'unpack_int4', 'transpose_pack_int4', 'w4a16_gemm', 'sgemm', 'gemm_tf32x3', 'set_tf32x3', 'set_solve_super', 'set_solve_fused', 'set_tf32_kchunk', 'set_syrk_kchunk', 'set_w4a16_path',
+           'gptq_solve', 'gptq_solve_static', 'pack_int4', 'unpack_int4', 'transpose_pack_int4', 'w4a16_gemm', 'gemm_f16_nt', 'sgemm', 'gemm_tf32x3', 'set_tf32x3', 'set_solve_super', 'set_solve_fused', 'set_tf32_kchunk', 'set_syrk_kchunk', 'set_w4a16_path',
            'GptqB200Error']
 
 
@@ -388,6 +388,21 @@ def w4a16_dequant(qweight: torch.Tensor, scale_t: torch.Tensor, qzero_t: torch.T
         check(lib.gq_w4a16_dequant(ptr(qweight), ptr(scale_t), ptr(qzero_t), ptr(dense), N, K, int(group),
                                    _cabi.DTYPE_CODE[scale_t.dtype], stream_of(qweight)), 'gq_w4a16_dequant')
     return dense
+
+
+def gemm_f16_nt(x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
+    """y (M, N) = x (M, K) @ w (N, K)^T in x.dtype (fp16 / bf16), fp32 accumulation on tcgen05 CTA pairs: the dense GEMM of
+    K6's large-batch route (the reference's nn.Linear on the reconstructed weights, llama.py:172-177)."""
+    dev = require_cuda(x, w)
+    require_contig(x=x, w=w)
+    if x.dim() != 2 or w.dim() != 2 or x.shape[1] != w.shape[1] or x.dtype != w.dtype or x.dtype not in (torch.float16, torch.bfloat16):
+        raise GptqB200Error(f'gemm_f16_nt: x {tuple(x.shape)} {x.dtype} / w {tuple(w.shape)} {w.dtype}')
+    M, K = x.shape
+    N = w.shape[0]
+    y = torch.empty(M, N, dtype=x.dtype, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.gq_gemm_f16_nt(ptr(x), ptr(w), ptr(y), M, N, K, _cabi.DTYPE_CODE[x.dtype], stream_of(x)), 'gq_gemm_f16_nt')
+    return y
 
 
 def sgemm(A, B, C_, M, N, K, lda, ldb, ldc, alpha, beta, flags) -> None:

@@ -44,6 +44,7 @@ SIGNATURES = {
     'gq_unpack_int4': (_i, [_vp, _vp, _i, _i, _vp]),
     'gq_transpose_pack_int4': (_i, [_vp, _vp, _vp, _i, _i, _vp]),
     'gq_w4a16_dequant': (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
+    'gq_gemm_f16_nt': (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     'gq_w4a16_workspace_bytes': (C.c_size_t, [_i, _i, _i]),
     'gq_w4a16_gemm': (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     'gq_gemm_tf32x3': (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _f, _i, _vp]),

@@ -27,6 +27,7 @@ def build(verbose: bool = False) -> str:
     built = os.path.join(bdir, 'gptq_c.so')
     try:
         cpp_extension.load(name='gptq_c', sources=[src], build_directory=bdir, verbose=verbose, is_python_module=False, with_cuda=True,
+                           extra_cflags=['-fvisibility=hidden'],
                            extra_ldflags=[f'-L{LIB}', '-lgptq_b200', "-Wl,-rpath,'$$ORIGIN'"])
     except OSError:
         # torch loads the fresh library from the build directory, where libgptq_b200.so is not beside it ($ORIGIN) and, in

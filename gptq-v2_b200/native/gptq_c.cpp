@@ -33,8 +33,9 @@ void accumulate(torch::Tensor& H, const torch::Tensor& X, int dtype, c10::Scalar
            "accumulate_hessian");
 }
 
-}  // namespace
-
+// Internal linkage on purpose: the reference's own extension defines global functions with these very names; if both
+// libraries are loaded into one process (the tests do that) the dynamic linker would otherwise bind this module's calls to
+// whichever definition was loaded first.
 void accumulate_hessian_fp16_fp32(torch::Tensor& H, const torch::Tensor& X) { accumulate(H, X, GQ_DTYPE_F16, torch::kFloat16); }
 void accumulate_hessian_bf16_fp32(torch::Tensor& H, const torch::Tensor& X) { accumulate(H, X, GQ_DTYPE_BF16, torch::kBFloat16); }
 
@@ -59,6 +60,8 @@ void quantize_range(torch::Tensor quant, torch::Tensor scale, torch::Tensor out_
                              error.data_ptr<float>(), C, R, a, b, stream),
            "gptq_quantize_range");
 }
+
+}  // namespace
 
 PYBIND11_MODULE(gptq_c, m) {
   m.def("accumulate_hessian_fp16_fp32", &accumulate_hessian_fp16_fp32, "H += X.t() @ X (FP16 x FP16 = FP32 matmul)");

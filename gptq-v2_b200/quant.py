@@ -200,8 +200,9 @@ class W4A16Linear(nn.Module):
     """y = x W_hat^T from packed int4 codes.  Batches below `dense_rows(N, K)` rows run K6 (dequantisation fused into the
     GEMM, no dense copy of W_hat exists).  Larger batches are compute-bound and K6 would dequantise the weights again
     for every 256 batch columns: there the packed weights are dequantised ONCE into a transient 16-bit matrix
-    (gq_w4a16_dequant, the reference's construct_matrix rounding) and multiplied by a dense GEMM -- what the reference
-    does for every batch size (quant.py:262-279 + nn.Linear), but from 4x fewer resident bytes.  Crossovers measured on
+    (gq_w4a16_dequant, the reference's construct_matrix rounding) and multiplied by this build's dense tcgen05 GEMM
+    (gq_gemm_f16_nt) -- what the reference does for every batch size with cuBLAS (quant.py:262-279 + nn.Linear), but from
+    4x fewer resident bytes and without a library call.  Crossovers measured on
     B200 (profiles/r01_v29_w4a16_sweep.jsonl): 128 rows for N*K <= 2^26 (all Llama-2-7B shapes), 512 rows above."""
     dense_route = True
 
@@ -230,7 +231,7 @@ class W4A16Linear(nn.Module):
         if self.dense_route and x2.shape[0] >= self.dense_rows(self.out_features, self.in_features):
             dense = _ops.w4a16_dequant(self.qweight_packed, scale_t, self.qzero_t, self.group_size)   # transient
             xp = x2.index_select(1, self.perm) if self.perm is not None else x2
-            y = xp @ dense.t()
+            y = _ops.gemm_f16_nt(xp.contiguous(), dense)                                              # own tcgen05 GEMM, no library call
         else:
             y = _ops.w4a16_gemm(x2, self.qweight_packed, scale_t, self.qzero_t, self.perm, self.group_size)
         return y.view(*lead, self.out_features)

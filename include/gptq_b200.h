@@ -146,6 +146,11 @@ int gq_transpose_pack_int4(const uint8_t* codes_t, uint8_t* codes, uint32_t* pac
  * aligned; K % 8 == 0, group % 8 == 0, K % group == 0. */
 int gq_w4a16_dequant(const uint32_t* qweight, const void* scale_t, const uint8_t* qzero_t, void* dense, int N, int K, int group,
                      int dtype, void* stream);
+/* Dense 16-bit GEMM  y (M, N) = x (M, K) * w (N, K)^T  (fp32 accumulation, tcgen05 CTA pairs): the GEMM of the large-batch
+ * route of K6 (gq_w4a16_dequant once, then this) -- the reference's nn.Linear forward on the reconstructed weights
+ * (quant.py:262-279, llama.py:172-177) without a library GEMM.  x, w, y row-major contiguous of the same GQ_DTYPE_F16 / BF16,
+ * 16-byte aligned; K % 8 == 0, N % 2 == 0. */
+int gq_gemm_f16_nt(const void* x, const void* w, void* y, int M, int N, int K, int dtype, void* stream);
 /* ---- K6: y (M, N) = x[:, perm] (M, K) * dequant(qweight)^T, replacing reconstruct_nn_linear +
  * nn.Linear (quant.py:262-279, llama.py:172-177).  x, y, scale_t share `dtype` (f16/bf16).  scale_t and
  * qzero_t are GROUP-MAJOR: (K/group, N) 16-bit and (K/group, N) uint8 (the transposes of quant_meta's scale /

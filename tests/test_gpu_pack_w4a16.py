@@ -228,3 +228,46 @@ def test_w4a16_linear_large_batch_route(M):
     for y in (y_dense_route, y_fused):
         assert ((y - want).norm() / want.norm()).item() <= 1e-2
     assert ((y_dense_route - want).norm() / want.norm()).item() <= 2e-3     # same 16-bit weights, fp32 accumulation
+
+
+@pytest.mark.parametrize('dtype', [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize('M,N,K', [(1, 256, 64), (128, 256, 128), (300, 520, 200), (257, 1000, 4096), (2048, 4096, 4096),
+                                   (513, 11008, 4096), (96, 4096, 11008)])
+def test_dense_gemm_nt_vs_fp32_reference(M, N, K, dtype):
+    """gq_gemm_f16_nt (the GEMM of K6's large-batch route): y = x w^T against a float32 matmul of the same 16-bit operands;
+    ragged M / N / K edges (TMA zero fill, partial stores) included.  Tolerance: one 16-bit rounding of y plus fp32
+    accumulation-order noise."""
+    import gptq
+    g = torch.Generator(device='cuda').manual_seed(M + N + K)
+    x = torch.randn(M, K, device='cuda', generator=g).to(dtype)
+    w = (torch.randn(N, K, device='cuda', generator=g) * 0.05).to(dtype)
+    y = gptq.gemm_f16_nt(x, w)
+    want = x.float() @ w.float().t()
+    assert y.shape == (M, N) and y.dtype == dtype
+    eps = 2.0 ** -10 if dtype == torch.float16 else 2.0 ** -7
+    err = (y.float() - want).abs()
+    bound = eps * want.abs() + 1e-4 * (x.float().abs() @ w.float().abs().t())
+    assert bool((err <= bound).all()), float((err / bound.clamp_min(1e-30)).max())
+
+
+def test_w4a16_linear_large_batch_route_uses_own_gemm():
+    """W4A16Linear above its dense_rows threshold: one dequantisation + gq_gemm_f16_nt, no torch.matmul; result within 1e-2 of
+    the reference's dense forward (a8)."""
+    import gptq
+    from quant import W4A16Linear, pack_quant_meta, reconstruct_nn_linear
+    R, C = 512, 1024
+    g = torch.Generator().manual_seed(4)
+    meta = {'qweight': torch.randint(0, 16, (R, C), generator=g, dtype=torch.uint8),
+            'scale': (torch.rand(R, C // 128, generator=g) * 0.01 + 1e-3).half(),
+            'qzero': torch.randint(0, 16, (R, C // 128), generator=g, dtype=torch.uint8),
+            'qscale': None, 'sscale': None, 'perm_inv': torch.randperm(C, generator=g).to(torch.int16),
+            'group_sizes': torch.full((C // 128,), 128, dtype=torch.int16),
+            'group_bit_widths': torch.full((C // 128,), 4, dtype=torch.uint8), 'scale_bit_width': None}
+    lin = W4A16Linear(pack_quant_meta(meta, torch.device('cuda')))
+    ref = reconstruct_nn_linear(meta, torch.float16, torch.device('cuda'))
+    x = torch.randn(2, 700, C, device='cuda', dtype=torch.float16)
+    n0 = gptq.lib.gq_launch_count()
+    y = lin(x)
+    assert gptq.lib.gq_launch_count() - n0 >= 2                  # dequant + GEMM are this library's launches
+    want = ref(x)
+    assert float((y.float() - want.float()).norm() / want.float().norm()) <= 1e-2

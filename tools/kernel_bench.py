@@ -221,6 +221,19 @@ def bench_w4a16():
         del qs, dense
 
 
+def bench_gemmnt():
+    """gq_gemm_f16_nt (the dense GEMM of K6's large-batch route) beside torch.matmul (cuBLAS) on the same operands."""
+    for N, K in ((4096, 4096), (11008, 4096), (4096, 11008), (8192, 8192), (28672, 8192), (8192, 28672)):
+        w = (torch.randn(N, K, device=dev) * 0.02).half()
+        for M in (128, 256, 512, 1024, 2048, 4096):
+            x = torch.randn(M, K, device=dev).half()
+            t = timeit(lambda: gptq.gemm_f16_nt(x, w), iters=7, warm=2)
+            tb = timeit(lambda: torch.matmul(x, w.t()), iters=7, warm=2)
+            print(json.dumps({'k': 'gemm_f16_nt', 'M': M, 'N': N, 'K': K, 'us': t * 1e6, 'tflops': 2.0 * M * N * K / t / 1e12,
+                              'frac_bf16_peak': 2.0 * M * N * K / t / PEAK_BF16, 'cublas_us': tb * 1e6, 'vs_cublas': tb / t}))
+        del w
+
+
 def bench_refext():
     """The reference's own CUDA extension (oracle/_ref/gptq_c.so, built from /root/reference/package/gptq) on this
     B200, beside ours: a2 CUTLASS Hessian GEMM and a6 gptq_quantize_range over a whole 4096x4096 linear."""
