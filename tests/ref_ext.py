@@ -15,7 +15,9 @@ def load():
     if not os.path.exists(SO):
         return None
     import torch  # noqa: F401  (libtorch must be loaded before the extension)
-    spec = importlib.util.spec_from_file_location('gptq_c', SO)
+    # spec name 'reference_ext.gptq_c': the init symbol is still PyInit_gptq_c, but pybind11 (3.x) caches module objects per
+    # interpreter by spec NAME, so under the plain name this module and the repository's own lib/gptq_c.so would alias
+    spec = importlib.util.spec_from_file_location('reference_ext.gptq_c', SO)
     mod = importlib.util.module_from_spec(spec)
     spec.loader.exec_module(mod)
     _mod = mod
