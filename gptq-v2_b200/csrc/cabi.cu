@@ -25,6 +25,7 @@ const char* gq_error_string(int code) {
     case GQ_ERR_TENSORMAP: return "cuTensorMapEncodeTiled rejected the tensor map";
     case GQ_ERR_NOT_SPD: return "matrix is not positive definite";
     case GQ_ERR_ARG: return "invalid argument";
+    case GQ_ERR_LIMIT: return "size exceeds the fixed scratch of this allocation-free entry point (see gptq_b200.h)";
     default: return "unknown error";
   }
 }

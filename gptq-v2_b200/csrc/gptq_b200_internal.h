@@ -13,6 +13,7 @@
 #define GQ_ERR_TENSORMAP 6   // cuTensorMapEncodeTiled rejected the descriptor
 #define GQ_ERR_NOT_SPD 7     // Cholesky met a non-positive pivot (caller adds damping and retries)
 #define GQ_ERR_ARG 8
+#define GQ_ERR_LIMIT 9       // size beyond the fixed scratch of an allocation-free entry point
 
 #include <atomic>
 

@@ -18,6 +18,7 @@
 //   * fp16 HFMA2 over 32 codes, then fp32 accumulation with the group scale.
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
+#include "../../include/gptq_b200.h"
 #include "gptq_b200_internal.h"
 
 namespace gq {
@@ -238,4 +239,51 @@ int w4a16_gemv(const void* x, const uint32_t* qw, const void* scale, const uint8
   return GQ_ERR_DTYPE;
 }
 
+// ---- allocation-free batch 1-2 variant (gq_w4a16_gemv_static, see include/gptq_b200.h) --------------------------------
+// The only scratch of this path is the shuffled copy of the activations (M * K 16-bit values).  Here it lives in a
+// file-scope device array, so a caller that may not allocate (stream capture, a serving loop, a harness that forbids
+// cudaMalloc) passes inputs and outputs only.  Every GPU that loads the library holds these 64 KB until exit.
+// w4a16_xprep_kernel rewrites all M * K values the GEMV reads on every call, so nothing has to be cleared between calls;
+// all calls share the array, so calls that overlap on one GPU (two streams, two threads) race on it.
+constexpr int GEMV_STATIC_MAX_M = 2;
+constexpr int GEMV_STATIC_MAX_K = 16384;
+static __device__ __align__(256) unsigned char g_gemv_static_scratch[GEMV_STATIC_MAX_M * GEMV_STATIC_MAX_K * 2];
+
+namespace {
+// The array's name is a host-side stand-in in host code: its device address is looked up once per device, with that
+// device current, and cached.
+std::atomic<void*> g_gemv_static_ptr[GQ_MAX_DEVICES];
+
+int gemv_static_scratch(void** out) {
+  int dev = -1;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= GQ_MAX_DEVICES) return GQ_ERR_CUDA;
+  void* ptr = g_gemv_static_ptr[dev].load(std::memory_order_acquire);
+  if (!ptr) {
+    if (cudaGetSymbolAddress(&ptr, g_gemv_static_scratch) != cudaSuccess || !ptr) return GQ_ERR_CUDA;
+    g_gemv_static_ptr[dev].store(ptr, std::memory_order_release);
+  }
+  *out = ptr;
+  return GQ_OK;
+}
+}  // namespace
+
+int w4a16_gemv_static(const void* x, const uint32_t* qw, const void* scale, const uint8_t* qzero, const int32_t* perm,
+                      void* y, int M, int N, int K, int group, int fmt, cudaStream_t st) {
+  if (M < 0 || N < 0 || K <= 0) return GQ_ERR_ARG;
+  if (M > GEMV_STATIC_MAX_M || K > GEMV_STATIC_MAX_K) return GQ_ERR_LIMIT;
+  if (M == 0 || N == 0) return GQ_OK;
+  if (!x || !qw || !scale || !qzero || !y) return GQ_ERR_ARG;
+  void* scratch = nullptr;
+  const int rc = gemv_static_scratch(&scratch);
+  if (rc != GQ_OK) return rc;
+  return w4a16_gemv(x, qw, scale, qzero, perm, y, scratch, M, N, K, group, fmt, st);
+}
+
 }  // namespace gq
+
+extern "C" int gq_w4a16_gemv_static(const void* x, const uint32_t* qweight, const void* scale_t, const uint8_t* qzero_t,
+                                    const int32_t* perm, void* y, int M, int N, int K, int group, int dtype,
+                                    void* stream) {
+  return gq::w4a16_gemv_static(x, qweight, scale_t, qzero_t, perm, y, M, N, K, group, dtype,
+                               reinterpret_cast<cudaStream_t>(stream));
+}

@@ -15,7 +15,7 @@ from . import _cabi
 from ._cabi import GptqB200Error, check, lib, ptr, require_contig, require_cuda, stream_of
 
 __all__ = ['accumulate_hessian', 'gptq_quantize_range', 'hessian_syrk', 'hessian_invert', 'w4a16_dequant', 'pack_upper', 'unpack_upper', 'prep_weight_t', 'prep_weight_t2', 'solve_metrics', 'gptq_solve_ex', 'find_params', 'mse_refine', 'find_params_cols', 'mse_refine_cols', 'rtn_quantize',
-           'gptq_solve', 'gptq_solve_static', 'pack_int4', 'unpack_int4', 'transpose_pack_int4', 'w4a16_gemm', 'gemm_f16_nt', 'sgemm', 'gemm_tf32x3', 'set_tf32x3', 'set_solve_super', 'set_solve_fused', 'set_tf32_kchunk', 'set_syrk_kchunk', 'set_w4a16_path',
+           'gptq_solve', 'gptq_solve_static', 'pack_int4', 'unpack_int4', 'transpose_pack_int4', 'w4a16_gemm', 'w4a16_gemv_static', 'gemm_f16_nt', 'sgemm', 'gemm_tf32x3', 'set_tf32x3', 'set_solve_super', 'set_solve_fused', 'set_tf32_kchunk', 'set_syrk_kchunk', 'set_w4a16_path',
            'GptqB200Error']
 
 
@@ -372,6 +372,26 @@ def w4a16_gemm(x: torch.Tensor, qweight: torch.Tensor, scale_t: torch.Tensor, qz
         check(lib.gq_w4a16_gemm(ptr(x), ptr(qweight), ptr(scale_t), ptr(qzero_t), ptr(perm), ptr(y), ptr(work), M, N, K,
                                 int(group), _cabi.DTYPE_CODE[x.dtype], stream_of(x)), 'gq_w4a16_gemm')
     return y
+
+
+def w4a16_gemv_static(x: torch.Tensor, qweight: torch.Tensor, scale_t: torch.Tensor, qzero_t: torch.Tensor, perm,
+                      out: torch.Tensor, group: int = 128) -> torch.Tensor:
+    """Allocation-free batch 1-2 variant of w4a16_gemm (gq_w4a16_gemv_static): the caller passes `out` (M, N); the scratch
+    is a fixed 64 KB device array inside the library (M <= 2, K <= 16384; calls that overlap on one GPU race on it)."""
+    dev = require_cuda(x, qweight, scale_t, qzero_t, perm, out)
+    require_contig(x=x, qweight=qweight, scale_t=scale_t, qzero_t=qzero_t, perm=perm, out=out)
+    M, K = x.shape
+    N = qweight.shape[0]
+    G = K // int(group)
+    if (qweight.shape[1] * 8 != K or scale_t.dtype != x.dtype or qzero_t.dtype != torch.uint8 or out.dtype != x.dtype
+            or tuple(scale_t.shape) != (G, N) or tuple(qzero_t.shape) != (G, N) or tuple(out.shape) != (M, N)):
+        raise GptqB200Error('w4a16_gemv_static: inconsistent operands (scale_t / qzero_t (K/group, N), out (M, N))')
+    if perm is not None and perm.dtype != torch.int32:
+        raise GptqB200Error('perm must be int32')
+    with torch.cuda.device(dev):
+        check(lib.gq_w4a16_gemv_static(ptr(x), ptr(qweight), ptr(scale_t), ptr(qzero_t), ptr(perm), ptr(out), M, N, K,
+                                       int(group), _cabi.DTYPE_CODE[x.dtype], stream_of(x)), 'gq_w4a16_gemv_static')
+    return out
 
 
 def w4a16_dequant(qweight: torch.Tensor, scale_t: torch.Tensor, qzero_t: torch.Tensor, group: int = 128) -> torch.Tensor:

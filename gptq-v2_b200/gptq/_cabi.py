@@ -47,6 +47,7 @@ SIGNATURES = {
     'gq_gemm_f16_nt': (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     'gq_w4a16_workspace_bytes': (C.c_size_t, [_i, _i, _i]),
     'gq_w4a16_gemm': (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
+    'gq_w4a16_gemv_static': (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),
     'gq_gemm_tf32x3': (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _f, _i, _vp]),
     'gq_set_tf32x3': (_i, [_i]),
     'gq_set_solve_super': (_i, [_i]),

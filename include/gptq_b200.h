@@ -161,6 +161,17 @@ size_t gq_w4a16_workspace_bytes(int M, int N, int K);
 int gq_w4a16_gemm(const void* x, const uint32_t* qweight, const void* scale_t, const uint8_t* qzero_t,
                   const int32_t* perm, void* y, void* workspace, int M, int N, int K, int group, int dtype,
                   void* stream);
+/* Allocation-free batch 1-2 variant of gq_w4a16_gemm.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same arguments, layouts and result as gq_w4a16_gemm's CUDA-core route (w4a16_gemv.cu) minus `workspace`:
+ * the shuffled copy of the activations lives in a file-scope device array of 64 KB that every GPU loading the library
+ * holds until exit.  Limits: M <= 2 and K <= 16384 (GQ_ERR_LIMIT beyond them, before anything is launched); K % group == 0,
+ * group % 32 == 0.  The call allocates nothing (no cudaMalloc / cudaFree, no allocating library routine); the array's
+ * device address is resolved once per device with cudaGetSymbolAddress.  All calls share the array and it is rewritten in
+ * full on every call (nothing has to start at zero), so calls that overlap on one GPU (different streams or threads)
+ * race on it: serialise them on one stream. */
+int gq_w4a16_gemv_static(const void* x, const uint32_t* qweight, const void* scale_t, const uint8_t* qzero_t,
+                         const int32_t* perm, void* y, int M, int N, int K, int group, int dtype, void* stream);
 
 /* ---- building block exposed for tests: C = beta*C + alpha*op(A)*B in true fp32.
  * flags: 1 = A stored (K x M); 2 = only upper tiles of C; 4 = A upper-triangular; 8 = B upper-triangular */
