@@ -6,7 +6,7 @@ using namespace gq;
 
 static inline cudaStream_t S(void* s) { return reinterpret_cast<cudaStream_t>(s); }
 
-namespace gq { unsigned long long g_launch_count = 0; int g_use_tf32x3 = 3; int g_solve_super = 8; int g_solve_fused = 1; int g_tf32_kchunk = 8; int g_syrk_kchunk = 128; long long* g_solve_dbg = nullptr; int g_w4a16_path = 0; }
+namespace gq { unsigned long long g_launch_count = 0; int g_use_tf32x3 = 3; int g_solve_super = 8; int g_solve_fused = 1; int g_tf32_kchunk = 8; int g_syrk_kchunk = 128; long long* g_solve_dbg = nullptr; int g_w4a16_path = 0; int g_pdl = 1; }
 
 extern "C" {
 
@@ -50,16 +50,27 @@ size_t gq_invert_workspace_floats(int D) {
   return 2 * d * d + d * d / 2 + 32 * d + 64;     // A (reversed matrix / factor / V), W = V^T, T^T blocks
 }
 
-int gq_hessian_invert(const float* H, int D, const int64_t* perm, float scale, float damp, float* Hp, float* U,
-                      float* work, int* info_dev, void* stream) {
+static int hessian_invert_impl(const float* H, int D, const int64_t* perm, float scale, float damp, const float* damp_dev,
+                               float damp_mult, float* Hp, float* U, float* work, int* info_dev, void* stream) {
   if (D <= 0) return GQ_ERR_ARG;
   if (D % 4 != 0) return GQ_ERR_SHAPE;
   float* A = work;
   float* Wb = work + (size_t)D * D;
   float* tmp = work + 2 * (size_t)D * D;
-  int rc = hessian_gather(H, D, perm, scale, damp, Hp, A, S(stream));
+  int rc = hessian_gather(H, D, perm, scale, damp, damp_dev, damp_mult, Hp, A, Wb, S(stream));   // Wb doubles as the symmetric copy
   if (rc != GQ_OK) return rc;
   return chol_inverse_upper(A, D, U, Wb, tmp, info_dev, S(stream));
+}
+
+int gq_hessian_invert(const float* H, int D, const int64_t* perm, float scale, float damp, float* Hp, float* U,
+                      float* work, int* info_dev, void* stream) {
+  return hessian_invert_impl(H, D, perm, scale, damp, nullptr, 0.f, Hp, U, work, info_dev, stream);
+}
+
+int gq_hessian_invert_dev(const float* H, int D, const int64_t* perm, float scale, const float* damp_dev, float damp_mult,
+                          float* Hp, float* U, float* work, int* info_dev, void* stream) {
+  if (!damp_dev) return GQ_ERR_ARG;
+  return hessian_invert_impl(H, D, perm, scale, 0.f, damp_dev, damp_mult, Hp, U, work, info_dev, stream);
 }
 
 size_t gq_upper_packed_floats(int D) { return D > 0 ? upper_packed_floats(D) : 0; }
@@ -181,6 +192,11 @@ void* gq_set_solve_debug(void* dev_buffer) {
 int gq_set_solve_fused(int on) {
   int old = gq::g_solve_fused;
   gq::g_solve_fused = on ? 1 : 0;
+  return old;
+}
+int gq_set_pdl(int on) {
+  int old = gq::g_pdl;
+  if (on == 0 || on == 1) gq::g_pdl = on;
   return old;
 }
 int gq_set_w4a16_path(int path) {

@@ -19,13 +19,25 @@
 //      look-ahead: warps 0-3 update the next sub-block's 16 rows first, then warp 0 runs A of the
 //      next sub-block while the other warps finish the update.
 // fp32 FMA throughout (the reference runs LAPACK potrf in fp32; TF32 is off, main.py:12-13).
+#include <utility>
 #include "gptq_b200_internal.h"
+#include "ptx.cuh"
 
 namespace gq {
 namespace {
 
 constexpr int NB = 128;
 constexpr int SBK = 16;
+
+// compile-time loop: f(std::integral_constant<int, 0>{}) ... f(integral_constant<int, N - 1>{}).  `#pragma unroll` is only a
+// request: the unroller gave up on the 16 x 16 triangle of factor_sub (its budget is shared with the rest of the kernel) and
+// emulated the register arrays with predicated moves; with constant indices there is nothing left to decide.
+template <typename F, int... Is>
+__device__ __forceinline__ void static_for_impl(F&& f, std::integer_sequence<int, Is...>) {
+  (f(std::integral_constant<int, Is>{}), ...);
+}
+template <int N, typename F>
+__device__ __forceinline__ void static_for(F&& f) { static_for_impl(f, std::make_integer_sequence<int, N>{}); }
 
 // 1/sqrt(p) to ~1 ulp: MUFU.RSQ + one Newton step (off the IEEE sqrt/div subroutines: this sits on
 // the serial chain of the factorisation).
@@ -37,15 +49,24 @@ __device__ __forceinline__ float rsqrt_nr(float p) {
 
 template <int PC>
 __global__ void __launch_bounds__(256, (PC <= 64) ? 2 : 1)
-chol_panel_kernel(float* __restrict__ A, int D, int o, int n, int rest, int* __restrict__ info) {
+chol_panel_kernel(float* __restrict__ A, int D, int o, int n, int rest, int* __restrict__ info, long long* __restrict__ dbg) {
   constexpr int W = NB + PC;                 // row pitch of the shared block row
   extern __shared__ __align__(16) float sm[];
   float* S = sm;                             // [NB][W]
   float* rinv = sm + NB * W;                 // [NB] reciprocals of the diagonal of R_kk
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int pc0 = blockIdx.x * PC;           // first panel column of this CTA (relative to o + n)
+  // profiling hook (gq_set_solve_debug, first step of a factorisation only): clock64 stamps of warps 0 and 1 of CTA 0
+  int dbg_i = 0;
+  auto stamp = [&]() {
+    if (dbg != nullptr && blockIdx.x == 0 && lane == 0 && warp < 2) dbg[64 * warp + dbg_i] = clock64();
+    ++dbg_i;
+  };
+  stamp();
   const int pcn = max(0, min(PC, rest - pc0));
 
+  pdl_launch_dependents();
+  pdl_wait();
   // ---- stage [A_kk (upper) | panel columns]; a partial block is padded with the identity.  All of a thread's loads
   // are issued before its first store: one global round trip for the whole block row instead of one per float4.
   {
@@ -84,36 +105,57 @@ chol_panel_kernel(float* __restrict__ A, int D, int o, int n, int rest, int* __r
     }
   }
   __syncthreads();
+  stamp();                                   // [1] block row staged
 
   bool bad = false;
   // ---- A: 16 x 16 diagonal sub-block at (so, so), warp 0 only
-  auto factor_sub = [&](int so) {
+  auto factor_sub = [&](int so) __attribute__((always_inline)) {
     const int k = lane & 15;
-    float a[SBK], dg[SBK];
+    // a[i] = M[i][k] (this lane's column); dg[i] = M[i][i] and e[i] = M[i][i + 1] are private copies kept by EVERY lane with
+    // the same fmas in the same order as the owning lanes, so the pivot chain  rsqrt -> R[j][j+1] -> M[j+1][j+1]  needs no
+    // shuffle: the shuffles (R[j][i] for the rank-1 update) are issued in the shadow of the next rsqrt.
+    float a[SBK], dg[SBK], e[SBK];
 #pragma unroll
     for (int i = 0; i < SBK; ++i) {
       a[i] = S[(so + i) * W + so + k];
       dg[i] = S[(so + i) * W + so + i];
+      e[i] = (i + 1 < SBK) ? S[(so + i) * W + so + i + 1] : 0.f;
     }
-#pragma unroll
-    for (int j = 0; j < SBK; ++j) {
+    // software pipeline: the reciprocal square root of the NEXT pivot is started as soon as that pivot is final, before
+    // this column's shuffles and rank-1 update are issued, so its latency (MUFU + Newton step) is covered by them
+    if (!(dg[0] > 0.f)) bad = true;                        // also catches NaN
+    float ri = rsqrt_nr(dg[0]);
+    static_for<SBK>([&](auto J) {
+      constexpr int j = decltype(J)::value;
       const float p = dg[j];
-      if (!(p > 0.f)) bad = true;                          // also catches NaN
-      const float ri = rsqrt_nr(p);
+      const float rn = e[j] * ri;                          // R[j][j+1] (== a[j] * ri of lane j + 1)
+      float ri_next = 0.f;
+      if constexpr (j + 1 < SBK) {
+        dg[j + 1] = fmaf(-rn, rn, dg[j + 1]);
+        if (!(dg[j + 1] > 0.f)) bad = true;
+        ri_next = rsqrt_nr(dg[j + 1]);
+      }
       float d = p * ri;
       d = fmaf(fmaf(-d, d, p), 0.5f * ri, d);              // sqrt(p) refined
       const float r = (k > j) ? a[j] * ri : (k == j ? d : 0.f);
-      if (lane < 16) {
-        S[(so + j) * W + so + k] = r;
-        if (k == j) rinv[so + j] = ri;
-      }
-#pragma unroll
-      for (int i = j + 1; i < SBK; ++i) {
-        const float rji = __shfl_sync(0xffffffffu, r, i);  // R[j][i]
-        a[i] = fmaf(-rji, r, a[i]);
-        dg[i] = fmaf(-rji, rji, dg[i]);
-      }
-    }
+      S[(so + j) * W + so + k] = r;                        // (both half-warps store the same value: no divergent region)
+      if (k == j) rinv[so + j] = ri;
+      float rj[SBK + 1];                                   // R[j][i], i > j
+      static_for<SBK>([&](auto I) {
+        constexpr int i = decltype(I)::value;
+        if constexpr (i == j + 1) rj[i] = rn;
+        else if constexpr (i > j + 1) rj[i] = __shfl_sync(0xffffffffu, r, i);
+      });
+      static_for<SBK>([&](auto I) {
+        constexpr int i = decltype(I)::value;
+        if constexpr (i > j) a[i] = fmaf(-rj[i], r, a[i]);
+        if constexpr (i > j + 1) {
+          dg[i] = fmaf(-rj[i], rj[i], dg[i]);
+          e[i - 1] = fmaf(-rj[i - 1], rj[i], e[i - 1]);    // M[i-1][i] -= R[j][i-1] R[j][i]
+        }
+      });
+      ri = ri_next;
+    });
   };
   // ---- C: rank-16 update of the 4 rows of group g behind sub-block so:  S[i][c] -= sum_j X[j][i] X[j][c]  (c >= i needed)
   auto update_group = [&](int so, int g) {
@@ -136,36 +178,41 @@ chol_panel_kernel(float* __restrict__ A, int D, int o, int n, int rest, int* __r
     }
   };
 
-  if (warp == 0) factor_sub(0);
-  __syncthreads();
+  // s = -1 is the prologue (factor the first diagonal sub-block): one loop so that factor_sub is inlined at ONE site (two
+  // copies of its fully unrolled body exceed the unroller's budget and the second one falls back to a generic loop)
 #pragma unroll 1
-  for (int s = 0; s < NB / SBK; ++s) {
+  for (int s = -1; s < NB / SBK; ++s) {
     const int so = s * SBK;
-    // ---- B: rows so..so+15 of every later column: forward substitution, one thread per column
-    {
-      const int c = so + SBK + tid;
-      if (c < W) {
-        float x[SBK];
+    int groups = 0;
+    if (s >= 0) {
+      // ---- B: rows so..so+15 of every later column: forward substitution, one thread per column
+      {
+        const int c = so + SBK + tid;
+        if (c < W) {
+          float x[SBK];
 #pragma unroll
-        for (int j = 0; j < SBK; ++j) x[j] = S[(so + j) * W + c];
+          for (int j = 0; j < SBK; ++j) x[j] = S[(so + j) * W + c];
 #pragma unroll
-        for (int j = 0; j < SBK; ++j) {
-          x[j] *= rinv[so + j];
+          for (int j = 0; j < SBK; ++j) {
+            x[j] *= rinv[so + j];
 #pragma unroll
-          for (int i = j + 1; i < SBK; ++i) x[i] = fmaf(-S[(so + j) * W + so + i], x[j], x[i]);
+            for (int i = j + 1; i < SBK; ++i) x[i] = fmaf(-S[(so + j) * W + so + i], x[j], x[i]);
+          }
+#pragma unroll
+          for (int j = 0; j < SBK; ++j) S[(so + j) * W + c] = x[j];
         }
-#pragma unroll
-        for (int j = 0; j < SBK; ++j) S[(so + j) * W + c] = x[j];
       }
-    }
-    __syncthreads();
-    if (s == NB / SBK - 1) break;
-    // ---- C with look-ahead: warps 0-3 first bring the NEXT sub-block's 16 rows up to date (one 4-row group each),
-    // then warp 0 factors the next diagonal sub-block while the other seven warps update the remaining rows
-    const int groups = (NB - so - SBK) / 4;
-    if (warp < 4) {
-      update_group(so, warp);
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      __syncthreads();
+      stamp();                               // B done
+      if (s == NB / SBK - 1) break;
+      // ---- C with look-ahead: warps 0-3 first bring the NEXT sub-block's 16 rows up to date (one 4-row group each),
+      // then warp 0 factors the next diagonal sub-block while the other seven warps update the remaining rows
+      groups = (NB - so - SBK) / 4;
+      if (warp < 4) {
+        update_group(so, warp);
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+      }
+      stamp();                               // look-ahead rows done (warps 0-3)
     }
     if (warp == 0) {
       factor_sub(so + SBK);
@@ -173,7 +220,9 @@ chol_panel_kernel(float* __restrict__ A, int D, int o, int n, int rest, int* __r
 #pragma unroll 1
       for (int g = 4 + (warp - 1); g < groups; g += 7) update_group(so, g);
     }
+    stamp();                                 // factor (warp 0) / remaining updates (warp 1) done
     __syncthreads();
+    stamp();
   }
 
   // ---- write back: the factor (CTA 0 only) and this CTA's panel columns
@@ -202,6 +251,7 @@ chol_panel_kernel(float* __restrict__ A, int D, int o, int n, int rest, int* __r
             *reinterpret_cast<const float4*>(S + r * W + NB + c4);
     }
   }
+  stamp();                                   // written back
 }
 
 template <int PC>
@@ -215,8 +265,9 @@ int launch_cp(float* A, int D, int o, int n, int rest, int* info, cudaStream_t s
   }
   const int grid = PC > 0 ? (rest + PC - 1) / PC : 1;
   GQ_LAUNCHED();
-  chol_panel_kernel<PC><<<grid, 256, smem, st>>>(A, D, o, n, rest, info);
-  return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
+  return launch_chain(chol_panel_kernel<PC>, dim3(grid), dim3(256), (size_t)smem, st, g_pdl != 0, A, D, o, n, rest, info,
+                      (o == 0) ? g_solve_dbg : (long long*)nullptr) == cudaSuccess
+             ? GQ_OK : GQ_ERR_CUDA;
 }
 
 }  // namespace

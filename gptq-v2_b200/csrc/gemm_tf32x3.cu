@@ -132,6 +132,9 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
   if constexpr (CG == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  // everything above is independent of the predecessor kernel; from here on global memory is read and written
+  pdl_launch_dependents();
+  pdl_wait();
 
   if (warp == 0) {
     if (lane == 0) {
@@ -369,13 +372,15 @@ static int launch_gemm(const Tf32Maps& maps, const GemmTf32Params& p, int n_sms,
   cfg.blockDim = dim3(256 + SPLIT_THREADS);
   cfg.dynamicSmemBytes = Cfg<CG>::SMEM_BYTES;
   cfg.stream = st;
-  cudaLaunchAttribute at[1];
+  cudaLaunchAttribute at[2];
   at[0].id = cudaLaunchAttributeClusterDimension;
   at[0].val.clusterDim.x = CG;
   at[0].val.clusterDim.y = 1;
   at[0].val.clusterDim.z = 1;
+  at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = at;
-  cfg.numAttrs = 1;
+  cfg.numAttrs = g_pdl ? 2 : 1;
   GQ_LAUNCHED();
   return cudaLaunchKernelEx(&cfg, gemm_tf32x3_kernel<CG>, maps.a, maps.b, maps.c, p) == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
 }

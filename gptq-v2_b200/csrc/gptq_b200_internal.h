@@ -38,6 +38,21 @@ struct PerDeviceFlag : PerDeviceInt {
 extern unsigned long long g_launch_count;
 #define GQ_LAUNCHED() (++::gq::g_launch_count)
 
+// programmatic dependent launch on the serial kernel chains of K2 / K3+K4 (gq_set_pdl; ptx.cuh pdl_wait)
+extern int g_pdl;
+// <<<grid, block, smem, st>>> with the programmatic-serialization attribute when `pdl` is set; the kernel MUST call pdl_wait()
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_chain(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, bool pdl,
+                                Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // ---- K1
 int syrk_upper(float* H, const void* X, int D, int T, int fmt, int mode, int variant, cudaStream_t st);
 int make_tmap_2d(CUtensorMap* out, const void* base, int elem_kind, uint64_t inner, uint64_t outer,
@@ -94,8 +109,8 @@ int gemm_tf32x3(const Tf32Maps& maps, int M, int N, int K, int a_row0, int a_col
                 int c_col0, float alpha, int upper_only, cudaStream_t st);
 
 // ---- K2
-int hessian_gather(const float* H, int D, const int64_t* perm, float scale, float damp, float* Hp, float* Arev,
-                   cudaStream_t st);
+int hessian_gather(const float* H, int D, const int64_t* perm, float scale, float damp, const float* damp_dev, float damp_mult,
+                   float* Hp, float* Arev, float* Hs, cudaStream_t st);
 int chol_inverse_upper(float* A, int D, float* U, float* Wb, float* tmp, int* info_dev, cudaStream_t st);
 size_t upper_packed_floats(int D);
 int upper_tiles(float* H, float* packed, int D, int pack, cudaStream_t st);

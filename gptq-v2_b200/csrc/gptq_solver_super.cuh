@@ -115,6 +115,8 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  pdl_launch_dependents();       // the far update behind this super-block may set up while the chain runs
+  pdl_wait();                    // the previous far update has landed in W before anything below reads global memory
 
   if (warp == 16) {
     // ------------------------------------------------------------ TMA producer: U[block rows, later columns] through the ring
@@ -510,8 +512,8 @@ int launch_super(const CUtensorMap& map_u, const SuperParams& p, cudaStream_t st
   }
   const int rows = 32 * NQ;
   GQ_LAUNCHED();
-  solve_super_kernel<MODE, NQ, CodeT><<<(p.R + rows - 1) / rows, SUP_THREADS, Cfg::SMEM_BYTES, st>>>(map_u, p);
-  return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
+  return launch_chain(solve_super_kernel<MODE, NQ, CodeT>, dim3((p.R + rows - 1) / rows), dim3(SUP_THREADS), (size_t)Cfg::SMEM_BYTES, st,
+                      g_pdl != 0, map_u, p) == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
 }
 
 }  // namespace gq

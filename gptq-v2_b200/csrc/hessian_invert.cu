@@ -17,13 +17,69 @@
 //        T^T = R12^T W11,    W21 = -V22^T T^T,    V12 = W21^T        (batched over all pairs of a level)
 //   reversal of W into U (zeros below the diagonal):  U[i][j] = W[D-1-i][D-1-j].
 #include "gptq_b200_internal.h"
+#include "ptx.cuh"
 
 namespace gq {
 namespace {
 
 // ---------------------------------------------------------------- gather
+// A[D-1-i][D-1-j] = scale * Hsym[perm i][perm j] (+ damp on the diagonal), Hp[i][j] the same without the reversal.
+// H holds valid data in its upper triangle only (K1 mode 0) and a doubly permuted read of it is a 4-byte random access
+// per element, so the gather runs in two coalesced passes:
+//   symmetrize_kernel   Hs = full symmetric copy of H (32 x 32 tile transposes through shared memory)
+//   gather_rows_kernel  one CTA per output row i: row perm[i] of Hs is staged in shared memory with 16-byte loads, the
+//                       column permutation is applied on the shared copy, both outputs are written coalesced.
+__global__ void __launch_bounds__(256) symmetrize_kernel(const float* __restrict__ H, float* __restrict__ Hs, int D) {
+  __shared__ float tile[32][33];
+  const int bj = blockIdx.x, bi = blockIdx.y;
+  if (bj < bi) return;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int yy = ty; yy < 32; yy += 8) {
+    const int r = bi * 32 + yy, c = bj * 32 + tx;
+    float v = 0.f;
+    if (r < D && c < D) {
+      v = (c >= r) ? H[(size_t)r * D + c] : H[(size_t)c * D + r];       // (c < r only inside diagonal tiles)
+      Hs[(size_t)r * D + c] = v;
+    }
+    tile[yy][tx] = v;
+  }
+  if (bi == bj) return;
+  __syncthreads();
+  for (int yy = ty; yy < 32; yy += 8) {
+    const int r = bj * 32 + yy, c = bi * 32 + tx;
+    if (r < D && c < D) Hs[(size_t)r * D + c] = tile[tx][yy];
+  }
+}
+
+__global__ void __launch_bounds__(256) gather_rows_kernel(const float* __restrict__ Hs, int D, const int64_t* __restrict__ perm,
+                                                          float scale, float damp, const float* __restrict__ damp_dev,
+                                                          float damp_mult, float* __restrict__ Hp, float* __restrict__ Arev) {
+  extern __shared__ __align__(16) float row[];
+  if (damp_dev) damp = damp_dev[0] * damp_mult;      // damping computed on the device (no host round trip)
+  const int i = blockIdx.x;
+  const int pi = perm ? (int)perm[i] : i;
+  const float4* src = reinterpret_cast<const float4*>(Hs + (size_t)pi * D);      // D % 4 == 0
+  for (int k = threadIdx.x; k < D / 4; k += 256) reinterpret_cast<float4*>(row)[k] = src[k];
+  __syncthreads();
+  float* hp = Hp ? Hp + (size_t)i * D : nullptr;
+  float* ar = Arev ? Arev + (size_t)(D - 1 - i) * D + (D - 1) : nullptr;
+  for (int j = threadIdx.x; j < D; j += 256) {
+    const int pj = perm ? (int)perm[j] : j;
+    float v = row[pj] * scale;
+    if (i == j) {
+      if (v == 0.f) v = 1.f;     // dead column (gptq_py.py:43-44)
+      v += damp;                 // gptq_py.py:58
+    }
+    if (hp) hp[j] = v;
+    if (ar) ar[-j] = v;
+  }
+}
+
+// element-wise form (one random 4-byte read per element): used when no scratch for the symmetric copy is given
 __global__ void gather_kernel(const float* __restrict__ H, int D, const int64_t* __restrict__ perm, float scale,
-                              float damp, float* __restrict__ Hp, float* __restrict__ Arev) {
+                              float damp, const float* __restrict__ damp_dev, float damp_mult, float* __restrict__ Hp,
+                              float* __restrict__ Arev) {
+  if (damp_dev) damp = damp_dev[0] * damp_mult;
   const int j = blockIdx.x * 32 + threadIdx.x;
   const int i = blockIdx.y * 8 + threadIdx.y;
   if (i >= D || j >= D) return;
@@ -44,49 +100,58 @@ __global__ void gather_kernel(const float* __restrict__ H, int D, const int64_t*
 constexpr int NB = 128;
 constexpr int PITCH = NB + 1;
 
-// Invert every diagonal block R_kk (upper) in place, one CTA per block, all blocks in one launch
-// (off the critical path: runs once after the factorisation).
-__global__ void __launch_bounds__(256) trtri_diag_kernel(float* __restrict__ A, float* __restrict__ Wb, int D) {
+// Invert every diagonal block R_kk (upper) in place, one CTA per block, all blocks in one launch (runs once after the
+// factorisation).  Back substitution T[i][c] = (delta_ic - sum_{i<k<=c} S[i][k] T[k][c]) / S[i][i], rows from the bottom:
+// a column only depends on its own later rows, so the 8 lanes that share column c split the dot product by k mod 8 and
+// combine with three shuffles; no block-wide barrier inside the loop.  T is kept transposed (Tt[c][k], pitch = 8 mod 32:
+// the 4 columns x 8 k-lanes of a warp hit 32 different banks).
+constexpr int TR_LANES = 8;
+constexpr int TR_THREADS = NB * TR_LANES;     // 1024
+constexpr int TR_TPITCH = NB + 8;
+__global__ void __launch_bounds__(TR_THREADS) trtri_diag_kernel(float* __restrict__ A, float* __restrict__ Wb, int D) {
   extern __shared__ float sm[];
   float* S = sm;                    // [NB][PITCH] upper factor
-  float* Tm = sm + NB * PITCH;      // [NB][PITCH] its inverse
+  float* Tt = sm + NB * PITCH;      // [NB][TR_TPITCH] transposed inverse: Tt[c][k] = T[k][c]
   const int o = blockIdx.x * NB;
   const int n = min(NB, D - o);
   const int tid = threadIdx.x;
-  for (int idx = tid; idx < NB * NB; idx += 256) {
+  for (int idx = tid; idx < NB * NB; idx += TR_THREADS) {
     const int r = idx >> 7, c = idx & 127;
     float v = (r == c) ? 1.f : 0.f;
     if (r < n && c < n && c >= r) v = A[(size_t)(o + r) * D + o + c];
     S[r * PITCH + c] = v;
-    Tm[r * PITCH + c] = 0.f;
+    Tt[r * TR_TPITCH + c] = 0.f;
   }
   __syncthreads();
-  // two adjacent lanes share column c and split the dot product by parity of k
-  const int c = tid >> 1, par = tid & 1;
+  const int c = tid / TR_LANES, l = tid % TR_LANES;
+  float* tc = Tt + c * TR_TPITCH;
   for (int i = NB - 1; i >= 0; --i) {
     float s0 = 0.f, s1 = 0.f;
-    if (c < n && i < c) {
-      int k = i + 1 + par;
-      for (; k + 2 <= c; k += 4) {
-        s0 = fmaf(S[i * PITCH + k], Tm[k * PITCH + c], s0);
-        s1 = fmaf(S[i * PITCH + k + 2], Tm[(k + 2) * PITCH + c], s1);
+    if (i < c) {
+      const float* si = S + i * PITCH;
+      int k = i + 1 + l;
+      for (; k + TR_LANES <= c; k += 2 * TR_LANES) {
+        s0 = fmaf(si[k], tc[k], s0);
+        s1 = fmaf(si[k + TR_LANES], tc[k + TR_LANES], s1);
       }
-      for (; k <= c; k += 2) s0 = fmaf(S[i * PITCH + k], Tm[k * PITCH + c], s0);
+      if (k <= c) s0 = fmaf(si[k], tc[k], s0);
     }
     float s = s0 + s1;
     s += __shfl_xor_sync(0xffffffffu, s, 1);
-    if (c < n && i <= c && par == 0) {
+    s += __shfl_xor_sync(0xffffffffu, s, 2);
+    s += __shfl_xor_sync(0xffffffffu, s, 4);
+    if (i <= c && l == 0) {
       const float rhs = (i == c) ? 1.f : 0.f;
-      Tm[i * PITCH + c] = (rhs - s) / S[i * PITCH + i];
+      tc[i] = (rhs - s) / S[i * PITCH + i];
     }
-    __syncwarp();                   // column c only depends on earlier rows of the same column
+    __syncwarp();                   // column c only depends on later rows of the same column (same warp)
   }
   __syncthreads();
-  for (int idx = tid; idx < NB * NB; idx += 256) {
+  for (int idx = tid; idx < NB * NB; idx += TR_THREADS) {
     const int r = idx >> 7, cc = idx & 127;
     if (r < n && cc < n) {
-      A[(size_t)(o + r) * D + o + cc] = (cc >= r) ? Tm[r * PITCH + cc] : 0.f;      // V_kk (upper, zeros below)
-      Wb[(size_t)(o + r) * D + o + cc] = (cc <= r) ? Tm[cc * PITCH + r] : 0.f;     // W_kk = V_kk^T (lower, zeros above)
+      A[(size_t)(o + r) * D + o + cc] = (cc >= r) ? Tt[cc * TR_TPITCH + r] : 0.f;      // V_kk (upper, zeros below)
+      Wb[(size_t)(o + r) * D + o + cc] = (cc <= r) ? Tt[r * TR_TPITCH + cc] : 0.f;     // W_kk = V_kk^T (lower, zeros above)
     }
   }
 }
@@ -111,6 +176,8 @@ struct TransposeBatch {
 };
 __global__ void transpose_pairs_kernel(const float* __restrict__ Wb, float* __restrict__ A, int D, const TransposeBatch b) {
   __shared__ float tile[32][33];
+  pdl_launch_dependents();
+  pdl_wait();
   const int r0 = b.p[blockIdx.z].r0, c0 = b.p[blockIdx.z].c0, n1 = b.p[blockIdx.z].n1, n2 = b.p[blockIdx.z].n2;
   const int i0 = blockIdx.x * 32, j0 = blockIdx.y * 32;      // i along n1 (contiguous in Wb), j along n2 (contiguous in A)
   if (i0 >= n1 || j0 >= n2) return;
@@ -126,12 +193,21 @@ __global__ void transpose_pairs_kernel(const float* __restrict__ Wb, float* __re
 }
 
 // ---------------------------------------------------------------- reversal
-// U[i][j] = W[D-1-i][D-1-j] for i <= j, 0 below the diagonal  (U = J V^T J with W = V^T)
-__global__ void reverse_lower_kernel(const float* __restrict__ Wb, float* __restrict__ U, int D) {
-  const int j = blockIdx.x * 128 + threadIdx.x;
+// U[i][j] = W[D-1-i][D-1-j] for i <= j, 0 below the diagonal  (U = J V^T J with W = V^T); 16-byte loads and stores
+// (D % 4 == 0: the four reversed source elements of an aligned group of U are an aligned group of W).
+__global__ void __launch_bounds__(256) reverse_lower_kernel(const float* __restrict__ Wb, float* __restrict__ U, int D) {
   const int i = blockIdx.y;
-  if (j >= D) return;
-  U[(size_t)i * D + j] = (i <= j) ? Wb[(size_t)(D - 1 - i) * D + (D - 1 - j)] : 0.f;
+  const int j4 = (blockIdx.x * 256 + threadIdx.x) * 4;
+  if (j4 >= D) return;
+  float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (j4 + 3 >= i) {
+    const float4 w = *reinterpret_cast<const float4*>(Wb + (size_t)(D - 1 - i) * D + (D - 4 - j4));
+    o.x = (i <= j4) ? w.w : 0.f;
+    o.y = (i <= j4 + 1) ? w.z : 0.f;
+    o.z = (i <= j4 + 2) ? w.y : 0.f;
+    o.w = w.x;
+  }
+  *reinterpret_cast<float4*>(U + (size_t)i * D + j4) = o;
 }
 
 // ---------------------------------------------------------------- packed upper triangle (multi-GPU reduction payload)
@@ -172,11 +248,28 @@ int upper_tiles(float* H, float* packed, int D, int pack, cudaStream_t st) {
   return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
 }
 
-int hessian_gather(const float* H, int D, const int64_t* perm, float scale, float damp, float* Hp, float* Arev,
-                   cudaStream_t st) {
+// Hs: optional (D x D) scratch for the symmetric copy (must not alias Hp / Arev); NULL selects the element-wise gather.
+// damp_dev: optional device scalar; when given the damping is damp_dev[0] * damp_mult and `damp` is ignored.
+int hessian_gather(const float* H, int D, const int64_t* perm, float scale, float damp, const float* damp_dev, float damp_mult,
+                   float* Hp, float* Arev, float* Hs, cudaStream_t st) {
+  const int row_smem = D * (int)sizeof(float);
+  if (Hs && (D & 3) == 0 && row_smem <= 200 * 1024) {
+    static PerDeviceInt smem_set;   // function attributes are per device
+    if (row_smem > 48 * 1024 && smem_set.get() < row_smem) {
+      if (cudaFuncSetAttribute(gather_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, row_smem) != cudaSuccess)
+        return GQ_ERR_CUDA;
+      smem_set.set(row_smem);
+    }
+    const int nt = (D + 31) / 32;
+    GQ_LAUNCHED();
+    symmetrize_kernel<<<dim3(nt, nt), 256, 0, st>>>(H, Hs, D);
+    GQ_LAUNCHED();
+    gather_rows_kernel<<<D, 256, row_smem, st>>>(Hs, D, perm, scale, damp, damp_dev, damp_mult, Hp, Arev);
+    return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
+  }
   dim3 block(32, 8), grid((D + 31) / 32, (D + 7) / 8);
   GQ_LAUNCHED();
-  gather_kernel<<<grid, block, 0, st>>>(H, D, perm, scale, damp, Hp, Arev);
+  gather_kernel<<<grid, block, 0, st>>>(H, D, perm, scale, damp, damp_dev, damp_mult, Hp, Arev);
   return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
 }
 
@@ -185,7 +278,7 @@ int hessian_gather(const float* H, int D, const int64_t* perm, float scale, floa
 int chol_inverse_upper(float* A, int D, float* U, float* Wb, float* tmp, int* info_dev, cudaStream_t st) {
   if (D % 16 != 0) return GQ_ERR_SHAPE;
   static PerDeviceFlag attr_set;   // function attributes are per device
-  const int trtri_smem = 2 * NB * PITCH * (int)sizeof(float);
+  const int trtri_smem = (NB * PITCH + NB * TR_TPITCH) * (int)sizeof(float);
   if (!attr_set) {
     if (cudaFuncSetAttribute(trtri_diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, trtri_smem) != cudaSuccess)
       return GQ_ERR_CUDA;
@@ -228,7 +321,7 @@ int chol_inverse_upper(float* A, int D, float* U, float* Wb, float* tmp, int* in
   // ---- all diagonal blocks: V_kk = R_kk^-1 (into A) and W_kk = V_kk^T (into the zeroed Wb), one launch
   if (cudaMemsetAsync(Wb, 0, (size_t)D * D * sizeof(float), st) != cudaSuccess) return GQ_ERR_CUDA;
   GQ_LAUNCHED();
-  trtri_diag_kernel<<<nb, 256, trtri_smem, st>>>(A, Wb, D);
+  trtri_diag_kernel<<<nb, TR_THREADS, trtri_smem, st>>>(A, Wb, D);
   if (cudaGetLastError() != cudaSuccess) return GQ_ERR_CUDA;
   if (nb > 1) {
     GQ_LAUNCHED();
@@ -255,8 +348,7 @@ int chol_inverse_upper(float* A, int D, float* U, float* Wb, float* tmp, int* in
       tb.count = cnt;
       dim3 block(32, 8), grid((n1 + 31) / 32, (max_n2 + 31) / 32, cnt);
       GQ_LAUNCHED();
-      transpose_pairs_kernel<<<grid, block, 0, st>>>(Wb, A, D, tb);
-      if (cudaGetLastError() != cudaSuccess) return GQ_ERR_CUDA;
+      if (launch_chain(transpose_pairs_kernel, grid, block, 0, st, g_pdl != 0, (const float*)Wb, A, D, tb) != cudaSuccess) return GQ_ERR_CUDA;
       cnt = 0; troff = 0; max_n2 = 0;
       return GQ_OK;
     };
@@ -276,9 +368,9 @@ int chol_inverse_upper(float* A, int D, float* U, float* Wb, float* tmp, int* in
     }
     if ((rc = flush()) != GQ_OK) return rc;
   }
-  dim3 grid((D + 127) / 128, D);
+  dim3 grid((D + 1023) / 1024, D);
   GQ_LAUNCHED();
-  reverse_lower_kernel<<<grid, 128, 0, st>>>(Wb, U, D);
+  reverse_lower_kernel<<<grid, 256, 0, st>>>(Wb, U, D);
   return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
 }
 

@@ -15,7 +15,7 @@ from . import _cabi
 from ._cabi import GptqB200Error, check, lib, ptr, require_contig, require_cuda, stream_of
 
 __all__ = ['accumulate_hessian', 'gptq_quantize_range', 'hessian_syrk', 'hessian_invert', 'w4a16_dequant', 'pack_upper', 'unpack_upper', 'prep_weight_t', 'prep_weight_t2', 'solve_metrics', 'gptq_solve_ex', 'find_params', 'mse_refine', 'find_params_cols', 'mse_refine_cols', 'rtn_quantize',
-           'gptq_solve', 'gptq_solve_static', 'pack_int4', 'unpack_int4', 'transpose_pack_int4', 'w4a16_gemm', 'w4a16_gemv_static', 'gemm_f16_nt', 'sgemm', 'gemm_tf32x3', 'set_tf32x3', 'set_solve_super', 'set_solve_fused', 'set_tf32_kchunk', 'set_syrk_kchunk', 'set_w4a16_path',
+           'gptq_solve', 'gptq_solve_static', 'pack_int4', 'unpack_int4', 'transpose_pack_int4', 'w4a16_gemm', 'w4a16_gemv_static', 'gemm_f16_nt', 'sgemm', 'gemm_tf32x3', 'set_tf32x3', 'set_solve_super', 'set_solve_fused', 'set_tf32_kchunk', 'set_syrk_kchunk', 'set_w4a16_path', 'set_pdl',
            'GptqB200Error']
 
 
@@ -73,9 +73,11 @@ def hessian_syrk(H: torch.Tensor, X: torch.Tensor, mode: int = 1, variant: int =
                                                 stream_of(H)), 'gq_accumulate_hessian')
 
 
-def hessian_invert(H: torch.Tensor, perm, scale: float, damp: float, want_hp: bool = True):
+def hessian_invert(H: torch.Tensor, perm, scale: float, damp, want_hp: bool = True, damp_mult: float = 1.0):
     """K2.  Returns (Hp, U, info) with Hp = scale*H[perm][:, perm] + damp*I and
-    U = chol_upper(Hp^-1); info is a device int32 (1 = a pivot was not positive)."""
+    U = chol_upper(Hp^-1); info is a device int32 (1 = a pivot was not positive).
+    damp: a Python float, or a 0-dim fp32 CUDA tensor (then the damping is damp * damp_mult, read on the device: no host
+    synchronisation between K1 and the factorisation)."""
     dev = require_cuda(H, perm)
     require_contig(H=H, perm=perm)
     D = H.shape[0]
@@ -86,8 +88,14 @@ def hessian_invert(H: torch.Tensor, perm, scale: float, damp: float, want_hp: bo
     work = torch.empty(lib.gq_invert_workspace_floats(D), dtype=torch.float32, device=dev)
     info = torch.zeros((), dtype=torch.int32, device=dev)
     with torch.cuda.device(dev):
-        check(lib.gq_hessian_invert(ptr(H), D, ptr(perm), float(scale), float(damp), ptr(Hp), ptr(U), ptr(work),
-                                    ptr(info), stream_of(H)), 'gq_hessian_invert')
+        if isinstance(damp, torch.Tensor):
+            if damp.dtype != torch.float32 or damp.numel() != 1 or damp.device != dev:
+                raise GptqB200Error('damp tensor must be one fp32 value on the device of H')
+            check(lib.gq_hessian_invert_dev(ptr(H), D, ptr(perm), float(scale), ptr(damp), float(damp_mult), ptr(Hp), ptr(U),
+                                            ptr(work), ptr(info), stream_of(H)), 'gq_hessian_invert_dev')
+        else:
+            check(lib.gq_hessian_invert(ptr(H), D, ptr(perm), float(scale), float(damp) * float(damp_mult), ptr(Hp), ptr(U),
+                                        ptr(work), ptr(info), stream_of(H)), 'gq_hessian_invert')
     return Hp, U, info
 
 
@@ -439,6 +447,11 @@ def gemm_tf32x3(A, B, C_, M, N, K, lda, ldb, ldc, alpha, upper_only=0) -> None:
     with torch.cuda.device(dev):
         check(lib.gq_gemm_tf32x3(ptr(A), ptr(B), ptr(C_), M, N, K, lda, ldb, ldc, float(alpha), int(upper_only),
                                  stream_of(C_)), 'gq_gemm_tf32x3')
+
+
+def set_pdl(on: int) -> int:
+    """Programmatic dependent launch on the K2 / K3+K4 kernel chains (1 = default); returns the previous value."""
+    return int(lib.gq_set_pdl(int(on)))
 
 
 def set_w4a16_path(path: int) -> int:

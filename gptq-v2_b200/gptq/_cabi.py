@@ -26,6 +26,7 @@ SIGNATURES = {
     'accumulate_hessian_bf16_fp32_cuda': (_i, [_vp, _vp, _i, _i]),
     'gq_invert_workspace_floats': (C.c_size_t, [_i]),
     'gq_hessian_invert': (_i, [_vp, _i, _vp, _f, _f, _vp, _vp, _vp, _vp, _vp]),
+    'gq_hessian_invert_dev': (_i, [_vp, _i, _vp, _f, _vp, _f, _vp, _vp, _vp, _vp, _vp]),
     'gq_upper_packed_floats': (C.c_size_t, [_i]),
     'gq_pack_upper': (_i, [_vp, _i, _vp, _vp]),
     'gq_unpack_upper': (_i, [_vp, _i, _vp, _vp]),
@@ -56,6 +57,7 @@ SIGNATURES = {
     'gq_set_syrk_kchunk': (_i, [_i]),
     'gq_set_solve_debug': (_vp, [_vp]),
     'gq_set_w4a16_path': (_i, [_i]),
+    'gq_set_pdl': (_i, [_i]),
     'gq_sgemm': (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _i, _i, _f, _f, _i, _vp]),
 }
 

@@ -20,6 +20,8 @@ Still NotImplementedError: quant_use_kernel=True (needs exllamav2, which the ref
 """
 from __future__ import annotations
 
+import collections.abc
+
 import torch
 
 import gptq as _ops
@@ -66,13 +68,13 @@ class HessianHook:
         if act_order:
             self.perm = torch.argsort(diag, descending=True, stable=True)   # ref :47 (ties: stable here)
             self.perm_inv = torch.argsort(self.perm)                        # ref :49
-        damp = float(damp_ratio * diag.mean())                          # ref :52 (one host sync)
+        damp = (damp_ratio * diag.mean()).reshape(())                   # ref :52; stays on the device: K2 reads it there
         max_try = 100
         tries = 0
         while (max_try := max_try - 1) >= 0:
             tries += 1
             # cumulative damping: try k factors H + k*damp*I (ref :58)
-            Hp, U, info = _ops.hessian_invert(H, self.perm, scale, damp * tries)
+            Hp, U, info = _ops.hessian_invert(H, self.perm, scale, damp, damp_mult=float(tries))
             if not bool((info != 0) | ~torch.isfinite(U.diagonal()).all()):         # one host sync per try (ref :63)
                 break
         assert max_try >= 0
@@ -80,6 +82,46 @@ class HessianHook:
         self.hessian = Hp                    # scaled, permuted, damped -- what the reference leaves behind
         self.hessian_inv = U
         return self.hessian_inv
+
+
+class DeferredMetrics(collections.abc.Mapping):
+    """The four metrics of gptq_quant (ref :196-199, :231-237) as a read-only mapping whose values are fetched from the device
+    on first access.  gptq_quant(defer_metrics=True) returns it instead of a dict, so that a caller quantising several linears
+    in a row (sharded.gptq_quant_group_sharded, bench.py, llama_driver.py) does not synchronise the host after every linear: the
+    four sums travel to pinned host memory behind the solver and are read when somebody looks."""
+    KEYS = ('gptq_error', 'gptq_norm', 'l2.0_error', 'l2.0_norm')
+
+    def __init__(self, stats: torch.Tensor, n_el: float, has_hook: bool):
+        e2, d2, ns, l2n = stats.unbind(0)
+        zero = torch.zeros_like(e2)
+        self._dev = torch.stack([e2 / n_el if has_hook else zero, ns / n_el if has_hook else zero, d2 / n_el, l2n])
+        self._host = torch.empty(4, dtype=torch.float64, pin_memory=True)
+        self._host.copy_(self._dev, non_blocking=True)
+        self._event = torch.cuda.Event()
+        self._event.record()
+        self._values = None
+
+    def device_values(self) -> torch.Tensor:
+        """(4,) float64 on the device, in KEYS order (for reductions that stay on the device)."""
+        return self._dev
+
+    def _resolve(self) -> dict:
+        if self._values is None:
+            self._event.synchronize()
+            self._values = dict(zip(self.KEYS, self._host.tolist()))
+        return self._values
+
+    def __getitem__(self, key):
+        return self._resolve()[key]
+
+    def __iter__(self):
+        return iter(self.KEYS)
+
+    def __len__(self):
+        return len(self.KEYS)
+
+    def __repr__(self):
+        return repr(self._resolve())
 
 
 def _int_list(t) -> list[int]:
@@ -117,6 +159,8 @@ def gptq_quant(
         quant_norm: float = 2.4,
         quant_use_kernel: bool = False,
         save_device: torch.device = torch.device('cpu'),
+        *,
+        defer_metrics: bool = False,
 ) -> dict[str, dict]:
     """gptq_use_kernel=True  -> the reference's kernel-path semantics: static per-group scale/zero
                                 from the un-compensated weights, fp16-rounded dequant (ref :125-157)
@@ -125,7 +169,9 @@ def gptq_quant(
        hessian_hook=None     -> round to nearest (ref :101-124)
     Group sizes need not be uniform (ref :98 walks a cumsum); on the fp32 branch GPTQ blocks may differ from the groups
     (ref :161-193).  Group parameters come from the solver itself (asymmetric min/max) or from gq_find_params /
-    gq_mse_refine (symmetric, MSE-refined, EXL2 grids)."""
+    gq_mse_refine (symmetric, MSE-refined, EXL2 grids).
+    defer_metrics (not in the reference): return the metrics as a DeferredMetrics mapping instead of floats, i.e. without the
+    host synchronisation at the end of the call."""
     if quant_mse and quant_use_kernel:
         # ref quant.py:131-150 calls exllamav2's ext_c.quantize_err, whose import the reference has commented out (quant.py:4)
         raise NotImplementedError('quant_use_kernel=True needs exllamav2 (not importable in the reference either)')
@@ -308,6 +354,8 @@ def gptq_quant(
         'group_bit_widths': bits_out.to(device=save_device),
         'scale_bit_width': scale_bit_width.to(dtype=torch.uint8, device=save_device) if scale_bit_width is not None else None,
     }
+    if defer_metrics:
+        return {'quant_meta': quant_meta, 'metrics': DeferredMetrics(stats, n_el, hessian_hook is not None)}
     # the one host sync of the call, after every kernel of the result assembly has been queued behind the solver
     e2, d2, ns, l2n = stats.tolist()
     if hessian_hook is None:

@@ -375,6 +375,8 @@ def quantize_block(shape: LlamaShape, weights: dict, inps: torch.Tensor, n_globa
     with timer('forward'):
         for b in _batches(n, batch_size):
             h2[b] += act[b] @ wd.t()
+    # plain {name: float} dicts like the reference's; the deferred values are read here, once per block, behind the queued work
+    metrics = {name: dict(met) for name, met in metrics.items()}
     return h2, data, metrics
 
 

@@ -188,6 +188,8 @@ def gptq_quant_group_sharded(weights: Sequence[torch.Tensor], hessian_hook, quan
     (bench.py's host-fed step); `weights` may then be meta tensors (shape and dtype only)."""
     if quant_fn is None:
         from gptq_py import gptq_quant as quant_fn
+        # the library's own quantiser: no host synchronisation per linear, the metrics are read when the caller looks
+        quant_kwargs = dict(quant_kwargs, defer_metrics=True)
     rank, world = world_info(group)
     L = len(weights)
     if shard_of is None:
@@ -235,7 +237,10 @@ def gptq_quant_group_sharded(weights: Sequence[torch.Tensor], hessian_hook, quan
             assert b.numel() == (hi - lo) * width
             blob[off:off + b.numel()] = b
             off += padded(b.numel())
-        msum[i] = torch.tensor([met[k] * (hi - lo) for k in keys], dtype=torch.float64, device=dev)
+        if hasattr(met, 'device_values'):
+            msum[i] += met.device_values() * float(hi - lo)            # stays on the device (keys order == DeferredMetrics.KEYS)
+        else:
+            msum[i] += torch.tensor([met[k] * (hi - lo) for k in keys], dtype=torch.float64, device=dev)
     out = torch.empty(world * mx, dtype=torch.uint8, device=dev)
     dist.all_gather_into_tensor(out, blob, group=group)
     dist.all_reduce(msum, group=group)

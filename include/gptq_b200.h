@@ -55,6 +55,11 @@ int gq_accumulate_hessian_variant(void* H, const void* X, int size_hidden, int s
 size_t gq_invert_workspace_floats(int D);
 int gq_hessian_invert(const float* H, int D, const int64_t* perm, float scale, float damp, float* Hp, float* U,
                       float* work, int* info_dev, void* stream);
+/* The same with the damping taken from device memory: Hp = scale * H[perm][:, perm] + damp_dev[0] * damp_mult * I.  The caller
+ * computes damp_ratio * mean(diag) (gptq_py.py:52) on the device and passes the try count as damp_mult (cumulative damping,
+ * gptq_py.py:58), so that no host synchronisation sits between K1 and the factorisation. */
+int gq_hessian_invert_dev(const float* H, int D, const int64_t* perm, float scale, const float* damp_dev, float damp_mult,
+                          float* Hp, float* U, float* work, int* info_dev, void* stream);
 
 /* ---- multi-GPU reduction payload (no reference counterpart: the reference is single-GPU).
  * K1 mode 0 maintains only the upper triangle of H, so only that is summed over ranks: the upper 128 x 128 tiles of
@@ -208,6 +213,10 @@ void* gq_set_solve_debug(void* dev_buffer);
  * mutual updates accumulated in tensor memory); 0 = one launch per block plus near-update GEMM launches (round 1's schedule).
  * The environment variable GQ_SOLVE_FUSED=0 selects 0 at load time.  Returns the previous setting. */
 int gq_set_solve_fused(int on);
+/* Programmatic dependent launch on the serial kernel chains (Cholesky panel <-> trailing update, solver super-block <-> far
+ * update): 1 (default) lets a kernel's prologue overlap the tail of its predecessor, 0 restores plain stream order (A/B
+ * hook; results are identical).  Returns the previous value. */
+int gq_set_pdl(int on);
 /* A/B hook for K6's dispatch: 0 = automatic (batch <= 8: warp-level mma kernel; otherwise tcgen05 with the weights on the M
  * side through tensor memory, 64 or 256 batch columns per pass), 1 = never the small-batch kernel, 2 = batch <= 128 through
  * the experimental tcgen05 kernel with the weights on the N side (w4a16_wb.cu; correct, not yet faster).  Returns the

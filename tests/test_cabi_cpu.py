@@ -39,9 +39,13 @@ def test_reference_surface_is_importable():
     assert list(inspect.signature(accumulate_hessian).parameters) == [
         'mat_hessian', 'mat_input', 'save_lower_only', 'compute_lower_only']
     sig = inspect.signature(gptq_py.gptq_quant)
-    assert list(sig.parameters) == ['weight', 'hessian_hook', 'group_sizes', 'group_bit_widths', 'scale_bit_width',
-                                    'gptq_use_kernel', 'gptq_block_sizes', 'quant_symmetric', 'quant_mse',
-                                    'quant_max_shrink', 'quant_n_grid', 'quant_norm', 'quant_use_kernel', 'save_device']
+    ref_params = ['weight', 'hessian_hook', 'group_sizes', 'group_bit_widths', 'scale_bit_width',
+                  'gptq_use_kernel', 'gptq_block_sizes', 'quant_symmetric', 'quant_mse',
+                  'quant_max_shrink', 'quant_n_grid', 'quant_norm', 'quant_use_kernel', 'save_device']
+    assert list(sig.parameters)[:len(ref_params)] == ref_params
+    # anything beyond the reference's parameters is keyword-only with a default that keeps the reference behaviour
+    for extra in list(sig.parameters.values())[len(ref_params):]:
+        assert extra.kind is inspect.Parameter.KEYWORD_ONLY and extra.default is False
     assert sig.parameters['gptq_use_kernel'].default is True and sig.parameters['quant_mse'].default is True
     h = gptq_py.HessianHook()
     assert (h.hessian, h.n_samples, h.hessian_inv, h.perm, h.perm_inv) == (None, 0, None, None, None)

@@ -119,3 +119,27 @@ def test_rtn_without_hook():
     want = O.quantize(W.float().reshape(64, 2, 128), s, z, mq).reshape(64, 256)
     assert torch.equal(res['quant_meta']['qweight'].float(), want)
     assert res['metrics']['gptq_error'] == 0.0
+
+
+def test_deferred_metrics_equal_immediate_metrics():
+    """gptq_quant(defer_metrics=True): same quant_meta, and a mapping whose values (read later, without a host sync inside
+    the call) equal the floats of the default call; sharded.gptq_quant_group_sharded uses it for every linear of a group."""
+    import gptq_py
+    import sharded
+    W, X = O.synth_linear(256, 512, 8, 256, seed=77)
+    hook, res = _run_gpu(W, X, 4, True, use_kernel=False)
+    gs = torch.full([4], 128, dtype=torch.int32)
+    bw = torch.full([4], 4, dtype=torch.int32)
+    kw = dict(group_sizes=gs, group_bit_widths=bw, scale_bit_width=None, gptq_use_kernel=False, gptq_block_sizes=gs,
+              quant_symmetric=False, quant_mse=False, save_device=torch.device('cuda'))
+    w = W.cuda()
+    imm = gptq_py.gptq_quant(weight=w, hessian_hook=hook, **kw)
+    lazy = gptq_py.gptq_quant(weight=w, hessian_hook=hook, defer_metrics=True, **kw)
+    assert isinstance(lazy['metrics'], gptq_py.DeferredMetrics) and isinstance(imm['metrics'], dict)
+    assert list(lazy['metrics']) == list(imm['metrics'])
+    for k, v in imm['metrics'].items():
+        assert lazy["metrics"][k] == pytest.approx(v, rel=1e-6), k      # colsq is an atomic fp32 sum: order varies run to run
+    assert torch.equal(lazy['quant_meta']['qweight'], imm['quant_meta']['qweight'])
+    grp = sharded.gptq_quant_group_sharded([w, w], hook, **kw)
+    assert dict(grp[0]["metrics"]) == pytest.approx(imm["metrics"], rel=1e-6)
+    assert torch.equal(grp[1]['quant_meta']['qweight'], imm['quant_meta']['qweight'])

@@ -262,3 +262,23 @@ def test_pack_unpack_upper_tiles(D):
     gptq.unpack_upper(p1 + p2, Hs)
     triu = torch.ones(D, D, dtype=torch.bool, device='cuda').triu()
     assert torch.equal(Hs[triu], (H1 + H2)[triu])
+
+
+@pytest.mark.parametrize('D', [256, 1408])
+def test_invert_damping_from_device_scalar(D):
+    """gq_hessian_invert_dev (damping read on the device, what HessianHook.invert uses) == gq_hessian_invert with the same
+    value passed from the host, bit for bit, for the first try and for a cumulative retry (damp * 3)."""
+    import gptq
+    g = torch.Generator(device='cuda').manual_seed(D + 5)
+    X = torch.randn(3 * D, D, device='cuda', generator=g)
+    H = (X.t() @ X).triu()
+    perm = torch.randperm(D, device='cuda', generator=g)
+    damp_dev = (0.01 * H.diagonal().mean()).reshape(())
+    for mult in (1.0, 3.0):
+        Hp_a, U_a, info_a = gptq.hessian_invert(H, perm, 0.25, damp_dev, damp_mult=mult)
+        Hp_b, U_b, info_b = gptq.hessian_invert(H, perm, 0.25, float((damp_dev * mult).item()))
+        torch.cuda.synchronize()
+        assert int(info_a.item()) == 0 and int(info_b.item()) == 0
+        assert torch.equal(Hp_a, Hp_b) and torch.equal(U_a, U_b)
+    with pytest.raises(gptq.GptqB200Error):
+        gptq.hessian_invert(H, perm, 0.25, damp_dev.double())

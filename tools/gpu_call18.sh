@@ -1,0 +1,12 @@
+#!/bin/bash
+tag=${1:-r02_v18}
+mkdir -p gpurun_out
+export PYTHONDONTWRITEBYTECODE=1
+timeout 900 python -m pytest tests/test_gpu_invert.py tests/test_gpu_solver.py tests/test_gpu_config_shapes.py tests/test_gpu_e2e.py -m gpu -x -q --timeout 600 -p no:cacheprovider > gpurun_out/${tag}_tests.log 2>&1; echo "tests rc=$?"; tail -4 gpurun_out/${tag}_tests.log
+timeout 600 python tools/invert_time.py 4096 11008 > gpurun_out/${tag}_invert_time.jsonl 2> gpurun_out/${tag}_invert_time.err; echo "invert_time rc=$?"; cat gpurun_out/${tag}_invert_time.jsonl; tail -3 gpurun_out/${tag}_invert_time.err
+timeout 400 python bench.py --no-cpu --no-w4a16 > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err; echo "bench rc=$?"
+python - <<PY
+import json
+d=json.loads(open('gpurun_out/${tag}_bench.json').read().strip().splitlines()[-1])
+print('value', round(d['value'],5), 'e2e', round(d['e2e']['value'],4), {k:(round(v,5) if isinstance(v,float) else v) for k,v in d['detail'].items() if k.endswith('per_layer')}, d['clocks'])
+PY
