@@ -48,12 +48,13 @@ __device__ __forceinline__ float rsqrt_nr(float p) {
 }
 
 template <int PC>
-__global__ void __launch_bounds__(256, (PC <= 64) ? 2 : 1)
+__global__ void __launch_bounds__(256, 1)
 chol_panel_kernel(float* __restrict__ A, int D, int o, int n, int rest, int* __restrict__ info, long long* __restrict__ dbg) {
   constexpr int W = NB + PC;                 // row pitch of the shared block row
   extern __shared__ __align__(16) float sm[];
   float* S = sm;                             // [NB][W]
   float* rinv = sm + NB * W;                 // [NB] reciprocals of the diagonal of R_kk
+  int* work_ctr = reinterpret_cast<int*>(sm + NB * W + NB);   // next unclaimed update unit of the current sub-block
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int pc0 = blockIdx.x * PC;           // first panel column of this CTA (relative to o + n)
   // profiling hook (gq_set_solve_debug, first step of a factorisation only): clock64 stamps of warps 0 and 1 of CTA 0
@@ -157,24 +158,35 @@ chol_panel_kernel(float* __restrict__ A, int D, int o, int n, int rest, int* __r
       ri = ri_next;
     });
   };
-  // ---- C: rank-16 update of the 4 rows of group g behind sub-block so:  S[i][c] -= sum_j X[j][i] X[j][c]  (c >= i needed)
-  auto update_group = [&](int so, int g) {
-    const int i0 = so + SBK + 4 * g;
-    float4 xi[SBK];
+  // ---- C: rank-16 update of the 8 rows of group g behind sub-block so:  S[i][c] -= sum_j X[j][i] X[j][c]  (c >= i needed),
+  // 32-column chunks [first, last) counted from the chunk that holds the group's own diagonal.  The update is bound by
+  // shared-memory traffic: per chunk a lane reads 16 values of its column and reads + writes its 8 outputs for 128 fmas
+  // (the row factors X[j][i] stay in registers), 1 B/fma against the 1.5 B/fma of 4-row groups.
+  auto update_group = [&](int so, int g, int first, int last) {
+    const int i0 = so + SBK + 8 * g;
+    float4 xa[SBK], xb[SBK];
 #pragma unroll
-    for (int j = 0; j < SBK; ++j) xi[j] = *reinterpret_cast<const float4*>(S + (so + j) * W + i0);
+    for (int j = 0; j < SBK; ++j) {
+      xa[j] = *reinterpret_cast<const float4*>(S + (so + j) * W + i0);
+      xb[j] = *reinterpret_cast<const float4*>(S + (so + j) * W + i0 + 4);
+    }
+    const int c_begin = (i0 & ~31) + 32 * first + lane;
+    const int c_end = min(W, (i0 & ~31) + 32 * last);
 #pragma unroll 1
-    for (int c = (i0 & ~31) + lane; c < W; c += 32) {
-      float a0 = S[(i0 + 0) * W + c], a1 = S[(i0 + 1) * W + c];
-      float a2 = S[(i0 + 2) * W + c], a3 = S[(i0 + 3) * W + c];
+    for (int c = c_begin; c < c_end; c += 32) {
+      float a[8];
+#pragma unroll
+      for (int r = 0; r < 8; ++r) a[r] = S[(i0 + r) * W + c];
 #pragma unroll
       for (int j = 0; j < SBK; ++j) {
         const float xc = S[(so + j) * W + c];
-        a0 = fmaf(-xi[j].x, xc, a0); a1 = fmaf(-xi[j].y, xc, a1);
-        a2 = fmaf(-xi[j].z, xc, a2); a3 = fmaf(-xi[j].w, xc, a3);
+        a[0] = fmaf(-xa[j].x, xc, a[0]); a[1] = fmaf(-xa[j].y, xc, a[1]);
+        a[2] = fmaf(-xa[j].z, xc, a[2]); a[3] = fmaf(-xa[j].w, xc, a[3]);
+        a[4] = fmaf(-xb[j].x, xc, a[4]); a[5] = fmaf(-xb[j].y, xc, a[5]);
+        a[6] = fmaf(-xb[j].z, xc, a[6]); a[7] = fmaf(-xb[j].w, xc, a[7]);
       }
-      S[(i0 + 0) * W + c] = a0; S[(i0 + 1) * W + c] = a1;
-      S[(i0 + 2) * W + c] = a2; S[(i0 + 3) * W + c] = a3;
+#pragma unroll
+      for (int r = 0; r < 8; ++r) S[(i0 + r) * W + c] = a[r];
     }
   };
 
@@ -185,61 +197,82 @@ chol_panel_kernel(float* __restrict__ A, int D, int o, int n, int rest, int* __r
     const int so = s * SBK;
     int groups = 0;
     if (s >= 0) {
-      // ---- B: rows so..so+15 of every later column: forward substitution, one thread per column
+      // ---- B: rows so..so+15 of every later column: forward substitution, one thread per column; the 16 x 16 factor is
+      // read with 16-byte broadcast loads (36 instead of 120 shared-memory instructions per thread)
       {
         const int c = so + SBK + tid;
         if (c < W) {
           float x[SBK];
 #pragma unroll
           for (int j = 0; j < SBK; ++j) x[j] = S[(so + j) * W + c];
+          float ri[SBK];
 #pragma unroll
-          for (int j = 0; j < SBK; ++j) {
-            x[j] *= rinv[so + j];
-#pragma unroll
-            for (int i = j + 1; i < SBK; ++i) x[i] = fmaf(-S[(so + j) * W + so + i], x[j], x[i]);
+          for (int q = 0; q < SBK / 4; ++q) {
+            const float4 v = *reinterpret_cast<const float4*>(rinv + so + 4 * q);
+            ri[4 * q] = v.x; ri[4 * q + 1] = v.y; ri[4 * q + 2] = v.z; ri[4 * q + 3] = v.w;
           }
+          static_for<SBK>([&](auto J) {
+            constexpr int j = decltype(J)::value;
+            x[j] *= ri[j];
+            static_for<SBK / 4>([&](auto Q) {
+              constexpr int q = decltype(Q)::value;
+              if constexpr (4 * q + 3 > j) {
+                const float4 v = *reinterpret_cast<const float4*>(S + (so + j) * W + so + 4 * q);
+                if constexpr (4 * q + 0 > j) x[4 * q + 0] = fmaf(-v.x, x[j], x[4 * q + 0]);
+                if constexpr (4 * q + 1 > j) x[4 * q + 1] = fmaf(-v.y, x[j], x[4 * q + 1]);
+                if constexpr (4 * q + 2 > j) x[4 * q + 2] = fmaf(-v.z, x[j], x[4 * q + 2]);
+                if constexpr (4 * q + 3 > j) x[4 * q + 3] = fmaf(-v.w, x[j], x[4 * q + 3]);
+              }
+            });
+          });
 #pragma unroll
           for (int j = 0; j < SBK; ++j) S[(so + j) * W + c] = x[j];
         }
+        if (tid == 0) *work_ctr = 0;
       }
       __syncthreads();
       stamp();                               // B done
       if (s == NB / SBK - 1) break;
-      // ---- C with look-ahead: warps 0-3 first bring the NEXT sub-block's 16 rows up to date (one 4-row group each),
-      // then warp 0 factors the next diagonal sub-block while the other seven warps update the remaining rows
-      groups = (NB - so - SBK) / 4;
-      if (warp < 4) {
-        update_group(so, warp);
-        asm volatile("bar.sync 1, 128;" ::: "memory");
+      // ---- C with look-ahead: warps 0-1 first bring the chunk that holds the NEXT diagonal sub-block up to date (one
+      // 8-row group each, one 32-column chunk), then warp 0 factors it while everybody else -- and warp 0 afterwards --
+      // claims the remaining update units from a shared counter
+      groups = (NB - so - SBK) / 8;
+      if (warp < 2) {
+        update_group(so, warp, 0, 1);
+        asm volatile("bar.sync 1, 64;" ::: "memory");
       }
-      stamp();                               // look-ahead rows done (warps 0-3)
+      stamp();                               // look-ahead chunk done (warps 0-1)
     }
-    if (warp == 0) {
-      factor_sub(so + SBK);
-    } else {
-#pragma unroll 1
-      for (int g = 4 + (warp - 1); g < groups; g += 7) update_group(so, g);
+    if (warp == 0) factor_sub(so + SBK);
+    if (s >= 0) {
+      stamp();                               // factor done (warp 0)
+      // units: groups 2.. whole (longest first), then the rest of the two look-ahead groups
+      for (;;) {
+        int u = 0;
+        if (lane == 0) u = atomicAdd(work_ctr, 1);
+        u = __shfl_sync(0xffffffffu, u, 0);
+        if (u >= groups) break;
+        if (u < groups - 2) update_group(so, u + 2, 0, 8);
+        else update_group(so, u - (groups - 2), 1, 8);
+      }
     }
-    stamp();                                 // factor (warp 0) / remaining updates (warp 1) done
+    stamp();                                 // updates done
     __syncthreads();
     stamp();
   }
 
   // ---- write back: the factor (CTA 0 only) and this CTA's panel columns
   if (blockIdx.x == 0) {
+    // the whole diagonal block in 16-byte stores, zeros below the diagonal (nothing reads that part of A again before
+    // trtri_diag_kernel overwrites the block; branch-free, CTA 0 is the last one to finish)
     for (int idx = tid; idx < n * (n / 4); idx += 256) {
       const int r = idx / (n / 4), c4 = (idx - r * (n / 4)) * 4;
-      if (c4 + 3 >= r) {                       // only groups that touch the upper triangle; entries below it untouched
-        float4 v = *reinterpret_cast<const float4*>(S + r * W + c4);
-        float* dst = A + (size_t)(o + r) * D + o + c4;
-        if (c4 >= r) *reinterpret_cast<float4*>(dst) = v;
-        else {
-          if (c4 + 0 >= r) dst[0] = v.x;
-          if (c4 + 1 >= r) dst[1] = v.y;
-          if (c4 + 2 >= r) dst[2] = v.z;
-          if (c4 + 3 >= r) dst[3] = v.w;
-        }
-      }
+      float4 v = *reinterpret_cast<const float4*>(S + r * W + c4);
+      v.x = (c4 + 0 >= r) ? v.x : 0.f;
+      v.y = (c4 + 1 >= r) ? v.y : 0.f;
+      v.z = (c4 + 2 >= r) ? v.z : 0.f;
+      v.w = (c4 + 3 >= r) ? v.w : 0.f;
+      *reinterpret_cast<float4*>(A + (size_t)(o + r) * D + o + c4) = v;
     }
     if (bad) atomicExch(info, 1);
   }
@@ -256,7 +289,7 @@ chol_panel_kernel(float* __restrict__ A, int D, int o, int n, int rest, int* __r
 
 template <int PC>
 int launch_cp(float* A, int D, int o, int n, int rest, int* info, cudaStream_t st) {
-  const int smem = (NB * (NB + PC) + NB) * (int)sizeof(float);
+  const int smem = (NB * (NB + PC) + NB + 4) * (int)sizeof(float);
   static PerDeviceFlag attr_set;   // function attributes are per device
   if (!attr_set) {
     if (cudaFuncSetAttribute(chol_panel_kernel<PC>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess)
@@ -277,6 +310,14 @@ int launch_cp(float* A, int D, int o, int n, int rest, int* info, cudaStream_t s
 int chol_factor_panel(float* A, int D, int o, int n, int rest, int* info_dev, cudaStream_t st) {
   if ((n & 3) || (rest & 3) || (D & 3)) return GQ_ERR_SHAPE;
   if (rest <= 0) return launch_cp<0>(A, D, o, n, 0, info_dev, st);
+  // one CTA per SM (the update tiles want > 128 registers): 64 panel columns per CTA while that fits one wave, else 128
+  static int n_sms = 0;
+  if (n_sms == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n_sms <= 0) n_sms = 148;
+  }
+  if ((rest + 63) / 64 > n_sms) return launch_cp<128>(A, D, o, n, rest, info_dev, st);
   return launch_cp<64>(A, D, o, n, rest, info_dev, st);
 }
 

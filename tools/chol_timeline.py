@@ -23,7 +23,7 @@ labels = ['entry', 'staged', 'factor(0) done', 'sync']
 for s in range(8):
     labels += [f's{s} B done']
     if s < 7:
-        labels += [f's{s} look-ahead done', f's{s} factor / updates done', f's{s} sync']
+        labels += [f's{s} look-ahead chunk done', f's{s} factor done (warp 0)', f's{s} updates done', f's{s} sync']
 labels += ['written back']
 for i, name in enumerate(labels):
     print(f'  {name:28s} {t[i] - t0:8d} | {t[64 + i] - t0:8d}')
