@@ -55,17 +55,20 @@ template <> struct Pair<__half> { using type = __half2; };
 template <> struct Pair<__nv_bfloat16> { using type = __nv_bfloat162; };
 template <> struct Pair<float> { using type = float2; };
 
+// Tile of PREP_ROWS weight rows x 64 source columns: W is read in its own order (4- / 8-byte loads along a row), every
+// destination column gets PREP_ROWS contiguous floats (512 B) and one atomic for its sum of squares.
+constexpr int PREP_ROWS = 128;
 template <typename T>
 __global__ void __launch_bounds__(256) prep_weight_scatter_kernel(const T* __restrict__ W, const int64_t* __restrict__ pinv,
                                                                   float* __restrict__ Wt, T* __restrict__ orig_t,
                                                                   float* __restrict__ colsq, int R, int C) {
   using T2 = typename Pair<T>::type;
-  __shared__ T tile[64][34];                       // [source column][row], pitch 34: 2-element stores hit distinct banks
-  const int r0 = blockIdx.x * 32, k0 = blockIdx.y * 64;
+  __shared__ T tile[64][PREP_ROWS + 2];            // [source column][row], pitch + 2: 2-element stores hit distinct banks
+  const int r0 = blockIdx.x * PREP_ROWS, k0 = blockIdx.y * 64;
   const int tx = threadIdx.x, ty = threadIdx.y;    // (32, 8)
   const int k = k0 + 2 * tx;
-#pragma unroll
-  for (int yy = ty; yy < 32; yy += 8) {
+#pragma unroll 4
+  for (int yy = ty; yy < PREP_ROWS; yy += 8) {
     const int r = r0 + yy;
     T a = T(0.f), b = T(0.f);
     if (r < R && k + 1 < C) {                      // C is even (checked by the launcher)
@@ -76,20 +79,24 @@ __global__ void __launch_bounds__(256) prep_weight_scatter_kernel(const T* __res
     tile[2 * tx + 1][yy] = b;
   }
   __syncthreads();
-  const int r = r0 + tx;
-#pragma unroll
+#pragma unroll 2
   for (int kk = ty; kk < 64; kk += 8) {
     const int ks = k0 + kk;                        // warp-uniform
     if (ks >= C) break;
     const int c = pinv ? (int)pinv[ks] : ks;
-    const T w = tile[kk][tx];
-    const float v = to_f32<T>(w);
-    if (r < R) {
-      Wt[(size_t)c * R + r] = v;
-      if (orig_t) orig_t[(size_t)c * R + r] = w;
+    float sq = 0.f;
+#pragma unroll
+    for (int q = 0; q < PREP_ROWS / 32; ++q) {
+      const int r = r0 + tx + 32 * q;
+      const T w = tile[kk][tx + 32 * q];
+      const float v = to_f32<T>(w);
+      if (r < R) {
+        Wt[(size_t)c * R + r] = v;
+        if (orig_t) orig_t[(size_t)c * R + r] = w;
+      }
+      sq = fmaf(v, v, sq);                         // rows past R hold zeros
     }
     if (colsq) {
-      float sq = v * v;                            // rows past R hold zeros
 #pragma unroll
       for (int o = 16; o > 0; o >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, o);
       if (tx == 0) atomicAdd(colsq + c, sq);
@@ -206,6 +213,52 @@ __global__ void transpose_pack_kernel(const uint8_t* __restrict__ codes_t, uint8
   }
 }
 
+// codes_t (C, R) -> codes (R, C) / packed (R, C/8) for R % 4 == 0 and C % 8 == 0: 128 x 128 tiles, 4 x 4 byte blocks are
+// transposed in registers (__byte_perm), so global and shared memory only ever see 4-byte accesses: a lane reads 4 rows of
+// codes_t (4 bytes along r each), writes four words [r][4 c] to shared memory, and rows of 128 codes leave as 128-byte
+// stores (64 bytes for the packed nibbles).
+__global__ void __launch_bounds__(256) transpose_pack4_kernel(const uint8_t* __restrict__ codes_t, uint8_t* __restrict__ codes,
+                                                              uint32_t* __restrict__ packed, int R, int C) {
+  __shared__ uint32_t T[128][33];                  // [r][c / 4]
+  const int c0 = blockIdx.x * 128, r0 = blockIdx.y * 128;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int jl = lane & 7, il = lane >> 3;         // 8 r-blocks x 4 c-blocks per warp step
+#pragma unroll
+  for (int step = warp; step < 32; step += 8) {    // 32 steps: (c-block group of 4) x (r-block group of 8)
+    const int i = (step >> 2) * 4 + il;            // c-block 0..31
+    const int j = (step & 3) * 8 + jl;             // r-block 0..31
+    const int c = c0 + 4 * i, r = r0 + 4 * j;
+    uint32_t v0 = 0, v1 = 0, v2 = 0, v3 = 0;
+    if (r < R) {                                   // R % 4 == 0: the whole word is in range
+      if (c + 0 < C) v0 = *reinterpret_cast<const uint32_t*>(codes_t + (size_t)(c + 0) * R + r);
+      if (c + 1 < C) v1 = *reinterpret_cast<const uint32_t*>(codes_t + (size_t)(c + 1) * R + r);
+      if (c + 2 < C) v2 = *reinterpret_cast<const uint32_t*>(codes_t + (size_t)(c + 2) * R + r);
+      if (c + 3 < C) v3 = *reinterpret_cast<const uint32_t*>(codes_t + (size_t)(c + 3) * R + r);
+    }
+    // v_k = bytes (r..r+3) of column c + k  ->  w_m = bytes (c..c+3) of row r + m
+    const uint32_t t0 = __byte_perm(v0, v1, 0x5140), t1 = __byte_perm(v0, v1, 0x7362);   // [v0.b0 v1.b0 v0.b1 v1.b1], [v0.b2 v1.b2 v0.b3 v1.b3]
+    const uint32_t t2 = __byte_perm(v2, v3, 0x5140), t3 = __byte_perm(v2, v3, 0x7362);
+    T[4 * j + 0][i] = __byte_perm(t0, t2, 0x5410);
+    T[4 * j + 1][i] = __byte_perm(t0, t2, 0x7632);
+    T[4 * j + 2][i] = __byte_perm(t1, t3, 0x5410);
+    T[4 * j + 3][i] = __byte_perm(t1, t3, 0x7632);
+  }
+  __syncthreads();
+#pragma unroll 4
+  for (int rr = warp; rr < 128; rr += 8) {
+    const int r = r0 + rr, c = c0 + 4 * lane;
+    const uint32_t w = T[rr][lane];
+    if (r < R && c < C) {                          // C % 8 == 0: the whole word is in range
+      if (codes) *reinterpret_cast<uint32_t*>(codes + (size_t)r * C + c) = w;
+    }
+    if (packed) {
+      const uint32_t nib = (w & 0xFu) | ((w >> 4) & 0xF0u) | ((w >> 8) & 0xF00u) | ((w >> 12) & 0xF000u);
+      const uint32_t hi = __shfl_down_sync(0xffffffffu, nib, 1);
+      if (!(lane & 1) && r < R && c < C) packed[(size_t)r * (C / 8) + c / 8] = nib | (hi << 16);
+    }
+  }
+}
+
 }  // namespace
 
 int prep_weight_t(const void* W, int fmt, const int64_t* perm, float* Wt, void* orig_t, float* colsq, int R, int C,
@@ -224,7 +277,7 @@ int prep_weight_scatter(const void* W, int fmt, const int64_t* perm_inv, float* 
                         cudaStream_t st) {
   if (C & 1) return GQ_ERR_SHAPE;
   if (reinterpret_cast<uintptr_t>(W) & 7) return GQ_ERR_ALIGN;
-  dim3 block(32, 8), grid((R + 31) / 32, (C + 63) / 64);
+  dim3 block(32, 8), grid((R + PREP_ROWS - 1) / PREP_ROWS, (C + 63) / 64);
   if (colsq && cudaMemsetAsync(colsq, 0, (size_t)C * sizeof(float), st) != cudaSuccess) return GQ_ERR_CUDA;
   GQ_LAUNCHED();
   if (fmt == 0) prep_weight_scatter_kernel<__half><<<grid, block, 0, st>>>((const __half*)W, perm_inv, Wt, (__half*)orig_t, colsq, R, C);
@@ -286,8 +339,12 @@ int unpack_int4(const uint32_t* packed, uint8_t* codes, int R, int C, cudaStream
 int transpose_pack_int4(const uint8_t* codes_t, uint8_t* codes, uint32_t* packed, int R, int C, cudaStream_t st) {
   if (C % 8 != 0) return GQ_ERR_SHAPE;
   if (R == 0 || C == 0) return GQ_OK;
-  dim3 block(32, 8), grid((C + 31) / 32, (R + 31) / 32);
   GQ_LAUNCHED();
+  if ((R & 3) == 0 && (C & 7) == 0 && ((reinterpret_cast<uintptr_t>(codes_t) | reinterpret_cast<uintptr_t>(codes)) & 3) == 0) {
+    transpose_pack4_kernel<<<dim3((C + 127) / 128, (R + 127) / 128), 256, 0, st>>>(codes_t, codes, packed, R, C);
+    return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
+  }
+  dim3 block(32, 8), grid((C + 31) / 32, (R + 31) / 32);
   transpose_pack_kernel<<<grid, block, 0, st>>>(codes_t, codes, packed, R, C);
   return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
 }
