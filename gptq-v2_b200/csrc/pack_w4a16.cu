@@ -171,6 +171,7 @@ __global__ void unpack_kernel(const uint32_t* __restrict__ packed, uint8_t* __re
 template <typename T> __device__ __forceinline__ T from_f32(float v);
 template <> __device__ __forceinline__ __half from_f32<__half>(float v) { return __float2half_rn(v); }
 template <> __device__ __forceinline__ __nv_bfloat16 from_f32<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+template <> __device__ __forceinline__ float from_f32<float>(float v) { return v; }
 
 template <typename T>
 __global__ void dequant_w4_kernel(const uint32_t* __restrict__ qw, const T* __restrict__ scale_t,
@@ -210,6 +211,76 @@ __global__ void transpose_pack_kernel(const uint8_t* __restrict__ codes_t, uint8
         packed[(size_t)r * (C / 8) + c / 8] = w;
       }
     }
+  }
+}
+
+// Result assembly of one linear (gptq_py.py:196-199, 216-237) behind the solver, replacing five torch passes:
+//   scale_out (R, G) = T(scale_gr (G, R)^T), qzero_out (R, G) = uint8(qzero_gr^T)        32 x 32 tiles through shared memory
+//   stats[2] += sum_i colsq[i] / U[p_i][p_i]^2, p_i = perm[i]   (the reference's gptq_norm, W unpermuted against diag(U))
+template <typename T>
+__global__ void __launch_bounds__(256) finalize_params_kernel(const float* __restrict__ scale_gr, const float* __restrict__ qzero_gr,
+                                                              int R, int G, T* __restrict__ scale_out, uint8_t* __restrict__ qzero_out,
+                                                              const float* __restrict__ colsq, const int64_t* __restrict__ perm,
+                                                              const float* __restrict__ U, int C, double* __restrict__ stats) {
+  __shared__ float ts[32][33], tz[32][33];
+  const int g0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int yy = ty; yy < 32; yy += 8) {
+    const int g = g0 + yy, r = r0 + tx;
+    const bool in = g < G && r < R;
+    ts[yy][tx] = in ? scale_gr[(size_t)g * R + r] : 0.f;
+    tz[yy][tx] = in ? qzero_gr[(size_t)g * R + r] : 0.f;
+  }
+  __syncthreads();
+  for (int yy = ty; yy < 32; yy += 8) {
+    const int r = r0 + yy, g = g0 + tx;
+    if (r < R && g < G) {
+      scale_out[(size_t)r * G + g] = from_f32<T>(ts[tx][yy]);
+      qzero_out[(size_t)r * G + g] = (uint8_t)(int)tz[tx][yy];
+    }
+  }
+  if (U != nullptr && blockIdx.y == 0) {
+    double acc = 0.0;
+    for (int i = blockIdx.x * 256 + threadIdx.x; i < C; i += gridDim.x * 256) {
+      const size_t p = perm ? (size_t)perm[i] : (size_t)i;
+      const double d = (double)U[p * C + p];
+      acc += (double)colsq[i] / (d * d);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (tx == 0 && acc != 0.0) atomicAdd(stats + 2, acc);
+  }
+}
+
+// stats[3] += sum T(w * w) over the n weights (gptq_py.py:237 squares in the weight dtype; the mean is taken by the caller)
+template <typename T>
+__global__ void __launch_bounds__(256) sumsq_kernel(const T* __restrict__ W, size_t n, double* __restrict__ stats) {
+  float acc = 0.f;
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  constexpr int V = 16 / (int)sizeof(T);                    // elements per 16-byte load
+  const size_t nv = ((reinterpret_cast<uintptr_t>(W) & 15) == 0) ? n / V : 0;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += stride) {
+    const uint4 raw = reinterpret_cast<const uint4*>(W)[i];
+    const T* e = reinterpret_cast<const T*>(&raw);
+#pragma unroll
+    for (int k = 0; k < V; ++k) {
+      const float w = to_f32<T>(e[k]);
+      acc += to_f32<T>(from_f32<T>(w * w));
+    }
+  }
+  for (size_t i = nv * V + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const float w = to_f32<T>(W[i]);
+    acc += to_f32<T>(from_f32<T>(w * w));
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  __shared__ float part[8];
+  if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int w = 0; w < 8; ++w) t += (double)part[w];
+    atomicAdd(stats + 3, t);
   }
 }
 
@@ -346,6 +417,34 @@ int transpose_pack_int4(const uint8_t* codes_t, uint8_t* codes, uint32_t* packed
   }
   dim3 block(32, 8), grid((C + 31) / 32, (R + 31) / 32);
   transpose_pack_kernel<<<grid, block, 0, st>>>(codes_t, codes, packed, R, C);
+  return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
+}
+
+// Everything gptq_quant needs after the solver, queued with one call: stats4 = [sum err^2, sum (quant - W)^2, gptq_norm sum,
+// sum T(w^2)] (doubles, overwritten) and the (R, G) scale / zero-point tables of quant_meta.
+int finalize_quant(const float* err_t, const float* quant_t, const void* orig_t, const void* W, int fmt, int R, int C,
+                   const float* scale_gr, const float* qzero_gr, int G, void* scale_out, uint8_t* qzero_out, const float* colsq,
+                   const int64_t* perm, const float* U, double* stats4, cudaStream_t st) {
+  if (R <= 0 || C <= 0 || G <= 0) return GQ_ERR_ARG;
+  if (fmt < 0 || fmt > 2) return GQ_ERR_DTYPE;
+  const size_t n = (size_t)R * C;
+  if (cudaMemsetAsync(stats4, 0, 4 * sizeof(double), st) != cudaSuccess) return GQ_ERR_CUDA;
+  int rc = solve_metrics(err_t ? err_t : quant_t, quant_t, orig_t, fmt, n, stats4, st);      // zeroes and fills stats4[0..1]
+  if (rc != GQ_OK) return rc;
+  if (U != nullptr && colsq == nullptr) return GQ_ERR_ARG;
+  const dim3 grid((G + 31) / 32, (R + 31) / 32);
+  const unsigned sblocks = (unsigned)((n / 8 + 255) / 256 < 148 * 8 ? (n / 8 + 255) / 256 + 1 : 148 * 8);
+  GQ_LAUNCHED(); GQ_LAUNCHED();
+  if (fmt == 0) {
+    finalize_params_kernel<__half><<<grid, 256, 0, st>>>(scale_gr, qzero_gr, R, G, (__half*)scale_out, qzero_out, colsq, perm, U, C, stats4);
+    sumsq_kernel<__half><<<sblocks, 256, 0, st>>>((const __half*)W, n, stats4);
+  } else if (fmt == 1) {
+    finalize_params_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(scale_gr, qzero_gr, R, G, (__nv_bfloat16*)scale_out, qzero_out, colsq, perm, U, C, stats4);
+    sumsq_kernel<__nv_bfloat16><<<sblocks, 256, 0, st>>>((const __nv_bfloat16*)W, n, stats4);
+  } else {
+    finalize_params_kernel<float><<<grid, 256, 0, st>>>(scale_gr, qzero_gr, R, G, (float*)scale_out, qzero_out, colsq, perm, U, C, stats4);
+    sumsq_kernel<float><<<sblocks, 256, 0, st>>>((const float*)W, n, stats4);
+  }
   return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
 }
 

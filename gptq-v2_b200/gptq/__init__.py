@@ -14,7 +14,7 @@ import torch
 from . import _cabi
 from ._cabi import GptqB200Error, check, lib, ptr, require_contig, require_cuda, stream_of
 
-__all__ = ['accumulate_hessian', 'gptq_quantize_range', 'hessian_syrk', 'hessian_invert', 'w4a16_dequant', 'pack_upper', 'unpack_upper', 'prep_weight_t', 'prep_weight_t2', 'solve_metrics', 'gptq_solve_ex', 'find_params', 'mse_refine', 'find_params_cols', 'mse_refine_cols', 'rtn_quantize',
+__all__ = ['accumulate_hessian', 'gptq_quantize_range', 'hessian_syrk', 'hessian_invert', 'w4a16_dequant', 'pack_upper', 'unpack_upper', 'prep_weight_t', 'prep_weight_t2', 'solve_metrics', 'finalize_quant', 'gptq_solve_ex', 'find_params', 'mse_refine', 'find_params_cols', 'mse_refine_cols', 'rtn_quantize',
            'gptq_solve', 'gptq_solve_static', 'pack_int4', 'unpack_int4', 'transpose_pack_int4', 'w4a16_gemm', 'w4a16_gemv_static', 'gemm_f16_nt', 'sgemm', 'gemm_tf32x3', 'set_tf32x3', 'set_solve_super', 'set_solve_fused', 'set_tf32_kchunk', 'set_syrk_kchunk', 'set_w4a16_path', 'set_pdl',
            'GptqB200Error']
 
@@ -169,6 +169,30 @@ def solve_metrics(err_t: torch.Tensor, quant_t: torch.Tensor, orig_t: torch.Tens
         check(lib.gq_solve_metrics(ptr(err_t), ptr(quant_t), ptr(orig_t), _cabi.DTYPE_CODE[orig_t.dtype], err_t.numel(),
                                    ptr(out), stream_of(err_t)), 'gq_solve_metrics')
     return out
+
+
+def finalize_quant(err_t, quant_t: torch.Tensor, orig_t: torch.Tensor, W: torch.Tensor, scale_gr: torch.Tensor,
+                   qzero_gr: torch.Tensor, colsq, perm, U):
+    """Result assembly behind the solver in one library call (gq_finalize_quant): -> (stats, scale, qzero) with stats a
+    float64 device tensor [sum err^2, sum (quant - W)^2, sum_i colsq[i] / U[perm_i, perm_i]^2, sum dtype(w^2)], scale (R, G) in
+    W.dtype and qzero (R, G) uint8 (the transposes of the solver's (G, R) fp32 tables)."""
+    dev = require_cuda(err_t, quant_t, orig_t, W, scale_gr, qzero_gr, colsq, perm, U)
+    require_contig(err_t=err_t, quant_t=quant_t, orig_t=orig_t, W=W, scale_gr=scale_gr, qzero_gr=qzero_gr, colsq=colsq,
+                   perm=perm, U=U)
+    C_, R = quant_t.shape
+    G = scale_gr.shape[0]
+    assert tuple(W.shape) == (R, C_) and orig_t.shape == quant_t.shape and orig_t.dtype == W.dtype
+    assert tuple(scale_gr.shape) == (G, R) == tuple(qzero_gr.shape) and scale_gr.dtype == qzero_gr.dtype == torch.float32
+    if perm is not None and perm.dtype != torch.int64:
+        raise GptqB200Error('perm must be int64')
+    stats = torch.empty(4, dtype=torch.float64, device=dev)
+    scale = torch.empty(R, G, dtype=W.dtype, device=dev)
+    qzero = torch.empty(R, G, dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.gq_finalize_quant(ptr(err_t), ptr(quant_t), ptr(orig_t), ptr(W), _cabi.DTYPE_CODE[W.dtype], R, C_,
+                                    ptr(scale_gr), ptr(qzero_gr), G, ptr(scale), ptr(qzero), ptr(colsq), ptr(perm), ptr(U),
+                                    ptr(stats), stream_of(quant_t)), 'gq_finalize_quant')
+    return stats, scale, qzero
 
 
 def gptq_solve(Wt: torch.Tensor, U: torch.Tensor, group: int, maxq: float, want_quant: bool = True):

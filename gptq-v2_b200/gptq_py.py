@@ -84,6 +84,12 @@ class HessianHook:
         return self.hessian_inv
 
 
+def _mean_in_dtype(total: float, n: float, dtype: torch.dtype) -> float:
+    """mean of n values whose (fp32-accumulated) sum is `total`, rounded to `dtype` like torch's reduction (ref :237 takes
+    (weight.abs() ** 2.).mean() in the weight dtype)."""
+    return float(torch.tensor(total / n, dtype=torch.float32).to(dtype))
+
+
 class DeferredMetrics(collections.abc.Mapping):
     """The four metrics of gptq_quant (ref :196-199, :231-237) as a read-only mapping whose values are fetched from the device
     on first access.  gptq_quant(defer_metrics=True) returns it instead of a dict, so that a caller quantising several linears
@@ -91,24 +97,29 @@ class DeferredMetrics(collections.abc.Mapping):
     four sums travel to pinned host memory behind the solver and are read when somebody looks."""
     KEYS = ('gptq_error', 'gptq_norm', 'l2.0_error', 'l2.0_norm')
 
-    def __init__(self, stats: torch.Tensor, n_el: float, has_hook: bool):
-        e2, d2, ns, l2n = stats.unbind(0)
-        zero = torch.zeros_like(e2)
-        self._dev = torch.stack([e2 / n_el if has_hook else zero, ns / n_el if has_hook else zero, d2 / n_el, l2n])
+    def __init__(self, stats: torch.Tensor, n_el: float, has_hook: bool, dtype: torch.dtype):
+        self._stats, self._n_el, self._has_hook, self._dtype = stats, n_el, has_hook, dtype
         self._host = torch.empty(4, dtype=torch.float64, pin_memory=True)
-        self._host.copy_(self._dev, non_blocking=True)
+        self._host.copy_(stats, non_blocking=True)
         self._event = torch.cuda.Event()
         self._event.record()
         self._values = None
 
     def device_values(self) -> torch.Tensor:
         """(4,) float64 on the device, in KEYS order (for reductions that stay on the device)."""
-        return self._dev
+        e2, d2, ns, l2s = self._stats.unbind(0)
+        zero = torch.zeros_like(e2)
+        l2n = (l2s / self._n_el).to(torch.float32).to(self._dtype).double()
+        return torch.stack([e2 / self._n_el if self._has_hook else zero, ns / self._n_el if self._has_hook else zero,
+                            d2 / self._n_el, l2n])
 
     def _resolve(self) -> dict:
         if self._values is None:
             self._event.synchronize()
-            self._values = dict(zip(self.KEYS, self._host.tolist()))
+            e2, d2, ns, l2s = self._host.tolist()
+            n = self._n_el
+            self._values = dict(zip(self.KEYS, (e2 / n if self._has_hook else 0.0, ns / n if self._has_hook else 0.0, d2 / n,
+                                                _mean_in_dtype(l2s, n, self._dtype))))
         return self._values
 
     def __getitem__(self, key):
@@ -304,23 +315,12 @@ def gptq_quant(
     #   gptq_error = mean(err^2);  gptq_norm = mean((W / diag(U))^2) with W unpermuted against the permuted-order diag(U),
     #   reproduced as is (ref :198) = sum_c colsq_orig[c] / diag(U)[c]^2 / (R C);  l2.0_error = mean((quant - W)^2), which
     #   does not depend on the column order;  l2.0_norm in the weight dtype like the reference.
-    sums = _ops.solve_metrics(err_t if err_t is not None else quant_t, quant_t, orig_t)   # float64 [sum err^2, sum (quant - W)^2]
-    if hessian_hook is None:
-        norm_sum = torch.zeros((), dtype=torch.float64, device=device)
-    else:
-        if perm is not None:
-            colsq_orig = torch.empty_like(colsq)
-            colsq_orig[perm] = colsq
-        else:
-            colsq_orig = colsq
-        norm_sum = (colsq_orig.double() / U.diagonal().double() ** 2).sum()
-    l2_norm = (weight.abs() ** 2.).mean()                                        # ref :237 (fp16 / bf16 arithmetic)
+    # One library call queues all of it (gq_finalize_quant): the four sums and the (R, G) scale / zero tables of quant_meta.
+    stats, scale, qzero = _ops.finalize_quant(err_t, quant_t, orig_t, weight_c, scale_gr, qzero_gr,
+                                              colsq if hessian_hook is not None else None, perm, U)
     n_el = float(n_rows * n_columns)
-    stats = torch.stack([sums[0], sums[1], norm_sum, l2_norm.double()])          # read back AFTER the result assembly is queued
 
     qweight, _ = _ops.transpose_pack_int4(codes_t, want_codes=True, want_packed=False)   # (R, C) uint8, permuted order
-    scale = scale_gr.t().to(dtype=dtype).contiguous()                           # (R, G)
-    qzero = qzero_gr.t().to(dtype=torch.uint8).contiguous()                     # (R, G)
     qscale = qscale_gr.t().to(dtype=torch.uint8).contiguous() if exl2 else None  # (R, G)   ref :217
     sscale = sscale_g.to(dtype=dtype) if exl2 else None                          # (G)      ref :218
     if perm is not None:
@@ -341,7 +341,10 @@ def gptq_quant(
         scale, qzero, bits_out = scale[:, ig].contiguous(), qzero[:, ig].contiguous(), bits_out[ig.to(bits_out.device)]
         if exl2:
             qscale, sscale = qscale[:, ig].contiguous(), sscale[ig]
-    perm_inv = perm16.argsort().to(dtype=torch.int16)                           # ref :226
+    if order == list(range(n_groups)) and perm is not None and getattr(hessian_hook, 'perm_inv', None) is not None:
+        perm_inv = hessian_hook.perm_inv.to(dtype=torch.int16)                  # == perm16.argsort() (ref :226) without the sort
+    else:
+        perm_inv = perm16.argsort().to(dtype=torch.int16)                       # ref :226
 
     quant_meta: dict[str, torch.Tensor] = {
         'qweight': qweight.to(device=save_device),
@@ -355,9 +358,10 @@ def gptq_quant(
         'scale_bit_width': scale_bit_width.to(dtype=torch.uint8, device=save_device) if scale_bit_width is not None else None,
     }
     if defer_metrics:
-        return {'quant_meta': quant_meta, 'metrics': DeferredMetrics(stats, n_el, hessian_hook is not None)}
+        return {'quant_meta': quant_meta, 'metrics': DeferredMetrics(stats, n_el, hessian_hook is not None, dtype)}
     # the one host sync of the call, after every kernel of the result assembly has been queued behind the solver
-    e2, d2, ns, l2n = stats.tolist()
+    e2, d2, ns, l2s = stats.tolist()
+    l2n = _mean_in_dtype(l2s, n_el, dtype)
     if hessian_hook is None:
         gptq_error, gptq_norm = 0.0, 0.0                                         # ref :198 (error == 0)
     else:
