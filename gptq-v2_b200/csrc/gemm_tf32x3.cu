@@ -10,14 +10,16 @@
 //   A^T B ~= hi^T hi + hi^T lo + lo^T hi        (3 x kind::tf32, fp32 accumulation in TMEM)
 // whose relative error (~2^-21) is below what reordering an fp32 sum already causes.
 //
-// Pipeline per CTA (persistent over 128 x 256 output tiles, or CTA pairs over 256 x 256 tiles: Cfg<2>; 384 threads):
+// Pipeline per CTA (persistent over 128 x 256 output tiles, or CTA pairs over 256 x 256 tiles: Cfg<2>; 512 threads):
 //   warp 0      TMA producer: [16 k][32 cols] fp32 boxes, SWIZZLE_128B_ATOM_32B (both operands MN-major)
 //   warps 8-11  split: read the landed tile, write hi back in place and lo next to it
 //               (element-wise on identical swizzled addresses, so no layout knowledge needed)
 //   warp 1      one thread issues 3 x tcgen05.mma.kind::tf32 per 8-deep k-slice
-//   warps 4-7   epilogue: tcgen05.ld -> * alpha -> swizzled smem -> TMA reduce-add
-//               (cp.reduce.async.bulk.tensor ... add.f32): C is never read by the SM, the
-//               read-modify-write happens in L2, edges are clipped by the tensor map.
+//   warps 4-7, 12-15  epilogue (32 rows x 128 columns per warp): the k range of a tile leaves tensor memory in chunks
+//               (tcgen05.ld) that are summed in REGISTERS in fp32 round-to-nearest (128 accumulators per thread, paid for
+//               with setmaxnreg: the control and split warps give registers up); at the end of the tile
+//               * alpha -> swizzled smem -> TMA reduce-add (cp.reduce.async.bulk.tensor ... add.f32): C is never read by
+//               the SM, the read-modify-write happens in L2, edges are clipped by the tensor map.
 #include "gptq_b200_internal.h"
 #include "ptx.cuh"
 
@@ -27,6 +29,8 @@ namespace {
 constexpr int TN = 256, BK = 16;
 constexpr int SUB = BK * 128;                       // one [16 k][32 fp32] box = 2 KB
 constexpr int SPLIT_THREADS = 128;                  // warps 8..11 split the landed tile into hi / lo
+constexpr int GEMM_THREADS = 512;                   // 4 control warps, 4 + 4 epilogue warps, 4 split warps
+constexpr int EPI_WARPS = 8;
 constexpr int EPI_BUF = 32 * 128;                   // one 32 x 32 fp32 staging tile
 // CG = 1: one CTA per 128 x 256 output tile.  CG = 2: a CTA pair (cluster of 2, tcgen05 cta_group::2) per 256 x 256
 // tile: each CTA stages its own 128 rows of A and only HALF of B (128 columns), so the shared-memory traffic per flop
@@ -39,7 +43,7 @@ template <int CG> struct Cfg {
   static constexpr int HI_BYTES = (A_SUBS + B_SUBS) * SUB;        // 24 KB / 16 KB
   static constexpr int STAGE_BYTES = 2 * HI_BYTES;                // hi + lo
   static constexpr int STAGES = (CG == 2) ? 6 : 4;                // 192 KB either way
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 4 * 2 * EPI_BUF + 1024 + 256;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_WARPS * EPI_BUF + 1024 + 256;
 };
 
 struct GemmTf32Params {
@@ -82,6 +86,7 @@ __device__ __forceinline__ void tma_store_2d(const void* tmap, uint32_t src, int
 }
 __device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ float rna_tf32(float x) {
   uint32_t r;
@@ -90,7 +95,7 @@ __device__ __forceinline__ float rna_tf32(float x) {
 }
 
 template <int CG>
-__global__ void __launch_bounds__(256 + SPLIT_THREADS, 1)
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
                    const __grid_constant__ CUtensorMap map_c, const GemmTf32Params p) {
   using C = Cfg<CG>;
@@ -100,7 +105,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   uint8_t* smem_gen = smem_raw + (smem_base - smem_u32(smem_raw));
   const uint32_t epi_base = smem_base + STAGES * STAGE_BYTES;
-  const uint32_t bar_base = epi_base + 4 * 2 * EPI_BUF;
+  const uint32_t bar_base = epi_base + EPI_WARPS * EPI_BUF;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto ready_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
   auto empty_bar = [&](int s) { return bar_base + 8u * (2 * STAGES + s); };
@@ -124,7 +129,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
     // full: this CTA's own TMA bytes (its split warps wait on it); ready: one arrival per CTA of the pair (after its split warps have
     // synchronised) on the leader's barrier; empty / tfull: the leader's tcgen05.commit, multicast to both CTAs; tempty: 4 epilogue warps per CTA
     for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(ready_bar(s), CG == 2 ? 2 : SPLIT_THREADS); mbar_init(empty_bar(s), 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 4 * CG); }
+    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), EPI_WARPS * CG); }
     fence_mbar_init();
   }
   if (warp == 2) { tmem_alloc<CG>(tmem_slot, 512); tmem_relinquish<CG>(); }
@@ -135,7 +140,12 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
   // everything above is independent of the predecessor kernel; from here on global memory is read and written
   pdl_launch_dependents();
   pdl_wait();
+  // register file: 512 threads start with 128 registers each; the control (0-3) and split (8-11) warpgroups keep 80, the two
+  // epilogue warpgroups (4-7, 12-15) take 176 for their 128 fp32 accumulators per thread  (128 * (80 + 80 + 176 + 176) = 64 K)
+  // (issued at the top of every role branch: ptxas budgets the registers of the code a setmaxnreg dominates)
+  const bool is_epi = (warp >= 4 && warp < 8) || warp >= 12;
 
+  if (warp < 4) asm volatile("setmaxnreg.dec.sync.aligned.u32 80;");
   if (warp == 0) {
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
@@ -205,8 +215,9 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
         }
       }
     }
-  } else if (warp >= 8) {
+  } else if (warp >= 8 && warp < 12) {
     // ---- split hi / lo, element-wise over the 24 KB that just landed
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 80;");
     const int tid = threadIdx.x - 256;                 // 0..SPLIT_THREADS-1
     int stage = 0; uint32_t phase = 0;
     const uint32_t lead_ready0 = (CG == 2) ? mapa(ready_bar(0), 0) : 0u;     // the leader's ready barriers
@@ -260,56 +271,59 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
         if (++stage == STAGES) { stage = 0; phase ^= 1u; }
       }
     }
-  } else if (warp >= 4) {
-    // ---- epilogue
-    const int we = warp - 4;
-    const uint32_t stg0 = epi_base + we * 2 * EPI_BUF;
+  } else if (is_epi) {
+    // ---- epilogue: warp (we, half) owns TMEM lanes [32 we, 32 we + 32) (its hardware lane quarter) and accumulator columns
+    // [128 half, 128 half + 128): one output row and 128 columns per thread
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 176;");
+    const int we = warp & 3, half = warp >= 12 ? 1 : 0;
+    const uint32_t stg = epi_base + (we + 4 * half) * EPI_BUF;
     int it = 0;
-    int buf = 0;
     for (int t = walker; t < n_tiles; t += n_walkers) {
       const TileInfo ti = decode_tile<CG>(p, t);
       if (ti.skip) continue;
       const Tf32Problem& pq = p.p[ti.prob];
-      const int m0 = ti.m0 + row_off, n0 = ti.n0;
+      const int m0 = ti.m0 + row_off, n0 = ti.n0 + 128 * half;
       const int kstep = p.kchunk > 0 ? p.kchunk : (ti.kb1 - ti.kb0 > 0 ? ti.kb1 - ti.kb0 : 1);
-      for (int kc = ti.kb0; kc < ti.kb1 || kc == ti.kb0; kc += kstep) {
-      // the first chunk of a store-mode tile is stored, the others are added to it: the store must have completed
-      const bool plain_store = (p.flags & TF32_STORE) && kc == ti.kb0;
-      if ((p.flags & TF32_STORE) && kc == ti.kb0 + kstep) {
-        if (lane == 0) bulk_wait_all();
-        __syncwarp();
-      }
-      const int acc = it & 1;
-      const uint32_t acc_phase = (it >> 1) & 1u;
-      ++it;
-      mbar_wait(tfull_bar(acc), acc_phase);
-      tc_fence_after();
-      const uint32_t t_row = tmem_base + (uint32_t(32 * we) << 16) + acc * TN;
-      const bool rows_live = (m0 + 32 * we) < pq.M;
+      float accv[128];
+#pragma unroll
+      for (int i = 0; i < 128; ++i) accv[i] = 0.f;
 #pragma unroll 1
-      for (int c = 0; c < TN / 32; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32(t_row + c * 32, v);
-        tmem_ld_wait();
-        if (c == TN / 32 - 1) {
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) {
-            if constexpr (CG == 2) mbar_arrive_cluster(mapa(tempty_bar(acc), 0));
-            else mbar_arrive(tempty_bar(acc));
-          }
+      for (int kc = ti.kb0; kc < ti.kb1 || kc == ti.kb0; kc += kstep) {
+        const int acc = it & 1;
+        const uint32_t acc_phase = (it >> 1) & 1u;
+        ++it;
+        mbar_wait(tfull_bar(acc), acc_phase);
+        tc_fence_after();
+        const uint32_t t_row = tmem_base + (uint32_t(32 * we) << 16) + acc * TN + 128 * half;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          uint32_t v[32];
+          tmem_ld_32x32(t_row + c * 32, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int q = 0; q < 32; ++q) accv[32 * c + q] += __uint_as_float(v[q]);   // fp32 round-to-nearest: the chunk sums never meet TMEM's truncating adder
         }
+        // this warp has read its part of the accumulator buffer: hand it back to the MMA issuer
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          if constexpr (CG == 2) mbar_arrive_cluster(mapa(tempty_bar(acc), 0));
+          else mbar_arrive(tempty_bar(acc));
+        }
+      }
+      // ---- the tile's sum leaves: * alpha -> swizzled staging tile -> one TMA store / reduce-add per 32 x 32 box
+      const bool rows_live = (m0 + 32 * we) < pq.M;
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
         if (rows_live && n0 + c * 32 < pq.N) {
-          const uint32_t stg = stg0 + buf * EPI_BUF;
-          // the reduce issued from THIS buffer two chunks ago must have finished reading it; the one issued from the
-          // other buffer one chunk ago may still be in flight (one bulk group per chunk, so "at most 1 pending")
-          if (lane == 0) bulk_wait_read1();
+          // the copy issued from this staging tile for the previous box must have finished reading it
+          if (lane == 0) bulk_wait_read0();
           __syncwarp();
 #pragma unroll
           for (int q = 0; q < 8; ++q) {
             float4 o;
-            o.x = p.alpha * __uint_as_float(v[4 * q + 0]); o.y = p.alpha * __uint_as_float(v[4 * q + 1]);
-            o.z = p.alpha * __uint_as_float(v[4 * q + 2]); o.w = p.alpha * __uint_as_float(v[4 * q + 3]);
+            o.x = p.alpha * accv[32 * c + 4 * q + 0]; o.y = p.alpha * accv[32 * c + 4 * q + 1];
+            o.z = p.alpha * accv[32 * c + 4 * q + 2]; o.w = p.alpha * accv[32 * c + 4 * q + 3];
             // SWIZZLE_128B staging: row = lane, 16-byte chunk q lands at q ^ (row & 7)
             const uint32_t addr = stg + lane * 128 + ((q ^ (lane & 7)) << 4);
             asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};"
@@ -318,13 +332,11 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
           fence_proxy_async();
           __syncwarp();
           if (lane == 0) {
-            if (plain_store) tma_store_2d(&map_c, stg, pq.c_col0 + n0 + c * 32, pq.c_row0 + m0 + 32 * we);
+            if (p.flags & TF32_STORE) tma_store_2d(&map_c, stg, pq.c_col0 + n0 + c * 32, pq.c_row0 + m0 + 32 * we);
             else tma_reduce_add_2d(&map_c, stg, pq.c_col0 + n0 + c * 32, pq.c_row0 + m0 + 32 * we);
             bulk_commit();
           }
-          buf ^= 1;
         }
-      }
       }
     }
     if (lane == 0) bulk_wait_all();
@@ -369,7 +381,7 @@ static int launch_gemm(const Tf32Maps& maps, const GemmTf32Params& p, int n_sms,
   if (walkers > tiles) walkers = tiles;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(CG * walkers);
-  cfg.blockDim = dim3(256 + SPLIT_THREADS);
+  cfg.blockDim = dim3(GEMM_THREADS);
   cfg.dynamicSmemBytes = Cfg<CG>::SMEM_BYTES;
   cfg.stream = st;
   cudaLaunchAttribute at[2];
