@@ -139,11 +139,11 @@ int gq_solve_metrics(const float* err_t, const float* quant_t, const void* orig_
   return solve_metrics(err_t, quant_t, orig_t, dtype, n, out2, S(stream));
 }
 
-int gq_finalize_quant(const float* err_t, const float* quant_t, const void* orig_t, const void* W, int dtype, int R, int C,
+int gq_finalize_quant(const float* err_t, const float* quant_t, const void* orig_t, int dtype, int R, int C,
                       const float* scale_gr, const float* qzero_gr, int G, void* scale_out, uint8_t* qzero_out,
-                      const float* colsq, const int64_t* perm, const float* U, double* stats4, void* stream) {
-  return finalize_quant(err_t, quant_t, orig_t, W, dtype, R, C, scale_gr, qzero_gr, G, scale_out, qzero_out, colsq, perm, U,
-                        stats4, S(stream));
+                      const int64_t* perm, const float* U, const int* seg_bounds, int nseg, double* stats, void* stream) {
+  return finalize_quant(err_t, quant_t, orig_t, dtype, R, C, scale_gr, qzero_gr, G, scale_out, qzero_out, perm, U, seg_bounds,
+                        nseg, stats, S(stream));
 }
 
 int gq_pack_int4(const uint8_t* codes, uint32_t* packed, int R, int C, void* stream) {

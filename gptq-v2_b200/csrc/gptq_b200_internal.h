@@ -131,9 +131,10 @@ int mse_refine(const float* Wt, int R, int group, int n_groups, const float* max
 int pack_int4(const uint8_t* codes, uint32_t* packed, int R, int C, cudaStream_t st);
 int unpack_int4(const uint32_t* packed, uint8_t* codes, int R, int C, cudaStream_t st);
 int transpose_pack_int4(const uint8_t* codes_t, uint8_t* codes, uint32_t* packed, int R, int C, cudaStream_t st);
-int finalize_quant(const float* err_t, const float* quant_t, const void* orig_t, const void* W, int fmt, int R, int C,
-                   const float* scale_gr, const float* qzero_gr, int G, void* scale_out, uint8_t* qzero_out, const float* colsq,
-                   const int64_t* perm, const float* U, double* stats4, cudaStream_t st);
+constexpr int GQ_MAX_SEGMENTS = 8;   // linears that may be solved as one (row segments of the stacked weight)
+int finalize_quant(const float* err_t, const float* quant_t, const void* orig_t, int fmt, int R, int C, const float* scale_gr,
+                   const float* qzero_gr, int G, void* scale_out, uint8_t* qzero_out, const int64_t* perm, const float* U,
+                   const int* seg_bounds, int nseg, double* stats, cudaStream_t st);
 int gemm_f16_nt(const void* x, const void* w, void* y, int M, int N, int K, int fmt, cudaStream_t st);
 int w4a16_dequant(const uint32_t* qw, const void* scale_t, const uint8_t* qzero_t, void* out, int N, int K, int group, int fmt,
                   cudaStream_t st);

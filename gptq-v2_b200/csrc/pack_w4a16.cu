@@ -10,6 +10,7 @@
 // 3-bit codes (maxq = 7) use the same nibble container.
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
+#include <algorithm>
 #include "gptq_b200_internal.h"
 
 namespace gq {
@@ -214,14 +215,15 @@ __global__ void transpose_pack_kernel(const uint8_t* __restrict__ codes_t, uint8
   }
 }
 
-// Result assembly of one linear (gptq_py.py:196-199, 216-237) behind the solver, replacing five torch passes:
+// Result assembly (gptq_py.py:196-199, 216-237) behind the solver, replacing five torch passes.  The rows of the solver's
+// (C, R) arrays may belong to several linears that were solved as one (they share U: q / k / v, up / gate): every sum is
+// taken per row segment.
+struct SegTable { int n; int bound[GQ_MAX_SEGMENTS + 1]; };   // rows [bound[s], bound[s + 1]) belong to segment s
+
 //   scale_out (R, G) = T(scale_gr (G, R)^T), qzero_out (R, G) = uint8(qzero_gr^T)        32 x 32 tiles through shared memory
-//   stats[2] += sum_i colsq[i] / U[p_i][p_i]^2, p_i = perm[i]   (the reference's gptq_norm, W unpermuted against diag(U))
 template <typename T>
 __global__ void __launch_bounds__(256) finalize_params_kernel(const float* __restrict__ scale_gr, const float* __restrict__ qzero_gr,
-                                                              int R, int G, T* __restrict__ scale_out, uint8_t* __restrict__ qzero_out,
-                                                              const float* __restrict__ colsq, const int64_t* __restrict__ perm,
-                                                              const float* __restrict__ U, int C, double* __restrict__ stats) {
+                                                              int R, int G, T* __restrict__ scale_out, uint8_t* __restrict__ qzero_out) {
   __shared__ float ts[32][33], tz[32][33];
   const int g0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
@@ -239,48 +241,52 @@ __global__ void __launch_bounds__(256) finalize_params_kernel(const float* __res
       qzero_out[(size_t)r * G + g] = (uint8_t)(int)tz[tx][yy];
     }
   }
-  if (U != nullptr && blockIdx.y == 0) {
-    double acc = 0.0;
-    for (int i = blockIdx.x * 256 + threadIdx.x; i < C; i += gridDim.x * 256) {
-      const size_t p = perm ? (size_t)perm[i] : (size_t)i;
-      const double d = (double)U[p * C + p];
-      acc += (double)colsq[i] / (d * d);
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-    if (tx == 0 && acc != 0.0) atomicAdd(stats + 2, acc);
-  }
 }
 
-// stats[3] += sum T(w * w) over the n weights (gptq_py.py:237 squares in the weight dtype; the mean is taken by the caller)
+// stats[s] = [sum err^2, sum (quant - w)^2, sum_j sum_r w[j][r]^2 / U[p_j][p_j]^2, sum T(w^2)] over the rows of segment s, all from ONE
+// pass over err_t / quant_t / orig_t (C, R).  Row j of orig_t holds original column p_j = perm[j] of W, and the reference divides
+// the UNPERMUTED W by the permuted-order diag(U) (gptq_py.py:198), hence U[p_j][p_j]; the squares of the fourth sum are rounded
+// to the weight dtype like (weight.abs() ** 2.) in gptq_py.py:237.  blockIdx.y = segment.
 template <typename T>
-__global__ void __launch_bounds__(256) sumsq_kernel(const T* __restrict__ W, size_t n, double* __restrict__ stats) {
-  float acc = 0.f;
-  const size_t stride = (size_t)gridDim.x * blockDim.x;
-  constexpr int V = 16 / (int)sizeof(T);                    // elements per 16-byte load
-  const size_t nv = ((reinterpret_cast<uintptr_t>(W) & 15) == 0) ? n / V : 0;
-  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += stride) {
-    const uint4 raw = reinterpret_cast<const uint4*>(W)[i];
-    const T* e = reinterpret_cast<const T*>(&raw);
-#pragma unroll
-    for (int k = 0; k < V; ++k) {
-      const float w = to_f32<T>(e[k]);
-      acc += to_f32<T>(from_f32<T>(w * w));
+__global__ void __launch_bounds__(256) result_sums_kernel(const float* __restrict__ err_t, const float* __restrict__ quant_t,
+                                                          const T* __restrict__ orig_t, int R, int C,
+                                                          const int64_t* __restrict__ perm, const float* __restrict__ U,
+                                                          const SegTable seg, double* __restrict__ stats) {
+  const int s = blockIdx.y;
+  const int lo = seg.bound[s], w4 = (seg.bound[s + 1] - lo) >> 2;
+  const size_t items = (size_t)C * w4;
+  float e2 = 0.f, d2 = 0.f, ns = 0.f, l2 = 0.f;
+  for (size_t it = (size_t)blockIdx.x * 256 + threadIdx.x; it < items; it += (size_t)gridDim.x * 256) {
+    const int j = (int)(it / w4);
+    const size_t i = (size_t)j * R + lo + 4 * (size_t)(it - (size_t)j * w4);
+    const float4 e = *reinterpret_cast<const float4*>(err_t + i);
+    const float4 q = *reinterpret_cast<const float4*>(quant_t + i);
+    const float o0 = to_f32<T>(orig_t[i]), o1 = to_f32<T>(orig_t[i + 1]), o2 = to_f32<T>(orig_t[i + 2]), o3 = to_f32<T>(orig_t[i + 3]);
+    e2 += e.x * e.x + e.y * e.y + e.z * e.z + e.w * e.w;
+    const float a = q.x - o0, b = q.y - o1, c = q.z - o2, d = q.w - o3;
+    d2 += a * a + b * b + c * c + d * d;
+    const float s0 = o0 * o0, s1 = o1 * o1, s2 = o2 * o2, s3 = o3 * o3;
+    l2 += (to_f32<T>(from_f32<T>(s0)) + to_f32<T>(from_f32<T>(s1))) + (to_f32<T>(from_f32<T>(s2)) + to_f32<T>(from_f32<T>(s3)));
+    if (U != nullptr) {
+      const size_t pj = perm ? (size_t)perm[j] : (size_t)j;
+      const float dj = U[pj * C + pj];
+      ns += ((s0 + s1) + (s2 + s3)) / (dj * dj);
     }
   }
-  for (size_t i = nv * V + (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    const float w = to_f32<T>(W[i]);
-    acc += to_f32<T>(from_f32<T>(w * w));
-  }
+  __shared__ float red[4][8];
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-  __shared__ float part[8];
-  if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = acc;
+  for (int o = 16; o > 0; o >>= 1) {
+    e2 += __shfl_xor_sync(0xffffffffu, e2, o); d2 += __shfl_xor_sync(0xffffffffu, d2, o);
+    ns += __shfl_xor_sync(0xffffffffu, ns, o); l2 += __shfl_xor_sync(0xffffffffu, l2, o);
+  }
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) { red[0][warp] = e2; red[1][warp] = d2; red[2][warp] = ns; red[3][warp] = l2; }
   __syncthreads();
-  if (threadIdx.x == 0) {
+  if (threadIdx.x < 4) {
     double t = 0.0;
-    for (int w = 0; w < 8; ++w) t += (double)part[w];
-    atomicAdd(stats + 3, t);
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += (double)red[threadIdx.x][w];
+    atomicAdd(stats + 4 * s + threadIdx.x, t);
   }
 }
 
@@ -420,30 +426,37 @@ int transpose_pack_int4(const uint8_t* codes_t, uint8_t* codes, uint32_t* packed
   return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
 }
 
-// Everything gptq_quant needs after the solver, queued with one call: stats4 = [sum err^2, sum (quant - W)^2, gptq_norm sum,
-// sum T(w^2)] (doubles, overwritten) and the (R, G) scale / zero-point tables of quant_meta.
-int finalize_quant(const float* err_t, const float* quant_t, const void* orig_t, const void* W, int fmt, int R, int C,
-                   const float* scale_gr, const float* qzero_gr, int G, void* scale_out, uint8_t* qzero_out, const float* colsq,
-                   const int64_t* perm, const float* U, double* stats4, cudaStream_t st) {
-  if (R <= 0 || C <= 0 || G <= 0) return GQ_ERR_ARG;
+// Everything gptq_quant needs after the solver, queued with one call: stats (nseg x 4 doubles, overwritten) = per row segment
+// [sum err^2, sum (quant - W)^2, gptq_norm sum, sum T(w^2)] and the (R, G) scale / zero-point tables of quant_meta.
+int finalize_quant(const float* err_t, const float* quant_t, const void* orig_t, int fmt, int R, int C, const float* scale_gr,
+                   const float* qzero_gr, int G, void* scale_out, uint8_t* qzero_out, const int64_t* perm, const float* U,
+                   const int* seg_bounds, int nseg, double* stats, cudaStream_t st) {
+  if (R <= 0 || C <= 0 || G <= 0 || nseg <= 0 || nseg > GQ_MAX_SEGMENTS) return GQ_ERR_ARG;
   if (fmt < 0 || fmt > 2) return GQ_ERR_DTYPE;
-  const size_t n = (size_t)R * C;
-  if (cudaMemsetAsync(stats4, 0, 4 * sizeof(double), st) != cudaSuccess) return GQ_ERR_CUDA;
-  int rc = solve_metrics(err_t ? err_t : quant_t, quant_t, orig_t, fmt, n, stats4, st);      // zeroes and fills stats4[0..1]
-  if (rc != GQ_OK) return rc;
-  if (U != nullptr && colsq == nullptr) return GQ_ERR_ARG;
-  const dim3 grid((G + 31) / 32, (R + 31) / 32);
-  const unsigned sblocks = (unsigned)((n / 8 + 255) / 256 < 148 * 8 ? (n / 8 + 255) / 256 + 1 : 148 * 8);
+  SegTable seg;
+  seg.n = nseg;
+  int max_rows = 0;
+  for (int s = 0; s <= nseg; ++s) {
+    seg.bound[s] = seg_bounds ? seg_bounds[s] : (s == 0 ? 0 : R);
+    if ((seg.bound[s] & 3) || (s > 0 && seg.bound[s] <= seg.bound[s - 1])) return GQ_ERR_SHAPE;
+    if (s > 0) max_rows = std::max(max_rows, seg.bound[s] - seg.bound[s - 1]);
+  }
+  if (seg.bound[0] != 0 || seg.bound[nseg] != R) return GQ_ERR_SHAPE;
+  if (cudaMemsetAsync(stats, 0, (size_t)nseg * 4 * sizeof(double), st) != cudaSuccess) return GQ_ERR_CUDA;
+  const float* e = err_t ? err_t : quant_t;
+  const size_t items = (size_t)C * (max_rows / 4);
+  const dim3 sgrid((unsigned)std::min<size_t>((items + 255) / 256, 148 * 8), nseg);
+  const dim3 pgrid((G + 31) / 32, (R + 31) / 32);
   GQ_LAUNCHED(); GQ_LAUNCHED();
   if (fmt == 0) {
-    finalize_params_kernel<__half><<<grid, 256, 0, st>>>(scale_gr, qzero_gr, R, G, (__half*)scale_out, qzero_out, colsq, perm, U, C, stats4);
-    sumsq_kernel<__half><<<sblocks, 256, 0, st>>>((const __half*)W, n, stats4);
+    result_sums_kernel<__half><<<sgrid, 256, 0, st>>>(e, quant_t, (const __half*)orig_t, R, C, perm, U, seg, stats);
+    finalize_params_kernel<__half><<<pgrid, 256, 0, st>>>(scale_gr, qzero_gr, R, G, (__half*)scale_out, qzero_out);
   } else if (fmt == 1) {
-    finalize_params_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(scale_gr, qzero_gr, R, G, (__nv_bfloat16*)scale_out, qzero_out, colsq, perm, U, C, stats4);
-    sumsq_kernel<__nv_bfloat16><<<sblocks, 256, 0, st>>>((const __nv_bfloat16*)W, n, stats4);
+    result_sums_kernel<__nv_bfloat16><<<sgrid, 256, 0, st>>>(e, quant_t, (const __nv_bfloat16*)orig_t, R, C, perm, U, seg, stats);
+    finalize_params_kernel<__nv_bfloat16><<<pgrid, 256, 0, st>>>(scale_gr, qzero_gr, R, G, (__nv_bfloat16*)scale_out, qzero_out);
   } else {
-    finalize_params_kernel<float><<<grid, 256, 0, st>>>(scale_gr, qzero_gr, R, G, (float*)scale_out, qzero_out, colsq, perm, U, C, stats4);
-    sumsq_kernel<float><<<sblocks, 256, 0, st>>>((const float*)W, n, stats4);
+    result_sums_kernel<float><<<sgrid, 256, 0, st>>>(e, quant_t, (const float*)orig_t, R, C, perm, U, seg, stats);
+    finalize_params_kernel<float><<<pgrid, 256, 0, st>>>(scale_gr, qzero_gr, R, G, (float*)scale_out, qzero_out);
   }
   return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
 }

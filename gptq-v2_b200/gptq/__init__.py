@@ -9,6 +9,8 @@ are what this build's own gptq_py.HessianHook / gptq_quant call.
 """
 from __future__ import annotations
 
+import ctypes
+
 import torch
 
 from . import _cabi
@@ -133,7 +135,7 @@ def prep_weight_t(W: torch.Tensor, perm) -> torch.Tensor:
     return Wt
 
 
-def prep_weight_t2(W: torch.Tensor, perm, perm_inv=None):
+def prep_weight_t2(W: torch.Tensor, perm, perm_inv=None, want_colsq: bool = True):
     """prep_weight_t plus what the result metrics need later: orig_t (C, R) in W's dtype (the same elements, kept because
     the solver consumes Wt) and colsq (C) fp32 = sum_r W[r, perm[c]]^2.  Returns Wt, orig_t, colsq.
     With perm_inv (HessianHook.perm_inv, or no permutation at all) the scatter-form kernel runs: W read in its own
@@ -143,7 +145,7 @@ def prep_weight_t2(W: torch.Tensor, perm, perm_inv=None):
     R, C_ = W.shape
     Wt = torch.empty(C_, R, dtype=torch.float32, device=dev)
     orig_t = torch.empty(C_, R, dtype=W.dtype, device=dev)
-    colsq = torch.empty(C_, dtype=torch.float32, device=dev)
+    colsq = torch.empty(C_, dtype=torch.float32, device=dev) if want_colsq else None
     scatter = (perm is None or perm_inv is not None) and C_ % 2 == 0
     with torch.cuda.device(dev):
         if scatter:
@@ -171,26 +173,33 @@ def solve_metrics(err_t: torch.Tensor, quant_t: torch.Tensor, orig_t: torch.Tens
     return out
 
 
-def finalize_quant(err_t, quant_t: torch.Tensor, orig_t: torch.Tensor, W: torch.Tensor, scale_gr: torch.Tensor,
-                   qzero_gr: torch.Tensor, colsq, perm, U):
+def finalize_quant(err_t, quant_t: torch.Tensor, orig_t: torch.Tensor, scale_gr: torch.Tensor, qzero_gr: torch.Tensor, perm, U,
+                   row_segments=None):
     """Result assembly behind the solver in one library call (gq_finalize_quant): -> (stats, scale, qzero) with stats a
-    float64 device tensor [sum err^2, sum (quant - W)^2, sum_i colsq[i] / U[perm_i, perm_i]^2, sum dtype(w^2)], scale (R, G) in
-    W.dtype and qzero (R, G) uint8 (the transposes of the solver's (G, R) fp32 tables)."""
-    dev = require_cuda(err_t, quant_t, orig_t, W, scale_gr, qzero_gr, colsq, perm, U)
-    require_contig(err_t=err_t, quant_t=quant_t, orig_t=orig_t, W=W, scale_gr=scale_gr, qzero_gr=qzero_gr, colsq=colsq,
-                   perm=perm, U=U)
+    float64 device tensor (n_segments, 4) = per row segment [sum err^2, sum (quant - W)^2, sum_j sum_r W_t[j, r]^2 /
+    U[perm_j, perm_j]^2, sum dtype(w^2)], scale (R, G) in orig_t.dtype and qzero (R, G) uint8 (the transposes of the solver's
+    (G, R) fp32 tables).  row_segments: row counts of the linears that were solved as one stacked weight (default: one)."""
+    dev = require_cuda(err_t, quant_t, orig_t, scale_gr, qzero_gr, perm, U)
+    require_contig(err_t=err_t, quant_t=quant_t, orig_t=orig_t, scale_gr=scale_gr, qzero_gr=qzero_gr, perm=perm, U=U)
     C_, R = quant_t.shape
     G = scale_gr.shape[0]
-    assert tuple(W.shape) == (R, C_) and orig_t.shape == quant_t.shape and orig_t.dtype == W.dtype
+    assert orig_t.shape == quant_t.shape and quant_t.dtype == torch.float32
     assert tuple(scale_gr.shape) == (G, R) == tuple(qzero_gr.shape) and scale_gr.dtype == qzero_gr.dtype == torch.float32
     if perm is not None and perm.dtype != torch.int64:
         raise GptqB200Error('perm must be int64')
-    stats = torch.empty(4, dtype=torch.float64, device=dev)
-    scale = torch.empty(R, G, dtype=W.dtype, device=dev)
+    rows = [int(R)] if row_segments is None else [int(n) for n in row_segments]
+    if sum(rows) != R or min(rows) <= 0:
+        raise GptqB200Error('row_segments must add up to the number of rows')
+    bounds = [0]
+    for n in rows:
+        bounds.append(bounds[-1] + n)
+    c_bounds = (ctypes.c_int * len(bounds))(*bounds)
+    stats = torch.empty(len(rows), 4, dtype=torch.float64, device=dev)
+    scale = torch.empty(R, G, dtype=orig_t.dtype, device=dev)
     qzero = torch.empty(R, G, dtype=torch.uint8, device=dev)
     with torch.cuda.device(dev):
-        check(lib.gq_finalize_quant(ptr(err_t), ptr(quant_t), ptr(orig_t), ptr(W), _cabi.DTYPE_CODE[W.dtype], R, C_,
-                                    ptr(scale_gr), ptr(qzero_gr), G, ptr(scale), ptr(qzero), ptr(colsq), ptr(perm), ptr(U),
+        check(lib.gq_finalize_quant(ptr(err_t), ptr(quant_t), ptr(orig_t), _cabi.DTYPE_CODE[orig_t.dtype], R, C_, ptr(scale_gr),
+                                    ptr(qzero_gr), G, ptr(scale), ptr(qzero), ptr(perm), ptr(U), c_bounds, len(rows),
                                     ptr(stats), stream_of(quant_t)), 'gq_finalize_quant')
     return stats, scale, qzero
 

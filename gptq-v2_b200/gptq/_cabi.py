@@ -41,7 +41,7 @@ SIGNATURES = {
     'gq_prep_weight_t2': (_i, [_vp, _i, _vp, _vp, _vp, _vp, _i, _i, _vp]),
     'gq_prep_weight_t3': (_i, [_vp, _i, _vp, _vp, _vp, _vp, _i, _i, _vp]),
     'gq_solve_metrics': (_i, [_vp, _vp, _vp, _i, C.c_size_t, _vp, _vp]),
-    'gq_finalize_quant': (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _vp, _vp]),
+    'gq_finalize_quant': (_i, [_vp, _vp, _vp, _i, _i, _i, _vp, _vp, _i, _vp, _vp, _vp, _vp, _vp, _i, _vp, _vp]),
     'gq_pack_int4': (_i, [_vp, _vp, _i, _i, _vp]),
     'gq_unpack_int4': (_i, [_vp, _vp, _i, _i, _vp]),
     'gq_transpose_pack_int4': (_i, [_vp, _vp, _vp, _i, _i, _vp]),

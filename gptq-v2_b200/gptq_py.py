@@ -90,6 +90,13 @@ def _mean_in_dtype(total: float, n: float, dtype: torch.dtype) -> float:
     return float(torch.tensor(total / n, dtype=torch.float32).to(dtype))
 
 
+def _metrics_from_sums(sums, n_el: float, has_hook: bool, dtype: torch.dtype) -> dict:
+    """[sum err^2, sum (quant - W)^2, gptq_norm sum, sum dtype(w^2)] -> the reference's four metrics (ref :196-199, :231-237)."""
+    e2, d2, ns, l2s = sums
+    return {'gptq_error': e2 / n_el if has_hook else 0.0, 'gptq_norm': ns / n_el if has_hook else 0.0,      # ref :198 (0 without H)
+            'l2.0_error': d2 / n_el, 'l2.0_norm': _mean_in_dtype(l2s, n_el, dtype)}
+
+
 class DeferredMetrics(collections.abc.Mapping):
     """The four metrics of gptq_quant (ref :196-199, :231-237) as a read-only mapping whose values are fetched from the device
     on first access.  gptq_quant(defer_metrics=True) returns it instead of a dict, so that a caller quantising several linears
@@ -116,10 +123,7 @@ class DeferredMetrics(collections.abc.Mapping):
     def _resolve(self) -> dict:
         if self._values is None:
             self._event.synchronize()
-            e2, d2, ns, l2s = self._host.tolist()
-            n = self._n_el
-            self._values = dict(zip(self.KEYS, (e2 / n if self._has_hook else 0.0, ns / n if self._has_hook else 0.0, d2 / n,
-                                                _mean_in_dtype(l2s, n, self._dtype))))
+            self._values = _metrics_from_sums(self._host.tolist(), self._n_el, self._has_hook, self._dtype)
         return self._values
 
     def __getitem__(self, key):
@@ -172,6 +176,7 @@ def gptq_quant(
         save_device: torch.device = torch.device('cpu'),
         *,
         defer_metrics: bool = False,
+        _row_segments=None,
 ) -> dict[str, dict]:
     """gptq_use_kernel=True  -> the reference's kernel-path semantics: static per-group scale/zero
                                 from the un-compensated weights, fp16-rounded dequant (ref :125-157)
@@ -208,7 +213,8 @@ def gptq_quant(
     U = hessian_hook.hessian_inv.contiguous() if hessian_hook is not None else None
 
     # (C, R) fp32, permuted (ref :90-94,128); orig_t / colsq feed the result metrics after the solver has consumed Wt
-    Wt, orig_t, colsq = _ops.prep_weight_t2(weight_c, perm, getattr(hessian_hook, 'perm_inv', None) if perm is not None else None)
+    Wt, orig_t, _ = _ops.prep_weight_t2(weight_c, perm, getattr(hessian_hook, 'perm_inv', None) if perm is not None else None,
+                                        want_colsq=False)
     scale_gr = torch.empty(n_groups, n_rows, dtype=torch.float32, device=device)
     qzero_gr = torch.empty_like(scale_gr)
     qscale_gr = sscale_g = None
@@ -316,9 +322,8 @@ def gptq_quant(
     #   reproduced as is (ref :198) = sum_c colsq_orig[c] / diag(U)[c]^2 / (R C);  l2.0_error = mean((quant - W)^2), which
     #   does not depend on the column order;  l2.0_norm in the weight dtype like the reference.
     # One library call queues all of it (gq_finalize_quant): the four sums and the (R, G) scale / zero tables of quant_meta.
-    stats, scale, qzero = _ops.finalize_quant(err_t, quant_t, orig_t, weight_c, scale_gr, qzero_gr,
-                                              colsq if hessian_hook is not None else None, perm, U)
-    n_el = float(n_rows * n_columns)
+    seg_rows = [n_rows] if _row_segments is None else [int(n) for n in _row_segments]
+    stats, scale, qzero = _ops.finalize_quant(err_t, quant_t, orig_t, scale_gr, qzero_gr, perm, U, seg_rows)   # stats (n_seg, 4)
 
     qweight, _ = _ops.transpose_pack_int4(codes_t, want_codes=True, want_packed=False)   # (R, C) uint8, permuted order
     qscale = qscale_gr.t().to(dtype=torch.uint8).contiguous() if exl2 else None  # (R, G)   ref :217
@@ -357,15 +362,38 @@ def gptq_quant(
         'group_bit_widths': bits_out.to(device=save_device),
         'scale_bit_width': scale_bit_width.to(dtype=torch.uint8, device=save_device) if scale_bit_width is not None else None,
     }
-    if defer_metrics:
-        return {'quant_meta': quant_meta, 'metrics': DeferredMetrics(stats, n_el, hessian_hook is not None, dtype)}
-    # the one host sync of the call, after every kernel of the result assembly has been queued behind the solver
-    e2, d2, ns, l2s = stats.tolist()
-    l2n = _mean_in_dtype(l2s, n_el, dtype)
-    if hessian_hook is None:
-        gptq_error, gptq_norm = 0.0, 0.0                                         # ref :198 (error == 0)
-    else:
-        gptq_error, gptq_norm = e2 / n_el, ns / n_el
-    metrics: dict[str, float] = {'gptq_error': gptq_error, 'gptq_norm': gptq_norm,
-                                 'l2.0_error': d2 / n_el, 'l2.0_norm': l2n}
-    return {'quant_meta': quant_meta, 'metrics': metrics}
+    has_hook = hessian_hook is not None
+    if _row_segments is None:
+        if defer_metrics:
+            return {'quant_meta': quant_meta, 'metrics': DeferredMetrics(stats[0], float(n_rows * n_columns), has_hook, dtype)}
+        # the one host sync of the call, after every kernel of the result assembly has been queued behind the solver
+        return {'quant_meta': quant_meta, 'metrics': _metrics_from_sums(stats[0].tolist(), float(n_rows * n_columns), has_hook, dtype)}
+    # several linears solved as one stacked weight (gptq_quant_stacked): one result per row segment, the row-wise tensors
+    # are slices of the stacked ones, everything else is shared
+    host_stats = None if defer_metrics else stats.tolist()
+    results, lo = [], 0
+    for si, n in enumerate(seg_rows):
+        meta = dict(quant_meta)
+        for k in ('qweight', 'scale', 'qzero'):
+            meta[k] = quant_meta[k][lo:lo + n]
+        n_el = float(n * n_columns)
+        met = (DeferredMetrics(stats[si], n_el, has_hook, dtype) if defer_metrics
+               else _metrics_from_sums(host_stats[si], n_el, has_hook, dtype))
+        results.append({'quant_meta': meta, 'metrics': met})
+        lo += n
+    return results
+
+
+@torch.no_grad()
+def gptq_quant_stacked(weights, hessian_hook, **kwargs) -> list[dict]:
+    """gptq_quant of several linears that share one Hessian (q / k / v, up / gate) as ONE solve of the row-stacked weight:
+    GPTQ rows are independent given U (ref :187-193), so the results are those of the separate calls, but the serial column
+    recurrence runs once over 128-row tiles instead of once per linear over 32-row tiles.  Returns one {'quant_meta',
+    'metrics'} dict per linear.  Not for EXL2 scale quantisation (scale_bit_width), whose grid is a maximum over all rows."""
+    if kwargs.get('scale_bit_width') is not None:
+        raise NotImplementedError('EXL2 scale quantisation couples the rows of a linear: quantise the linears one by one')
+    weights = list(weights)
+    if len(weights) == 1:
+        return [gptq_quant(weight=weights[0], hessian_hook=hessian_hook, **kwargs)]
+    stacked = torch.cat(weights, dim=0)
+    return gptq_quant(weight=stacked, hessian_hook=hessian_hook, _row_segments=[w.shape[0] for w in weights], **kwargs)

@@ -176,6 +176,20 @@ def plan_group(rows: Sequence[int], world: int, multiple: int = 4) -> list[tuple
     return plan
 
 
+def _solve_cost(rows: int, n_sms: int = 148) -> float:
+    """Relative time of the fused solver for one weight of `rows` rows (measured on B200, profiles/r02_v24_quant_time.jsonl:
+    32-row CTAs 1.0, 64-row 1.35, 128-row 1.95 per wave; the library picks the smallest tile that fits one wave)."""
+    for tile, cost in ((32, 1.0), (64, 1.35), (128, 1.95)):
+        if -(-rows // tile) <= n_sms:
+            return cost
+    return 1.95 * -(-(-(-rows // 128)) // n_sms)
+
+
+def _stacking_pays(rows: Sequence[int]) -> bool:
+    """Solve the linears of a Hessian group as one row-stacked weight?  (7B q/k/v: 3 x 1.0 -> 1.95; up/gate: 2 x 1.95 -> 3.9, no.)"""
+    return len(rows) > 1 and len(rows) <= 8 and all(r % 4 == 0 for r in rows) and _solve_cost(sum(rows)) < 0.95 * sum(_solve_cost(r) for r in rows)
+
+
 def gptq_quant_group_sharded(weights: Sequence[torch.Tensor], hessian_hook, quant_fn: Optional[Callable] = None, group=None,
                              shard_of: Optional[Callable[[int, int, int], torch.Tensor]] = None,
                              **quant_kwargs) -> list[dict]:
@@ -186,7 +200,8 @@ def gptq_quant_group_sharded(weights: Sequence[torch.Tensor], hessian_hook, quan
     the metric sums.
     shard_of(i, lo, hi): optional source of rows [lo, hi) of linear i for callers that stage only the rows a rank solves
     (bench.py's host-fed step); `weights` may then be meta tensors (shape and dtype only)."""
-    if quant_fn is None:
+    own_quant = quant_fn is None
+    if own_quant:
         from gptq_py import gptq_quant as quant_fn
         # the library's own quantiser: no host synchronisation per linear, the metrics are read when the caller looks
         quant_kwargs = dict(quant_kwargs, defer_metrics=True)
@@ -196,6 +211,12 @@ def gptq_quant_group_sharded(weights: Sequence[torch.Tensor], hessian_hook, quan
         def shard_of(i, lo, hi):
             return weights[i][lo:hi]
     if world == 1:
+        if own_quant and _stacking_pays([w.shape[0] for w in weights]) and quant_kwargs.get('scale_bit_width') is None \
+                and len({(w.shape[1], w.dtype) for w in weights}) == 1:
+            # the linears share U and GPTQ rows are independent: one solve of the row-stacked weight (128-row tiles, one wave)
+            # instead of one serial column recurrence per linear
+            from gptq_py import gptq_quant_stacked
+            return gptq_quant_stacked([shard_of(i, 0, w.shape[0]) for i, w in enumerate(weights)], hessian_hook, **quant_kwargs)
         return [quant_fn(weight=shard_of(i, 0, w.shape[0]), hessian_hook=hessian_hook, **quant_kwargs)
                 for i, w in enumerate(weights)]
     if quant_kwargs.get('scale_bit_width') is not None:

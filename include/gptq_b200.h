@@ -137,16 +137,18 @@ int gq_prep_weight_t3(const void* W, int dtype, const int64_t* perm_inv, float* 
  * orig_t)^2 over n = R*C elements (n % 4 == 0); out2 is two doubles on the device, overwritten. */
 int gq_solve_metrics(const float* err_t, const float* quant_t, const void* orig_t, int dtype, size_t n, double* out2,
                      void* stream);
-/* Result assembly of one linear behind the solver in one call (gptq_py.py:196-199, 216-218, 231-237; replaces five torch
- * passes): stats4 (four doubles on the device, overwritten) = [sum err_t^2, sum (quant_t - orig_t)^2,
- * sum_i colsq[i] / U[p_i][p_i]^2 with p_i = perm[i] (the reference's gptq_norm numerator: W unpermuted against the
- * permuted-order diag(U), reproduced as is), sum T(w^2) over the R*C weights W in their own dtype];
+/* Result assembly behind the solver in one call (gptq_py.py:196-199, 216-218, 231-237; replaces five torch passes).
+ * The R rows may belong to up to 8 linears that share U and were solved as one stacked weight: seg_bounds (HOST array of
+ * nseg + 1 ints, multiples of 4, seg_bounds[0] = 0, seg_bounds[nseg] = R; NULL = one segment) gives their row ranges.
+ * stats (nseg x 4 doubles on the device, overwritten) = per segment [sum err_t^2, sum (quant_t - orig_t)^2,
+ * sum_j sum_r orig_t[j][r]^2 / U[p_j][p_j]^2 with p_j = perm[j] (the reference's gptq_norm numerator: W unpermuted against the
+ * permuted-order diag(U), reproduced as is), sum T(w^2) with the squares rounded to the weight dtype];
  * scale_out (R, G) of `dtype` and qzero_out (R, G) uint8 = the transposes of the solver's (G, R) fp32 tables.
- * err_t NULL: quant_t is used in its place (round to nearest: both sums are taken, the caller reports 0).  U NULL: stats4[2]
- * = 0 (then colsq / perm are not read); perm NULL = identity.  R*C % 4 == 0. */
-int gq_finalize_quant(const float* err_t, const float* quant_t, const void* orig_t, const void* W, int dtype, int R, int C,
+ * err_t NULL: quant_t is used in its place (round to nearest: the caller reports 0).  U NULL: the third sum is 0;
+ * perm NULL = identity. */
+int gq_finalize_quant(const float* err_t, const float* quant_t, const void* orig_t, int dtype, int R, int C,
                       const float* scale_gr, const float* qzero_gr, int G, void* scale_out, uint8_t* qzero_out,
-                      const float* colsq, const int64_t* perm, const float* U, double* stats4, void* stream);
+                      const int64_t* perm, const float* U, const int* seg_bounds, int nseg, double* stats, void* stream);
 
 /* ---- K5: int4 storage (new in this build; the reference stores one code per byte, gptq_py.py:217).
  * packed (R, C/8) uint32, column 8k+i in bits [4i, 4i+4) of word k.  C % 8 == 0. */

@@ -45,7 +45,7 @@ def test_reference_surface_is_importable():
     assert list(sig.parameters)[:len(ref_params)] == ref_params
     # anything beyond the reference's parameters is keyword-only with a default that keeps the reference behaviour
     for extra in list(sig.parameters.values())[len(ref_params):]:
-        assert extra.kind is inspect.Parameter.KEYWORD_ONLY and extra.default is False
+        assert extra.kind is inspect.Parameter.KEYWORD_ONLY and extra.default in (False, None)
     assert sig.parameters['gptq_use_kernel'].default is True and sig.parameters['quant_mse'].default is True
     h = gptq_py.HessianHook()
     assert (h.hessian, h.n_samples, h.hessian_inv, h.perm, h.perm_inv) == (None, 0, None, None, None)

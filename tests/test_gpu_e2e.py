@@ -143,3 +143,35 @@ def test_deferred_metrics_equal_immediate_metrics():
     grp = sharded.gptq_quant_group_sharded([w, w], hook, **kw)
     assert dict(grp[0]["metrics"]) == pytest.approx(imm["metrics"], rel=1e-6)
     assert torch.equal(grp[1]['quant_meta']['qweight'], imm['quant_meta']['qweight'])
+
+
+@pytest.mark.parametrize('rows', [(256, 128, 384), (4096, 4096, 4096)])
+def test_stacked_group_equals_separate_calls(rows):
+    """gptq_quant_stacked (linears that share U solved as one row-stacked weight: what sharded.gptq_quant_group_sharded does
+    for q / k / v on one rank) == one gptq_quant call per linear: identical codes / scales / zeros (rows are independent given
+    U; at 3 x 4096 rows the stacked solve runs on 128-row tiles, the separate ones on 32-row tiles) and per-linear metrics
+    equal to summation order."""
+    import gptq_py
+    import sharded
+    C = 512
+    W, X = O.synth_linear(sum(rows), C, 8, 256, seed=rows[0])
+    hook, _ = _run_gpu(W[:64], X, 4, True, use_kernel=False)
+    gs = torch.full([C // 128], 128, dtype=torch.int32)
+    bw = torch.full([C // 128], 4, dtype=torch.int32)
+    kw = dict(group_sizes=gs, group_bit_widths=bw, scale_bit_width=None, gptq_use_kernel=False, gptq_block_sizes=gs,
+              quant_symmetric=False, quant_mse=False, save_device=torch.device('cuda'))
+    ws, lo = [], 0
+    for n in rows:
+        ws.append(W[lo:lo + n].cuda().contiguous())
+        lo += n
+    sep = [gptq_py.gptq_quant(weight=w, hessian_hook=hook, **kw) for w in ws]
+    stk = gptq_py.gptq_quant_stacked(ws, hook, **kw)
+    assert sharded._stacking_pays([4096, 4096, 4096]) and not sharded._stacking_pays([11008, 11008])
+    grp = sharded.gptq_quant_group_sharded(ws, hook, **kw)
+    for a, b, c in zip(sep, stk, grp):
+        for k in ('qweight', 'scale', 'qzero', 'perm_inv'):
+            assert torch.equal(a['quant_meta'][k], b['quant_meta'][k]), k
+            assert torch.equal(a['quant_meta'][k], c['quant_meta'][k]), k
+        for k, v in a['metrics'].items():
+            assert b['metrics'][k] == pytest.approx(v, rel=1e-5), k
+            assert c['metrics'][k] == pytest.approx(v, rel=1e-5), k
