@@ -99,6 +99,16 @@ def apply_rope(x: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor) -> torch.T
     return x * cos + rot * sin
 
 
+def linear(x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
+    """x (..., K) @ w (N, K)^T.  The replay of a quantised linear (llama.py:172-177) is K6's large-batch route: the weights are
+    dequantised once (reconstruct_nn_linear) and multiplied on the library's own tcgen05 GEMM (gq_gemm_f16_nt), not cuBLAS."""
+    if x.is_cuda and x.dtype in (torch.float16, torch.bfloat16) and w.dtype == x.dtype and x.shape[-1] % 8 == 0 and w.shape[0] % 2 == 0:
+        import gptq as _ops
+        y = _ops.gemm_f16_nt(x.reshape(-1, x.shape[-1]).contiguous(), w.contiguous())
+        return y.view(*x.shape[:-1], w.shape[0])
+    return x @ w.t()
+
+
 def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int, cos, sin) -> torch.Tensor:
     B, N, Hd = q.shape
     hd = Hd // heads
@@ -337,7 +347,7 @@ def quantize_block(shape: LlamaShape, weights: dict, inps: torch.Tensor, n_globa
     with timer('forward'):
         for b in _batches(n, batch_size):
             x = h1[b]
-            att[b] = attention(x @ wq.t(), x @ wk.t(), x @ wv.t(), shape.heads, cos, sin)
+            att[b] = attention(linear(x, wq), linear(x, wk), linear(x, wv), shape.heads, cos, sin)
     del h1, wq, wk, wv
     for b in _batches(n, batch_size):
         grp.add(att[b])
@@ -350,7 +360,7 @@ def quantize_block(shape: LlamaShape, weights: dict, inps: torch.Tensor, n_globa
     h3 = torch.empty_like(inps)
     with timer('forward'):
         for b in _batches(n, batch_size):
-            h2[b] = inps[b] + att[b] @ wo.t()
+            h2[b] = inps[b] + linear(att[b], wo)
             h3[b] = rms_norm(h2[b], weights['post_attention_layernorm'], shape.rms_eps)
     del att, wo
     for b in _batches(n, batch_size):
@@ -364,7 +374,7 @@ def quantize_block(shape: LlamaShape, weights: dict, inps: torch.Tensor, n_globa
     with timer('forward'):
         for b in _batches(n, batch_size):
             x = h3[b]
-            act[b] = F.silu(x @ wg.t()) * (x @ wu.t())
+            act[b] = F.silu(linear(x, wg)) * linear(x, wu)
     del h3, wu, wg
     for b in _batches(n, batch_size):
         grp.add(act[b])
@@ -374,7 +384,7 @@ def quantize_block(shape: LlamaShape, weights: dict, inps: torch.Tensor, n_globa
     # ---- inputs of the next block (llama.py:181-189)
     with timer('forward'):
         for b in _batches(n, batch_size):
-            h2[b] += act[b] @ wd.t()
+            h2[b] += linear(act[b], wd)
     # plain {name: float} dicts like the reference's; the deferred values are read here, once per block, behind the queued work
     metrics = {name: dict(met) for name, met in metrics.items()}
     return h2, data, metrics
