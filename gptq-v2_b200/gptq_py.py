@@ -67,7 +67,9 @@ class HessianHook:
         diag = torch.where(diag == 0.0, torch.ones_like(diag), diag)   # ref :43-44
         if act_order:
             self.perm = torch.argsort(diag, descending=True, stable=True)   # ref :47 (ties: stable here)
-            self.perm_inv = torch.argsort(self.perm)                        # ref :49
+            # ref :49 takes argsort(perm); the inverse of a permutation is one scatter
+            self.perm_inv = torch.empty_like(self.perm)
+            self.perm_inv[self.perm] = torch.arange(self.perm.numel(), device=self.perm.device, dtype=self.perm.dtype)
         damp = (damp_ratio * diag.mean()).reshape(())                   # ref :52; stays on the device: K2 reads it there
         max_try = 100
         tries = 0

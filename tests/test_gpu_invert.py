@@ -282,3 +282,28 @@ def test_invert_damping_from_device_scalar(D):
         assert torch.equal(Hp_a, Hp_b) and torch.equal(U_a, U_b)
     with pytest.raises(gptq.GptqB200Error):
         gptq.hessian_invert(H, perm, 0.25, damp_dev.double())
+
+
+def test_programmatic_dependent_launch_changes_nothing():
+    """gq_set_pdl(0 / 1): the same kernels in the same order, only their set-up overlaps the predecessor's tail; U, Hp and the
+    solver outputs are bit-identical."""
+    import gptq
+    D = 1408
+    g = torch.Generator(device='cuda').manual_seed(3)
+    X = torch.randn(3 * D, D, device='cuda', generator=g)
+    H = (X.t() @ X).triu()
+    perm = torch.randperm(D, device='cuda', generator=g)
+    Wt0 = torch.randn(D, 192, device='cuda', generator=g) * 0.02
+    outs = []
+    for pdl in (1, 0):
+        old = gptq.set_pdl(pdl)
+        try:
+            Hp, U, info = gptq.hessian_invert(H, perm, 0.5, 0.01 * float(H.diagonal().mean()))
+            sol = gptq.gptq_solve(Wt0.clone(), U, 128, 15.0)
+            torch.cuda.synchronize()
+        finally:
+            gptq.set_pdl(old)
+        assert int(info.item()) == 0
+        outs.append((Hp, U) + tuple(sol))
+    for a, b in zip(*outs):
+        assert torch.equal(a, b)

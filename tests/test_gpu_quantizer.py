@@ -280,3 +280,43 @@ def test_kernel_branch_with_nonuniform_and_wide_groups():
         assert O.code_match(m['qweight'], q_t.t()) >= 0.999
         assert torch.equal(m['scale'].float(), torch.cat(scales, dim=1).to(torch.float16).float())   # static parameters: bit-exact
         assert m['group_sizes'].tolist() == sizes
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('dtype', [torch.float16, torch.bfloat16, torch.float32])
+def test_finalize_quant_sums_per_row_segment(dtype):
+    """gq_finalize_quant: the four sums per row segment and the transposed scale / zero tables against plain torch on the same
+    arrays (gptq_py.py:196-199, 231-237 semantics: W unpermuted against the permuted-order diag(U); squares rounded to the
+    weight dtype for the l2 norm)."""
+    import gptq
+    R, C, G = 416, 384, 3
+    rows = [160, 64, 192]
+    g = torch.Generator(device='cuda').manual_seed(11)
+    err_t = torch.randn(C, R, device='cuda', generator=g)
+    quant_t = torch.randn(C, R, device='cuda', generator=g) * 0.02
+    orig_t = (torch.randn(C, R, device='cuda', generator=g) * 0.02).to(dtype)
+    scale_gr = torch.rand(G, R, device='cuda', generator=g) + 0.5
+    qzero_gr = torch.randint(0, 16, (G, R), device='cuda', generator=g).float()
+    perm = torch.randperm(C, device='cuda', generator=g)
+    U = torch.triu(torch.rand(C, C, device='cuda', generator=g) + 0.5)
+    for segs, pm, u in ((rows, perm, U), (None, None, U), (rows, perm, None)):
+        stats, scale, qzero = gptq.finalize_quant(err_t, quant_t, orig_t, scale_gr, qzero_gr, pm, u, segs)
+        torch.cuda.synchronize()
+        assert torch.equal(scale, scale_gr.t().to(dtype).contiguous()) and torch.equal(qzero, qzero_gr.t().to(torch.uint8).contiguous())
+        lo = 0
+        for si, n in enumerate(segs or [R]):
+            sl = slice(lo, lo + n)
+            o = orig_t[:, sl].double()
+            want = [float((err_t[:, sl].double() ** 2).sum()), float(((quant_t[:, sl].double() - o) ** 2).sum())]
+            if u is not None:
+                d = u.diagonal().double()[pm] if pm is not None else u.diagonal().double()
+                want.append(float(((o ** 2).sum(dim=1) / d ** 2).sum()))
+            else:
+                want.append(0.0)
+            want.append(float((orig_t[:, sl] * orig_t[:, sl]).double().sum()))
+            got = stats[si].tolist()
+            for a, b in zip(got, want):
+                assert a == pytest.approx(b, rel=2e-6, abs=1e-12), (si, got, want)
+            lo += n
+    with pytest.raises(gptq.GptqB200Error):
+        gptq.finalize_quant(err_t, quant_t, orig_t, scale_gr, qzero_gr, perm, U, [100, 316 + 1])

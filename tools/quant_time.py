@@ -66,7 +66,13 @@ def main():
         tp, _ = timed(lambda: gptq.transpose_pack_int4(codes_t, want_codes=True, want_packed=False))
         glue, _ = timed(lambda: (scale_gr.t().to(torch.float16).contiguous(), qzero_gr.t().to(torch.uint8).contiguous(),
                                  (W.abs() ** 2.).mean()))
-        print(json.dumps({'R': R, 'C': C, 'gptq_quant_ms': round(whole, 3), 'gptq_quant_with_host_sync_ms': round(sync_call, 3),
+        extra = {}
+        if (R, C) == (4096, 4096):
+            from gptq_py import gptq_quant_stacked
+            W3 = [W, W.clone(), W.clone()]
+            t3, _ = timed(lambda: gptq_quant_stacked(W3, hook, defer_metrics=True, **kw))
+            extra = {'stacked_3x4096_rows_ms': round(t3, 3), 'three_separate_calls_ms': round(3 * whole, 3)}
+        print(json.dumps({**extra, 'R': R, 'C': C, 'gptq_quant_ms': round(whole, 3), 'gptq_quant_with_host_sync_ms': round(sync_call, 3),
                           'prep_ms': round(prep, 3), 'solve_ms': round(solve_t - clone_t, 3), 'metrics_ms': round(met, 3),
                           'transpose_ms': round(tp, 3), 'scale_zero_l2norm_glue_ms': round(glue, 3)}))
 
