@@ -59,6 +59,8 @@ int make_tmap_2d(CUtensorMap* out, const void* base, int elem_kind, uint64_t inn
                  uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_outer, int swizzle_atom32 = 0);
 
 // general form: cu_dtype is a CUtensorMapDataType, cu_swizzle a CUtensorMapSwizzle
+int make_tmap_f32_colgroups(CUtensorMap* out, const float* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows,
+                            uint32_t box_groups);
 int make_tmap_2d_raw(CUtensorMap* out, const void* base, int cu_dtype, uint64_t inner, uint64_t outer,
                      uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_outer, int cu_swizzle);
 

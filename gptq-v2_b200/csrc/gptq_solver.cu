@@ -12,7 +12,8 @@ struct SolveParams;
 GQ_DECL(0, 32) GQ_DECL(0, 64) GQ_DECL(0, 128) GQ_DECL(1, 32) GQ_DECL(1, 64) GQ_DECL(1, 128)
 #undef GQ_DECL
 struct SuperParams;
-#define GQ_DECL(MODE, NQ) int launch_solve_super_m##MODE##_nq##NQ(const CUtensorMap& map_u, const SuperParams& p, cudaStream_t st);
+struct SuperMaps;
+#define GQ_DECL(MODE, NQ) int launch_solve_super_m##MODE##_nq##NQ(const SuperMaps& maps_u, const SuperParams& p, cudaStream_t st);
 GQ_DECL(0, 1) GQ_DECL(0, 2) GQ_DECL(0, 4) GQ_DECL(1, 1) GQ_DECL(1, 2) GQ_DECL(1, 4)
 #undef GQ_DECL
 
@@ -21,7 +22,7 @@ GQ_DECL(0, 1) GQ_DECL(0, 2) GQ_DECL(0, 4) GQ_DECL(1, 1) GQ_DECL(1, 2) GQ_DECL(1,
 namespace gq {
 
 // rows per CTA of the fused super-block kernel: the smallest tile that still fits the linear into one wave of CTAs
-static int launch_super_nq(int mode, const CUtensorMap& map_u, const SuperParams& p, int n_sms, cudaStream_t st) {
+static int launch_super_nq(int mode, const SuperMaps& map_u, const SuperParams& p, int n_sms, cudaStream_t st) {
   const int nq = (p.R + 31) / 32 <= n_sms ? 1 : (p.R + 63) / 64 <= n_sms ? 2 : 4;
   if (mode == 0) {
     switch (nq) {
@@ -109,9 +110,13 @@ int gptq_solve(float* Wt, const float* U, float* quant_t, void* codes_t, int cod
       cudaGetDevice(&dev);
       if (cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n_sms <= 0) n_sms = 148;
     }
-    CUtensorMap map_u;
-    int rc = make_tmap_2d(&map_u, U, 2, (uint64_t)C, (uint64_t)C, (uint64_t)C * 4, 32, 8, 1);
-    if (rc != GQ_OK) return rc;
+    SuperMaps map_u;
+    int rc = GQ_OK;
+    for (int g = 0; g < 3; ++g)
+      if ((rc = make_tmap_f32_colgroups(&map_u.m[g], U, (uint64_t)C, (uint64_t)C, (uint64_t)C, 8, 4 * (g + 1))) != GQ_OK) return rc;
+    for (int g = 0; g < 8; ++g)
+      if ((rc = make_tmap_2d_raw(&map_u.upk[g], U, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, (uint64_t)C, (uint64_t)C, (uint64_t)C * 4,
+                                 128 - 16 * g, 16, CU_TENSOR_MAP_SWIZZLE_NONE)) != GQ_OK) return rc;
     const int per = std::min(g_solve_super, (int)SUP_MAXBLK);
     const int n_blocks = (int)blocks.size();
     for (int b0 = 0; b0 < n_blocks; b0 += per) {

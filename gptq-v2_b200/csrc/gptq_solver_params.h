@@ -1,4 +1,5 @@
 #pragma once
+#include <cuda.h>
 namespace gq {
 struct SolveParams {
   float* Wt;            // (C, R) in/out
@@ -30,5 +31,12 @@ struct SuperParams {
   int static_params;    // MODE 0 only: scale / qzero are inputs
   long long* dbg;       // profiling hook (gq_set_solve_debug): clock64 stamps of CTA 0's first chain warp, or null
 };
+
+// U as (32 columns, rows, column groups): box of 8 rows x 4 / 8 / 12 column groups = the later columns of one / two / three
+// blocks of a super-block in ONE TMA instruction per 8-deep k-slice (m[g] holds the box with 4 (g + 1) groups)
+// upk[g]: plain box of 16 rows x (128 - 16 g) columns = rows [16 g, 16 g + 16) of a diagonal block of U from their first kept
+// column on: the packed diagonal block arrives in 8 TMA instructions (128 row-wise bulk copies kept the TMA issue slot busy
+// for ~7000 cycles per block, in front of the ring loads)
+struct SuperMaps { CUtensorMap m[3]; CUtensorMap upk[8]; };
 
 }  // namespace gq

@@ -75,7 +75,7 @@ __device__ __forceinline__ float sup_lo(float x) {            // rna_tf32(x - tr
 
 template <int MODE, int NQ, typename CodeT>
 __global__ void __launch_bounds__(SUP_THREADS, 1)
-solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams p) {
+solve_super_kernel(const __grid_constant__ SuperMaps maps_u, const SuperParams p) {
   using Cfg = SupCfg<MODE, NQ>;
   constexpr int STAGES = Cfg::STAGES;
   extern __shared__ uint8_t sup_smem[];
@@ -102,7 +102,8 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
   const int R = p.R;
 
   if (threadIdx.x == 0) {
-    tma_prefetch_desc(&map_u);
+    tma_prefetch_desc(&maps_u.m[0]); tma_prefetch_desc(&maps_u.m[1]); tma_prefetch_desc(&maps_u.m[2]);
+    for (int g = 0; g < 8; ++g) tma_prefetch_desc(&maps_u.upk[g]);
     for (int s = 0; s < STAGES; ++s) { mbar_init(bfull(s), 1); mbar_init(bready(s), SUP_SPLIT_THREADS); mbar_init(bempty(s), 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(aready(i), NQ); mbar_init(aempty(i), 1); }
     for (int r = 0; r < 3; ++r) mbar_init(accfull(r), 1);
@@ -128,19 +129,17 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
         if (lane == 0) mbar_expect_tx(ubar(t & 1), SUP_UPK_BYTES);
         __syncwarp();
       };
-      auto upk_rows = [&](int t, int r0) {                       // rows r0 .. r0 + 31 of block t's diagonal block
+      auto upk_group = [&](int t, int g) {                       // rows [16 g, 16 g + 16) of block t's diagonal block
         const int cb = p.c0 + SUP_NB * t;
         float* Upk = Upk0 + (t % NUPK) * UPK_FLOATS<SUP_NB>;
-        const int jr = r0 + lane, sbj = jr / SB, cs = sbj * SB;  // first column kept for this row
-        bulk_load_1d(smem_u32(Upk + upk_base<SUP_NB>(sbj) + (jr - cs) * (SUP_NB - cs)),
-                     p.U + (size_t)(cb + jr) * p.C + cb + cs, (SUP_NB - cs) * 4, ubar(t & 1));
+        if (lane == 0) tma_load_2d(smem_u32(Upk + upk_base<SUP_NB>(g)), &maps_u.upk[g], ubar(t & 1), cb + 16 * g, cb + 16 * g);
       };
       auto wait_free = [&](int bnd) {                            // boundary `bnd` passed: everyone is done with block bnd - 1
         if (lane == 0) mbar_wait(ufree, bnd & 1u);
         __syncwarp();
       };
       upk_begin(0);
-      for (int r0 = 0; r0 < SUP_NB; r0 += 32) upk_rows(0, r0);
+      for (int g = 0; g < SUP_NB / SB; ++g) upk_group(0, g);
       int stage = 0; uint32_t phase = 0;
       for (int b = 0; b + 1 < p.nblk; ++b) {
         const int nsub = 4 * (p.nblk - 1 - b);
@@ -149,20 +148,23 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
         if (NUPK == 1 && t >= 1) {                               // single buffer: needed at once
           wait_free(t);
           upk_begin(t);
-          for (int r0 = 0; r0 < SUP_NB; r0 += 32) upk_rows(t, r0);
+          for (int g = 0; g < SUP_NB / SB; ++g) upk_group(t, g);
         }
         for (int k8 = 0; k8 < SUP_NB / 8; ++k8) {
           if (lane == 0) {
             mbar_wait(bempty(stage), phase ^ 1u);
             mbar_expect_tx(bfull(stage), nsub * SUP_SUBTILE);
             const uint32_t dst = ring + stage * SUP_STAGE_BYTES;
-            for (int j = 0; j < nsub; ++j) tma_load_2d(dst + j * SUP_SUBTILE, &map_u, bfull(stage), col + 32 * j, row + 8 * k8);
+            // one instruction per k-slice: nsub consecutive [8 k][32 col] sub-tiles (a box per sub-tile kept the TMA issue
+            // slot busy for ~3000 cycles per sub-block: the tensor core fell 8000 cycles behind the chain by the end of a block)
+            tma_load_3d(dst, &maps_u.m[nsub / 4 - 1], bfull(stage), 0, row + 8 * k8, col / 32);
           }
           __syncwarp();
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
-          if (NUPK == 2 && k8 >= 3 && k8 <= 9 && (k8 & 1)) {     // after k-slices 3, 5, 7, 9: 32 rows each
+          if (NUPK == 2 && k8 >= 3 && k8 <= 9 && (k8 & 1)) {     // after k-slices 3, 5, 7, 9: two 16-row groups each
             if (k8 == 3) { wait_free(b); upk_begin(t); }
-            upk_rows(t, 16 * (k8 - 3));
+            upk_group(t, k8 - 3);
+            upk_group(t, k8 - 2);
           }
         }
       }
@@ -170,7 +172,7 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
         const int t = p.nblk - 1;
         wait_free(t);
         upk_begin(t);
-        for (int r0 = 0; r0 < SUP_NB; r0 += 32) upk_rows(t, r0);
+        for (int g = 0; g < SUP_NB / SB; ++g) upk_group(t, g);
       }
     }
   } else if (warp == 17 || warp == 18) {
@@ -198,17 +200,22 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
       const uint32_t idesc128 = umma_idesc(2u, 0u, 1u, 128, 128), idesc256 = umma_idesc(2u, 0u, 1u, 128, 256);
       int stage = 0; uint32_t phase = 0;
       int u = 0;
+      long long* mdbg = (p.dbg && blockIdx.x == 0) ? p.dbg + 256 * 4 : nullptr;   // profiling: (aready, bready, issued) per sub-block
+      int mdi = 0;
+      auto mstamp = [&]() { if (mdbg && mdi < 256) mdbg[mdi++] = clock64(); };
       for (int b = 0; b + 1 < p.nblk; ++b) {
         const int nreg = p.nblk - 1 - b;                       // accumulator regions this block feeds
         for (int sb = 0; sb < SUP_NB / SB; ++sb, ++u) {
           const int abuf = u & 1;
           mbar_wait(aready(abuf), (u >> 1) & 1u);
+          mstamp();
           const int st0 = stage; const uint32_t ph0 = phase;
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
           const int st1 = stage; const uint32_t ph1 = phase;
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
           mbar_wait(bready(st0), ph0);
           mbar_wait(bready(st1), ph1);
+          mstamp();
           tc_fence_after();
           const uint32_t a_hi = tmem_base + SUP_TMEM_A + abuf * 32, a_lo = a_hi + 16;
           const uint32_t first = (b == 0 && sb == 0) ? 0u : 1u;
@@ -263,6 +270,7 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
           tc_commit_cg1(bempty(st0));
           tc_commit_cg1(bempty(st1));
           tc_commit_cg1(aempty(abuf));
+          mstamp();
         }
       }
     }
@@ -344,9 +352,11 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
         // W_global - (updates of the super-block's earlier blocks, accumulated in tensor memory); the global loads are in
         // flight while the last MMAs of the previous block finish
         prefetch_w(b);
+        stamp();
         float* ws_q = Qp(my_q);
         if (b > 0) {
           mbar_wait(accfull(b - 1), 0);
+          stamp();
           tc_fence_after();
           const uint32_t t = tmem_base + (uint32_t(32 * my_q) << 16) + SUP_NB * (b - 1) + part_c0;
 #pragma unroll
@@ -358,6 +368,8 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
             for (int i = 0; i < 16; ++i) wv[16 * h + i] = __fsub_rn(wv[16 * h + i], __uint_as_float(a[i]));
           }
         }
+        else stamp();
+        stamp();
         float mx = -INFINITY, mn = INFINITY;
 #pragma unroll
         for (int i = 0; i < 48; ++i) {
@@ -368,7 +380,7 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
         }
         ws_q[OFF_MM + part * 32 + lane] = mx;
         ws_q[OFF_MM + (4 + part) * 32 + lane] = mn;
-      }
+      } else { stamp(); stamp(); stamp(); }
       stamp();
       named_bar_sync(1, SUP_COMPUTE_THREADS);                    // the block's weights and min / max partials are in place
       // the NEXT block's diagonal block of U and reciprocals start travelling now
@@ -501,7 +513,7 @@ solve_super_kernel(const __grid_constant__ CUtensorMap map_u, const SuperParams 
 }
 
 template <int MODE, int NQ, typename CodeT>
-int launch_super(const CUtensorMap& map_u, const SuperParams& p, cudaStream_t st) {
+int launch_super(const SuperMaps& maps_u, const SuperParams& p, cudaStream_t st) {
   using Cfg = SupCfg<MODE, NQ>;
   static PerDeviceFlag attr_set;   // function attributes are per device
   if (!attr_set) {
@@ -513,7 +525,7 @@ int launch_super(const CUtensorMap& map_u, const SuperParams& p, cudaStream_t st
   const int rows = 32 * NQ;
   GQ_LAUNCHED();
   return launch_chain(solve_super_kernel<MODE, NQ, CodeT>, dim3((p.R + rows - 1) / rows), dim3(SUP_THREADS), (size_t)Cfg::SMEM_BYTES, st,
-                      g_pdl != 0, map_u, p) == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
+                      g_pdl != 0, maps_u, p) == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
 }
 
 }  // namespace gq

@@ -1,6 +1,6 @@
 #include "gptq_solver_super.cuh"
 namespace gq {
-int launch_solve_super_m0_nq1(const CUtensorMap& map_u, const SuperParams& p, cudaStream_t st) {
-  return launch_super<0, 1, uint8_t>(map_u, p, st);
+int launch_solve_super_m0_nq1(const SuperMaps& maps_u, const SuperParams& p, cudaStream_t st) {
+  return launch_super<0, 1, uint8_t>(maps_u, p, st);
 }
 }  // namespace gq

@@ -94,6 +94,11 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* tmap, uint
                " [%0], [%1, {%3, %4}], [%2];"
                :: "r"(dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar), "r"(c0), "r"(c1) : "memory");
 }
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const void* tmap, uint32_t bar, int c0, int c1, int c2) {
+  asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes"
+               " [%0], [%1, {%3, %4, %5}], [%2];"
+               :: "r"(dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
 // 2D tile load issued inside a CTA pair; `bar` is a shared::cluster address
 // (the leader CTA's barrier), data lands in this CTA's smem.
 __device__ __forceinline__ void tma_load_2d_cg2(uint32_t dst, const void* tmap, uint32_t bar, int c0, int c1) {

@@ -319,6 +319,24 @@ int make_tmap_2d(CUtensorMap* out, const void* base, int elem_kind, uint64_t inn
   return r == CUDA_SUCCESS ? GQ_OK : GQ_ERR_TENSORMAP;
 }
 
+// fp32 matrix (rows x cols, cols % 32 == 0) seen as (32 columns, rows, cols / 32 column groups): one box of (32, box_rows,
+// box_groups) lands as box_groups consecutive [box_rows][32] sub-tiles (SWIZZLE_128B_ATOM_32B, the MN-major tf32 operand
+// layout) -- one TMA instruction where a 2D map needs one per 32-column group.
+int make_tmap_f32_colgroups(CUtensorMap* out, const float* base, uint64_t rows, uint64_t cols, uint64_t ld, uint32_t box_rows,
+                            uint32_t box_groups) {
+  PFN_encodeTiled enc = get_encode_fn();
+  if (!enc) return GQ_ERR_DRIVER;
+  if (cols % 32 != 0 || ld % 4 != 0) return GQ_ERR_SHAPE;
+  cuuint64_t dims[3] = {32, rows, cols / 32};
+  cuuint64_t strides[2] = {ld * 4, 128};
+  cuuint32_t box[3] = {32, box_rows, box_groups};
+  cuuint32_t estr[3] = {1, 1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(base), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  return r == CUDA_SUCCESS ? GQ_OK : GQ_ERR_TENSORMAP;
+}
+
 int make_tmap_2d_raw(CUtensorMap* out, const void* base, int cu_dtype, uint64_t inner, uint64_t outer,
                      uint64_t row_stride_bytes, uint32_t box_inner, uint32_t box_outer, int cu_swizzle) {
   PFN_encodeTiled enc = get_encode_fn();
