@@ -97,7 +97,8 @@ __device__ __forceinline__ float rna_tf32(float x) {
 template <int CG>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b,
-                   const __grid_constant__ CUtensorMap map_c, const GemmTf32Params p) {
+                   const __grid_constant__ CUtensorMap map_c, const __grid_constant__ CUtensorMap map_a3,
+                   const __grid_constant__ CUtensorMap map_b3, const GemmTf32Params p) {
   using C = Cfg<CG>;
   constexpr int TM = C::TM, A_SUBS = C::A_SUBS, B_SUBS = C::B_SUBS, HI_BYTES = C::HI_BYTES, STAGE_BYTES = C::STAGE_BYTES,
                 STAGES = C::STAGES;
@@ -126,6 +127,7 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&map_a); tma_prefetch_desc(&map_b); tma_prefetch_desc(&map_c);
+    tma_prefetch_desc(&map_a3); tma_prefetch_desc(&map_b3);
     // full: this CTA's own TMA bytes (its split warps wait on it); ready: one arrival per CTA of the pair (after its split warps have
     // synchronised) on the leader's barrier; empty / tfull: the leader's tcgen05.commit, multicast to both CTAs; tempty: 4 epilogue warps per CTA
     for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(ready_bar(s), CG == 2 ? 2 : SPLIT_THREADS); mbar_init(empty_bar(s), 1); }
@@ -158,12 +160,19 @@ gemm_tf32x3_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_const
           mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t sa = smem_base + stage * STAGE_BYTES;
           mbar_expect_tx(full_bar(stage), HI_BYTES);
+          if (p.flags & TF32_COLGROUPS) {
+            // one instruction per operand: A_SUBS / B_SUBS consecutive [16 k][32 col] sub-tiles (a box per sub-tile costs the
+            // TMA issue slot ~100 cycles each, 8 - 12 of them per 16-deep k-block of ~760 tensor cycles)
+            tma_load_3d(sa, &map_a3, full_bar(stage), 0, q.a_row0 + kb * BK, (q.a_col0 + m0) >> 5);
+            tma_load_3d(sa + A_SUBS * SUB, &map_b3, full_bar(stage), 0, q.b_row0 + kb * BK, (q.b_col0 + n0) >> 5);
+          } else {
 #pragma unroll
-          for (int i = 0; i < A_SUBS; ++i)
-            tma_load_2d(sa + i * SUB, &map_a, full_bar(stage), q.a_col0 + m0 + 32 * i, q.a_row0 + kb * BK);
+            for (int i = 0; i < A_SUBS; ++i)
+              tma_load_2d(sa + i * SUB, &map_a, full_bar(stage), q.a_col0 + m0 + 32 * i, q.a_row0 + kb * BK);
 #pragma unroll
-          for (int j = 0; j < B_SUBS; ++j)
-            tma_load_2d(sa + (A_SUBS + j) * SUB, &map_b, full_bar(stage), q.b_col0 + n0 + 32 * j, q.b_row0 + kb * BK);
+            for (int j = 0; j < B_SUBS; ++j)
+              tma_load_2d(sa + (A_SUBS + j) * SUB, &map_b, full_bar(stage), q.b_col0 + n0 + 32 * j, q.b_row0 + kb * BK);
+          }
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
       }
@@ -364,6 +373,14 @@ int gemm_tf32x3_maps(Tf32Maps* maps, const float* A, int a_rows, int a_cols, int
   if ((rc = make_map_f32(&maps->a, A, a_rows, a_cols, lda, 32, BK, 1)) != GQ_OK) return rc;
   if ((rc = make_map_f32(&maps->b, B, b_rows, b_cols, ldb, 32, BK, 1)) != GQ_OK) return rc;
   if ((rc = make_map_f32(&maps->c, C, c_rows, c_cols, ldc, 32, 32, 0)) != GQ_OK) return rc;
+  maps->groups_ok = (a_cols % 32 == 0) && (b_cols % 32 == 0);
+  if (maps->groups_ok) {
+    if ((rc = make_tmap_f32_colgroups(&maps->a3, A, (uint64_t)a_rows, (uint64_t)a_cols, (uint64_t)lda, BK, 4)) != GQ_OK) return rc;
+    if ((rc = make_tmap_f32_colgroups(&maps->b3_8, B, (uint64_t)b_rows, (uint64_t)b_cols, (uint64_t)ldb, BK, 8)) != GQ_OK) return rc;
+    if ((rc = make_tmap_f32_colgroups(&maps->b3_4, B, (uint64_t)b_rows, (uint64_t)b_cols, (uint64_t)ldb, BK, 4)) != GQ_OK) return rc;
+  } else {
+    maps->a3 = maps->a; maps->b3_8 = maps->b; maps->b3_4 = maps->b;      // never used: the kernel takes the 2D boxes
+  }
   return GQ_OK;
 }
 
@@ -394,7 +411,8 @@ static int launch_gemm(const Tf32Maps& maps, const GemmTf32Params& p, int n_sms,
   cfg.attrs = at;
   cfg.numAttrs = g_pdl ? 2 : 1;
   GQ_LAUNCHED();
-  return cudaLaunchKernelEx(&cfg, gemm_tf32x3_kernel<CG>, maps.a, maps.b, maps.c, p) == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
+  return cudaLaunchKernelEx(&cfg, gemm_tf32x3_kernel<CG>, maps.a, maps.b, maps.c, maps.a3, CG == 2 ? maps.b3_4 : maps.b3_8, p) == cudaSuccess
+             ? GQ_OK : GQ_ERR_CUDA;
 }
 
 int gemm_tf32x3_batch(const Tf32Maps& maps, const Tf32Problem* probs, int count, float alpha, int flags, cudaStream_t st) {
@@ -410,6 +428,7 @@ int gemm_tf32x3_batch(const Tf32Maps& maps, const Tf32Problem* probs, int count,
   p.count = 0; p.tiles_m = 0; p.tiles_n = 0; p.alpha = alpha;
   p.flags = flags | (g_use_tf32x3 >= 2 ? TF32_RAW_HI : 0);
   p.kchunk = g_tf32_kchunk;
+  bool groups = maps.groups_ok != 0;
   int max_m = 0, max_n = 0;
   for (int i = 0; i < count; ++i) {
     const Tf32Problem& q = probs[i];
@@ -418,10 +437,12 @@ int gemm_tf32x3_batch(const Tf32Maps& maps, const Tf32Problem* probs, int count,
     // the tensor maps clip at the edge of the WHOLE matrix, not of the window: a store-mode window must be tile-exact
     // in N (32-column boxes) and M (32-row boxes) unless it ends at the matrix edge -- callers guarantee % 32 == 0
     p.p[p.count++] = q;
+    groups = groups && ((q.a_col0 | q.b_col0) & 31) == 0;
     max_m = max(max_m, q.M);
     max_n = max(max_n, q.N);
   }
   if (p.count == 0) return GQ_OK;
+  if (groups) p.flags |= TF32_COLGROUPS;
   p.tiles_n = (max_n + TN - 1) / TN;
   // CTA pairs (256-row tiles) whenever they need no more waves than single CTAs would: a pair's main loop moves a third
   // less through shared memory per flop, which also shortens the one-tile-per-CTA near updates on the critical path

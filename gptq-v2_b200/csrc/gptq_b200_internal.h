@@ -88,7 +88,9 @@ extern long long* g_solve_dbg;  // profiling hook: device buffer for the fused s
 extern int g_solve_fused;  // K3/K4: 1 (default) = 128-column blocks run through the fused super-block kernel (near updates in tensor memory); 0 = one launch per block + near-update GEMMs
 extern int g_solve_super;  // K4: blocks per super-block of the two-level lazy-batch update (1 = update everything after every block)
 extern int g_use_tf32x3;   // 3 (default): K4 / Cholesky updates on tcgen05 3xTF32, truncation split (TF32_RAW_HI), 256 x 256 tiles on CTA pairs (cta_group::2) when there is more than one wave of tiles; 2: truncation split, single-CTA tiles only; 1: round-to-nearest split; 0: fp32 SIMT GEMM (A/B parity hook)
-struct Tf32Maps { CUtensorMap a, b, c; };
+// a3 / b3_8 / b3_4: the same operands seen as (32 columns, rows, column groups), boxes of 16 rows x 4 / 8 / 4 groups: one TMA
+// instruction per operand and k-block (groups_ok: both matrices have a multiple of 32 columns)
+struct Tf32Maps { CUtensorMap a, b, c, a3, b3_8, b3_4; int groups_ok; };
 // one GEMM of a batched launch: windows into the matrices the three tensor maps describe
 struct Tf32Problem {
   int M, N, K;
@@ -103,6 +105,7 @@ enum : int {
   TF32_A_UPPER = 4,        // A (K x M) is upper triangular: k range of a tile ends at m0 + 128
   TF32_B_LOWER = 8,        // B (K x N) is lower triangular: k range of a tile starts at n0
   TF32_RAW_HI = 16,        // split stage keeps the landed fp32 tile as hi (the MMA truncates it) and writes only lo
+  TF32_COLGROUPS = 32,     // (set by the launcher) operand windows start at multiples of 32 columns: 3D column-group boxes
 };
 int gemm_tf32x3_batch(const Tf32Maps& maps, const Tf32Problem* probs, int count, float alpha, int flags, cudaStream_t st);
 int gemm_tf32x3_maps(Tf32Maps* maps, const float* A, int a_rows, int a_cols, int lda, const float* B, int b_rows,
