@@ -49,6 +49,7 @@ struct SyrkParams {
   int NT;         // ceil(D / 256)
   int n_tiles;    // NT (NT + 1) / 2
   int kchunk;     // 64-token k-blocks accumulated in tensor memory before the partial sum is added to H (0 = all of T)
+  int groups;     // D % 64 == 0: operands through the 3D column-group map (one TMA instruction per operand and k-block)
 };
 
 // Tile order.  Super-tiles that run at the same time should share operand panels: the 74 CTA pairs walk the upper
@@ -95,7 +96,7 @@ __device__ __forceinline__ void decode_tile(int s, int NT, int& a, int& nj) {
 
 template <int CG>
 __global__ void __launch_bounds__(256, 1)
-syrk_upper_kernel(const __grid_constant__ CUtensorMap tmap, const SyrkParams p) {
+syrk_upper_kernel(const __grid_constant__ CUtensorMap tmap, const __grid_constant__ CUtensorMap tmap3, const SyrkParams p) {
   using C = SyrkCfg<CG>;
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
@@ -118,7 +119,7 @@ syrk_upper_kernel(const __grid_constant__ CUtensorMap tmap, const SyrkParams p) 
   const int num_kb = (p.T + C::BK - 1) / C::BK;
 
   if (warp == 0 && lane == 0) {
-    tma_prefetch_desc(&tmap);
+    tma_prefetch_desc(&tmap); tma_prefetch_desc(&tmap3);
     for (int s = 0; s < C::STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
     for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 4 * CG); }
     fence_mbar_init();
@@ -148,12 +149,18 @@ syrk_upper_kernel(const __grid_constant__ CUtensorMap tmap, const SyrkParams p) 
             // all bytes of both CTAs are accounted on the leader's barrier
             const uint32_t lead_full = full_bar(stage) & 0xFEFFFFFFu;
             if (rank == 0) mbar_expect_tx(full_bar(stage), 2u * C::STAGE_BYTES);
+            if (p.groups) {
+              // X as (64 columns, tokens, column groups): both 64-column sub-tiles of an operand in one instruction
+              tma_load_3d_cg2(sa, &tmap3, lead_full, 0, t0, m_base >> 6);
+              tma_load_3d_cg2(sa + C::A_SUBS * C::SUB_BYTES, &tmap3, lead_full, 0, t0, n_base >> 6);
+            } else {
 #pragma unroll
             for (int i = 0; i < C::A_SUBS; ++i)
               tma_load_2d_cg2(sa + i * C::SUB_BYTES, &tmap, lead_full, m_base + 64 * i, t0);
 #pragma unroll
             for (int j = 0; j < C::B_SUBS; ++j)
               tma_load_2d_cg2(sa + (C::A_SUBS + j) * C::SUB_BYTES, &tmap, lead_full, n_base + 64 * j, t0);
+            }
           } else {
             mbar_expect_tx(full_bar(stage), C::STAGE_BYTES);
 #pragma unroll
@@ -352,7 +359,7 @@ int make_tmap_2d_raw(CUtensorMap* out, const void* base, int cu_dtype, uint64_t 
 }
 
 template <int CG>
-static int launch_syrk(const CUtensorMap& tmap, const SyrkParams& p, int n_sms, cudaStream_t st) {
+static int launch_syrk(const CUtensorMap& tmap, const CUtensorMap& tmap3, const SyrkParams& p, int n_sms, cudaStream_t st) {
   using C = SyrkCfg<CG>;
   static PerDeviceFlag attr_set;   // function attributes are per device
   if (!attr_set) {
@@ -376,7 +383,7 @@ static int launch_syrk(const CUtensorMap& tmap, const SyrkParams& p, int n_sms, 
   cfg.attrs = at;
   cfg.numAttrs = 1;
   GQ_LAUNCHED();
-  cudaError_t e = cudaLaunchKernelEx(&cfg, syrk_upper_kernel<CG>, tmap, p);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, syrk_upper_kernel<CG>, tmap, tmap3, p);
   return e == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
 }
 
@@ -393,11 +400,25 @@ int syrk_upper(float* H, const void* X, int D, int T, int fmt, int mode, int var
   p.NT = (D + 255) / 256;
   p.n_tiles = p.NT * (p.NT + 1) / 2;
   p.kchunk = g_syrk_kchunk;
+  p.groups = (D % 64 == 0) ? 1 : 0;
+  CUtensorMap tmap3 = tmap;
+  if (p.groups) {
+    PFN_encodeTiled enc = get_encode_fn();
+    if (!enc) return GQ_ERR_DRIVER;
+    cuuint64_t dims[3] = {64, (cuuint64_t)T, (cuuint64_t)(D / 64)};
+    cuuint64_t strides[2] = {(cuuint64_t)D * 2, 128};
+    cuuint32_t box[3] = {64, 64, 2};
+    cuuint32_t estr[3] = {1, 1, 1};
+    if (enc(&tmap3, fmt == 0 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(X), dims,
+            strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS)
+      return GQ_ERR_TENSORMAP;
+  }
   int dev = 0, n_sms = 0;
   cudaGetDevice(&dev);
   cudaDeviceGetAttribute(&n_sms, cudaDevAttrMultiProcessorCount, dev);
-  if (variant == 1) return launch_syrk<1>(tmap, p, n_sms, st);
-  return launch_syrk<2>(tmap, p, n_sms, st);
+  if (variant == 1) return launch_syrk<1>(tmap, tmap3, p, n_sms, st);
+  return launch_syrk<2>(tmap, tmap3, p, n_sms, st);
 }
 
 }  // namespace gq
