@@ -68,45 +68,61 @@ chol_panel_kernel(float* __restrict__ A, int D, int o, int n, int rest, int* __r
 
   pdl_launch_dependents();
   pdl_wait();
-  // ---- stage [A_kk (upper) | panel columns]; a partial block is padded with the identity.  All of a thread's loads
-  // are issued before its first store: one global round trip for the whole block row instead of one per float4.
-  {
-    constexpr int ND = NB * (NB / 4) / 256;          // float4 per thread, diagonal block (16)
-    float4 v[ND];
+  // ---- stage [A_kk (upper) | panel columns]; a partial block is padded with the identity.  Warp 0 fetches only what the
+  // first diagonal sub-block's factorisation needs (rows 0..15 of A_kk) and starts on it while warps 1-7 stage the rest.
+  auto load_diag = [&](int r, int c4) {
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (r < n && c4 < n) v = *reinterpret_cast<const float4*>(A + (size_t)(o + r) * D + o + c4);   // n % 4 == 0
+    if (r >= n) { v.x = (c4 == r) ? 1.f : 0.f; v.y = (c4 + 1 == r) ? 1.f : 0.f; v.z = (c4 + 2 == r) ? 1.f : 0.f; v.w = (c4 + 3 == r) ? 1.f : 0.f; }
+    return v;
+  };
+  if (warp == 0) {
+    float4 v[SBK];
 #pragma unroll
-    for (int k = 0; k < ND; ++k) {
-      const int idx = tid + k * 256;
-      const int r = idx / (NB / 4), c4 = (idx - r * (NB / 4)) * 4;
-      v[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (r < n && c4 < n) v[k] = *reinterpret_cast<const float4*>(A + (size_t)(o + r) * D + o + c4);   // n % 4 == 0
-      if (r >= n) { v[k].x = (c4 == r) ? 1.f : 0.f; v[k].y = (c4 + 1 == r) ? 1.f : 0.f; v[k].z = (c4 + 2 == r) ? 1.f : 0.f; v[k].w = (c4 + 3 == r) ? 1.f : 0.f; }
+    for (int k = 0; k < SBK; ++k) v[k] = load_diag(k, 4 * lane);                  // row k, 128 columns across the warp
+#pragma unroll
+    for (int k = 0; k < SBK; ++k) *reinterpret_cast<float4*>(S + k * W + 4 * lane) = v[k];
+    __syncwarp();
+  } else {
+    const int wt = tid - 32;                                                       // 0..223
+    constexpr int DI = (NB - SBK) * (NB / 4);                                      // diagonal block, rows 16..127
+    constexpr int UNR = 8;                                                         // loads in flight per thread
+    for (int base = 0; base < DI; base += 224 * UNR) {
+      float4 v[UNR];
+#pragma unroll
+      for (int k = 0; k < UNR; ++k) {
+        const int idx = base + wt + k * 224;
+        const int r = SBK + idx / (NB / 4), c4 = (idx % (NB / 4)) * 4;
+        if (idx < DI) v[k] = load_diag(r, c4);
+      }
+#pragma unroll
+      for (int k = 0; k < UNR; ++k) {
+        const int idx = base + wt + k * 224;
+        const int r = SBK + idx / (NB / 4), c4 = (idx % (NB / 4)) * 4;
+        if (idx < DI) *reinterpret_cast<float4*>(S + r * W + c4) = v[k];
+      }
     }
     if constexpr (PC > 0) {
-      constexpr int NP = NB * (PC / 4) / 256;        // float4 per thread, panel (8 for PC = 64)
-      float4 pv[NP];
+      constexpr int PI = NB * (PC / 4);
+      for (int base = 0; base < PI; base += 224 * UNR) {
+        float4 v[UNR];
 #pragma unroll
-      for (int k = 0; k < NP; ++k) {
-        const int idx = tid + k * 256;
-        const int r = idx / (PC / 4), c4 = (idx - r * (PC / 4)) * 4;
-        pv[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (r < n && c4 < pcn) pv[k] = *reinterpret_cast<const float4*>(A + (size_t)(o + r) * D + o + n + pc0 + c4);   // rest % 4 == 0
+        for (int k = 0; k < UNR; ++k) {
+          const int idx = base + wt + k * 224;
+          const int r = idx / (PC / 4), c4 = (idx % (PC / 4)) * 4;
+          v[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (idx < PI && r < n && c4 < pcn) v[k] = *reinterpret_cast<const float4*>(A + (size_t)(o + r) * D + o + n + pc0 + c4);   // rest % 4 == 0
+        }
+#pragma unroll
+        for (int k = 0; k < UNR; ++k) {
+          const int idx = base + wt + k * 224;
+          const int r = idx / (PC / 4), c4 = (idx % (PC / 4)) * 4;
+          if (idx < PI) *reinterpret_cast<float4*>(S + r * W + NB + c4) = v[k];
+        }
       }
-#pragma unroll
-      for (int k = 0; k < NP; ++k) {
-        const int idx = tid + k * 256;
-        const int r = idx / (PC / 4), c4 = (idx - r * (PC / 4)) * 4;
-        *reinterpret_cast<float4*>(S + r * W + NB + c4) = pv[k];
-      }
-    }
-#pragma unroll
-    for (int k = 0; k < ND; ++k) {
-      const int idx = tid + k * 256;
-      const int r = idx / (NB / 4), c4 = (idx - r * (NB / 4)) * 4;
-      *reinterpret_cast<float4*>(S + r * W + c4) = v[k];
     }
   }
-  __syncthreads();
-  stamp();                                   // [1] block row staged
+  stamp();                                   // [1] this warp's share of the block row staged (no block-wide barrier here)
 
   bool bad = false;
   // ---- A: 16 x 16 diagonal sub-block at (so, so), warp 0 only
@@ -232,6 +248,32 @@ chol_panel_kernel(float* __restrict__ A, int D, int o, int n, int rest, int* __r
       }
       __syncthreads();
       stamp();                               // B done
+      // rows so..so+15 are final (factor rows and solved panel rows): they leave now, under the updates of the later rows
+      // (warps 2-7; warps 0-1 are on the look-ahead's path), instead of in one burst at the end of the kernel
+      if (warp >= 2) {
+        const int wt = tid - 64;                                                   // 0..191
+        if (blockIdx.x == 0) {
+          for (int idx = wt; idx < SBK * (NB / 4); idx += 192) {
+            const int r = so + idx / (NB / 4), c4 = (idx % (NB / 4)) * 4;
+            if (r < n && c4 < n) {
+              float4 v = *reinterpret_cast<const float4*>(S + r * W + c4);         // zeros below the diagonal
+              v.x = (c4 + 0 >= r) ? v.x : 0.f;
+              v.y = (c4 + 1 >= r) ? v.y : 0.f;
+              v.z = (c4 + 2 >= r) ? v.z : 0.f;
+              v.w = (c4 + 3 >= r) ? v.w : 0.f;
+              *reinterpret_cast<float4*>(A + (size_t)(o + r) * D + o + c4) = v;
+            }
+          }
+        }
+        if constexpr (PC > 0) {
+          for (int idx = wt; idx < SBK * (PC / 4); idx += 192) {
+            const int r = so + idx / (PC / 4), c4 = (idx % (PC / 4)) * 4;
+            if (r < n && c4 < pcn)
+              *reinterpret_cast<float4*>(A + (size_t)(o + r) * D + o + n + pc0 + c4) =
+                  *reinterpret_cast<const float4*>(S + r * W + NB + c4);
+          }
+        }
+      }
       if (s == NB / SBK - 1) break;
       // ---- C with look-ahead: warps 0-1 first bring the chunk that holds the NEXT diagonal sub-block up to date (one
       // 8-row group each, one 32-column chunk), then warp 0 factors it while everybody else -- and warp 0 afterwards --
@@ -261,29 +303,8 @@ chol_panel_kernel(float* __restrict__ A, int D, int o, int n, int rest, int* __r
     stamp();
   }
 
-  // ---- write back: the factor (CTA 0 only) and this CTA's panel columns
-  if (blockIdx.x == 0) {
-    // the whole diagonal block in 16-byte stores, zeros below the diagonal (nothing reads that part of A again before
-    // trtri_diag_kernel overwrites the block; branch-free, CTA 0 is the last one to finish)
-    for (int idx = tid; idx < n * (n / 4); idx += 256) {
-      const int r = idx / (n / 4), c4 = (idx - r * (n / 4)) * 4;
-      float4 v = *reinterpret_cast<const float4*>(S + r * W + c4);
-      v.x = (c4 + 0 >= r) ? v.x : 0.f;
-      v.y = (c4 + 1 >= r) ? v.y : 0.f;
-      v.z = (c4 + 2 >= r) ? v.z : 0.f;
-      v.w = (c4 + 3 >= r) ? v.w : 0.f;
-      *reinterpret_cast<float4*>(A + (size_t)(o + r) * D + o + c4) = v;
-    }
-    if (bad) atomicExch(info, 1);
-  }
-  if constexpr (PC > 0) {
-    for (int idx = tid; idx < n * (PC / 4); idx += 256) {
-      const int r = idx / (PC / 4), c4 = (idx - r * (PC / 4)) * 4;
-      if (c4 < pcn)
-        *reinterpret_cast<float4*>(A + (size_t)(o + r) * D + o + n + pc0 + c4) =
-            *reinterpret_cast<const float4*>(S + r * W + NB + c4);
-    }
-  }
+  // (every row group was written back when it became final)
+  if (blockIdx.x == 0 && bad) atomicExch(info, 1);
   stamp();                                   // written back
 }
 
