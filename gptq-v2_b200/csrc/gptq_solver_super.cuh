@@ -185,9 +185,16 @@ solve_super_kernel(const __grid_constant__ SuperMaps maps_u, const SuperParams p
         mbar_wait(bfull(stage), phase);
         const float4* hi = reinterpret_cast<const float4*>(ring_gen + stage * SUP_STAGE_BYTES);
         float4* lo = reinterpret_cast<float4*>(ring_gen + stage * SUP_STAGE_BYTES + SUP_STAGE_HI);
-        for (int i = tid; i < n4; i += SUP_SPLIT_THREADS) {
-          const float4 v = hi[i];
-          lo[i] = make_float4(sup_lo(v.x), sup_lo(v.y), sup_lo(v.z), sup_lo(v.w));
+        // n4 = 256 float4 per accumulator region: 4, 8 or 12 per thread, four loads in flight at a time (with one at a time
+        // the two split warps only just kept pace with a three-region block and the tensor core waited for them)
+#pragma unroll 1
+        for (int i = tid; i < n4; i += 4 * SUP_SPLIT_THREADS) {
+          float4 v[4];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) v[k] = hi[i + k * SUP_SPLIT_THREADS];
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            lo[i + k * SUP_SPLIT_THREADS] = make_float4(sup_lo(v[k].x), sup_lo(v[k].y), sup_lo(v[k].z), sup_lo(v[k].w));
         }
         fence_proxy_async();
         mbar_arrive(bready(stage));
