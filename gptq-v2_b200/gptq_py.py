@@ -60,7 +60,10 @@ class HessianHook:
             _ops.hessian_syrk(self.hessian, inp.contiguous(), mode=0)   # upper triangle only: invert() reads nothing else
 
     @torch.no_grad()
-    def invert(self, damp_ratio: float = 1e-2, act_order: bool = True) -> torch.Tensor:
+    def invert(self, damp_ratio: float = 1e-2, act_order: bool = True, *, defer_check: bool = False) -> torch.Tensor:
+        """ref :39-66.  defer_check (not in the reference): queue the first factorisation and return without the host
+        synchronisation that decides about a damping retry; the caller queues the work that consumes `hessian_inv` behind it
+        and then calls settle(), which does the check (and the reference's retry loop if the first try failed)."""
         H = self.hessian
         scale = 2.0 / self.n_samples                                   # ref :41
         diag = H.diagonal() * scale
@@ -71,19 +74,41 @@ class HessianHook:
             self.perm_inv = torch.empty_like(self.perm)
             self.perm_inv[self.perm] = torch.arange(self.perm.numel(), device=self.perm.device, dtype=self.perm.dtype)
         damp = (damp_ratio * diag.mean()).reshape(())                   # ref :52; stays on the device: K2 reads it there
-        max_try = 100
-        tries = 0
-        while (max_try := max_try - 1) >= 0:
-            tries += 1
-            # cumulative damping: try k factors H + k*damp*I (ref :58)
-            Hp, U, info = _ops.hessian_invert(H, self.perm, scale, damp, damp_mult=float(tries))
-            if not bool((info != 0) | ~torch.isfinite(U.diagonal()).all()):         # one host sync per try (ref :63)
-                break
-        assert max_try >= 0
+        self._pending = (H, scale, damp, 1, None)
+        self._factor_once()
+        if not defer_check:
+            self.settle()
+        return self.hessian_inv
+
+    def _factor_once(self) -> None:
+        H, scale, damp, tries, _ = self._pending
+        # cumulative damping: try k factors H + k*damp*I (ref :58)
+        Hp, U, info = _ops.hessian_invert(H, self.perm, scale, damp, damp_mult=float(tries))
+        self._pending = (H, scale, damp, tries, info)
         self.invert_tries = tries
         self.hessian = Hp                    # scaled, permuted, damped -- what the reference leaves behind
         self.hessian_inv = U
-        return self.hessian_inv
+
+    def settle(self) -> bool:
+        """The check invert(defer_check=True) left out: one host synchronisation; on a non-positive pivot or a non-finite
+        diag(U) the reference's retry loop (ref :55-65) runs now.  Returns True when the FIRST factorisation was good, i.e.
+        when everything that was queued behind it used the final `hessian_inv`; False means it has to be redone."""
+        pending = getattr(self, '_pending', None)
+        if pending is None:
+            return True
+        first_ok = True
+        max_try = 100
+        while True:
+            H, scale, damp, tries, info = self._pending
+            if not bool((info != 0) | ~torch.isfinite(self.hessian_inv.diagonal()).all()):   # one host sync per try (ref :63)
+                break
+            first_ok = False
+            max_try -= 1
+            assert max_try > 0
+            self._pending = (H, scale, damp, tries + 1, None)
+            self._factor_once()
+        self._pending = None
+        return first_ok
 
 
 def _mean_in_dtype(total: float, n: float, dtype: torch.dtype) -> float:

@@ -265,7 +265,7 @@ class _GroupQuantizer:
         with self.timer('allreduce'):
             sharded.allreduce_hessian(self.hook, self.n_global, self.pgroup)
         with self.timer('invert'):
-            self.hook.invert(self.damp, self.act_order)                  # llama.py:138
+            self.hook.invert(self.damp, self.act_order, defer_check=True)   # llama.py:138; checked behind the queued solves (settle)
 
     def quantize(self, weight: torch.Tensor) -> tuple[dict, dict, torch.Tensor]:
         """-> (quant_meta on save_device, metrics, dense reconstructed weight on the GPU)."""
@@ -283,6 +283,7 @@ class _GroupQuantizer:
                 # EXL2 scales are a maximum over all rows (quant.py:110): row sharding refuses them, one rank's worth of
                 # work on every rank instead
                 from gptq_py import gptq_quant
+                self.hook.settle()
                 results = [gptq_quant(weight=w, hessian_hook=self.hook, group_sizes=gs, group_bit_widths=gb,
                                       gptq_use_kernel=self.use_kernel_semantics, gptq_block_sizes=gs, save_device=dev,
                                       **self.quant_options) for w in weights]

@@ -176,6 +176,18 @@ def plan_group(rows: Sequence[int], world: int, multiple: int = 4) -> list[tuple
     return plan
 
 
+class _Unchecked:
+    """View of a HessianHook whose deferred check is still pending, for the work that is queued before settle()."""
+
+    def __init__(self, hook):
+        self._hook = hook
+
+    def __getattr__(self, name):
+        if name == '_pending':
+            return None
+        return getattr(self._hook, name)
+
+
 def _solve_cost(rows: int, n_sms: int = 148) -> float:
     """Relative time of the fused solver for one weight of `rows` rows (measured on B200, profiles/r02_v24_quant_time.jsonl:
     32-row CTAs 1.0, 64-row 1.35, 128-row 1.95 per wave; the library picks the smallest tile that fits one wave)."""
@@ -210,6 +222,13 @@ def gptq_quant_group_sharded(weights: Sequence[torch.Tensor], hessian_hook, quan
     if shard_of is None:
         def shard_of(i, lo, hi):
             return weights[i][lo:hi]
+    if own_quant and getattr(hessian_hook, '_pending', None) is not None:
+        # HessianHook.invert(defer_check=True): the group is queued behind the unchecked factorisation, the check (one host
+        # synchronisation) comes after; if the first try was bad (rare: a damping retry), everything is redone with the final U
+        first = gptq_quant_group_sharded(weights, _Unchecked(hessian_hook), None, group, shard_of, **{k: v for k, v in quant_kwargs.items() if k != 'defer_metrics'})
+        if hessian_hook.settle():
+            return first
+        return gptq_quant_group_sharded(weights, hessian_hook, None, group, shard_of, **{k: v for k, v in quant_kwargs.items() if k != 'defer_metrics'})
     if world == 1:
         if own_quant and _stacking_pays([w.shape[0] for w in weights]) and quant_kwargs.get('scale_bit_width') is None \
                 and len({(w.shape[1], w.dtype) for w in weights}) == 1:

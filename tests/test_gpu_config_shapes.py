@@ -319,3 +319,41 @@ def test_reference_launcher_symbols_compute(dtype, name):
     torch.cuda.synchronize()
     want = H0.double() + X.double().t() @ X.double()
     assert float((H.double() - want).norm() / want.norm()) <= 1e-5
+
+
+@pytest.mark.parametrize('force_retry', [False, True])
+def test_deferred_retry_check_equals_immediate_check(force_retry):
+    """HessianHook.invert(defer_check=True) + sharded.gptq_quant_group_sharded (which settles the check behind the queued
+    solves and redoes them if the first factorisation had to be retried) == the reference's order (check, then solve)."""
+    import sharded
+    from gptq_py import HessianHook
+    D = 512
+    g = torch.Generator().manual_seed(6)
+    A = torch.randn(4 * D, D, generator=g, dtype=torch.float64)
+    H0 = A.t() @ A
+    if force_retry:                                             # as in test_forced_damping_retry: first try indefinite
+        lam0 = float(torch.linalg.eigvalsh(H0)[0])
+        m0 = float(H0.diagonal().mean())
+        d = 0.01 * (m0 - lam0) / 1.015
+        H0 = H0 - (lam0 + 1.5 * d) * torch.eye(D, dtype=torch.float64)
+    W = [(torch.randn(r, D, generator=g) * 0.02).half().to(DEV) for r in (128, 64)]
+    gs = torch.full([D // 128], 128, dtype=torch.int32)
+    bw = torch.full([D // 128], 4, dtype=torch.int32)
+    kw = dict(group_sizes=gs, group_bit_widths=bw, scale_bit_width=None, gptq_use_kernel=False, gptq_block_sizes=gs,
+              quant_symmetric=False, quant_mse=False, save_device=DEV)
+    res = []
+    for defer in (False, True):
+        hook = HessianHook()
+        hook.hessian = H0.float().to(DEV).clone()
+        hook.n_samples = 2
+        hook.invert(1e-2, act_order=True, defer_check=defer)
+        assert (getattr(hook, '_pending', None) is not None) == defer
+        out = sharded.gptq_quant_group_sharded(W, hook, **kw)
+        assert getattr(hook, '_pending', None) is None and hook.settle()
+        assert hook.invert_tries == (2 if force_retry else 1)
+        res.append((hook.hessian_inv.clone(), out))
+    assert torch.equal(res[0][0], res[1][0])
+    for a, b in zip(res[0][1], res[1][1]):
+        for k in ('qweight', 'scale', 'qzero', 'perm_inv'):
+            assert torch.equal(a['quant_meta'][k], b['quant_meta'][k]), k
+        assert dict(a['metrics']) == pytest.approx(dict(b['metrics']), rel=1e-6)
