@@ -14,7 +14,7 @@ GQ_DECL(0, 32) GQ_DECL(0, 64) GQ_DECL(0, 128) GQ_DECL(1, 32) GQ_DECL(1, 64) GQ_D
 struct SuperParams;
 struct SuperMaps;
 #define GQ_DECL(MODE, NQ) int launch_solve_super_m##MODE##_nq##NQ(const SuperMaps& maps_u, const SuperParams& p, cudaStream_t st);
-GQ_DECL(0, 1) GQ_DECL(0, 2) GQ_DECL(0, 4) GQ_DECL(1, 1) GQ_DECL(1, 2) GQ_DECL(1, 4)
+GQ_DECL(0, 1) GQ_DECL(0, 2) GQ_DECL(0, 3) GQ_DECL(0, 4) GQ_DECL(1, 1) GQ_DECL(1, 2) GQ_DECL(1, 3) GQ_DECL(1, 4)
 #undef GQ_DECL
 
 }  // namespace gq
@@ -23,17 +23,19 @@ namespace gq {
 
 // rows per CTA of the fused super-block kernel: the smallest tile that still fits the linear into one wave of CTAs
 static int launch_super_nq(int mode, const SuperMaps& map_u, const SuperParams& p, int n_sms, cudaStream_t st) {
-  const int nq = (p.R + 31) / 32 <= n_sms ? 1 : (p.R + 63) / 64 <= n_sms ? 2 : 4;
+  const int nq = (p.R + 31) / 32 <= n_sms ? 1 : (p.R + 63) / 64 <= n_sms ? 2 : (p.R + 95) / 96 <= n_sms ? 3 : 4;
   if (mode == 0) {
     switch (nq) {
       case 1: return launch_solve_super_m0_nq1(map_u, p, st);
       case 2: return launch_solve_super_m0_nq2(map_u, p, st);
+      case 3: return launch_solve_super_m0_nq3(map_u, p, st);
       default: return launch_solve_super_m0_nq4(map_u, p, st);
     }
   }
   switch (nq) {
     case 1: return launch_solve_super_m1_nq1(map_u, p, st);
     case 2: return launch_solve_super_m1_nq2(map_u, p, st);
+    case 3: return launch_solve_super_m1_nq3(map_u, p, st);
     default: return launch_solve_super_m1_nq4(map_u, p, st);
   }
 }

@@ -5,7 +5,7 @@
 // solve block b (20 us) -> one-tile-per-CTA near update of the super-block's later columns (18 us, tensor pipe 28 %
 // active: set-up and drain, not math) -> solve block b + 1 ...  Here the chain never leaves the SM:
 //
-//   * a CTA owns 32 NQ weight rows (NQ = 1, 2, 4 quarters of 32; lane = row) for the whole super-block;
+//   * a CTA owns 32 NQ weight rows (NQ = 1 .. 4 quarters of 32; lane = row) for the whole super-block;
 //   * the column recurrence of a block is the per-block kernel's (same SubSteps / update4 code, same arithmetic and
 //     order, so a block is still bit-exact against the oracle's in-block loop, gptq_py.py:186-192);
 //   * the errors of every finished 16-column sub-block go from the chain warp's registers straight into TENSOR MEMORY
@@ -307,12 +307,13 @@ solve_super_kernel(const __grid_constant__ SuperMaps maps_u, const SuperParams p
     const int part_w = part == 0 ? 48 : 40;
     // look-ahead item of this warp: (quarter la_q, column group la_g) or none (la_q < 0)
     int la_q = -1, la_g = 0;
-    if (NQ == 4) { la_q = my_q; la_g = warp >> 2; }
+    constexpr bool DENSE = NQ >= 3;          // three or four chain warps: a quarter's look-ahead stays on its own SM sub-partition
+    if (DENSE) { if (my_q < NQ) { la_q = my_q; la_g = warp >> 2; } }
     else if (warp >= NQ && warp < NQ + 4 * NQ) { la_q = (warp - NQ) >> 2; la_g = (warp - NQ) & 3; }
     // far-update / write-out helpers
-    constexpr int NH = NQ == 4 ? 12 : 4 * (4 - NQ);
-    const bool is_far = NQ == 4 ? warp >= 4 : my_q >= NQ;
-    const int far_i = NQ == 4 ? warp - 4 : (warp >> 2) * (4 - NQ) + (my_q - NQ);
+    constexpr int NH = DENSE ? 16 - NQ : 4 * (4 - NQ);
+    const bool is_far = DENSE ? warp >= NQ : my_q >= NQ;
+    const int far_i = DENSE ? warp - NQ : (warp >> 2) * (4 - NQ) + (my_q - NQ);
     // profiling hook: time stamps of CTA 0's chain warp
     // (reporters: lane 0 of warps 0, 1, 4 and 15 of CTA 0, 256 slots each)
     const int rep = warp == 0 ? 0 : warp == 1 ? 1 : warp == 4 ? 2 : warp == 15 ? 3 : -1;
