@@ -113,7 +113,7 @@ def test_solve_static_equals_per_group_range_calls(R, C, group):
 @pytest.mark.parametrize('R,C,mode', [(64, 512, 0), (100, 1024, 0), (4096, 1024, 0), (4800, 640, 0), (11008, 512, 0),
                                       (13824, 384, 0), (256, 640, 3), (4736, 1152, 3), (512, 1024, 4)])
 def test_fused_super_block_solver_vs_per_block_launches(R, C, mode):
-    """The fused super-block kernel (gptq_solver_super.cuh: near updates accumulated in tensor memory, 32 / 64 / 128 rows per
+    """The fused super-block kernel (gptq_solver_super.cuh: near updates accumulated in tensor memory, 32 / 64 / 96 / 128 rows per
     CTA chosen by R) against round 1's schedule (one launch per block + near-update GEMMs, gq_set_solve_fused(0)), which
     the tests above pin to the oracle: the first block of every call is bit-identical (no update involved), everything
     else differs only by the summation order of the cross-block updates (3xTF32 accumulation in TMEM per super-block vs
