@@ -307,7 +307,7 @@ solve_super_kernel(const __grid_constant__ SuperMaps maps_u, const SuperParams p
     const int part_w = part == 0 ? 48 : 40;
     // look-ahead item of this warp: (quarter la_q, column group la_g) or none (la_q < 0)
     int la_q = -1, la_g = 0;
-    constexpr bool DENSE = NQ >= 3;          // three or four chain warps: a quarter's look-ahead stays on its own SM sub-partition
+    constexpr bool DENSE = NQ >= 2;          // two or more chain warps: a quarter's look-ahead stays on its own SM sub-partition (NQ = 1: on the three others, 0.89 vs 0.98 ms)
     if (DENSE) { if (my_q < NQ) { la_q = my_q; la_g = warp >> 2; } }
     else if (warp >= NQ && warp < NQ + 4 * NQ) { la_q = (warp - NQ) >> 2; la_g = (warp - NQ) & 3; }
     // far-update / write-out helpers

@@ -190,11 +190,11 @@ class _Unchecked:
 
 def _solve_cost(rows: int, n_sms: int = 148) -> float:
     """Relative time of the fused solver for one weight of `rows` rows (measured on B200, profiles/r02_v24_quant_time.jsonl:
-    32-row CTAs 1.0, 64-row 1.35, 96-row 1.7, 128-row 1.95 per wave; the library picks the smallest tile that fits one wave)."""
-    for tile, cost in ((32, 1.0), (64, 1.35), (96, 1.7), (128, 1.95)):
+    32-row CTAs 1.0, 64-row 1.5, 96-row 1.9, 128-row 2.1 per wave; the library picks the smallest tile that fits one wave)."""
+    for tile, cost in ((32, 1.0), (64, 1.5), (96, 1.9), (128, 2.1)):
         if -(-rows // tile) <= n_sms:
             return cost
-    return 1.95 * -(-(-(-rows // 128)) // n_sms)
+    return 2.1 * -(-(-(-rows // 128)) // n_sms)
 
 
 def _stacking_pays(rows: Sequence[int]) -> bool:

@@ -33,7 +33,8 @@ def main():
     from gptq_py import HessianHook, gptq_quant
     dev = torch.device('cuda:0')
     hooks = {}
-    for R, C in ((4096, 4096), (11008, 4096), (4096, 11008)):
+    shapes = [tuple(int(v) for v in a.split('x')) for a in sys.argv[1:]] or [(4096, 4096), (11008, 4096), (4096, 11008)]
+    for R, C in shapes:
         if C not in hooks:
             g = torch.Generator(device=dev).manual_seed(C)
             cs = torch.exp(torch.rand(C, device=dev, generator=g) * 3.0 - 1.5)
