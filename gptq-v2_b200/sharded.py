@@ -267,10 +267,14 @@ def gptq_quant_group_sharded(weights: Sequence[torch.Tensor], hessian_hook, quan
     keys = ('gptq_error', 'gptq_norm', 'l2.0_error', 'l2.0_norm')
     msum = torch.zeros(L, len(keys), dtype=torch.float64, device=dev)
     off = 0
-    for i, lo, hi, r in plan:
-        if r != rank:
-            continue
-        res = quant_fn(weight=shard_of(i, lo, hi), hessian_hook=hessian_hook, **kw)
+    mine = [(i, lo, hi) for i, lo, hi, r in plan if r == rank]
+    if own_quant and _stacking_pays([hi - lo for _, lo, hi in mine]):
+        # this rank's shards of the group (rows of different linears, same U) as one row-stacked solve
+        from gptq_py import gptq_quant_stacked
+        mine_res = gptq_quant_stacked([shard_of(i, lo, hi) for i, lo, hi in mine], hessian_hook, **kw)
+    else:
+        mine_res = [quant_fn(weight=shard_of(i, lo, hi), hessian_hook=hessian_hook, **kw) for i, lo, hi in mine]
+    for (i, lo, hi), res in zip(mine, mine_res):
         meta, met = res['quant_meta'], res['metrics']
         for k, width, _ in fields:
             b = meta[k].to(dev).contiguous().view(torch.uint8).reshape(-1)
