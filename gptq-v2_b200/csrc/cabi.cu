@@ -208,7 +208,7 @@ int gq_set_pdl(int on) {
 }
 int gq_set_w4a16_path(int path) {
   int old = gq::g_w4a16_path;
-  if (path >= 0 && path <= 2) gq::g_w4a16_path = path;
+  if (path >= 0 && path <= 4) gq::g_w4a16_path = path;
   return old;
 }
 int gq_set_tf32x3(int enable) { int old = gq::g_use_tf32x3; gq::g_use_tf32x3 = (enable >= 0 && enable <= 3) ? enable : 1; return old; }

@@ -81,7 +81,7 @@ int sgemm(const GemmProblem& pr, float alpha, float beta, int flags, cudaStream_
 int sgemm_batched(const GemmBatch& b, float alpha, float beta, int flags, cudaStream_t st);
 
 // ---- fp32-faithful tensor-core GEMM  C += alpha * A^T B  (3 x TF32 split, tcgen05)
-extern int g_w4a16_path;   // K6 dispatch: 0 auto; 1 never the small-batch mma.sync kernel; 2 the weights-on-N tcgen05 kernel for batch <= 128
+extern int g_w4a16_path;   // K6 dispatch: 0 auto; 1 never the mma.sync kernels (small / mid batch); 2 the weights-on-N tcgen05 kernel for batch <= 128; 3 auto without the mid-batch kernel; 4 the mid-batch kernel wherever it supports the shape
 extern int g_syrk_kchunk;  // K1: 64-token k-blocks accumulated in tensor memory per partial sum (default 128 = 8192 tokens; 0 = a whole call)
 extern int g_tf32_kchunk;  // 3xTF32 GEMM: 16-deep k-blocks accumulated in tensor memory per partial sum (default 8 = 128 deep; 0 = unlimited)
 extern long long* g_solve_dbg;  // profiling hook: device buffer for the fused solver's clock64 stamps (first super-block of a call), or null
@@ -152,6 +152,9 @@ int w4a16_mma(const void* x, const uint32_t* qw, const void* scale_t, const uint
 bool w4a16_smallm_supports(int M, int N, int K, int group);
 int w4a16_smallm(const void* x, const uint32_t* qw, const void* scale_t, const uint8_t* qzero_t, const int32_t* perm,
                  void* y, void* workspace, int M, int N, int K, int group, int fmt, cudaStream_t st);
+bool w4a16_midm_supports(int M, int N, int K, int group);
+int w4a16_midm(const void* x, const uint32_t* qw, const void* scale_t, const uint8_t* qzero_t, const int32_t* perm,
+               void* y, void* workspace, int M, int N, int K, int group, int fmt, cudaStream_t st);
 bool w4a16_wb_supports(int M, int N, int K, int group);
 int w4a16_wb(const void* x, const uint32_t* qw, const void* scale_t, const uint8_t* qzero_t, const int32_t* perm, void* y,
              void* workspace, int M, int N, int K, int group, int fmt, cudaStream_t st);

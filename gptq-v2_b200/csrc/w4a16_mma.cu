@@ -365,7 +365,7 @@ int run_w4a16_mma(const void* x, const uint32_t* qw, const void* scale, const ui
 }  // namespace
 
 size_t w4a16_workspace_bytes(int M, int N, int K) {
-  // xs (M, K) 16-bit | max(yacc (M, N) fp32 of the tcgen05 split-K path, chunk sums (M, K/128) fp32 of the small-batch path)
+  // xs (M, K) 16-bit | max(yacc (M, N) fp32 of the tcgen05 split-K path, chunk sums (M, K/128) fp32 of the small / mid batch paths)
   const size_t tail = (size_t)M * sizeof(float) * (size_t)(N > K / 128 + 8 ? N : K / 128 + 8);
   return ((((size_t)M * K * 2) + 255) & ~(size_t)255) + tail;
 }
@@ -381,7 +381,8 @@ int w4a16_mma(const void* x, const uint32_t* qw, const void* scale, const uint8_
   return GQ_ERR_DTYPE;
 }
 
-// Batch 1-2 goes to the CUDA-core GEMV (w4a16_gemv.cu), everything else to the tcgen05 kernel: measured on B200, a
+// Batch <= 8 goes to the warp-level mma kernel (w4a16_smallm.cu), batch <= 16 to its windowed form (w4a16_midm.cu), batch
+// 1-2 on shapes those refuse to the CUDA-core GEMV (w4a16_gemv.cu), everything else to the tcgen05 kernel: measured on B200, a
 // tcgen05.mma with M = 128, K = 16 occupies the tensor core for 171.6 cycles for EVERY N from 16 to 256
 // (tools/micro/umma_small_n.cu), so with the weights on the M side the tensor path streams at most
 // 128*16/2 B / 171.6 clk * 148 SMs * 1.85 GHz = 1.6 TB/s of packed int4 however small the batch is.
@@ -389,7 +390,16 @@ int w4a16_gemm(const void* x, const uint32_t* qw, const void* scale_t, const uin
                void* workspace, int M, int N, int K, int group, int fmt, cudaStream_t st) {
   if (g_w4a16_path == 2 && M <= 128 && w4a16_wb_supports(M, N, K, group))      // experimental weights-on-N kernel, opt-in
     return w4a16_wb(x, qw, scale_t, qzero_t, perm, y, workspace, M, N, K, group, fmt, st);
-  if (g_w4a16_path == 0 && w4a16_smallm_supports(M, N, K, group)) return w4a16_smallm(x, qw, scale_t, qzero_t, perm, y, workspace, M, N, K, group, fmt, st);
+  if (g_w4a16_path == 4 && w4a16_midm_supports(M, N, K, group))                 // A/B: the windowed kernel wherever it runs
+    return w4a16_midm(x, qw, scale_t, qzero_t, perm, y, workspace, M, N, K, group, fmt, st);
+  if ((g_w4a16_path == 0 || g_w4a16_path == 3) && w4a16_smallm_supports(M, N, K, group))
+    return w4a16_smallm(x, qw, scale_t, qzero_t, perm, y, workspace, M, N, K, group, fmt, st);
+  // batch 9..16, and batch 3..8 on rows too long for the small-batch kernel's resident activation: its windowed form where
+  // it measured faster than the tcgen05 path (profiles/r02_v38_w4a16_midm_sweep.txt): a CTA needs several row tiles, and
+  // with two blocks of batch columns a K that is long for the number of rows (4096 x 11008) still favours the split over K
+  if (g_w4a16_path == 0 && M > 2 && (M <= 8 ? N >= 2048 : (N >= 8192 || (N >= 4096 && K <= 8192))) &&
+      w4a16_midm_supports(M, N, K, group))
+    return w4a16_midm(x, qw, scale_t, qzero_t, perm, y, workspace, M, N, K, group, fmt, st);
   if (M <= 2 && K <= 16384) return w4a16_gemv(x, qw, scale_t, qzero_t, perm, y, workspace, M, N, K, group, fmt, st);
   return w4a16_mma(x, qw, scale_t, qzero_t, perm, y, workspace, M, N, K, group, fmt, st);
 }

@@ -488,7 +488,8 @@ def set_pdl(on: int) -> int:
 
 
 def set_w4a16_path(path: int) -> int:
-    """K6 dispatch hook (0 auto, 1 never the small-batch kernel, 2 the experimental weights-on-N tcgen05 kernel for batch <= 128); returns the old value."""
+    """K6 dispatch hook (0 auto, 1 never the mma.sync kernels, 2 the experimental weights-on-N tcgen05 kernel for batch <= 128,
+    3 auto without the batch 9..16 kernel, 4 that kernel wherever it supports the shape); returns the old value."""
     return int(lib.gq_set_w4a16_path(int(path)))
 
 

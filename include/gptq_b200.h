@@ -229,10 +229,11 @@ int gq_set_solve_fused(int on);
  * update): 1 (default) lets a kernel's prologue overlap the tail of its predecessor, 0 restores plain stream order (A/B
  * hook; results are identical).  Returns the previous value. */
 int gq_set_pdl(int on);
-/* A/B hook for K6's dispatch: 0 = automatic (batch <= 8: warp-level mma kernel; otherwise tcgen05 with the weights on the M
+/* A/B hook for K6's dispatch: 0 = automatic (batch <= 8: warp-level mma kernel; batch 9..16: its windowed form; otherwise tcgen05 with the weights on the M
  * side through tensor memory, 64 or 256 batch columns per pass), 1 = never the small-batch kernel, 2 = batch <= 128 through
- * the experimental tcgen05 kernel with the weights on the N side (w4a16_wb.cu; correct, not yet faster).  Returns the
- * previous setting. */
+ * the experimental tcgen05 kernel with the weights on the N side (w4a16_wb.cu; correct, not yet faster), 3 = automatic
+ * without the batch 9..16 kernel (w4a16_midm.cu), i.e. the dispatch before it existed, 4 = that kernel for every batch <= 16
+ * it supports.  Returns the previous setting. */
 int gq_set_w4a16_path(int path);
 
 #ifdef __cplusplus

@@ -109,6 +109,53 @@ def test_w4a16_small_batch_kernel(M, N, K, group, use_perm, dtype):
 
 
 @pytest.mark.parametrize('dtype', [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize('M,N,K,group,use_perm', [(9, 256, 256, 128, True), (16, 4096, 4096, 128, True), (12, 1008, 11008, 128, True),
+                                                  (16, 2048, 2048, 256, False), (11, 592, 384, 128, True), (13, 320, 1024, 512, True),
+                                                  (4, 2048, 28672, 128, True), (8, 64, 16512, 128, False), (16, 28672, 8192, 128, True),
+                                                  (10, 16, 128, 128, False), (1, 2064, 4224, 128, True)])
+def test_w4a16_mid_batch_kernel(M, N, K, group, use_perm, dtype):
+    """Batch 9..16 (and batch 3..8 on rows too long for the small-batch kernel) path (w4a16_midm.cu): the small-batch
+    arithmetic with 1 / 2 blocks of 8 batch columns and the activation streamed through shared memory in windows (full and
+    ragged last windows, one to many rounds, CTAs with 1 .. 13 row tiles, warps without units in a round).  Forced through
+    set_w4a16_path(4) so that the shapes the automatic dispatch keeps on other kernels run it too.  Same bounds as the
+    small-batch test; the tcgen05 route (set_w4a16_path(3): the dispatch without this kernel) must agree to the 16-bit
+    rounding."""
+    import gptq
+    g = torch.Generator().manual_seed(M * 137 + N + K + group)
+    G = K // group
+    codes = torch.randint(0, 16, (N, K), generator=g, dtype=torch.uint8)
+    scale = (torch.rand(N, G, generator=g) * 0.01 + 1e-3).to(dtype)
+    qzero = torch.randint(0, 16, (N, G), generator=g, dtype=torch.uint8)
+    perm = torch.randperm(K, generator=g) if use_perm else None
+    x = (torch.randn(M, K, generator=g) + 1.5).to(dtype)
+    w = (codes.double() - qzero.double().repeat_interleave(group, dim=1)) * scale.double().repeat_interleave(group, dim=1)
+    xp = x.double()[:, perm] if use_perm else x.double()
+    want = xp @ w.t()
+    args = (x.cuda(), gptq.pack_int4(codes.cuda()), scale.t().contiguous().cuda(), qzero.t().contiguous().cuda(),
+            perm.to(torch.int32).cuda() if use_perm else None, group)
+    old = gptq.set_w4a16_path(4)
+    try:
+        y = gptq.w4a16_gemm(*args)
+        y2 = gptq.w4a16_gemm(*args)                # a second call: equal up to the order of the shared-memory adds of a tile's
+        torch.cuda.synchronize()                   # partial sums
+        gptq.set_w4a16_path(0)
+        y_auto = gptq.w4a16_gemm(*args)            # what the automatic dispatch picks for this shape
+        gptq.set_w4a16_path(3)
+        y_tc = gptq.w4a16_gemm(*args)
+        torch.cuda.synchronize()
+    finally:
+        gptq.set_w4a16_path(old)
+    rel = ((y.double().cpu() - want).norm() / want.norm()).item()
+    assert rel <= (6e-4 if dtype == torch.float16 else 4e-3), rel
+    bound = want.abs() * (2.0 ** -10 if dtype == torch.float16 else 2.0 ** -7) + 2e-6 * (xp.abs() @ w.abs().t())
+    assert ((y.double().cpu() - want).abs() <= bound).all()
+    assert ((y2.double().cpu() - want).abs() <= bound).all()
+    for other in (y_auto, y_tc):
+        rel_o = ((y.double() - other.double()).norm() / other.double().norm()).item()
+        assert rel_o <= (1.2e-3 if dtype == torch.float16 else 8e-3), rel_o
+
+
+@pytest.mark.parametrize('dtype', [torch.float16, torch.bfloat16])
 @pytest.mark.parametrize('M,N,K,group,use_perm', [(9, 256, 256, 128, True), (16, 200, 320, 64, False), (33, 1000, 1088, 32, True),
                                                   (64, 4096, 4096, 128, True), (100, 520, 2048, 128, False),
                                                   (128, 1024, 11008, 128, True), (24, 28672, 512, 128, False)])

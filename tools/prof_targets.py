@@ -8,6 +8,8 @@ import torch
 import gptq
 dev = torch.device('cuda')
 which = sys.argv[1]
+if os.environ.get('W4_PATH_FORCE'):
+    gptq.set_w4a16_path(int(os.environ['W4_PATH_FORCE']))
 if os.environ.get('GQ_TF32_MODE'):
     gptq.set_tf32x3(int(os.environ['GQ_TF32_MODE']))
 if which == 'tf32':
@@ -34,10 +36,10 @@ elif which == 'solve':
     for _ in range(2):
         gptq.gptq_solve(gptq.prep_weight_t(W, None), U, 128, 15.0)
 elif which == 'w4a16':
-    N, K = 28672, 8192
+    M, N, K = (int(v) for v in sys.argv[2:5]) if len(sys.argv) >= 5 else (1, 28672, 8192)     # batch 1..8 / 9..32: the mma.sync kernels
     q = torch.randint(-2 ** 31, 2 ** 31 - 1, (N, K // 8), device=dev, dtype=torch.int32)
     sc = (torch.rand(K // 128, N, device=dev) * 0.01).half(); qz = torch.randint(0, 16, (K // 128, N), device=dev, dtype=torch.uint8)
-    x = torch.randn(1, K, device=dev).half()
+    x = torch.randn(M, K, device=dev).half()
     for _ in range(3):
         gptq.w4a16_gemm(x, q, sc, qz, None, 128)
 elif which == 'w4a16mma':
