@@ -156,6 +156,20 @@ int gq_transpose_pack_int4(const uint8_t* codes_t, uint8_t* codes, uint32_t* pac
   return transpose_pack_int4(codes_t, codes, packed, R, C, S(stream));
 }
 
+int gq_llama_rms_norm(const void* x, const void* weight, void* y, long long rows, int D, float eps, int dtype, void* stream) {
+  return llama_rms_norm(x, weight, y, rows, D, eps, dtype, S(stream));
+}
+int gq_llama_rope(void* x, const void* cos_t, const void* sin_t, long long tokens, int heads, int head_dim, int seqlen, int dtype,
+                  void* stream) {
+  return llama_rope(x, cos_t, sin_t, tokens, heads, head_dim, seqlen, dtype, S(stream));
+}
+int gq_llama_silu_mul(const void* gate, const void* up, void* out, long long n, int dtype, void* stream) {
+  return llama_silu_mul(gate, up, out, n, dtype, S(stream));
+}
+int gq_reconstruct_dense(const uint8_t* qweight, const void* scale, const uint8_t* qzero, const int16_t* perm_inv, void* dense,
+                         int R, int C, int group, int dtype, void* stream) {
+  return reconstruct_dense(qweight, scale, qzero, perm_inv, dense, R, C, group, dtype, S(stream));
+}
 int gq_w4a16_dequant(const uint32_t* qweight, const void* scale_t, const uint8_t* qzero_t, void* dense, int N, int K, int group,
                      int dtype, void* stream) {
   return w4a16_dequant(qweight, scale_t, qzero_t, dense, N, K, group, dtype, S(stream));

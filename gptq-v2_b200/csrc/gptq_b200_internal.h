@@ -141,6 +141,12 @@ int finalize_quant(const float* err_t, const float* quant_t, const void* orig_t,
                    const float* qzero_gr, int G, void* scale_out, uint8_t* qzero_out, const int64_t* perm, const float* U,
                    const int* seg_bounds, int nseg, double* stats, cudaStream_t st);
 int gemm_f16_nt(const void* x, const void* w, void* y, int M, int N, int K, int fmt, cudaStream_t st);
+// ---- f1: elementwise steps of the decoder block between the quantised linears (llama_ops.cu)
+int llama_rms_norm(const void* x, const void* w, void* y, long long rows, int D, float eps, int fmt, cudaStream_t st);
+int llama_rope(void* x, const void* cos_t, const void* sin_t, long long tokens, int heads, int hd, int seqlen, int fmt, cudaStream_t st);
+int llama_silu_mul(const void* g, const void* u, void* out, long long n, int fmt, cudaStream_t st);
+int reconstruct_dense(const uint8_t* q, const void* scale, const uint8_t* qzero, const int16_t* perm_inv, void* out, int R, int C,
+                      int group, int fmt, cudaStream_t st);
 int w4a16_dequant(const uint32_t* qw, const void* scale_t, const uint8_t* qzero_t, void* out, int N, int K, int group, int fmt,
                   cudaStream_t st);
 size_t w4a16_workspace_bytes(int M, int N, int K);

@@ -336,6 +336,35 @@ __global__ void __launch_bounds__(256) transpose_pack4_kernel(const uint8_t* __r
   }
 }
 
+// Dense reconstruction of one linear from quant_meta as it is (one code per byte, (R, G) scales / zero points, perm_inv):
+//   out[r][c] = T(float(q[r][p] - z[r][p / group]) * float(s[r][p / group])),  p = perm_inv[c]      (quant.py:222-237, 262-279)
+// One CTA per row: codes, scales and zero points of the row in shared memory, the output written along c.
+template <typename T>
+__global__ void __launch_bounds__(256) reconstruct_dense_kernel(const uint8_t* __restrict__ q, const T* __restrict__ scale,
+                                                                const uint8_t* __restrict__ qzero, const int16_t* __restrict__ perm_inv,
+                                                                T* __restrict__ out, int C, int group) {
+  extern __shared__ __align__(16) unsigned char rsm[];
+  const int G = C / group;
+  uint8_t* sq = rsm;                                           // [C]
+  float* ss = reinterpret_cast<float*>(rsm + ((C + 15) & ~15));   // [G]
+  float* sz = ss + G;                                          // [G]
+  const size_t r = blockIdx.x;
+  const uint4* q4 = reinterpret_cast<const uint4*>(q + r * C);
+  for (int i = threadIdx.x; i < C / 16; i += blockDim.x) reinterpret_cast<uint4*>(sq)[i] = q4[i];
+  for (int g = threadIdx.x; g < G; g += blockDim.x) {
+    ss[g] = to_f32<T>(scale[r * G + g]);
+    sz[g] = (float)qzero[r * G + g];
+  }
+  __syncthreads();
+  const bool pow2 = (group & (group - 1)) == 0;
+  const int gshift = 31 - __clz(group);
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const int p = perm_inv ? (int)perm_inv[c] : c;
+    const int g = pow2 ? p >> gshift : p / group;
+    out[r * C + c] = from_f32<T>(((float)sq[p] - sz[g]) * ss[g]);
+  }
+}
+
 }  // namespace
 
 int prep_weight_t(const void* W, int fmt, const int64_t* perm, float* Wt, void* orig_t, float* colsq, int R, int C,
@@ -374,6 +403,20 @@ int w4a16_dequant(const uint32_t* qw, const void* scale_t, const uint8_t* qzero_
   GQ_LAUNCHED();
   if (fmt == 0) dequant_w4_kernel<__half><<<grid, 256, 0, st>>>(qw, (const __half*)scale_t, qzero_t, (__half*)out, N, K, group);
   else if (fmt == 1) dequant_w4_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(qw, (const __nv_bfloat16*)scale_t, qzero_t, (__nv_bfloat16*)out, N, K, group);
+  else return GQ_ERR_DTYPE;
+  return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
+}
+
+int reconstruct_dense(const uint8_t* q, const void* scale, const uint8_t* qzero, const int16_t* perm_inv, void* out, int R, int C,
+                      int group, int fmt, cudaStream_t st) {
+  if (R <= 0 || C <= 0) return GQ_OK;
+  if ((C & 15) || group < 1 || (C % group) || C > 32767) return GQ_ERR_SHAPE;      // perm_inv is int16 (gptq_py.py:75)
+  if (reinterpret_cast<uintptr_t>(q) & 15) return GQ_ERR_ALIGN;
+  const size_t smem = ((C + 15) & ~15) + (size_t)(C / group) * 8;
+  if (smem > 48 * 1024) return GQ_ERR_SHAPE;
+  GQ_LAUNCHED();
+  if (fmt == 0) reconstruct_dense_kernel<__half><<<R, 256, smem, st>>>(q, (const __half*)scale, qzero, perm_inv, (__half*)out, C, group);
+  else if (fmt == 1) reconstruct_dense_kernel<__nv_bfloat16><<<R, 256, smem, st>>>(q, (const __nv_bfloat16*)scale, qzero, perm_inv, (__nv_bfloat16*)out, C, group);
   else return GQ_ERR_DTYPE;
   return cudaGetLastError() == cudaSuccess ? GQ_OK : GQ_ERR_CUDA;
 }

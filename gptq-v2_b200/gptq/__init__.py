@@ -16,7 +16,7 @@ import torch
 from . import _cabi
 from ._cabi import GptqB200Error, check, lib, ptr, require_contig, require_cuda, stream_of
 
-__all__ = ['accumulate_hessian', 'gptq_quantize_range', 'hessian_syrk', 'hessian_invert', 'w4a16_dequant', 'pack_upper', 'unpack_upper', 'prep_weight_t', 'prep_weight_t2', 'solve_metrics', 'finalize_quant', 'gptq_solve_ex', 'find_params', 'mse_refine', 'find_params_cols', 'mse_refine_cols', 'rtn_quantize',
+__all__ = ['accumulate_hessian', 'gptq_quantize_range', 'hessian_syrk', 'hessian_invert', 'w4a16_dequant', 'reconstruct_dense', 'llama_rms_norm', 'llama_rope_', 'llama_silu_mul', 'pack_upper', 'unpack_upper', 'prep_weight_t', 'prep_weight_t2', 'solve_metrics', 'finalize_quant', 'gptq_solve_ex', 'find_params', 'mse_refine', 'find_params_cols', 'mse_refine_cols', 'rtn_quantize',
            'gptq_solve', 'gptq_solve_static', 'pack_int4', 'unpack_int4', 'transpose_pack_int4', 'w4a16_gemm', 'w4a16_gemv_static', 'gemm_f16_nt', 'sgemm', 'gemm_tf32x3', 'set_tf32x3', 'set_solve_super', 'set_solve_fused', 'set_tf32_kchunk', 'set_syrk_kchunk', 'set_w4a16_path', 'set_pdl',
            'GptqB200Error']
 
@@ -449,6 +449,75 @@ def w4a16_dequant(qweight: torch.Tensor, scale_t: torch.Tensor, qzero_t: torch.T
         check(lib.gq_w4a16_dequant(ptr(qweight), ptr(scale_t), ptr(qzero_t), ptr(dense), N, K, int(group),
                                    _cabi.DTYPE_CODE[scale_t.dtype], stream_of(qweight)), 'gq_w4a16_dequant')
     return dense
+
+
+def reconstruct_dense(qweight: torch.Tensor, scale: torch.Tensor, qzero: torch.Tensor, perm_inv: torch.Tensor | None,
+                      group: int) -> torch.Tensor:
+    """Dense (R, C) weight in scale.dtype straight from quant_meta's tensors (one code per byte, (R, G) scale / qzero, int16
+    perm_inv or None), uniform group size `group`: construct_matrix + the perm_inv gather of reconstruct_nn_linear
+    (quant.py:222-237, 262-279) in one launch, no host synchronisation."""
+    dev = require_cuda(qweight, scale, qzero)
+    require_contig(qweight=qweight, scale=scale, qzero=qzero)
+    R, C = qweight.shape
+    G = C // int(group)
+    if qweight.dtype != torch.uint8 or qzero.dtype != torch.uint8 or tuple(scale.shape) != (R, G) or tuple(qzero.shape) != (R, G):
+        raise GptqB200Error('reconstruct_dense: qweight (R, C) uint8, scale / qzero (R, C / group)')
+    if perm_inv is not None:
+        if perm_inv.dtype != torch.int16 or perm_inv.numel() != C or not perm_inv.is_contiguous() or perm_inv.device != dev:
+            raise GptqB200Error('reconstruct_dense: perm_inv must be a contiguous int16 tensor of C entries on the same device')
+    dense = torch.empty(R, C, dtype=scale.dtype, device=dev)
+    with torch.cuda.device(dev):
+        check(lib.gq_reconstruct_dense(ptr(qweight), ptr(scale), ptr(qzero), ptr(perm_inv), ptr(dense), R, C, int(group),
+                                       _cabi.DTYPE_CODE[scale.dtype], stream_of(qweight)), 'gq_reconstruct_dense')
+    return dense
+
+
+def llama_rms_norm(x: torch.Tensor, weight: torch.Tensor, eps: float, out: torch.Tensor | None = None) -> torch.Tensor:
+    """weight * (x.float() * rsqrt(mean(x.float()^2, -1) + eps)).to(x.dtype) over the last dimension (HF LlamaRMSNorm), one
+    pass; x fp16 / bf16 contiguous with at most 8192 entries per row; `out` (same shape, contiguous; may be x) or a new tensor."""
+    dev = require_cuda(x, weight)
+    require_contig(x=x, weight=weight)
+    D = x.shape[-1]
+    if weight.dtype != x.dtype or weight.numel() != D:
+        raise GptqB200Error('llama_rms_norm: weight must be (D) of x.dtype')
+    if out is None:
+        out = torch.empty_like(x)
+    elif out.shape != x.shape or out.dtype != x.dtype or not out.is_contiguous() or out.device != dev:
+        raise GptqB200Error('llama_rms_norm: out must be a contiguous tensor like x')
+    with torch.cuda.device(dev):
+        check(lib.gq_llama_rms_norm(ptr(x), ptr(weight), ptr(out), x.numel() // max(D, 1), D, float(eps), _cabi.DTYPE_CODE[x.dtype],
+                                    stream_of(x)), 'gq_llama_rms_norm')
+    return out
+
+
+def llama_rope_(x: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor, heads: int) -> torch.Tensor:
+    """In place: x (..., seqlen, heads * head_dim) <- x * cos + rotate_half(x) * sin per head (HF convention), every operation
+    rounded to x.dtype like the PyTorch expression; cos / sin (seqlen, head_dim) of x.dtype."""
+    dev = require_cuda(x, cos, sin)
+    require_contig(x=x, cos=cos, sin=sin)
+    seqlen, hd = cos.shape
+    if x.shape[-1] != heads * hd or x.shape[-2] != seqlen or cos.dtype != x.dtype or sin.dtype != x.dtype or sin.shape != cos.shape:
+        raise GptqB200Error('llama_rope_: x (..., seqlen, heads * head_dim), cos / sin (seqlen, head_dim) of x.dtype')
+    with torch.cuda.device(dev):
+        check(lib.gq_llama_rope(ptr(x), ptr(cos), ptr(sin), x.numel() // (heads * hd), int(heads), int(hd), int(seqlen),
+                                _cabi.DTYPE_CODE[x.dtype], stream_of(x)), 'gq_llama_rope')
+    return x
+
+
+def llama_silu_mul(gate: torch.Tensor, up: torch.Tensor, out: torch.Tensor | None = None) -> torch.Tensor:
+    """F.silu(gate) * up with PyTorch's roundings (silu in fp32 rounded once, the product in the model dtype), one pass."""
+    dev = require_cuda(gate, up)
+    require_contig(gate=gate, up=up)
+    if gate.shape != up.shape or gate.dtype != up.dtype:
+        raise GptqB200Error('llama_silu_mul: gate and up must have the same shape and dtype')
+    if out is None:
+        out = torch.empty_like(gate)
+    elif out.shape != gate.shape or out.dtype != gate.dtype or not out.is_contiguous() or out.device != dev:
+        raise GptqB200Error('llama_silu_mul: out must be a contiguous tensor like gate')
+    with torch.cuda.device(dev):
+        check(lib.gq_llama_silu_mul(ptr(gate), ptr(up), ptr(out), gate.numel(), _cabi.DTYPE_CODE[gate.dtype], stream_of(gate)),
+              'gq_llama_silu_mul')
+    return out
 
 
 def gemm_f16_nt(x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:

@@ -46,6 +46,10 @@ SIGNATURES = {
     'gq_unpack_int4': (_i, [_vp, _vp, _i, _i, _vp]),
     'gq_transpose_pack_int4': (_i, [_vp, _vp, _vp, _i, _i, _vp]),
     'gq_w4a16_dequant': (_i, [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
+    'gq_reconstruct_dense': (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp]),
+    'gq_llama_rms_norm': (_i, [_vp, _vp, _vp, C.c_longlong, _i, C.c_float, _i, _vp]),
+    'gq_llama_rope': (_i, [_vp, _vp, _vp, C.c_longlong, _i, _i, _i, _i, _vp]),
+    'gq_llama_silu_mul': (_i, [_vp, _vp, _vp, C.c_longlong, _i, _vp]),
     'gq_gemm_f16_nt': (_i, [_vp, _vp, _vp, _i, _i, _i, _i, _vp]),
     'gq_w4a16_workspace_bytes': (C.c_size_t, [_i, _i, _i]),
     'gq_w4a16_gemm': (_i, [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i, _i, _vp]),

@@ -80,16 +80,29 @@ def hf_block_weights(block, device: torch.device) -> dict:
     return out
 
 
-def rms_norm(x: torch.Tensor, weight: torch.Tensor, eps: float) -> torch.Tensor:
+def _fused_ok(*ts: torch.Tensor) -> bool:
+    """The one-pass kernels of csrc/llama_ops.cu take contiguous fp16 / bf16 CUDA tensors; everything else (the CPU tests of
+    the driver logic, fp32) stays on the PyTorch expressions below, which the kernels reproduce rounding for rounding."""
+    return all(t.is_cuda and t.dtype in (torch.float16, torch.bfloat16) and t.is_contiguous() for t in ts)
+
+
+def rms_norm(x: torch.Tensor, weight: torch.Tensor, eps: float, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    if _fused_ok(x, weight) and x.shape[-1] <= 8192 and x.shape[-1] % 8 == 0 and (out is None or _fused_ok(out)):
+        import gptq as _ops
+        return _ops.llama_rms_norm(x, weight, eps, out=out)
     xf = x.float()
-    return (weight * (xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + eps)).to(x.dtype))
+    y = (weight * (xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + eps)).to(x.dtype))
+    if out is None:
+        return y
+    out.copy_(y)
+    return out
 
 
 def rope_tables(seqlen: int, head_dim: int, theta: float, device, dtype):
     inv = 1.0 / (theta ** (torch.arange(0, head_dim, 2, device=device, dtype=torch.float32) / head_dim))
     ang = torch.outer(torch.arange(seqlen, device=device, dtype=torch.float32), inv)
     emb = torch.cat([ang, ang], dim=-1)
-    return emb.cos().to(dtype), emb.sin().to(dtype)
+    return emb.cos().to(dtype).contiguous(), emb.sin().to(dtype).contiguous()
 
 
 def apply_rope(x: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor) -> torch.Tensor:
@@ -97,6 +110,18 @@ def apply_rope(x: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor) -> torch.T
     hd = x.shape[-1]
     rot = torch.cat([-x[..., hd // 2:], x[..., :hd // 2]], dim=-1)
     return x * cos + rot * sin
+
+
+def silu_mul(gate: torch.Tensor, up: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """F.silu(gate) * up, into `out` when given."""
+    if _fused_ok(gate, up) and gate.numel() % 8 == 0 and (out is None or _fused_ok(out)):
+        import gptq as _ops
+        return _ops.llama_silu_mul(gate, up, out=out)
+    y = F.silu(gate) * up
+    if out is None:
+        return y
+    out.copy_(y)
+    return out
 
 
 def linear(x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
@@ -109,12 +134,24 @@ def linear(x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
     return x @ w.t()
 
 
-def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int, cos, sin) -> torch.Tensor:
+def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, heads: int, cos, sin, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """q, k, v (B, N, heads * hd), not used by the caller afterwards (the rotary embedding is applied in place on CUDA);
+    the result goes into `out` (B, N, heads * hd) when given: one transposing copy instead of two."""
     B, N, Hd = q.shape
     hd = Hd // heads
-    q, k, v = (t.view(B, N, heads, hd).transpose(1, 2) for t in (q, k, v))
-    o = F.scaled_dot_product_attention(apply_rope(q, cos, sin), apply_rope(k, cos, sin), v, is_causal=True)
-    return o.transpose(1, 2).reshape(B, N, Hd)
+    if _fused_ok(q, k, cos, sin) and hd % 16 == 0 and cos.shape == (N, hd):
+        import gptq as _ops
+        _ops.llama_rope_(q, cos, sin, heads)
+        _ops.llama_rope_(k, cos, sin, heads)
+        q, k, v = (t.view(B, N, heads, hd).transpose(1, 2) for t in (q, k, v))
+    else:
+        q, k, v = (t.view(B, N, heads, hd).transpose(1, 2) for t in (q, k, v))
+        q, k = apply_rope(q, cos, sin), apply_rope(k, cos, sin)
+    o = F.scaled_dot_product_attention(q, k, v, is_causal=True)
+    if out is None:
+        return o.transpose(1, 2).reshape(B, N, Hd)
+    out.view(B, N, heads, hd).copy_(o.transpose(1, 2))
+    return out
 
 
 @torch.no_grad()
@@ -295,7 +332,7 @@ class _GroupQuantizer:
         out = []
         for weight, res in zip(weights, results):
             with self.timer('reconstruct'):
-                what = reconstruct_nn_linear(res['quant_meta'], dtype=weight.dtype, device=dev).weight.data   # llama.py:172
+                what = reconstruct_nn_linear(res['quant_meta'], dtype=weight.dtype, device=dev, group_size=self.gsize).weight.data   # llama.py:172
             meta = res['quant_meta']
             if self.save_device != dev:
                 with self.timer('offload'):
@@ -336,7 +373,7 @@ def quantize_block(shape: LlamaShape, weights: dict, inps: torch.Tensor, n_globa
     h1 = torch.empty_like(inps)
     with timer('forward'):
         for b in _batches(n, batch_size):
-            h1[b] = rms_norm(inps[b], weights['input_layernorm'], shape.rms_eps)
+            rms_norm(inps[b], weights['input_layernorm'], shape.rms_eps, out=h1[b])
     for b in _batches(n, batch_size):
         grp.add(h1[b])
     grp.finish()
@@ -348,7 +385,7 @@ def quantize_block(shape: LlamaShape, weights: dict, inps: torch.Tensor, n_globa
     with timer('forward'):
         for b in _batches(n, batch_size):
             x = h1[b]
-            att[b] = attention(linear(x, wq), linear(x, wk), linear(x, wv), shape.heads, cos, sin)
+            attention(linear(x, wq), linear(x, wk), linear(x, wv), shape.heads, cos, sin, out=att[b])
     del h1, wq, wk, wv
     for b in _batches(n, batch_size):
         grp.add(att[b])
@@ -362,7 +399,7 @@ def quantize_block(shape: LlamaShape, weights: dict, inps: torch.Tensor, n_globa
     with timer('forward'):
         for b in _batches(n, batch_size):
             h2[b] = inps[b] + linear(att[b], wo)
-            h3[b] = rms_norm(h2[b], weights['post_attention_layernorm'], shape.rms_eps)
+            rms_norm(h2[b], weights['post_attention_layernorm'], shape.rms_eps, out=h3[b])
     del att, wo
     for b in _batches(n, batch_size):
         grp.add(h3[b])
@@ -375,7 +412,7 @@ def quantize_block(shape: LlamaShape, weights: dict, inps: torch.Tensor, n_globa
     with timer('forward'):
         for b in _batches(n, batch_size):
             x = h3[b]
-            act[b] = F.silu(linear(x, wg)) * linear(x, wu)
+            silu_mul(linear(x, wg), linear(x, wu), out=act[b])
     del h3, wu, wg
     for b in _batches(n, batch_size):
         grp.add(act[b])
@@ -491,7 +528,7 @@ def block_forward_any(shape: LlamaShape, weights: dict, x: torch.Tensor) -> torc
                   _linear(h, weights['self_attn.v_proj']), shape.heads, cos, sin)
     x = x + _linear(a, weights['self_attn.o_proj'])
     h = rms_norm(x, weights['post_attention_layernorm'], shape.rms_eps)
-    m = F.silu(_linear(h, weights['mlp.gate_proj'])) * _linear(h, weights['mlp.up_proj'])
+    m = silu_mul(_linear(h, weights['mlp.gate_proj']), _linear(h, weights['mlp.up_proj']))
     return x + _linear(m, weights['mlp.down_proj'])
 
 

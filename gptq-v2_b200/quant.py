@@ -10,6 +10,8 @@ matrix is produced by unpack -> elementwise torch ops exactly as the reference d
 """
 from __future__ import annotations
 
+from typing import Optional
+
 import torch
 from torch import nn
 
@@ -152,8 +154,40 @@ def construct_matrix_2(qweight, qzero, qscale, sscale, group_sizes):
     return (q - z) * _expand_groups(scale, group_sizes)
 
 
-def reconstruct_nn_linear(quant_meta: dict, dtype: torch.dtype, device: torch.device = torch.device('cpu')) -> nn.Linear:
-    """Reference-compatible dense reconstruction (quant.py:262-279)."""
+def _fused_reconstruction(quant_meta: dict, dtype: torch.dtype, device: torch.device, group_size: Optional[int]):
+    """The dense weight through gq_reconstruct_dense (one launch, no host synchronisation) when the metadata allows it:
+    CUDA target, 16-bit dtype, plain scales, and a uniform group size that is known WITHOUT reading a device tensor (the
+    caller's `group_size`, or group_sizes held on the host).  None otherwise: the torch route below handles the rest."""
+    if torch.device(device).type != 'cuda' or dtype not in (torch.float16, torch.bfloat16) or quant_meta.get('sscale') is not None:
+        return None
+    qweight = quant_meta['qweight']
+    R, C = qweight.shape
+    if group_size is None:
+        gs = quant_meta['group_sizes']
+        if gs.is_cuda or gs.numel() == 0 or int(gs.min()) != int(gs.max()):
+            return None
+        group_size = int(gs[0])
+    group_size = int(group_size)
+    if C % 16 or C > 32767 or group_size < 1 or C % group_size or C // group_size != quant_meta['scale'].shape[1]:
+        return None
+    perm_inv = quant_meta.get('perm_inv')
+    if perm_inv is not None:
+        perm_inv = perm_inv.to(device=device, dtype=torch.int16).contiguous()
+    return _ops.reconstruct_dense(qweight.to(device=device).contiguous(), quant_meta['scale'].to(dtype=dtype, device=device).contiguous(),
+                                  quant_meta['qzero'].to(device=device).contiguous(), perm_inv, group_size)
+
+
+def reconstruct_nn_linear(quant_meta: dict, dtype: torch.dtype, device: torch.device = torch.device('cpu'), *,
+                          group_size: Optional[int] = None) -> nn.Linear:
+    """Reference-compatible dense reconstruction (quant.py:262-279).  `group_size` (keyword-only, not in the reference): the
+    caller's promise that all groups have this size, which lets a CUDA reconstruction run as one kernel without reading
+    quant_meta['group_sizes'] back from the device (llama_driver.py passes it)."""
+    fused = _fused_reconstruction(quant_meta, dtype, device, group_size)
+    if fused is not None:
+        lin = nn.Linear(fused.shape[1], fused.shape[0], bias=False, dtype=dtype, device='meta')
+        lin.weight = nn.Parameter(fused)                          # requires_grad as nn.Linear's default, like the reference's
+        lin.eval()
+        return lin
     qweight = quant_meta['qweight'].to(device=device)
     if quant_meta.get('sscale') is not None:
         weight = construct_matrix_2(qweight, quant_meta['qzero'].to(device=device), quant_meta['qscale'].to(device=device),

@@ -163,6 +163,27 @@ int gq_transpose_pack_int4(const uint8_t* codes_t, uint8_t* codes, uint32_t* pac
  * aligned; K % 8 == 0, group % 8 == 0, K % group == 0. */
 int gq_w4a16_dequant(const uint32_t* qweight, const void* scale_t, const uint8_t* qzero_t, void* dense, int N, int K, int group,
                      int dtype, void* stream);
+
+/* Dense 16-bit reconstruction straight from quant_meta (replaces construct_matrix + the perm_inv gather of
+ * reconstruct_nn_linear, /root/reference/quant.py:222-237, 262-279, as the layer-by-layer driver calls it at llama.py:172):
+ * dense[r][c] = T(float(q[r][p] - z[r][p / group]) * float(s[r][p / group])), p = perm_inv[c] (perm_inv NULL: p = c).
+ * qweight (R, C) one code per byte, 16-byte aligned; scale (R, C / group) of dtype; qzero (R, C / group); perm_inv (C) int16
+ * as quant_meta stores it; uniform group size, C % 16 == 0, C <= 32767.  One launch, no host synchronisation. */
+int gq_reconstruct_dense(const uint8_t* qweight, const void* scale, const uint8_t* qzero, const int16_t* perm_inv, void* dense,
+                         int R, int C, int group, int dtype, void* stream);
+
+/* ---- f1 (driver costs): the elementwise steps of a Llama decoder block between the quantised linears, one pass each, with the
+ * roundings of the PyTorch expressions the reference's model code evaluates when quantize_llama replays the block
+ * (/root/reference/llama.py:121-125, 176-189 call transformers' LlamaDecoderLayer): no reference kernel counterpart.
+ * All tensors contiguous, 16-byte aligned, dtype GQ_DTYPE_F16 / BF16.
+ *   rms_norm: y = weight * T(float(x) * rsqrt(mean(float(x)^2) + eps)), rows x D, D % 8 == 0, D <= 8192 (y may alias x)
+ *   rope:     in place on x (tokens, heads, head_dim): x * cos + rotate_half(x) * sin, every operation rounded to T; cos / sin
+ *             (seqlen, head_dim), position = token % seqlen; head_dim % 16 == 0
+ *   silu_mul: out = T(T(silu(gate)) * up) over n elements, n % 8 == 0 (out may alias gate or up) */
+int gq_llama_rms_norm(const void* x, const void* weight, void* y, long long rows, int D, float eps, int dtype, void* stream);
+int gq_llama_rope(void* x, const void* cos_t, const void* sin_t, long long tokens, int heads, int head_dim, int seqlen, int dtype,
+                  void* stream);
+int gq_llama_silu_mul(const void* gate, const void* up, void* out, long long n, int dtype, void* stream);
 /* Dense 16-bit GEMM  y (M, N) = x (M, K) * w (N, K)^T  (fp32 accumulation, tcgen05 CTA pairs): the GEMM of the large-batch
  * route of K6 (gq_w4a16_dequant once, then this) -- the reference's nn.Linear forward on the reconstructed weights
  * (quant.py:262-279, llama.py:172-177) without a library GEMM.  x, w, y row-major contiguous of the same GQ_DTYPE_F16 / BF16,

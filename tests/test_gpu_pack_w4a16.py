@@ -250,6 +250,36 @@ def test_w4a16_dequant_matches_reference_construct_matrix(N, K, group, dtype):
     assert got.dtype == dtype and torch.equal(got.cpu(), want)
 
 
+@pytest.mark.parametrize('dtype', [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize('R,C,group,use_perm', [(64, 128, 128, True), (100, 384, 64, False), (4096, 4096, 128, True),
+                                                (24, 1024, 32, True), (130, 11008, 128, True), (16, 240, 48, True)])
+def test_reconstruct_nn_linear_fused_route_matches_torch_route(R, C, group, use_perm, dtype):
+    """reconstruct_nn_linear on CUDA with the group-size hint (gq_reconstruct_dense: construct_matrix + the perm_inv gather
+    in one launch) == the same function's torch route (device-resident group_sizes, no hint) == the oracle's restatement
+    of quant.py:222-237, 262-279, bit for bit; any group size that divides C, with and without act-order."""
+    import quant
+    g = torch.Generator().manual_seed(R + C + group)
+    G = C // group
+    meta = dict(qweight=torch.randint(0, 16, (R, C), generator=g, dtype=torch.uint8),
+                scale=(torch.rand(R, G, generator=g) * 0.01 + 1e-3).to(dtype),
+                qzero=torch.randint(0, 16, (R, G), generator=g, dtype=torch.uint8),
+                perm_inv=torch.randperm(C, generator=g).to(torch.int16) if use_perm else None,
+                group_sizes=torch.full((G,), group, dtype=torch.int16),
+                group_bit_widths=torch.full((G,), 4, dtype=torch.int16))
+    want = O.reconstruct_dense(meta, dtype)
+    dev = torch.device('cuda')
+    on_gpu = {k: (v.cuda() if torch.is_tensor(v) else v) for k, v in meta.items()}
+    fused = quant.reconstruct_nn_linear(on_gpu, dtype, dev, group_size=group)
+    assert quant._fused_reconstruction(on_gpu, dtype, dev, group) is not None          # the hint takes the kernel
+    assert quant._fused_reconstruction(on_gpu, dtype, dev, None) is None               # device group_sizes, no hint: torch route
+    assert quant._fused_reconstruction(meta, dtype, dev, None) is not None             # host group_sizes: read for free
+    plain = quant.reconstruct_nn_linear(on_gpu, dtype, dev)
+    torch.cuda.synchronize()
+    assert fused.weight.dtype == dtype and fused.weight.shape == (R, C) and fused.in_features == C and fused.out_features == R
+    assert torch.equal(fused.weight.data.cpu(), want)
+    assert torch.equal(plain.weight.data.cpu(), want)
+
+
 @pytest.mark.parametrize('M', [128, 600])
 def test_w4a16_linear_large_batch_route(M):
     """W4A16Linear switches to one dequantisation + a dense GEMM for compute-bound batches; both routes agree with the
