@@ -290,11 +290,11 @@ MidMPlan midm_plan(int M, int N, int K) {
 
 template <typename T, int NBK>
 int launch_midm(const MidMParams& p, const MidMPlan& pl, cudaStream_t st) {
-  static size_t smem_set = 0;
-  if (pl.smem > smem_set) {
+  static PerDeviceInt smem_set;   // function attributes are per device
+  if ((int)pl.smem > smem_set.get()) {
     if (cudaFuncSetAttribute(w4a16_midm_kernel<T, NBK>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem) != cudaSuccess)
       return GQ_ERR_CUDA;
-    smem_set = pl.smem;
+    smem_set.set((int)pl.smem);
   }
   GQ_LAUNCHED();
   w4a16_midm_kernel<T, NBK><<<pl.grid, SM_THREADS, pl.smem, st>>>(p);

@@ -246,11 +246,11 @@ __global__ void __launch_bounds__(SM_THREADS, 1) w4a16_smallm_kernel(const Small
 
 template <typename T, int MP, bool PRE>
 int launch_smallm(const SmallMParams& p, size_t smem, int grid, cudaStream_t st) {
-  static size_t smem_set = 0;
-  if (smem > smem_set) {
+  static PerDeviceInt smem_set;   // function attributes are per device
+  if ((int)smem > smem_set.get()) {
     if (cudaFuncSetAttribute(w4a16_smallm_kernel<T, MP, PRE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess)
       return GQ_ERR_CUDA;
-    smem_set = smem;
+    smem_set.set((int)smem);
   }
   GQ_LAUNCHED();
   w4a16_smallm_kernel<T, MP, PRE><<<grid, SM_THREADS, smem, st>>>(p);
