@@ -12,7 +12,8 @@ and adds the packed form K6 consumes:
 
 A packed layer holds: qweight_packed (R, C/8) int32 (column 8k+i in bits [4i, 4i+4) of word k, act-order column order),
 scale_t (G, R) 16-bit, qzero_t (G, R) uint8 (group-major, K6's layout), perm (C) int32 (quant position -> input
-column) or None, group_size, bits, shape (R, C): 0.5 B per weight + 3 B per group instead of 1 B per weight.
+column) or None, group_size, bits (None + group_bit_widths (G) uint8 when the widths are mixed), shape (R, C): 0.5 B per
+weight + 3 B per group instead of 1 B per weight.  Codes of 2 / 3 bits are kept one per nibble like 4-bit ones.
 """
 from __future__ import annotations
 
@@ -28,14 +29,19 @@ FORMAT = 'gptq_b200.packed.v1'
 
 
 def pack_layer(quant_meta: dict, device: torch.device) -> dict:
-    """One quant_meta (gptq_py.py:239-249) -> packed layer with CPU tensors.  4-bit codes only."""
+    """One quant_meta (gptq_py.py:239-249) -> packed layer with CPU tensors.  Codes of up to 4 bits, one per nibble: 4-bit
+    (llama.py:147), 3-bit (BASELINE configs[3]) and mixed per-group widths (their widths ride along in `group_bit_widths`;
+    K6 does not need them: a code is just a number below 16)."""
     bits = quant_meta['group_bit_widths']
-    if int(bits.max()) != 4 or int(bits.min()) != 4:
-        raise NotImplementedError('packed storage is defined for 4-bit codes (the reference\'s llama.py:147 setting)')
+    if int(bits.max()) > 4:
+        raise NotImplementedError('packed storage holds one code per nibble: bit widths up to 4')
     p = pack_quant_meta(quant_meta, device)
     R, C = quant_meta['qweight'].shape
     out = {k: (v.cpu() if torch.is_tensor(v) else v) for k, v in p.items()}
-    out.update({'bits': 4, 'shape': (int(R), int(C))})
+    uniform = int(bits.max()) == int(bits.min())
+    out.update({'bits': int(bits.max()) if uniform else None, 'shape': (int(R), int(C))})
+    if not uniform:
+        out['group_bit_widths'] = bits.detach().to('cpu', torch.uint8).clone()
     return out
 
 
@@ -57,7 +63,8 @@ def unpack_layer(layer: dict, device: torch.device = torch.device('cuda')) -> di
         'sscale': None,
         'perm_inv': perm_inv,
         'group_sizes': torch.full([G], gs, dtype=torch.int16),
-        'group_bit_widths': torch.full([G], int(layer.get('bits', 4)), dtype=torch.uint8),
+        'group_bit_widths': (layer['group_bit_widths'].to(torch.uint8).clone() if layer.get('group_bit_widths') is not None
+                             else torch.full([G], int(layer.get('bits') or 4), dtype=torch.uint8)),
         'scale_bit_width': None,
     }
 

@@ -108,3 +108,43 @@ def test_packed_roundtrip_and_quantised_model_eval(tmp_path):
     ppl_hf = float(_reference_ppl(dense, tok, 2))
     assert abs(ppl_dense - ppl_hf) <= 2e-2 * ppl_hf
     assert abs(ppl_packed - ppl_dense) <= 1e-2 * ppl_dense
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize('bits', [3, (4, 3, 2, 4)])
+def test_packed_roundtrip_3bit_and_mixed_widths(bits, tmp_path):
+    """BASELINE configs[3] is 3-bit: its quant_meta packs (one code per nibble), survives save / load bit for bit with
+    its group_bit_widths, and K6 evaluates it like the dense reconstruction (quant.py:262-279)."""
+    import checkpoint
+    from gptq_py import HessianHook, gptq_quant
+    from quant import reconstruct_nn_linear
+    dev = torch.device('cuda:0')
+    g = torch.Generator().manual_seed(5)
+    R, C, gs = 256, 512, 128
+    W = (torch.randn(R, C, generator=g) * 0.02).half().to(dev)
+    x = torch.randn(4, 1024, C, generator=g).half().to(dev)
+    hook = HessianHook()
+    hook.add_batch(x)
+    hook.invert()
+    G = C // gs
+    widths = torch.full([G], bits, dtype=torch.uint8) if isinstance(bits, int) else torch.tensor(bits, dtype=torch.uint8)
+    res = gptq_quant(W, hook, torch.full([G], gs, dtype=torch.int16), widths, gptq_use_kernel=False,
+                     gptq_block_sizes=torch.full([G], gs, dtype=torch.int16), quant_mse=False)
+    meta = res['quant_meta']
+    assert int(meta['qweight'].max()) <= 2 ** int(widths.max()) - 1
+    packed = checkpoint.pack_results({'data': {'lin': meta}, 'metrics': {'lin': res['metrics']}}, dev)
+    path = tmp_path / 'm.pt'
+    checkpoint.save_packed(packed, str(path))
+    loaded = checkpoint.load_packed(str(path))
+    back = checkpoint.unpack_layer(loaded['layers']['lin'], dev)
+    for k, v in meta.items():
+        if v is None:
+            assert back[k] is None
+        else:
+            assert back[k].dtype == v.dtype and torch.equal(back[k].cpu(), v.cpu()), k
+    lin = checkpoint.quantized_linears(loaded, dev, torch.float16)['lin']
+    dense = reconstruct_nn_linear(meta, dtype=torch.float16, device=dev)
+    xe = torch.randn(5, C, generator=g).half().to(dev)
+    with torch.no_grad():
+        want, got = dense(xe).float(), lin(xe).float()
+    assert ((got - want).norm() / want.norm()).item() <= 1e-2
